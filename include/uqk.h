@@ -1,0 +1,143 @@
+/*
+ * uqk.h -- C-ABI of libuqk.so: the B200 (sm_100a) UQ-inference hot path of
+ * TrondVQ/UncertaintyQuantification-SleepApnea-1DCNN.
+ *
+ * The reference has no FFI layer of its own: the path sits behind the Python module
+ * uncertainty_quantification/uq_techniques.py, which delegates the arithmetic to TensorFlow/Keras, NumPy and
+ * SciPy.  Each entry point below cites the reference call site(s) it replaces.  All pointers named *_dev are
+ * device pointers owned by the caller; the library allocates only its private workspace inside the handle
+ * (packed weights, BatchNorm statistics, activation scratch for the layer-synchronous path) and frees it in
+ * uqk_destroy().  Every function returns 0 on success or a negative UQK_E_* code; uqk_last_error() gives the
+ * text (thread-local).  Nothing throws across the boundary.  There is no CPU fallback: without an sm_100
+ * device every compute entry point fails with UQK_E_ARCH / UQK_E_CUDA.
+ *
+ * A handle is bound to one device and is not thread-safe.  Compute entry points enqueue work on the given
+ * stream and return without synchronising, except where noted.
+ */
+#ifndef UQK_H
+#define UQK_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define UQK_VERSION 100
+
+#define UQK_OK 0
+#define UQK_E_BADARG (-1)
+#define UQK_E_SHAPE (-2)
+#define UQK_E_ARCH (-3)   /* device is not sm_100 (B200) */
+#define UQK_E_CUDA (-4)
+#define UQK_E_STATE (-5)  /* e.g. model not set, statistics not calibrated */
+#define UQK_E_NOMEM (-6)
+#define UQK_E_KERNEL (-7) /* device-side watchdog / self-check failed */
+
+/* dtype of the window tensor x (N,60,4): prepare_numpy_datasets.py:93,233 saves float64 */
+#define UQK_F32 0
+#define UQK_F64 1
+
+/* BatchNormalization statistics used by the stochastic (training=True) passes */
+#define UQK_BN_INFERENCE 0  /* moving statistics (frozen BN; what model.predict uses, uq_techniques.py:29) */
+#define UQK_BN_BATCH 1      /* exact Keras training=True semantics: batch mean / biased variance over (N,L) of the
+                               whole call, per pass (uq_techniques.py:22); layer-synchronous fp32 path */
+#define UQK_BN_CALIBRATED 2 /* batch statistics estimated once by uqk_calibrate() and frozen for all passes */
+
+/* arithmetic of the forward passes */
+#define UQK_PREC_BF16_TC 0  /* fused tcgen05 kernel: bf16 operands, fp32 accumulate in TMEM */
+#define UQK_PREC_FP32 1     /* layer-synchronous CUDA-core kernels, fp32 throughout */
+
+typedef struct uqk_handle uqk_handle;
+
+/* Per-window outputs, each a device array of N elements; any pointer may be NULL (not produced).
+ * Replaces the arrays of uq_evaluation_dist (uq_techniques.py:69-91,103-108) and the drivers' inline
+ * per-window metrics (analyze_mcd_patient_level.py:109-117; analyze_de_patient_level.py:124-132). */
+typedef struct uqk_metrics_out {
+  float* mean_pred;                  /* uq_techniques.py:69 */
+  float* pred_variance;              /* :72, ddof=0, two-pass */
+  float* total_pred_entropy;         /* :78-79  H[(1-mean, mean)] in nats, clip 1e-10, renormalised */
+  float* expected_aleatoric_entropy; /* :83-87  mean_t H[(1-p_t, p_t)] */
+  float* mutual_info;                /* :91     max(total - expected, 0) */
+  float* entropy_bits;               /* analyze_mcd_patient_level.py:113-115  log2 form with +1e-9 */
+  int32_t* label;                    /* analyze_mcd_patient_level.py:117      mean > 0.5 */
+} uqk_metrics_out;
+
+int uqk_version(void);
+const char* uqk_last_error(void);
+
+/* Handle life cycle.  Synchronous. */
+int uqk_create(int device, uqk_handle** out);
+int uqk_destroy(uqk_handle* h);
+
+/* Install n_members networks.  blobs_host: n_members x 853441 float32, each in Keras get_weights() order
+ * (per block: conv kernel (k,Cin,Cout), bias, gamma, beta, moving_mean, moving_variance; then dense kernel
+ * (96,1), bias) -- the arrays tensorflow.keras.models.load_model() would hand to the reference
+ * (analyze_mcd_patient_level.py:199; analyze_de_patient_level.py:48).  Synchronous. */
+int uqk_set_model(uqk_handle* h, int n_members, const float* blobs_host, size_t floats_per_member);
+
+/* Deterministic forward, BN in inference mode, no dropout: replaces cnn_model(X, training=False)
+ * (analyze_mcd_patient_level.py:204) and model.predict (evaluation/evaluate_classification.py:30-31).
+ * probs_dev: (N,) float32. */
+int uqk_forward_det(uqk_handle* h, int member, const void* x_dev, int x_dtype, int64_t n_windows, int precision,
+                    float* probs_dev, void* stream);
+
+/* Estimate the per-layer batch statistics that Keras training=True would use, on n_windows windows and
+ * n_passes stochastic passes (exact layer-synchronous fp32 path), average them over the passes and freeze
+ * them for UQK_BN_CALIBRATED.  Enqueued on stream. */
+int uqk_calibrate(uqk_handle* h, const void* x_dev, int x_dtype, int64_t n_windows, int n_passes, uint64_t seed,
+                  void* stream);
+/* Read back / install the frozen statistics: mean and var are host arrays of 6 x 256 floats (layer-major,
+ * only the first Cout entries of each layer are used).  Synchronous on the handle's device. */
+int uqk_get_bn_stats(uqk_handle* h, float* mean_host, float* var_host);
+int uqk_set_bn_stats(uqk_handle* h, const float* mean_host, const float* var_host);
+
+/* MC-Dropout: n_passes stochastic passes of member 0 over all windows + the per-window reductions.
+ * Replaces mc_dropout_predict (uq_techniques.py:12-24) fused with uq_evaluation_dist (:40-112).
+ *   seed              Philox4x32-10 key; masks are a pure function of (seed, window_index_base + n, pass,
+ *                     layer, row, channel), hence independent of sharding.
+ *   mask_bits_dev     NULL, or explicit keep-masks (n_passes, N, 6, 60, 8) uint32, bit c%32 of word c/32 --
+ *                     the mask-injection mode used for exact parity with the oracle.
+ *   probs_dev         NULL, or (n_passes, N) float32: the tensor mc_dropout_predict returns.
+ *   out               NULL, or the per-window metrics. */
+int uqk_mcd(uqk_handle* h, const void* x_dev, int x_dtype, int64_t n_windows, int n_passes, uint64_t seed,
+            int bn_mode, int precision, int64_t window_index_base, const uint32_t* mask_bits_dev,
+            float* probs_dev, const uqk_metrics_out* out, void* stream);
+
+/* Deep Ensemble: members [0, n_members) in inference mode + the per-window reductions.
+ * Replaces deep_ensembles_predict (uq_techniques.py:26-32) fused with uq_evaluation_dist.
+ * probs_dev: NULL or (n_members, N). */
+int uqk_de(uqk_handle* h, const void* x_dev, int x_dtype, int64_t n_windows, int n_members, int precision,
+           float* probs_dev, const uqk_metrics_out* out, void* stream);
+
+/* Stand-alone reductions over an existing (n_passes, N) float32 probability tensor.
+ * Replaces uq_evaluation_dist (uq_techniques.py:40-112) and the inline metrics. */
+int uqk_reduce(const float* probs_dev, int n_passes, int64_t n_windows, const uqk_metrics_out* out, void* stream);
+
+/* Per-patient aggregation of per-window rows.  Replaces the pandas groupby of
+ * aggregate_patient_uq_metrics.py:34-46.  Rows of patient p are seg_offsets_dev[p] .. seg_offsets_dev[p+1]-1
+ * of the (already patient-sorted) columns.  out_dev: (n_patients, 8) float64 rows =
+ * [mean_var, median_var, std_var(ddof=1; 0 if n<=1), mean_ent, median_ent, std_ent, accuracy, num_windows]. */
+int uqk_patient_reduce(const float* variance_dev, const float* entropy_dev, const int32_t* true_label_dev,
+                       const int32_t* pred_label_dev, const int64_t* seg_offsets_dev, int64_t n_patients,
+                       double* out_dev, void* stream);
+
+/* Bootstrap aggregates behind bootstrap_metrics (uq_techniques.py:116-172): for each of n_boot index vectors
+ * idx_dev[b, :] (drawn on the host with np.random.choice exactly as :142), the six aggregate means of
+ * :150-157 computed as gather-means of the per-window metrics.  out_dev: (n_boot, 6) float64 in the order
+ * overall_mean_variance, mean_variance_class_0, mean_variance_class_1, mean_total_pred_entropy,
+ * mean_expected_aleatoric_entropy, mean_mutual_info. */
+int uqk_bootstrap(const float* variance_dev, const float* total_entropy_dev, const float* expected_entropy_dev,
+                  const float* mutual_info_dev, const int32_t* y_dev, const int64_t* idx_dev, int n_boot,
+                  int64_t n_windows, double* out_dev, void* stream);
+
+/* Diagnostics: number of kernel launches the library has issued on this handle since creation. */
+int64_t uqk_launch_count(uqk_handle* h);
+/* Diagnostics for tests: selects the fused-kernel variant (0 = default). */
+int uqk_set_option(uqk_handle* h, const char* key, int64_t value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* UQK_H */

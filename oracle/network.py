@@ -42,7 +42,7 @@ def _conv1d_same(x: np.ndarray, w: np.ndarray, b: np.ndarray) -> np.ndarray:
 
 def forward_f64(weights: Sequence[np.ndarray], x: np.ndarray, training: bool = False,
                 masks: Optional[List[np.ndarray]] = None, bn_mode: Optional[str] = None,
-                bn_stats: Optional[List] = None, return_stats: bool = False):
+                bn_stats: Optional[List] = None, return_stats: bool = False, return_acts: bool = False):
     """One forward pass of all N windows as ONE batch.
 
     training=False : BN uses moving statistics, dropout is the identity (uq_techniques.py:29,
@@ -57,6 +57,7 @@ def forward_f64(weights: Sequence[np.ndarray], x: np.ndarray, training: bool = F
     if bn_mode is None:
         bn_mode = "batch" if training else "inference"
     stats_out = []
+    acts_out = []
     for i, (cin, cout, k, rate) in enumerate(BLOCKS):
         w, b, g, be, mm, mv = [np.asarray(t, dtype=np.float64) for t in weights[6 * i:6 * i + 6]]
         a = np.maximum(_conv1d_same(a, w, b), 0.0)                       # Conv1D + ReLU
@@ -71,9 +72,12 @@ def forward_f64(weights: Sequence[np.ndarray], x: np.ndarray, training: bool = F
         a = g * (a - mu) / np.sqrt(var + BN_EPS) + be                    # BatchNormalization
         if training and masks is not None:
             a = a * masks[i] / (1.0 - rate)                               # Dropout: keep iff u >= rate
+        acts_out.append(a)
     gap = a.mean(axis=1)                                                  # GlobalAveragePooling1D
     z = gap @ np.asarray(weights[36], dtype=np.float64) + np.asarray(weights[37], dtype=np.float64)
     p = 1.0 / (1.0 + np.exp(-z))                                          # Dense(1, sigmoid)
+    if return_acts:
+        return p, acts_out
     if return_stats:
         return p, stats_out
     return p

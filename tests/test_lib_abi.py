@@ -1,0 +1,88 @@
+"""CPU-side checks of the boundary: the C-ABI library loads, exports every symbol include/uqk.h declares, and
+fails loudly (no CPU fallback) when no GPU is present.  No compute calls here."""
+import ctypes as C
+import importlib
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import PKG_NAME, ROOT
+
+
+def _declared_symbols():
+    hdr = open(os.path.join(ROOT, "include", "uqk.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    return sorted(set(re.findall(r"\b(uqk_[a-z_]+)\s*\(", hdr)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = importlib.import_module(PKG_NAME + "._lib")
+    cdll = lib.load()
+    syms = _declared_symbols()
+    assert len(syms) >= 15
+    for s in syms:
+        assert hasattr(cdll, s), f"{s} declared in include/uqk.h but not exported by libuqk.so"
+    assert set(lib.EXPORTS) == set(syms)
+    assert cdll.uqk_version() == 100
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU error path")
+def test_no_cpu_fallback_without_gpu():
+    lib = importlib.import_module(PKG_NAME + "._lib")
+    cdll = lib.load()
+    h = C.c_void_p()
+    rc = cdll.uqk_create(0, C.byref(h))
+    assert rc < 0 and b"no CPU fallback" in cdll.uqk_last_error()
+    engine = importlib.import_module(PKG_NAME + ".engine")
+    with pytest.raises(lib.UqkError):
+        engine.Engine(0)
+    # the drop-in module raises too instead of silently computing on the CPU
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, PKG_NAME, "uncertainty_quantification"))
+    uq = importlib.import_module("uq_techniques")
+    with pytest.raises(lib.UqkError):
+        uq.uq_evaluation_dist(np.random.rand(3, 5).astype(np.float32), np.zeros(5, dtype=int))
+
+
+def test_argument_errors_without_gpu_calls():
+    lib = importlib.import_module(PKG_NAME + "._lib")
+    cdll = lib.load()
+    assert cdll.uqk_reduce(None, 0, 10, None, None) == -1          # n_passes < 1
+    assert cdll.uqk_set_model(None, 1, None, 0) == -1
+    assert cdll.uqk_patient_reduce(None, None, None, None, None, -1, None, None) == -1
+    with pytest.raises(ValueError):
+        lib.check(cdll.uqk_reduce(None, 0, 10, None, None))
+
+
+def test_model_container_and_shim(tmp_path, uqk):
+    import sys
+    model = importlib.import_module(PKG_NAME + ".model")
+    m = model.synthetic_model(1)
+    assert len(m.get_weights()) == 38 and m.count_params() == 853441
+    path = str(tmp_path / "AlCNN1D_no_pool.keras")
+    m.save(path)
+    sys.path.insert(0, os.path.join(ROOT, PKG_NAME, "shim"))
+    try:
+        for k in [k for k in sys.modules if k == "tensorflow" or k.startswith("tensorflow.")]:
+            del sys.modules[k]
+        import tensorflow as tf
+        from tensorflow.keras.models import load_model
+        tf.random.set_seed(123)
+        m2 = load_model(path)
+        assert model.UQModel._global_seed == 123
+        assert isinstance(m2, tf.keras.Model)
+        np.testing.assert_array_equal(m2.blob(), m.blob())
+    finally:
+        sys.path.remove(os.path.join(ROOT, PKG_NAME, "shim"))
+        for k in [k for k in sys.modules if k == "tensorflow" or k.startswith("tensorflow.")]:
+            del sys.modules[k]
+        model.UQModel._global_seed = 2025
+    with pytest.raises(ValueError):
+        model.UQModel(m.get_weights()[:-1])
+    bad = tmp_path / "bad.keras"
+    bad.write_bytes(b"not a zip")
+    with pytest.raises(ValueError):
+        model.load_model(str(bad))

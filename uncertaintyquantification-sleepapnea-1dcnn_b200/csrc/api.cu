@@ -1,0 +1,371 @@
+// C-ABI of libuqk.so (declared in include/uqk.h): handle life cycle, model upload, and the entry points that
+// stand in for the reference's mc_dropout_predict / deep_ensembles_predict / uq_evaluation_dist
+// (uncertainty_quantification/uq_techniques.py:12-112).
+#include "common.cuh"
+#include "internal.h"
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+#include <algorithm>
+
+namespace uqk {
+
+static thread_local char g_err[512] = "";
+std::atomic<long long> g_launches{0};
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+struct Handle {
+  int device = 0;
+  int n_members = 0;
+  float* d_blobs = nullptr;       // n_members x kBlobFloats
+  uint16_t* d_packed = nullptr;   // n_members x packed image (bf16)
+  float* d_tables_inf = nullptr;  // n_members x kTableFloats: inference BN, no dropout (ensemble / deterministic)
+  float* d_table_mcd = nullptr;   // kTableFloats: MC-Dropout table (dropout scale folded), rebuilt per call
+  float* d_frozen = nullptr;      // 2 x 6 x 256: calibrated mean, var
+  bool have_frozen = false;
+  double* d_stats = nullptr;      // 6 x 256 x 2
+  float* d_affine = nullptr;      // 6 x 2 x 256
+  double* d_accum = nullptr;      // 2 x 6 x 256
+  int* d_err = nullptr;
+  // grow-on-demand workspace of the layer-synchronous path
+  float* d_x32 = nullptr; size_t x32_cap = 0;
+  float* d_act[2] = {nullptr, nullptr}; size_t act_cap = 0;
+  float* d_probs_tmp = nullptr; size_t probs_cap = 0;
+  float* d_dbg = nullptr;         // 6 x 128 x 256 debug dump of the fused kernel (tests)
+  int variant = 0;
+  int dbg_dump = 0;
+};
+
+static int ensure(float** p, size_t* cap, size_t need_floats) {
+  if (*cap >= need_floats) return UQK_OK;
+  if (*p) cudaFree(*p);
+  *p = nullptr; *cap = 0;
+  cudaError_t e = cudaMalloc(p, need_floats * sizeof(float));
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    set_error("workspace allocation of %zu bytes failed: %s", need_floats * sizeof(float), cudaGetErrorString(e));
+    return UQK_E_NOMEM;
+  }
+  *cap = need_floats;
+  return UQK_OK;
+}
+
+__global__ void average_stats_kernel(const double* __restrict__ accum, int n_passes, float* __restrict__ frozen) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < 2 * kBlocks * kMaxCh) frozen[i] = (float)(accum[i] / (double)n_passes);
+}
+
+static int check_x(const void* x, int dtype, int64_t n) {
+  if (n < 0) { set_error("n_windows must be >= 0"); return UQK_E_BADARG; }
+  if (n > 0 && x == nullptr) { set_error("x_dev is NULL"); return UQK_E_BADARG; }
+  if (dtype != UQK_F32 && dtype != UQK_F64) { set_error("x_dtype must be UQK_F32 or UQK_F64"); return UQK_E_BADARG; }
+  if (n > 0 && (reinterpret_cast<uintptr_t>(x) & 31)) { set_error("x_dev must be 32-byte aligned"); return UQK_E_BADARG; }
+  return UQK_OK;
+}
+
+// Layer-synchronous T passes (or M members) over all windows into probs (n_groups, n).
+static int run_layersync(Handle* h, const void* x, int x_dtype, int64_t n, int n_groups, bool de, bool dropout,
+                         int bn_mode, uint64_t seed, int64_t window_base, const uint32_t* mask_bits, float* probs,
+                         double* accum_mean, double* accum_var, cudaStream_t s) {
+  if (n == 0) return UQK_OK;
+  const int64_t chunk = bn_mode == UQK_BN_BATCH ? n : std::min<int64_t>(n, 16384);
+  int rc;
+  if ((rc = ensure(&h->d_x32, &h->x32_cap, (size_t)n * kL * kF))) return rc;
+  size_t cap0 = h->act_cap, cap1 = h->act_cap;
+  if ((rc = ensure(&h->d_act[0], &cap0, (size_t)chunk * kL * kMaxCh))) return rc;
+  if ((rc = ensure(&h->d_act[1], &cap1, (size_t)chunk * kL * kMaxCh))) { h->act_cap = 0; return rc; }
+  h->act_cap = std::min(cap0, cap1);
+  if ((rc = ls_cast_input(x, x_dtype, h->d_x32, n, s))) return rc;
+  for (int g = 0; g < n_groups; ++g) {
+    for (int64_t c0 = 0; c0 < n; c0 += chunk) {
+      const int64_t cn = std::min(chunk, n - c0);
+      LsPassParams p{};
+      p.blob_dev = h->d_blobs + (size_t)(de ? g : 0) * kBlobFloats;
+      p.x_f32 = h->d_x32 + (size_t)c0 * kL * kF;
+      p.act0 = h->d_act[0]; p.act1 = h->d_act[1];
+      p.n = cn; p.bn_mode = bn_mode; p.dropout = dropout ? 1 : 0; p.seed = seed; p.pass = g;
+      p.window_base = window_base + c0;
+      p.mask_bits = mask_bits ? mask_bits + ((size_t)g * n + c0) * kBlocks * kL * 8 : nullptr;
+      p.frozen_mean = h->d_frozen; p.frozen_var = h->d_frozen + kBlocks * kMaxCh;
+      p.stats_scratch = h->d_stats; p.affine_scratch = h->d_affine;
+      p.accum_mean = accum_mean; p.accum_var = accum_var;
+      p.probs_out = probs + (size_t)g * n + c0;
+      if ((rc = ls_forward_pass(p, s))) return rc;
+    }
+  }
+  return UQK_OK;
+}
+
+static int run_fused(Handle* h, const void* x, int x_dtype, int64_t n, int n_groups, bool de, bool dropout,
+                     uint64_t seed, int64_t window_base, const uint32_t* mask_bits, const float* tables, float* probs,
+                     const MetricsOut& out, cudaStream_t s) {
+  FusedParams p{};
+  p.x = x; p.x_dtype = x_dtype; p.n = n; p.n_groups = n_groups; p.mode_de = de ? 1 : 0; p.dropout = dropout ? 1 : 0;
+  p.seed = seed; p.window_base = window_base; p.mask_bits = mask_bits; p.packed = h->d_packed; p.tables = tables;
+  p.probs = probs; p.out = out; p.err_flag = h->d_err; p.variant = h->variant;
+  p.dbg_act = h->dbg_dump ? h->d_dbg : nullptr;
+  return fused_launch(p, s);
+}
+
+}  // namespace uqk
+
+using namespace uqk;
+
+extern "C" {
+
+int uqk_version(void) { return UQK_VERSION; }
+const char* uqk_last_error(void) { return g_err; }
+int64_t uqk_launch_count(uqk_handle*) { return (int64_t)g_launches.load(); }
+
+int uqk_create(int device, uqk_handle** out) {
+  if (!out) { set_error("out is NULL"); return UQK_E_BADARG; }
+  *out = nullptr;
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0) {
+    cudaGetLastError();
+    set_error("no CUDA device available (%s); libuqk has no CPU fallback", e == cudaSuccess ? "count=0" : cudaGetErrorString(e));
+    return UQK_E_CUDA;
+  }
+  if (device < 0 || device >= count) { set_error("device %d out of range (0..%d)", device, count - 1); return UQK_E_BADARG; }
+  cudaDeviceProp prop;
+  UQK_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) {
+    set_error("device %d is sm_%d%d; libuqk is built for sm_100a (B200) only", device, prop.major, prop.minor);
+    return UQK_E_ARCH;
+  }
+  UQK_CUDA(cudaSetDevice(device));
+  Handle* h = new Handle();
+  h->device = device;
+  UQK_CUDA(cudaMalloc(&h->d_table_mcd, sizeof(float) * kTableFloats));
+  UQK_CUDA(cudaMalloc(&h->d_frozen, sizeof(float) * 2 * kBlocks * kMaxCh));
+  UQK_CUDA(cudaMalloc(&h->d_stats, sizeof(double) * kBlocks * kMaxCh * 2));
+  UQK_CUDA(cudaMalloc(&h->d_affine, sizeof(float) * kBlocks * 2 * kMaxCh));
+  UQK_CUDA(cudaMalloc(&h->d_accum, sizeof(double) * 2 * kBlocks * kMaxCh));
+  UQK_CUDA(cudaMalloc(&h->d_err, sizeof(int)));
+  UQK_CUDA(cudaMalloc(&h->d_dbg, sizeof(float) * kBlocks * 128 * 256));
+  UQK_CUDA(cudaMemset(h->d_err, 0, sizeof(int)));
+  UQK_CUDA(cudaMemset(h->d_dbg, 0, sizeof(float) * kBlocks * 128 * 256));
+  *out = reinterpret_cast<uqk_handle*>(h);
+  return UQK_OK;
+}
+
+int uqk_destroy(uqk_handle* hh) {
+  if (!hh) return UQK_OK;
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  cudaSetDevice(h->device);
+  cudaDeviceSynchronize();
+  void* ptrs[] = {h->d_blobs, h->d_packed, h->d_tables_inf, h->d_table_mcd, h->d_frozen, h->d_stats, h->d_affine,
+                  h->d_accum, h->d_err, h->d_x32, h->d_act[0], h->d_act[1], h->d_probs_tmp, h->d_dbg};
+  for (void* p : ptrs) if (p) cudaFree(p);
+  cudaGetLastError();
+  delete h;
+  return UQK_OK;
+}
+
+int uqk_set_option(uqk_handle* hh, const char* key, int64_t value) {
+  if (!hh || !key) { set_error("NULL argument"); return UQK_E_BADARG; }
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  if (!strcmp(key, "variant")) { h->variant = (int)value; return UQK_OK; }
+  if (!strcmp(key, "dbg_dump")) { h->dbg_dump = (int)value; return UQK_OK; }
+  set_error("unknown option '%s'", key);
+  return UQK_E_BADARG;
+}
+
+int uqk_set_model(uqk_handle* hh, int n_members, const float* blobs_host, size_t floats_per_member) {
+  if (!hh || !blobs_host) { set_error("NULL argument"); return UQK_E_BADARG; }
+  if (n_members < 1 || n_members > 4096) { set_error("n_members must be in 1..4096"); return UQK_E_BADARG; }
+  if (floats_per_member != kBlobFloats) {
+    set_error("weight blob has %zu floats per member, the architecture needs %zu", floats_per_member, (size_t)kBlobFloats);
+    return UQK_E_SHAPE;
+  }
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  UQK_CUDA(cudaSetDevice(h->device));
+  UQK_CUDA(cudaDeviceSynchronize());
+  for (void* p : {(void*)h->d_blobs, (void*)h->d_packed, (void*)h->d_tables_inf}) if (p) cudaFree(p);
+  h->d_blobs = nullptr; h->d_packed = nullptr; h->d_tables_inf = nullptr; h->n_members = 0;
+  const size_t pb = fused_packed_bytes();
+  UQK_CUDA(cudaMalloc(&h->d_blobs, sizeof(float) * kBlobFloats * n_members));
+  UQK_CUDA(cudaMalloc(&h->d_packed, pb * n_members));
+  UQK_CUDA(cudaMalloc(&h->d_tables_inf, sizeof(float) * kTableFloats * n_members));
+  UQK_CUDA(cudaMemcpy(h->d_blobs, blobs_host, sizeof(float) * kBlobFloats * n_members, cudaMemcpyHostToDevice));
+  std::vector<uint16_t> packed(pb / 2);
+  for (int m = 0; m < n_members; ++m) {
+    fused_pack_member(blobs_host + (size_t)m * kBlobFloats, packed.data());
+    UQK_CUDA(cudaMemcpy(reinterpret_cast<uint8_t*>(h->d_packed) + (size_t)m * pb, packed.data(), pb, cudaMemcpyHostToDevice));
+    int rc = build_tables(h->d_blobs + (size_t)m * kBlobFloats, nullptr, nullptr, 0, h->d_tables_inf + (size_t)m * kTableFloats, 0);
+    if (rc) return rc;
+  }
+  UQK_CUDA(cudaDeviceSynchronize());
+  h->n_members = n_members;
+  h->have_frozen = false;
+  return UQK_OK;
+}
+
+int uqk_forward_det(uqk_handle* hh, int member, const void* x_dev, int x_dtype, int64_t n, int precision,
+                    float* probs_dev, void* stream) {
+  if (!hh) { set_error("handle is NULL"); return UQK_E_BADARG; }
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  if (h->n_members == 0) { set_error("uqk_set_model has not been called"); return UQK_E_STATE; }
+  if (member < 0 || member >= h->n_members) { set_error("member %d out of range", member); return UQK_E_BADARG; }
+  int rc = check_x(x_dev, x_dtype, n);
+  if (rc) return rc;
+  if (n > 0 && !probs_dev) { set_error("probs_dev is NULL"); return UQK_E_BADARG; }
+  UQK_CUDA(cudaSetDevice(h->device));
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (precision == UQK_PREC_FP32) {
+    // a one-member "ensemble" starting at `member`
+    Handle view = *h;
+    view.d_blobs = h->d_blobs + (size_t)member * kBlobFloats;
+    rc = run_layersync(&view, x_dev, x_dtype, n, 1, true, false, UQK_BN_INFERENCE, 0, 0, nullptr, probs_dev, nullptr,
+                       nullptr, s);
+    h->d_x32 = view.d_x32; h->x32_cap = view.x32_cap; h->d_act[0] = view.d_act[0]; h->d_act[1] = view.d_act[1];
+    h->act_cap = view.act_cap;
+    return rc;
+  }
+  if (precision != UQK_PREC_BF16_TC) { set_error("unknown precision %d", precision); return UQK_E_BADARG; }
+  Handle view = *h;
+  view.d_packed = reinterpret_cast<uint16_t*>(reinterpret_cast<uint8_t*>(h->d_packed) + (size_t)member * fused_packed_bytes());
+  return run_fused(&view, x_dev, x_dtype, n, 1, true, false, 0, 0, nullptr, h->d_tables_inf + (size_t)member * kTableFloats,
+                   probs_dev, MetricsOut{}, s);
+}
+
+int uqk_calibrate(uqk_handle* hh, const void* x_dev, int x_dtype, int64_t n, int n_passes, uint64_t seed, void* stream) {
+  if (!hh) { set_error("handle is NULL"); return UQK_E_BADARG; }
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  if (h->n_members == 0) { set_error("uqk_set_model has not been called"); return UQK_E_STATE; }
+  if (n < 1 || n_passes < 1) { set_error("calibration needs n_windows >= 1 and n_passes >= 1"); return UQK_E_BADARG; }
+  int rc = check_x(x_dev, x_dtype, n);
+  if (rc) return rc;
+  UQK_CUDA(cudaSetDevice(h->device));
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if ((rc = ensure(&h->d_probs_tmp, &h->probs_cap, (size_t)n * n_passes))) return rc;
+  UQK_CUDA(cudaMemsetAsync(h->d_accum, 0, sizeof(double) * 2 * kBlocks * kMaxCh, s));
+  rc = run_layersync(h, x_dev, x_dtype, n, n_passes, false, true, UQK_BN_BATCH, seed, 0, nullptr, h->d_probs_tmp,
+                     h->d_accum, h->d_accum + kBlocks * kMaxCh, s);
+  if (rc) return rc;
+  average_stats_kernel<<<(2 * kBlocks * kMaxCh + 255) / 256, 256, 0, s>>>(h->d_accum, n_passes, h->d_frozen);
+  UQK_LAUNCH_CHECK();
+  h->have_frozen = true;
+  return UQK_OK;
+}
+
+int uqk_get_bn_stats(uqk_handle* hh, float* mean_host, float* var_host) {
+  if (!hh || !mean_host || !var_host) { set_error("NULL argument"); return UQK_E_BADARG; }
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  if (!h->have_frozen) { set_error("no calibrated statistics (call uqk_calibrate or uqk_set_bn_stats)"); return UQK_E_STATE; }
+  UQK_CUDA(cudaSetDevice(h->device));
+  UQK_CUDA(cudaDeviceSynchronize());
+  UQK_CUDA(cudaMemcpy(mean_host, h->d_frozen, sizeof(float) * kBlocks * kMaxCh, cudaMemcpyDeviceToHost));
+  UQK_CUDA(cudaMemcpy(var_host, h->d_frozen + kBlocks * kMaxCh, sizeof(float) * kBlocks * kMaxCh, cudaMemcpyDeviceToHost));
+  return UQK_OK;
+}
+
+int uqk_set_bn_stats(uqk_handle* hh, const float* mean_host, const float* var_host) {
+  if (!hh || !mean_host || !var_host) { set_error("NULL argument"); return UQK_E_BADARG; }
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  UQK_CUDA(cudaSetDevice(h->device));
+  UQK_CUDA(cudaDeviceSynchronize());
+  UQK_CUDA(cudaMemcpy(h->d_frozen, mean_host, sizeof(float) * kBlocks * kMaxCh, cudaMemcpyHostToDevice));
+  UQK_CUDA(cudaMemcpy(h->d_frozen + kBlocks * kMaxCh, var_host, sizeof(float) * kBlocks * kMaxCh, cudaMemcpyHostToDevice));
+  h->have_frozen = true;
+  return UQK_OK;
+}
+
+int uqk_mcd(uqk_handle* hh, const void* x_dev, int x_dtype, int64_t n, int n_passes, uint64_t seed, int bn_mode,
+            int precision, int64_t window_base, const uint32_t* mask_bits_dev, float* probs_dev,
+            const uqk_metrics_out* out, void* stream) {
+  if (!hh) { set_error("handle is NULL"); return UQK_E_BADARG; }
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  if (h->n_members == 0) { set_error("uqk_set_model has not been called"); return UQK_E_STATE; }
+  if (n_passes < 1 || n_passes > 8192) { set_error("n_passes must be in 1..8192"); return UQK_E_BADARG; }
+  if (bn_mode != UQK_BN_INFERENCE && bn_mode != UQK_BN_BATCH && bn_mode != UQK_BN_CALIBRATED) {
+    set_error("unknown bn_mode %d", bn_mode); return UQK_E_BADARG;
+  }
+  if (bn_mode == UQK_BN_CALIBRATED && !h->have_frozen) {
+    set_error("UQK_BN_CALIBRATED needs uqk_calibrate() or uqk_set_bn_stats() first"); return UQK_E_STATE;
+  }
+  int rc = check_x(x_dev, x_dtype, n);
+  if (rc) return rc;
+  UQK_CUDA(cudaSetDevice(h->device));
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const MetricsOut mo = to_metrics(out);
+  if (precision == UQK_PREC_BF16_TC) {
+    if (bn_mode == UQK_BN_BATCH) {
+      set_error("exact batch-statistic BatchNorm couples all windows of a layer; it runs on the layer-synchronous "
+                "path only (precision = UQK_PREC_FP32). Use UQK_BN_CALIBRATED with the fused kernel.");
+      return UQK_E_BADARG;
+    }
+    const float* mean = bn_mode == UQK_BN_CALIBRATED ? h->d_frozen : nullptr;
+    const float* var = bn_mode == UQK_BN_CALIBRATED ? h->d_frozen + kBlocks * kMaxCh : nullptr;
+    if ((rc = build_tables(h->d_blobs, mean, var, 1, h->d_table_mcd, s))) return rc;
+    return run_fused(h, x_dev, x_dtype, n, n_passes, false, true, seed, window_base, mask_bits_dev, h->d_table_mcd,
+                     probs_dev, mo, s);
+  }
+  if (precision != UQK_PREC_FP32) { set_error("unknown precision %d", precision); return UQK_E_BADARG; }
+  float* probs = probs_dev;
+  if (!probs) {
+    if ((rc = ensure(&h->d_probs_tmp, &h->probs_cap, (size_t)n * n_passes))) return rc;
+    probs = h->d_probs_tmp;
+  }
+  rc = run_layersync(h, x_dev, x_dtype, n, n_passes, false, true, bn_mode, seed, window_base, mask_bits_dev, probs,
+                     nullptr, nullptr, s);
+  if (rc) return rc;
+  if (out) return launch_reduce(probs, n_passes, n, mo, s);
+  return UQK_OK;
+}
+
+int uqk_de(uqk_handle* hh, const void* x_dev, int x_dtype, int64_t n, int n_members, int precision, float* probs_dev,
+           const uqk_metrics_out* out, void* stream) {
+  if (!hh) { set_error("handle is NULL"); return UQK_E_BADARG; }
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  if (h->n_members == 0) { set_error("uqk_set_model has not been called"); return UQK_E_STATE; }
+  if (n_members < 1 || n_members > h->n_members) {
+    set_error("n_members=%d but the handle holds %d members", n_members, h->n_members); return UQK_E_BADARG;
+  }
+  int rc = check_x(x_dev, x_dtype, n);
+  if (rc) return rc;
+  UQK_CUDA(cudaSetDevice(h->device));
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const MetricsOut mo = to_metrics(out);
+  if (precision == UQK_PREC_BF16_TC)
+    return run_fused(h, x_dev, x_dtype, n, n_members, true, false, 0, 0, nullptr, h->d_tables_inf, probs_dev, mo, s);
+  if (precision != UQK_PREC_FP32) { set_error("unknown precision %d", precision); return UQK_E_BADARG; }
+  float* probs = probs_dev;
+  if (!probs) {
+    if ((rc = ensure(&h->d_probs_tmp, &h->probs_cap, (size_t)n * n_members))) return rc;
+    probs = h->d_probs_tmp;
+  }
+  rc = run_layersync(h, x_dev, x_dtype, n, n_members, true, false, UQK_BN_INFERENCE, 0, 0, nullptr, probs, nullptr,
+                     nullptr, s);
+  if (rc) return rc;
+  if (out) return launch_reduce(probs, n_members, n, mo, s);
+  return UQK_OK;
+}
+
+int uqk_reduce(const float* probs_dev, int n_passes, int64_t n, const uqk_metrics_out* out, void* stream) {
+  if (n < 0 || n_passes < 1) { set_error("need n_windows >= 0 and n_passes >= 1"); return UQK_E_BADARG; }
+  if (n > 0 && (!probs_dev || !out)) { set_error("NULL argument"); return UQK_E_BADARG; }
+  if (n == 0) return UQK_OK;
+  return launch_reduce(probs_dev, n_passes, n, to_metrics(out), static_cast<cudaStream_t>(stream));
+}
+
+// debug: copy the fused kernel's activation dump (6,128,256) to the host
+int uqk_debug_read_dump(uqk_handle* hh, float* host) {
+  if (!hh || !host) { set_error("NULL argument"); return UQK_E_BADARG; }
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  UQK_CUDA(cudaSetDevice(h->device));
+  UQK_CUDA(cudaDeviceSynchronize());
+  UQK_CUDA(cudaMemcpy(host, h->d_dbg, sizeof(float) * kBlocks * 128 * 256, cudaMemcpyDeviceToHost));
+  return UQK_OK;
+}
+
+}  // extern "C"

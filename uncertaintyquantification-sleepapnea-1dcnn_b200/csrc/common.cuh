@@ -1,0 +1,174 @@
+// Shared host/device declarations for libuqk.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <atomic>
+
+#include "../../include/uqk.h"
+
+namespace uqk {
+
+// ---- architecture (reference models/cnn_baseline_train.py:55-94) -------------------------------------------
+constexpr int kL = 60;        // time steps per window
+constexpr int kF = 4;         // input features
+constexpr int kBlocks = 6;
+constexpr int kMaxCh = 256;
+constexpr int kDenseIn = 96;
+constexpr float kBnEps = 1e-3f;
+
+struct BlockDef { int cin, cout, k, halo; float rate; };
+__host__ __device__ constexpr BlockDef block_def(int l) {
+  return l == 0 ? BlockDef{4, 128, 7, 3, 0.3f}
+       : l == 1 ? BlockDef{128, 192, 5, 2, 0.3f}
+       : l == 2 ? BlockDef{192, 224, 3, 1, 0.4f}
+       : l == 3 ? BlockDef{224, 96, 7, 3, 0.2f}
+       : l == 4 ? BlockDef{96, 256, 9, 4, 0.3f}
+                : BlockDef{256, 96, 9, 4, 0.5f};
+}
+// 16-bit dropout threshold: keep iff draw >= thr (TF: keep iff u >= rate)
+__host__ __device__ constexpr uint32_t drop_thr(int l) {
+  return l == 0 ? 19661u : l == 1 ? 19661u : l == 2 ? 26214u : l == 3 ? 13107u : l == 4 ? 19661u : 32768u;
+}
+
+// Offsets (in floats) into one member's Keras-order blob.
+struct BlobOffsets {
+  size_t conv_w[kBlocks], conv_b[kBlocks], gamma[kBlocks], beta[kBlocks], mmean[kBlocks], mvar[kBlocks];
+  size_t dense_w, dense_b, total;
+};
+inline BlobOffsets blob_offsets() {
+  BlobOffsets o{};
+  size_t p = 0;
+  for (int l = 0; l < kBlocks; ++l) {
+    BlockDef b = block_def(l);
+    o.conv_w[l] = p; p += (size_t)b.k * b.cin * b.cout;
+    o.conv_b[l] = p; p += b.cout;
+    o.gamma[l] = p; p += b.cout;
+    o.beta[l] = p; p += b.cout;
+    o.mmean[l] = p; p += b.cout;
+    o.mvar[l] = p; p += b.cout;
+  }
+  o.dense_w = p; p += kDenseIn;
+  o.dense_b = p; p += 1;
+  o.total = p;
+  return o;
+}
+constexpr size_t kBlobFloats = 853441;
+
+// Per-layer channel offsets into the per-member affine tables (sum of Cout = 992).
+__host__ __device__ constexpr int ch_off(int l) {
+  return l == 0 ? 0 : l == 1 ? 128 : l == 2 ? 320 : l == 3 ? 544 : l == 4 ? 640 : 896;
+}
+constexpr int kChTotal = 992;
+
+// ---- error plumbing --------------------------------------------------------------------------------------
+void set_error(const char* fmt, ...);
+extern std::atomic<long long> g_launches;
+
+#define UQK_CUDA(expr)                                                                            \
+  do {                                                                                            \
+    cudaError_t _e = (expr);                                                                      \
+    if (_e != cudaSuccess) {                                                                      \
+      ::uqk::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return UQK_E_CUDA;                                                                          \
+    }                                                                                             \
+  } while (0)
+
+#define UQK_LAUNCH_CHECK()                                                                        \
+  do {                                                                                            \
+    ::uqk::g_launches.fetch_add(1, std::memory_order_relaxed);                                    \
+    cudaError_t _e = cudaGetLastError();                                                          \
+    if (_e != cudaSuccess) {                                                                      \
+      ::uqk::set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return UQK_E_CUDA;                                                                          \
+    }                                                                                             \
+  } while (0)
+
+// ---- Philox4x32-10 (must match oracle/philox.py) ---------------------------------------------------------
+struct Philox4 { uint32_t x, y, z, w; };
+__device__ __forceinline__ Philox4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                                 uint32_t k0, uint32_t k1) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint64_t p0 = (uint64_t)0xD2511F53u * c0;
+    const uint64_t p1 = (uint64_t)0xCD9E8D57u * c2;
+    const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
+    const uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
+    c1 = (uint32_t)p1;
+    c3 = (uint32_t)p0;
+    c0 = n0;
+    c2 = n2;
+    k0 += 0x9E3779B9u;
+    k1 += 0xBB67AE85u;
+  }
+  return Philox4{c0, c1, c2, c3};
+}
+// 16-bit field e (0..7) of one Philox call: word e>>1, half e&1
+__device__ __forceinline__ uint32_t philox_field16(const Philox4& r, int e) {
+  const uint32_t w = (e >> 1) == 0 ? r.x : (e >> 1) == 1 ? r.y : (e >> 1) == 2 ? r.z : r.w;
+  return (e & 1) ? (w >> 16) : (w & 0xFFFFu);
+}
+
+// ---- per-window reductions, exact evaluation order of the reference's NumPy code ----------------------------
+// H[(1-p, p)] as scipy.stats.entropy(clip(.,1e-10,1-1e-10)) computes it in float32 (uq_techniques.py:35-38)
+__device__ __forceinline__ float safe_entropy2(float p) {
+  const float eps = 1e-10f;
+  float q0 = fminf(fmaxf(1.0f - p, eps), 1.0f);
+  float q1 = fminf(fmaxf(p, eps), 1.0f);
+  const float s = q0 + q1;
+  q0 = q0 / s;
+  q1 = q1 / s;
+  return (-q0 * logf(q0)) + (-q1 * logf(q1));
+}
+// log2 entropy of the drivers (analyze_mcd_patient_level.py:113-115), float32 with NumPy-2 weak scalars
+__device__ __forceinline__ float entropy_bits(float m) {
+  const float eps = 1e-9f;
+  return -(m * log2f(m + eps) + (1.0f - m) * log2f((1.0f - m) + eps));
+}
+
+struct MetricsOut {
+  float* mean_pred; float* pred_variance; float* total_pred_entropy; float* expected_aleatoric_entropy;
+  float* mutual_info; float* entropy_bits; int32_t* label;
+};
+inline MetricsOut to_metrics(const uqk_metrics_out* o) {
+  MetricsOut m{};
+  if (o) {
+    m.mean_pred = o->mean_pred; m.pred_variance = o->pred_variance; m.total_pred_entropy = o->total_pred_entropy;
+    m.expected_aleatoric_entropy = o->expected_aleatoric_entropy; m.mutual_info = o->mutual_info;
+    m.entropy_bits = o->entropy_bits; m.label = o->label;
+  }
+  return m;
+}
+
+// p points at n_pass probabilities with stride `stride`; sequential float32 accumulation along the pass axis,
+// exactly like np.mean/np.var(axis=0) on a C-contiguous (T,N) float32 array.
+template <typename Load>
+__device__ __forceinline__ void window_metrics(Load load, int n_pass, int64_t n, const MetricsOut& o) {
+  float sum = 0.f;
+  for (int t = 0; t < n_pass; ++t) sum += load(t);
+  const float mean = sum / (float)n_pass;
+  float ss = 0.f, hs = 0.f;
+  for (int t = 0; t < n_pass; ++t) {
+    const float p = load(t);
+    const float d = p - mean;
+    ss += d * d;
+    hs += safe_entropy2(p);
+  }
+  const float var = ss / (float)n_pass;
+  const float total = safe_entropy2(mean);
+  const float expected = hs / (float)n_pass;
+  if (o.mean_pred) o.mean_pred[n] = mean;
+  if (o.pred_variance) o.pred_variance[n] = var;
+  if (o.total_pred_entropy) o.total_pred_entropy[n] = total;
+  if (o.expected_aleatoric_entropy) o.expected_aleatoric_entropy[n] = expected;
+  if (o.mutual_info) o.mutual_info[n] = fmaxf(total - expected, 0.f);
+  if (o.entropy_bits) o.entropy_bits[n] = entropy_bits(mean);
+  if (o.label) o.label[n] = mean > 0.5f ? 1 : 0;
+}
+
+// ---- launchers implemented in the other translation units ---------------------------------------------------
+struct Handle;  // api.cu
+
+int launch_reduce(const float* probs, int n_pass, int64_t n, const MetricsOut& o, cudaStream_t s);
+
+}  // namespace uqk

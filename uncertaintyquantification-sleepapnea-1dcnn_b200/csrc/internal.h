@@ -1,0 +1,63 @@
+// Internal declarations shared by the translation units of libuqk.so.
+#pragma once
+#include "common.cuh"
+
+namespace uqk {
+
+// ---- layer-synchronous fp32 path (layersync.cu) -------------------------------------------------------------
+struct LsPassParams {
+  const float* blob_dev;    // one member's Keras-order blob on the device
+  const float* x_f32;       // (n,60,4) float32
+  float* act0;              // 2 activation buffers of n*60*256 floats
+  float* act1;
+  int64_t n;
+  int bn_mode;              // UQK_BN_*
+  int dropout;              // 1: apply dropout masks (training=True)
+  uint64_t seed;
+  int pass;
+  int64_t window_base;
+  const uint32_t* mask_bits;  // (n,6,60,8) keep bits for THIS pass, or null -> Philox
+  const float* frozen_mean;   // 6 x 256 (UQK_BN_CALIBRATED)
+  const float* frozen_var;
+  double* stats_scratch;      // 6 x 256 x 2 doubles
+  float* affine_scratch;      // 6 x 2 x 256 floats
+  double* accum_mean;         // optional 6 x 256 doubles: += batch mean (calibration)
+  double* accum_var;
+  float* probs_out;           // (n,)
+};
+int ls_cast_input(const void* x, int x_dtype, float* out, int64_t n_windows, cudaStream_t s);
+int ls_forward_pass(const LsPassParams& p, cudaStream_t s);
+
+// ---- fused tcgen05 path (fused.cu) ----------------------------------------------------------------------------
+// Per-set epilogue tables (a "set" is an ensemble member, or the single MC-Dropout network):
+//   float bias[992], scale[992], shift[992], dense_w[96], dense_b, pad[3]   -> kTableFloats floats
+constexpr int kTableFloats = 3 * kChTotal + kDenseIn + 4;
+// Packed bf16 weights of one member for the fused kernel (UMMA K-major, no swizzle), see fused.cu.
+size_t fused_packed_bytes();                      // bytes per member
+void fused_pack_member(const float* blob_host, uint16_t* packed_host);   // host-side packing
+
+struct FusedParams {
+  const void* x;              // (n,60,4) f32 or f64, device
+  int x_dtype;
+  int64_t n;
+  int n_groups;               // T passes (MCD) or M members (DE)
+  int mode_de;                // 1: group g uses member g's weights/tables, no dropout; 0: member 0, dropout
+  int dropout;
+  uint64_t seed;
+  int64_t window_base;
+  const uint32_t* mask_bits;  // (T,N,6,60,8) or null
+  const uint16_t* packed;     // n_members x packed bytes
+  const float* tables;        // n_sets x kTableFloats
+  float* probs;               // (n_groups, n) or null
+  MetricsOut out;
+  float* dbg_act;             // optional debug dump (6,128,256) floats of unit 0 / group 0 / tile 0
+  int* err_flag;              // device int: set !=0 by the in-kernel watchdog
+  int variant;                // kernel variant selector (tests)
+};
+int fused_launch(const FusedParams& p, cudaStream_t s);
+
+// tables builder: bias/scale/shift/dense for one set.  mean/var: 6x256 floats (frozen) or null -> moving stats.
+int build_tables(const float* blob_dev, const float* mean, const float* var, int fold_dropout, float* table_dev,
+                 cudaStream_t s);
+
+}  // namespace uqk

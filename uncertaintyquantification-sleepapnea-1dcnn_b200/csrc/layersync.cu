@@ -1,0 +1,279 @@
+// Layer-synchronous fp32 forward path (CUDA cores): one kernel per layer with activations in HBM.
+//
+// This is the EXACT restatement of Keras `model(x, training=True)` (reference uq_techniques.py:22): with
+// BatchNormalization in batch-statistics mode a layer cannot be normalised before the post-ReLU output of ALL
+// N windows of that layer exists, so layers are separated by grid-wide dependencies.
+// It is also the fp32 high-precision path for the deterministic / ensemble forward, and the calibration pass
+// that produces the frozen statistics of the fused tensor-core kernel (fused.cu).
+//
+// Layer semantics: cnn_baseline_train.py:59-94 -- Conv1D(same)+bias+ReLU -> BN -> Dropout, x6, GAP, Dense, sigmoid.
+#include "common.cuh"
+#include "internal.h"
+
+namespace uqk {
+
+// ---- input cast: (N,60,4) float64/float32 -> float32 --------------------------------------------------------
+template <typename T>
+__global__ void cast_input_kernel(const T* __restrict__ x, float* __restrict__ out, int64_t n_elems) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_elems; i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = (float)x[i];
+}
+
+// ---- Conv1D(same) + bias + ReLU, optional per-channel sum / sum-of-squares for batch-statistic BN -----------
+// One block per window. 128 threads = 8 channel-quads x 16 row-quads; output tile 60 rows x 32 channels per
+// iteration; the whole input window (+ zero halo) is staged in shared memory once.
+constexpr int kConvThreads = 128;
+
+template <int CIN, int COUT, int K>
+__global__ void __launch_bounds__(kConvThreads)
+conv_relu_kernel(const float* __restrict__ in, const float* __restrict__ w, const float* __restrict__ bias,
+                 float* __restrict__ out, double* __restrict__ stats, int64_t n) {
+  constexpr int H = (K - 1) / 2;
+  constexpr int ROWS = kL + 2 * H + 4;  // +4: row-quad 15 reads rows 60..63 (+j) -- keep them in bounds
+  constexpr int XS = CIN + 1;
+  extern __shared__ float smem[];
+  float* xs = smem;               // [ROWS][XS]
+  float* ssum = xs + ROWS * XS;   // [32][2]
+  const int tx = threadIdx.x & 7;   // channel quad within the 32-channel tile
+  const int ty = threadIdx.x >> 3;  // row quad: rows 4*ty .. 4*ty+3
+
+  for (int64_t win = blockIdx.x; win < n; win += gridDim.x) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < ROWS * CIN; i += kConvThreads) {
+      const int r = i / CIN, c = i % CIN;
+      const int src = r - H;
+      xs[r * XS + c] = (src >= 0 && src < kL) ? __ldg(in + ((size_t)win * kL + src) * CIN + c) : 0.f;
+    }
+    __syncthreads();
+    for (int ct = 0; ct < COUT / 32; ++ct) {
+      const int ch0 = ct * 32 + tx * 4;
+      float acc[4][4];
+      const float4 b4 = __ldg(reinterpret_cast<const float4*>(bias + ch0));
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { acc[i][0] = b4.x; acc[i][1] = b4.y; acc[i][2] = b4.z; acc[i][3] = b4.w; }
+      for (int j = 0; j < K; ++j) {
+        const float* xr = xs + (4 * ty + j) * XS;
+        const float* wr = w + (size_t)j * CIN * COUT + ch0;
+#pragma unroll 4
+        for (int c = 0; c < CIN; ++c) {
+          const float4 wv = __ldg(reinterpret_cast<const float4*>(wr + (size_t)c * COUT));
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float xv = xr[i * XS + c];
+            acc[i][0] = fmaf(xv, wv.x, acc[i][0]);
+            acc[i][1] = fmaf(xv, wv.y, acc[i][1]);
+            acc[i][2] = fmaf(xv, wv.z, acc[i][2]);
+            acc[i][3] = fmaf(xv, wv.w, acc[i][3]);
+          }
+        }
+      }
+      float s[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int row = 4 * ty + i;
+        if (row < kL) {
+          float4 v;
+          v.x = fmaxf(acc[i][0], 0.f); v.y = fmaxf(acc[i][1], 0.f);
+          v.z = fmaxf(acc[i][2], 0.f); v.w = fmaxf(acc[i][3], 0.f);
+          *reinterpret_cast<float4*>(out + ((size_t)win * kL + row) * COUT + ch0) = v;
+          s[0] += v.x; s[1] += v.y; s[2] += v.z; s[3] += v.w;
+          s2[0] += v.x * v.x; s2[1] += v.y * v.y; s2[2] += v.z * v.z; s2[3] += v.w * v.w;
+        }
+      }
+      if (stats != nullptr) {
+        if (threadIdx.x < 64) ssum[threadIdx.x] = 0.f;
+        __syncthreads();
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          atomicAdd(&ssum[(tx * 4 + q) * 2 + 0], s[q]);
+          atomicAdd(&ssum[(tx * 4 + q) * 2 + 1], s2[q]);
+        }
+        __syncthreads();
+        if (threadIdx.x < 64) atomicAdd(&stats[(size_t)(ct * 32) * 2 + threadIdx.x], (double)ssum[threadIdx.x]);
+        __syncthreads();
+      }
+    }
+  }
+}
+
+// ---- batch statistics -> affine (scale, shift); optionally accumulate mean/var for calibration ----------------
+// y = gamma * (x - mu) / sqrt(var + eps) + beta, then dropout scale 1/(1-rate) folded in when inv_keep != 1.
+__global__ void bn_finalize_kernel(const double* __restrict__ stats, double count, const float* __restrict__ gamma,
+                                   const float* __restrict__ beta, float inv_keep, int cout,
+                                   float* __restrict__ scale, float* __restrict__ shift,
+                                   double* __restrict__ accum_mean, double* __restrict__ accum_var) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= cout) return;
+  const double mu = stats[2 * c] / count;
+  double var = stats[2 * c + 1] / count - mu * mu;  // biased variance (Keras training mode)
+  if (var < 0) var = 0;
+  const float inv = (float)((double)gamma[c] / sqrt(var + (double)kBnEps));
+  scale[c] = inv * inv_keep;
+  shift[c] = (beta[c] - (float)mu * inv) * inv_keep;
+  if (accum_mean) { accum_mean[c] += mu; accum_var[c] += var; }
+}
+
+// affine from given (mean, var) arrays: moving statistics (inference) or frozen calibrated statistics
+__global__ void bn_affine_kernel(const float* __restrict__ mean, const float* __restrict__ var,
+                                 const float* __restrict__ gamma, const float* __restrict__ beta, float inv_keep,
+                                 int cout, float* __restrict__ scale, float* __restrict__ shift) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= cout) return;
+  const float inv = (float)((double)gamma[c] / sqrt((double)var[c] + (double)kBnEps));
+  scale[c] = inv * inv_keep;
+  shift[c] = (beta[c] - mean[c] * inv) * inv_keep;
+}
+
+// ---- BN affine + dropout, in place ----------------------------------------------------------------------------
+// One thread per (window, row, 8-channel chunk) = one Philox4x32-10 call.
+__global__ void bn_dropout_kernel(float* __restrict__ act, const float* __restrict__ scale,
+                                  const float* __restrict__ shift, int cout, int64_t n, int layer, int dropout,
+                                  uint32_t k0, uint32_t k1, uint32_t pass, int64_t window_base,
+                                  const uint32_t* __restrict__ mask_bits /* (N,6,60,8) for this pass or null */) {
+  const int nq = cout / 8;
+  const int64_t total = n * kL * nq;
+  const uint32_t thr = drop_thr(layer);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int q = (int)(i % nq);
+    const int64_t wr = i / nq;
+    const int row = (int)(wr % kL);
+    const int64_t win = wr / kL;
+    float4* p = reinterpret_cast<float4*>(act + (size_t)wr * cout + q * 8);
+    float4 a = p[0], b = p[1];
+    float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+    uint32_t keep = 0xFFu;
+    if (dropout) {
+      if (mask_bits) {
+        const uint32_t word = __ldg(mask_bits + (((size_t)win * kBlocks + layer) * kL + row) * 8 + (q >> 2));
+        keep = (word >> ((q & 3) * 8)) & 0xFFu;
+      } else {
+        const Philox4 r = philox4x32_10((uint32_t)(window_base + win), pass, ((uint32_t)layer << 16) | (uint32_t)row,
+                                        (uint32_t)q, k0, k1);
+        keep = 0;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) keep |= (philox_field16(r, e) >= thr ? 1u : 0u) << e;
+      }
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int c = q * 8 + e;
+      const float y = fmaf(v[e], __ldg(scale + c), __ldg(shift + c));
+      v[e] = ((keep >> e) & 1u) ? y : 0.f;
+    }
+    p[0] = make_float4(v[0], v[1], v[2], v[3]);
+    p[1] = make_float4(v[4], v[5], v[6], v[7]);
+  }
+}
+
+// ---- GlobalAveragePooling1D + Dense(96->1) + sigmoid: one warp per window ------------------------------------
+__global__ void head_kernel(const float* __restrict__ act, const float* __restrict__ wd, const float* __restrict__ bd,
+                            float* __restrict__ probs, int64_t n) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t win = warp; win < n; win += nwarps) {
+    const float* a = act + (size_t)win * kL * kDenseIn;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f;
+    for (int r = 0; r < kL; ++r) {
+      s0 += a[r * kDenseIn + lane];
+      s1 += a[r * kDenseIn + lane + 32];
+      s2 += a[r * kDenseIn + lane + 64];
+    }
+    const float inv = 1.0f / (float)kL;
+    float z = (s0 * inv) * __ldg(wd + lane) + (s1 * inv) * __ldg(wd + lane + 32) + (s2 * inv) * __ldg(wd + lane + 64);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) z += __shfl_xor_sync(0xffffffffu, z, o);
+    if (lane == 0) probs[win] = 1.0f / (1.0f + expf(-(z + __ldg(bd))));
+  }
+}
+
+// ---- host orchestration -------------------------------------------------------------------------------------
+template <int CIN, int COUT, int K>
+static int launch_conv(const float* in, const float* w, const float* b, float* out, double* stats, int64_t n,
+                       cudaStream_t s) {
+  constexpr int H = (K - 1) / 2;
+  const size_t smem = ((size_t)(kL + 2 * H + 4) * (CIN + 1) + 64) * sizeof(float);
+  if (smem > 48 * 1024)
+    UQK_CUDA(cudaFuncSetAttribute(conv_relu_kernel<CIN, COUT, K>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)smem));
+  const int grid = (int)std::min<int64_t>(n, 148 * 64);
+  conv_relu_kernel<CIN, COUT, K><<<grid, kConvThreads, smem, s>>>(in, w, b, out, stats, n);
+  UQK_LAUNCH_CHECK();
+  return UQK_OK;
+}
+
+static int launch_conv_layer(int l, const float* in, const float* w, const float* b, float* out, double* stats,
+                             int64_t n, cudaStream_t s) {
+  switch (l) {
+    case 0: return launch_conv<4, 128, 7>(in, w, b, out, stats, n, s);
+    case 1: return launch_conv<128, 192, 5>(in, w, b, out, stats, n, s);
+    case 2: return launch_conv<192, 224, 3>(in, w, b, out, stats, n, s);
+    case 3: return launch_conv<224, 96, 7>(in, w, b, out, stats, n, s);
+    case 4: return launch_conv<96, 256, 9>(in, w, b, out, stats, n, s);
+    default: return launch_conv<256, 96, 9>(in, w, b, out, stats, n, s);
+  }
+}
+
+int ls_cast_input(const void* x, int x_dtype, float* out, int64_t n_windows, cudaStream_t s) {
+  const int64_t ne = n_windows * kL * kF;
+  if (ne == 0) return UQK_OK;
+  const int grid = (int)std::min<int64_t>((ne + 255) / 256, 148 * 16);
+  if (x_dtype == UQK_F64) cast_input_kernel<double><<<grid, 256, 0, s>>>((const double*)x, out, ne);
+  else cast_input_kernel<float><<<grid, 256, 0, s>>>((const float*)x, out, ne);
+  UQK_LAUNCH_CHECK();
+  return UQK_OK;
+}
+
+// One forward pass of `n` windows (already float32, (n,60,4)) through the six blocks + head.
+// p: see LsPassParams in internal.h.
+int ls_forward_pass(const LsPassParams& p, cudaStream_t s) {
+  const BlobOffsets off = blob_offsets();
+  const float* blob = p.blob_dev;
+  const float* in = p.x_f32;
+  float* bufs[2] = {p.act0, p.act1};
+  int cur = 0;
+  for (int l = 0; l < kBlocks; ++l) {
+    const BlockDef b = block_def(l);
+    float* out = bufs[cur];
+    double* stats = nullptr;
+    if (p.bn_mode == UQK_BN_BATCH) {
+      stats = p.stats_scratch + (size_t)l * kMaxCh * 2;
+      UQK_CUDA(cudaMemsetAsync(stats, 0, sizeof(double) * 2 * b.cout, s));
+    }
+    int rc = launch_conv_layer(l, in, blob + off.conv_w[l], blob + off.conv_b[l], out, stats, p.n, s);
+    if (rc) return rc;
+    const float inv_keep = p.dropout ? 1.0f / (1.0f - b.rate) : 1.0f;
+    float* scale = p.affine_scratch + (size_t)l * kMaxCh * 2;
+    float* shift = scale + kMaxCh;
+    const int tb = 128, gb = (b.cout + tb - 1) / tb;
+    if (p.bn_mode == UQK_BN_BATCH) {
+      bn_finalize_kernel<<<gb, tb, 0, s>>>(stats, (double)p.n * kL, blob + off.gamma[l], blob + off.beta[l], inv_keep,
+                                           b.cout, scale, shift,
+                                           p.accum_mean ? p.accum_mean + (size_t)l * kMaxCh : nullptr,
+                                           p.accum_var ? p.accum_var + (size_t)l * kMaxCh : nullptr);
+    } else {
+      const float* mean = p.bn_mode == UQK_BN_CALIBRATED ? p.frozen_mean + (size_t)l * kMaxCh : blob + off.mmean[l];
+      const float* var = p.bn_mode == UQK_BN_CALIBRATED ? p.frozen_var + (size_t)l * kMaxCh : blob + off.mvar[l];
+      bn_affine_kernel<<<gb, tb, 0, s>>>(mean, var, blob + off.gamma[l], blob + off.beta[l], inv_keep, b.cout, scale,
+                                         shift);
+    }
+    UQK_LAUNCH_CHECK();
+    const int64_t total = p.n * kL * (b.cout / 8);
+    const int grid = (int)std::min<int64_t>((total + 255) / 256, 148 * 32);
+    bn_dropout_kernel<<<grid, 256, 0, s>>>(out, scale, shift, b.cout, p.n, l, p.dropout ? 1 : 0,
+                                           (uint32_t)(p.seed & 0xFFFFFFFFull), (uint32_t)(p.seed >> 32),
+                                           (uint32_t)p.pass, p.window_base, p.mask_bits);
+    UQK_LAUNCH_CHECK();
+    in = out;
+    cur ^= 1;
+  }
+  {
+    const int64_t threads = p.n * 32;
+    const int grid = (int)std::min<int64_t>((threads + 255) / 256, 148 * 32);
+    head_kernel<<<grid, 256, 0, s>>>(in, blob + off.dense_w, blob + off.dense_b, p.probs_out, p.n);
+    UQK_LAUNCH_CHECK();
+  }
+  return UQK_OK;
+}
+
+}  // namespace uqk

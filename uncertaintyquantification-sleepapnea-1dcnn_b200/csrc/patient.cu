@@ -1,0 +1,194 @@
+// K5: per-patient segmented reduction (replaces the pandas groupby of reference
+//     uncertainty_quantification/aggregate_patient_uq_metrics.py:34-46), and
+// K6: bootstrap aggregates as gather-means (replaces the resample + recompute loop of
+//     uq_techniques.py:137-158; the per-window metrics of preds[:, idx] are metrics[idx]).
+// Both are HBM/L2-bound integer+float work; no tensor cores.
+#include "common.cuh"
+#include "internal.h"
+
+namespace uqk {
+
+constexpr int kPatThreads = 256;
+constexpr int kPatMaxSeg = 8192;  // windows per patient that fit the in-smem sort (a 24 h night is 1440)
+
+__device__ __forceinline__ double block_sum(double v, double* red) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  __syncthreads();
+  if (l == 0) red[w] = v;
+  __syncthreads();
+  double t = 0;
+  for (int i = 0; i < kPatThreads / 32; ++i) t += red[i];
+  return t;
+}
+
+// bitonic sort of `m` (power of two) floats in shared memory
+__device__ void bitonic_sort(float* a, int m) {
+  for (int k = 2; k <= m; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      __syncthreads();
+      for (int i = threadIdx.x; i < m; i += kPatThreads) {
+        const int ixj = i ^ j;
+        if (ixj > i) {
+          const float x = a[i], y = a[ixj];
+          const bool up = (i & k) == 0;
+          if ((x > y) == up) { a[i] = y; a[ixj] = x; }
+        }
+      }
+    }
+  }
+  __syncthreads();
+}
+
+__device__ void column_stats(const float* __restrict__ col, int64_t s, int n, float* sbuf, double* red, double* mean_out,
+                             double* median_out, double* std_out) {
+  double acc = 0;
+  for (int i = threadIdx.x; i < n; i += kPatThreads) acc += (double)col[s + i];
+  const double mean = block_sum(acc, red) / (double)n;
+  acc = 0;
+  for (int i = threadIdx.x; i < n; i += kPatThreads) { const double d = (double)col[s + i] - mean; acc += d * d; }
+  const double ss = block_sum(acc, red);
+  int m = 1;
+  while (m < n) m <<= 1;
+  for (int i = threadIdx.x; i < m; i += kPatThreads) sbuf[i] = i < n ? col[s + i] : __int_as_float(0x7f800000);
+  bitonic_sort(sbuf, m);
+  const double med = (n & 1) ? (double)sbuf[n / 2] : 0.5 * ((double)sbuf[n / 2 - 1] + (double)sbuf[n / 2]);
+  if (threadIdx.x == 0) {
+    *mean_out = mean;
+    *median_out = med;
+    *std_out = n > 1 ? sqrt(ss / (double)(n - 1)) : 0.0;   // ddof=1; forced to 0 for single-window patients (:45-46)
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(kPatThreads)
+patient_reduce_kernel(const float* __restrict__ variance, const float* __restrict__ entropy,
+                      const int32_t* __restrict__ y_true, const int32_t* __restrict__ y_pred,
+                      const int64_t* __restrict__ seg, int64_t n_patients, double* __restrict__ out, int* err) {
+  __shared__ float sbuf[kPatMaxSeg];
+  __shared__ double red[kPatThreads / 32];
+  for (int64_t p = blockIdx.x; p < n_patients; p += gridDim.x) {
+    const int64_t s = seg[p], e = seg[p + 1];
+    const int64_t len = e - s;
+    double* o = out + p * 8;
+    if (len <= 0 || len > kPatMaxSeg) {
+      if (threadIdx.x == 0) {
+        if (len > kPatMaxSeg) atomicExch(err, 1);
+        for (int i = 0; i < 8; ++i) o[i] = len == 0 ? 0.0 : __longlong_as_double(0x7ff8000000000000ll);
+      }
+      continue;
+    }
+    const int n = (int)len;
+    column_stats(variance, s, n, sbuf, red, o + 0, o + 1, o + 2);
+    column_stats(entropy, s, n, sbuf, red, o + 3, o + 4, o + 5);
+    double c = 0;
+    for (int i = threadIdx.x; i < n; i += kPatThreads) c += (y_true[s + i] == y_pred[s + i]) ? 1.0 : 0.0;   // :34
+    c = block_sum(c, red);
+    if (threadIdx.x == 0) { o[6] = c / (double)n; o[7] = (double)n; }
+    __syncthreads();
+  }
+}
+
+// ---- bootstrap gather-means ---------------------------------------------------------------------------------------
+constexpr int kBootThreads = 256;
+__global__ void __launch_bounds__(kBootThreads)
+bootstrap_kernel(const float* __restrict__ var, const float* __restrict__ tot, const float* __restrict__ expc,
+                 const float* __restrict__ mi, const int32_t* __restrict__ y, const int64_t* __restrict__ idx,
+                 int64_t n, double* __restrict__ sums /* (n_boot, 8) */) {
+  const int b = blockIdx.y;
+  const int64_t* ib = idx + (size_t)b * n;
+  double a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (int64_t i = (int64_t)blockIdx.x * kBootThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kBootThreads) {
+    const int64_t j = __ldcs(ib + i);
+    const double v = (double)__ldg(var + j);
+    const int yy = __ldg(y + j);
+    a[0] += v;
+    if (yy == 0) { a[1] += v; a[2] += 1.0; }
+    if (yy == 1) { a[3] += v; a[4] += 1.0; }
+    a[5] += (double)__ldg(tot + j);
+    a[6] += (double)__ldg(expc + j);
+    a[7] += (double)__ldg(mi + j);
+  }
+  __shared__ double red[8][kBootThreads / 32];
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    double v = a[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (l == 0) red[k][w] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < 8) {
+    double t = 0;
+    for (int i = 0; i < kBootThreads / 32; ++i) t += red[threadIdx.x][i];
+    atomicAdd(&sums[(size_t)b * 8 + threadIdx.x], t);
+  }
+}
+
+__global__ void bootstrap_finalize_kernel(const double* __restrict__ sums, int n_boot, int64_t n, double* __restrict__ out) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= n_boot) return;
+  const double* s = sums + (size_t)b * 8;
+  double* o = out + (size_t)b * 6;
+  o[0] = s[0] / (double)n;
+  o[1] = s[2] > 0 ? s[1] / s[2] : 0.0;   // class absent -> 0.0 (uq_techniques.py:100-101)
+  o[2] = s[4] > 0 ? s[3] / s[4] : 0.0;
+  o[3] = s[5] / (double)n;
+  o[4] = s[6] / (double)n;
+  o[5] = s[7] / (double)n;
+}
+
+}  // namespace uqk
+
+using namespace uqk;
+
+extern "C" {
+
+int uqk_patient_reduce(const float* variance_dev, const float* entropy_dev, const int32_t* true_label_dev,
+                       const int32_t* pred_label_dev, const int64_t* seg_offsets_dev, int64_t n_patients,
+                       double* out_dev, void* stream) {
+  if (n_patients < 0) { set_error("n_patients must be >= 0"); return UQK_E_BADARG; }
+  if (n_patients == 0) return UQK_OK;
+  if (!variance_dev || !entropy_dev || !true_label_dev || !pred_label_dev || !seg_offsets_dev || !out_dev) {
+    set_error("NULL argument"); return UQK_E_BADARG;
+  }
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  int* d_err = nullptr;
+  UQK_CUDA(cudaMallocAsync(&d_err, sizeof(int), s));
+  UQK_CUDA(cudaMemsetAsync(d_err, 0, sizeof(int), s));
+  const int grid = (int)std::min<int64_t>(n_patients, 148 * 8);
+  patient_reduce_kernel<<<grid, kPatThreads, 0, s>>>(variance_dev, entropy_dev, true_label_dev, pred_label_dev,
+                                                     seg_offsets_dev, n_patients, out_dev, d_err);
+  UQK_LAUNCH_CHECK();
+  int herr = 0;
+  UQK_CUDA(cudaMemcpyAsync(&herr, d_err, sizeof(int), cudaMemcpyDeviceToHost, s));
+  UQK_CUDA(cudaStreamSynchronize(s));
+  UQK_CUDA(cudaFreeAsync(d_err, s));
+  if (herr) { set_error("a patient has more than %d windows; segment does not fit the in-kernel sort", kPatMaxSeg); return UQK_E_SHAPE; }
+  return UQK_OK;
+}
+
+int uqk_bootstrap(const float* variance_dev, const float* total_entropy_dev, const float* expected_entropy_dev,
+                  const float* mutual_info_dev, const int32_t* y_dev, const int64_t* idx_dev, int n_boot,
+                  int64_t n_windows, double* out_dev, void* stream) {
+  if (n_boot < 1 || n_windows < 1) { set_error("need n_boot >= 1 and n_windows >= 1"); return UQK_E_BADARG; }
+  if (!variance_dev || !total_entropy_dev || !expected_entropy_dev || !mutual_info_dev || !y_dev || !idx_dev || !out_dev) {
+    set_error("NULL argument"); return UQK_E_BADARG;
+  }
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  double* sums = nullptr;
+  UQK_CUDA(cudaMallocAsync(&sums, sizeof(double) * 8 * n_boot, s));
+  UQK_CUDA(cudaMemsetAsync(sums, 0, sizeof(double) * 8 * n_boot, s));
+  const int gx = (int)std::max<int64_t>(1, std::min<int64_t>((n_windows + kBootThreads * 8 - 1) / (kBootThreads * 8), 148));
+  bootstrap_kernel<<<dim3(gx, n_boot), kBootThreads, 0, s>>>(variance_dev, total_entropy_dev, expected_entropy_dev,
+                                                            mutual_info_dev, y_dev, idx_dev, n_windows, sums);
+  UQK_LAUNCH_CHECK();
+  bootstrap_finalize_kernel<<<(n_boot + 127) / 128, 128, 0, s>>>(sums, n_boot, n_windows, out_dev);
+  UQK_LAUNCH_CHECK();
+  UQK_CUDA(cudaFreeAsync(sums, s));
+  return UQK_OK;
+}
+
+}  // extern "C"

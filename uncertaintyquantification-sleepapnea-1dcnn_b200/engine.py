@@ -1,0 +1,257 @@
+"""Host-side driver of libuqk.so: device buffers (torch is used only as the allocator / stream provider),
+model upload, and the calls behind ``uq_techniques.mc_dropout_predict`` / ``deep_ensembles_predict`` /
+``uq_evaluation_dist`` (reference uncertainty_quantification/uq_techniques.py:12-112).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Dict, Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import _lib, arch
+
+METRIC_KEYS = ("mean_pred", "pred_variance", "total_pred_entropy", "expected_aleatoric_entropy", "mutual_info",
+               "entropy_bits", "label")
+_PREC = {"bf16": _lib.PREC_BF16_TC, "bf16_tc": _lib.PREC_BF16_TC, "fp32": _lib.PREC_FP32}
+_BN = {"inference": _lib.BN_INFERENCE, "frozen": _lib.BN_INFERENCE, "batch": _lib.BN_BATCH,
+       "calibrated": _lib.BN_CALIBRATED}
+
+
+def _require_cuda():
+    if not torch.cuda.is_available():
+        raise _lib.UqkError("no CUDA device: this package runs on B200 (sm_100a) only and has no CPU fallback")
+
+
+class Engine:
+    """One engine per GPU (wraps one ``uqk_handle``).  Not thread-safe."""
+
+    def __init__(self, device: Optional[int] = None):
+        _require_cuda()
+        self.lib = _lib.load()
+        self.device = torch.cuda.current_device() if device is None else int(device)
+        h = C.c_void_p()
+        _lib.check(self.lib.uqk_create(self.device, C.byref(h)), "uqk_create")
+        self._h = h
+        self.n_members = 0
+        self._model_key = None
+        self.calibrated = False
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.lib.uqk_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- plumbing ---------------------------------------------------------------------------------------------------
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _dev(self):
+        return torch.device("cuda", self.device)
+
+    def to_device(self, x):
+        """(N,60,4) float32/float64 host array, pinned torch tensor or CUDA tensor -> (CUDA tensor, dtype code)."""
+        if isinstance(x, torch.Tensor):
+            t = x
+        else:
+            a = np.asarray(x)
+            if a.dtype not in (np.float32, np.float64):
+                a = a.astype(np.float32)
+            t = torch.from_numpy(np.ascontiguousarray(a))
+        if t.dim() != 3 or t.shape[1] != arch.WINDOW_LEN or t.shape[2] != arch.WINDOW_FEATURES:
+            raise ValueError(f"windows must have shape (N, {arch.WINDOW_LEN}, {arch.WINDOW_FEATURES}), got {tuple(t.shape)}")
+        if t.dtype not in (torch.float32, torch.float64):
+            t = t.float()
+        if not t.is_cuda:
+            t = t.to(self._dev(), non_blocking=True)
+        t = t.contiguous()
+        return t, (_lib.F64 if t.dtype == torch.float64 else _lib.F32)
+
+    def option(self, key: str, value: int):
+        _lib.check(self.lib.uqk_set_option(self._h, key.encode(), int(value)), "uqk_set_option")
+
+    def launch_count(self) -> int:
+        return int(self.lib.uqk_launch_count(self._h))
+
+    # ---- model ------------------------------------------------------------------------------------------------------
+    def set_members(self, blobs: np.ndarray, key=None):
+        """blobs: (M, 853441) float32, each row one network in Keras ``get_weights()`` order."""
+        blobs = np.ascontiguousarray(blobs, dtype=np.float32)
+        if blobs.ndim == 1:
+            blobs = blobs[None]
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.uqk_set_model(self._h, blobs.shape[0], blobs.ctypes.data_as(C.c_void_p),
+                                              blobs.shape[1]), "uqk_set_model")
+        self.n_members = blobs.shape[0]
+        self._model_key = key
+        self.calibrated = False
+
+    def ensure_members(self, blobs_fn, key):
+        """Uploads only when ``key`` (identity of the model list) changed."""
+        if self._model_key != key or self.n_members == 0:
+            self.set_members(blobs_fn(), key)
+
+    # ---- outputs ----------------------------------------------------------------------------------------------------
+    def _alloc_metrics(self, n: int, want: Sequence[str]):
+        bufs, mo = {}, _lib.MetricsOut()
+        for k in METRIC_KEYS:
+            if k in want:
+                t = torch.empty(n, dtype=torch.int32 if k == "label" else torch.float32, device=self._dev())
+                bufs[k] = t
+                setattr(mo, k, t.data_ptr())
+        return bufs, mo
+
+    @staticmethod
+    def _finish(bufs, probs, device_out):
+        if device_out:
+            out = dict(bufs)
+            if probs is not None:
+                out["probs"] = probs
+            return out
+        out = {k: v.cpu().numpy() for k, v in bufs.items()}   # D2H (synchronises)
+        if probs is not None:
+            out["probs"] = probs.cpu().numpy()
+        return out
+
+    # ---- compute ----------------------------------------------------------------------------------------------------
+    def forward_det(self, x, member: int = 0, precision: str = "bf16", device_out: bool = False):
+        """Deterministic forward (BN inference mode, no dropout) -> (N,) float32."""
+        with torch.cuda.device(self.device):
+            xt, dt = self.to_device(x)
+            n = xt.shape[0]
+            probs = torch.empty(n, dtype=torch.float32, device=self._dev())
+            _lib.check(self.lib.uqk_forward_det(self._h, int(member), xt.data_ptr(), dt, n, _PREC[precision],
+                                                probs.data_ptr(), self._stream()), "uqk_forward_det")
+            return probs if device_out else probs.cpu().numpy()
+
+    def calibrate(self, x, n_windows: int = 4096, n_passes: int = 2, seed: int = 2025):
+        """Freezes the batch statistics Keras ``training=True`` would use, estimated on the first
+        ``n_windows`` windows with the exact layer-synchronous path (BN modes)."""
+        with torch.cuda.device(self.device):
+            if isinstance(x, torch.Tensor):
+                xs = x[:n_windows]
+            else:
+                xs = np.asarray(x)[:n_windows]
+            xt, dt = self.to_device(xs)
+            _lib.check(self.lib.uqk_calibrate(self._h, xt.data_ptr(), dt, xt.shape[0], int(n_passes),
+                                              C.c_uint64(seed & (2 ** 64 - 1)), self._stream()), "uqk_calibrate")
+            self.calibrated = True
+
+    def get_bn_stats(self):
+        mean = np.empty((arch.N_BLOCKS, arch.MAX_CH), dtype=np.float32)
+        var = np.empty_like(mean)
+        _lib.check(self.lib.uqk_get_bn_stats(self._h, mean.ctypes.data_as(C.c_void_p), var.ctypes.data_as(C.c_void_p)),
+                   "uqk_get_bn_stats")
+        return mean, var
+
+    def set_bn_stats(self, mean: np.ndarray, var: np.ndarray):
+        mean = np.ascontiguousarray(mean, dtype=np.float32).reshape(arch.N_BLOCKS, arch.MAX_CH)
+        var = np.ascontiguousarray(var, dtype=np.float32).reshape(arch.N_BLOCKS, arch.MAX_CH)
+        _lib.check(self.lib.uqk_set_bn_stats(self._h, mean.ctypes.data_as(C.c_void_p), var.ctypes.data_as(C.c_void_p)),
+                   "uqk_set_bn_stats")
+        self.calibrated = True
+
+    def mcd(self, x, n_passes: int = 50, seed: int = 2025, bn_mode: str = "calibrated", precision: str = "bf16",
+            masks=None, return_probs: bool = False, metrics: Sequence[str] = METRIC_KEYS, window_base: int = 0,
+            device_out: bool = False) -> Dict:
+        """T stochastic passes of member 0 + per-window reductions (uq_techniques.py:12-24 fused with :40-112).
+        ``masks``: optional (T,N,6,60,8) uint32 keep-bits (mask injection)."""
+        with torch.cuda.device(self.device):
+            xt, dt = self.to_device(x)
+            n = xt.shape[0]
+            bufs, mo = self._alloc_metrics(n, metrics)
+            probs = torch.empty((n_passes, n), dtype=torch.float32, device=self._dev()) if return_probs else None
+            mt = None
+            if masks is not None:
+                mt = masks if isinstance(masks, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(masks, dtype=np.uint32).view(np.int32))
+                if tuple(mt.shape) != (n_passes, n, arch.N_BLOCKS, arch.WINDOW_LEN, 8):
+                    raise ValueError(f"masks must have shape (T,N,6,60,8), got {tuple(mt.shape)}")
+                mt = mt.to(self._dev()).contiguous()
+            _lib.check(self.lib.uqk_mcd(self._h, xt.data_ptr(), dt, n, int(n_passes), C.c_uint64(seed & (2 ** 64 - 1)),
+                                        _BN[bn_mode], _PREC[precision], int(window_base),
+                                        mt.data_ptr() if mt is not None else None,
+                                        probs.data_ptr() if probs is not None else None,
+                                        C.byref(mo) if bufs else None, self._stream()), "uqk_mcd")
+            return self._finish(bufs, probs, device_out)
+
+    def de(self, x, n_members: Optional[int] = None, precision: str = "bf16", return_probs: bool = False,
+           metrics: Sequence[str] = METRIC_KEYS, device_out: bool = False) -> Dict:
+        """M ensemble members in inference mode + per-window reductions (uq_techniques.py:26-32 fused with :40-112)."""
+        with torch.cuda.device(self.device):
+            m = self.n_members if n_members is None else int(n_members)
+            xt, dt = self.to_device(x)
+            n = xt.shape[0]
+            bufs, mo = self._alloc_metrics(n, metrics)
+            probs = torch.empty((m, n), dtype=torch.float32, device=self._dev()) if return_probs else None
+            _lib.check(self.lib.uqk_de(self._h, xt.data_ptr(), dt, n, m, _PREC[precision],
+                                       probs.data_ptr() if probs is not None else None,
+                                       C.byref(mo) if bufs else None, self._stream()), "uqk_de")
+            return self._finish(bufs, probs, device_out)
+
+    def reduce(self, probs, metrics: Sequence[str] = METRIC_KEYS, device_out: bool = False) -> Dict:
+        """(T,N) float32 probabilities -> per-window metrics (uq_techniques.py:40-112)."""
+        with torch.cuda.device(self.device):
+            pt = probs if isinstance(probs, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(probs, dtype=np.float32))
+            if pt.dim() != 2:
+                raise ValueError(f"probabilities must be (T, N), got {tuple(pt.shape)}")
+            pt = pt.to(self._dev(), dtype=torch.float32).contiguous()
+            t, n = pt.shape
+            bufs, mo = self._alloc_metrics(n, metrics)
+            _lib.check(self.lib.uqk_reduce(pt.data_ptr(), int(t), int(n), C.byref(mo), self._stream()), "uqk_reduce")
+            return self._finish(bufs, None, device_out)
+
+    def bootstrap(self, metrics: Dict[str, np.ndarray], y_true: np.ndarray, idx: np.ndarray) -> np.ndarray:
+        """Gather-mean aggregates for bootstrap index vectors ``idx`` (B,N) int64 -> (B,6) float64
+        (uq_techniques.py:137-158)."""
+        with torch.cuda.device(self.device):
+            dev = self._dev()
+            f = lambda k: torch.as_tensor(np.ascontiguousarray(metrics[k], dtype=np.float32)).to(dev)
+            v, tt, ee, mi = f("pred_variance"), f("total_pred_entropy"), f("expected_aleatoric_entropy"), f("mutual_info")
+            y = torch.as_tensor(np.ascontiguousarray(y_true).astype(np.int32)).to(dev)
+            it = torch.as_tensor(np.ascontiguousarray(idx, dtype=np.int64)).to(dev)
+            b, n = it.shape
+            out = torch.empty((b, 6), dtype=torch.float64, device=dev)
+            _lib.check(self.lib.uqk_bootstrap(v.data_ptr(), tt.data_ptr(), ee.data_ptr(), mi.data_ptr(), y.data_ptr(),
+                                              it.data_ptr(), int(b), int(n), out.data_ptr(), self._stream()), "uqk_bootstrap")
+            return out.cpu().numpy()
+
+    def patient_reduce(self, variance, entropy, y_true, y_pred, seg_offsets) -> np.ndarray:
+        """Per-patient rows (P,8) float64 from patient-sorted columns (aggregate_patient_uq_metrics.py:34-46)."""
+        with torch.cuda.device(self.device):
+            dev = self._dev()
+            v = torch.as_tensor(np.ascontiguousarray(variance, dtype=np.float32)).to(dev)
+            e = torch.as_tensor(np.ascontiguousarray(entropy, dtype=np.float32)).to(dev)
+            yt = torch.as_tensor(np.ascontiguousarray(y_true).astype(np.int32)).to(dev)
+            yp = torch.as_tensor(np.ascontiguousarray(y_pred).astype(np.int32)).to(dev)
+            seg = torch.as_tensor(np.ascontiguousarray(seg_offsets, dtype=np.int64)).to(dev)
+            p = seg.shape[0] - 1
+            out = torch.empty((p, 8), dtype=torch.float64, device=dev)
+            _lib.check(self.lib.uqk_patient_reduce(v.data_ptr(), e.data_ptr(), yt.data_ptr(), yp.data_ptr(),
+                                                   seg.data_ptr(), int(p), out.data_ptr(), self._stream()),
+                       "uqk_patient_reduce")
+            return out.cpu().numpy()
+
+    def debug_dump(self) -> np.ndarray:
+        out = np.zeros((arch.N_BLOCKS, 128, 256), dtype=np.float32)
+        _lib.check(self.lib.uqk_debug_read_dump(self._h, out.ctypes.data_as(C.c_void_p)), "uqk_debug_read_dump")
+        return out
+
+
+_engines: Dict[int, Engine] = {}
+
+
+def get_engine(device: Optional[int] = None) -> Engine:
+    """Process-wide engine cache, one per device."""
+    _require_cuda()
+    d = torch.cuda.current_device() if device is None else int(device)
+    if d not in _engines:
+        _engines[d] = Engine(d)
+    return _engines[d]

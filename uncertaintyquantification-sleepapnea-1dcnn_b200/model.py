@@ -1,0 +1,124 @@
+"""Model objects the reference callers hand to the UQ functions.
+
+The reference passes whatever ``tensorflow.keras.models.load_model(path)`` returned
+(analyze_mcd_patient_level.py:199; analyze_de_patient_level.py:48) and uses it in three ways:
+``model(x, training=True)`` (uq_techniques.py:22), ``model(x, training=False).numpy()``
+(analyze_mcd_patient_level.py:204) and ``model.predict(x, verbose=0)`` (uq_techniques.py:29).
+``UQModel`` supports exactly those on the GPU; ``weights_of`` also accepts a genuine Keras model
+(duck-typed through ``get_weights()``) when TensorFlow exists.
+
+File format: TensorFlow/h5py are absent from this image, so ``save_model``/``load_model`` use an ``.npz``
+payload of the 38 ``get_weights()`` arrays stored under the ``*.keras`` file name the callers expect
+(SURVEY.md section 7.3 H6).
+"""
+from __future__ import annotations
+
+import io
+import zipfile
+from typing import List, Sequence
+
+import numpy as np
+
+from . import arch, synthetic
+
+_MAGIC_KEY = "uqk_format"
+
+
+class EagerArray(np.ndarray):
+    """ndarray that also answers ``.numpy()`` like a TF EagerTensor (analyze_mcd_patient_level.py:204)."""
+
+    def numpy(self):
+        return np.asarray(self)
+
+
+class UQModel:
+    """The 6-block 1D-CNN (models/cnn_baseline_train.py:55-94) as a bag of weights + GPU forward."""
+
+    _global_seed = 2025   # set by tf.random.set_seed in the shim (analyze_mcd_patient_level.py:31)
+
+    def __init__(self, weights: Sequence[np.ndarray], name: str = "Alarcon_1D_CNN_Model"):
+        self._blob = synthetic.weights_to_blob(weights)   # validates the 38 shapes
+        self.name = name
+        self.input_shape = (None, arch.WINDOW_LEN, arch.WINDOW_FEATURES)
+        self._stochastic_calls = 0
+
+    # Keras-like surface -------------------------------------------------------------------------------------------
+    def get_weights(self) -> List[np.ndarray]:
+        return synthetic.blob_to_weights(self._blob)
+
+    def set_weights(self, weights):
+        self._blob = synthetic.weights_to_blob(weights)
+
+    def count_params(self) -> int:
+        return int(self._blob.size)
+
+    def save(self, path: str):
+        save_model(self, path)
+
+    def blob(self) -> np.ndarray:
+        return self._blob
+
+    def __call__(self, x, training: bool = False):
+        from . import engine as _engine
+        eng = _engine.get_engine()
+        eng.ensure_members(lambda: self._blob[None], key=("single", id(self), self._blob.ctypes.data))
+        x = np.asarray(x)
+        if training:
+            # ONE stochastic pass with exact Keras semantics (batch-statistic BN + dropout); every call draws
+            # new masks: the call counter is folded into the Philox key.
+            seed = (UQModel._global_seed * 0x9E3779B97F4A7C15 + self._stochastic_calls) & (2 ** 64 - 1)
+            self._stochastic_calls += 1
+            out = eng.mcd(x, n_passes=1, seed=seed, bn_mode="batch", precision="fp32", return_probs=True, metrics=())
+            p = out["probs"].reshape(-1, 1)
+        else:
+            p = eng.forward_det(x, member=0, precision=_default_precision()).reshape(-1, 1)
+        return p.astype(np.float32).view(EagerArray)
+
+    def predict(self, x, verbose=0, batch_size=32, **_):
+        # Keras batches by 32 (uq_techniques.py:29); windows are independent in inference mode, so batching
+        # does not change the result and the GPU path takes the whole array.
+        return np.asarray(self(x, training=False))
+
+
+def _default_precision() -> str:
+    import os
+    return os.environ.get("UQK_PRECISION", "bf16")
+
+
+def weights_of(model) -> np.ndarray:
+    """Blob (853441,) float32 of a ``UQModel`` or of any object with Keras' ``get_weights()``."""
+    if isinstance(model, UQModel):
+        return model.blob()
+    if hasattr(model, "get_weights"):
+        return synthetic.weights_to_blob(model.get_weights())
+    raise TypeError(f"cannot extract weights from {type(model).__name__}: need UQModel or a Keras model")
+
+
+def save_model(model, path: str):
+    ws = synthetic.blob_to_weights(weights_of(model))
+    buf = io.BytesIO()
+    np.savez(buf, **{_MAGIC_KEY: np.array([1]), **{f"w{i:02d}": w for i, w in enumerate(ws)}})
+    with open(path, "wb") as f:
+        f.write(buf.getvalue())
+
+
+def load_model(path: str, compile: bool = True, **_) -> UQModel:   # noqa: A002 - Keras signature
+    with open(path, "rb") as f:
+        data = f.read()
+    try:
+        with zipfile.ZipFile(io.BytesIO(data)) as z:
+            names = set(z.namelist())
+    except zipfile.BadZipFile:
+        raise ValueError(f"{path}: not a model container this build can read")
+    if "model.weights.h5" in names or "config.json" in names:
+        raise NotImplementedError(
+            f"{path} is a genuine Keras v3 archive; reading its HDF5 weights needs h5py/TensorFlow, which are not in "
+            "this image. Export the weights with `np.savez(path, **{f'w{i:02d}': w for i, w in "
+            "enumerate(model.get_weights())})`.")
+    z = np.load(io.BytesIO(data), allow_pickle=False)
+    ws = [z[f"w{i:02d}"] for i in range(len(arch.blob_layout()))]
+    return UQModel(ws)
+
+
+def synthetic_model(member: int = 0) -> UQModel:
+    return UQModel(synthetic.make_member_weights(member))

@@ -1,0 +1,335 @@
+"""Drop-in replacement for the reference module ``uncertainty_quantification/uq_techniques.py``.
+
+Same ten public names, signatures, return types, dict keys and stdout markers as the reference
+(uq_techniques.py:12, 26, 35, 40, 116, 175, 210, 242, 258, 278), so the reference drivers
+``analyze_mcd_patient_level.py`` / ``analyze_de_patient_level.py`` / ``evaluate_*_global.py`` run unchanged with
+this file's directory first on ``sys.path`` (they do ``from uq_techniques import ...``).  The arithmetic runs
+in libuqk.so on a B200; nothing here falls back to the CPU for the forward passes or the per-window
+reductions.
+
+Build-side knobs (the callers' positional signatures are frozen, so these are environment variables):
+  UQK_BN_MODE    auto | batch | calibrated | inference      BatchNorm statistics of the MC-Dropout passes
+                 auto = exact Keras ``training=True`` semantics (batch statistics, fp32 layer-synchronous path)
+                 up to UQK_EXACT_MAX_WINDOWS windows, calibrated statistics + fused bf16 kernel above
+  UQK_PRECISION  bf16 | fp32
+  UQK_SEED       Philox key of the dropout masks (default: the seed given to tf.random.set_seed, else 2025)
+"""
+from __future__ import annotations
+
+import importlib
+import os
+import sys
+import time
+from typing import Dict, List, Optional
+
+import numpy as np
+
+_PKG_DIR = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+_ROOT = os.path.dirname(_PKG_DIR)
+if _ROOT not in sys.path:
+    sys.path.insert(0, _ROOT)
+_pkg = importlib.import_module(os.path.basename(_PKG_DIR))
+_engine = importlib.import_module(_pkg.__name__ + ".engine")
+_model = importlib.import_module(_pkg.__name__ + ".model")
+
+AGG_KEYS = ("overall_mean_variance", "mean_variance_class_0", "mean_variance_class_1",
+            "mean_total_pred_entropy", "mean_expected_aleatoric_entropy", "mean_mutual_info")
+
+
+def _env(name: str, default: str) -> str:
+    return os.environ.get(name, default)
+
+
+def _seed() -> int:
+    s = os.environ.get("UQK_SEED")
+    return int(s) if s is not None else int(_model.UQModel._global_seed)
+
+
+def _members_key(models):
+    return tuple(id(m) for m in models)
+
+
+# ===================== forward passes =====================
+def mc_dropout_predict(model, x_test_data: np.ndarray, n_pred: int = 50) -> np.ndarray:
+    """T stochastic forward passes of ``model`` over all windows -> (n_pred, N, 1) float32
+    (reference uq_techniques.py:12-24: ``np.stack([model(x, training=True) for _ in range(n_pred)])``)."""
+    t0 = time.time()
+    eng = _engine.get_engine()
+    eng.ensure_members(lambda: _model.weights_of(model)[None], key=("mcd", id(model)))
+    x = np.asarray(x_test_data)
+    n = x.shape[0]
+    mode = _env("UQK_BN_MODE", "auto")
+    prec = _env("UQK_PRECISION", "bf16")
+    if mode == "auto":
+        mode = "batch" if n <= int(_env("UQK_EXACT_MAX_WINDOWS", "16384")) else "calibrated"
+    if mode == "batch":
+        prec = "fp32"      # exact batch statistics couple all windows of a layer: layer-synchronous path
+    elif mode == "calibrated" and not eng.calibrated:
+        eng.calibrate(x, n_windows=int(_env("UQK_CALIB_WINDOWS", "4096")), n_passes=2, seed=_seed())
+    out = eng.mcd(x, n_passes=int(n_pred), seed=_seed(), bn_mode=mode, precision=prec, return_probs=True, metrics=())
+    mc_predictions = out["probs"].reshape(int(n_pred), n, 1)
+    print(f"MC Dropout completed in {time.time()-t0:.1f}s ({n_pred} passes)")
+    return mc_predictions
+
+
+def deep_ensembles_predict(ensemble_models: List, x_test_data: np.ndarray) -> np.ndarray:
+    """One inference-mode forward per ensemble member -> (M, N, 1) float32 (reference uq_techniques.py:26-32)."""
+    t0 = time.time()
+    eng = _engine.get_engine()
+    models = list(ensemble_models)
+    eng.ensure_members(lambda: np.stack([_model.weights_of(m) for m in models]), key=("de",) + _members_key(models))
+    x = np.asarray(x_test_data)
+    out = eng.de(x, n_members=len(models), precision=_env("UQK_PRECISION", "bf16"), return_probs=True, metrics=())
+    de_predictions = out["probs"].reshape(len(models), x.shape[0], 1)
+    print(f"Deep Ensemble completed in {time.time()-t0:.1f}s ({len(models)} models)")
+    return de_predictions
+
+
+# ===================== uncertainty metrics =====================
+def safe_entropy(probs: np.ndarray, axis: int = 1, epsilon: float = 1e-10) -> np.ndarray:
+    """Entropy (nats) of clipped, renormalised probability rows -- scipy.stats.entropy semantics
+    (reference uq_techniques.py:35-38).  Tiny helper kept on the host; the per-window entropies of the hot
+    path are computed in the reduction kernels."""
+    q = np.clip(probs, epsilon, 1 - epsilon)
+    q = q / np.sum(q, axis=axis, keepdims=True)
+    return -np.sum(q * np.log(q), axis=axis)
+
+
+def _as_2d(uq_predictions: np.ndarray) -> np.ndarray:
+    p = np.squeeze(uq_predictions)
+    if p.ndim == 0:
+        p = p.reshape(1, 1)
+    if p.ndim == 1:
+        p = p.reshape(1, -1)
+    return p
+
+
+def uq_evaluation_dist(uq_predictions: np.ndarray, y_true: np.ndarray) -> Dict[str, np.ndarray]:
+    """Per-window mean / variance / H[E p] / E[H p] / MI from a (T, N[,1]) probability tensor, plus the three
+    variance aggregates (reference uq_techniques.py:40-112; same dict keys :103-112).  Runs in the K4 kernel."""
+    predictions = _as_2d(np.asarray(uq_predictions))
+    if predictions.shape[0] == 1:
+        print("Warning: Only one set of predictions provided. Variance and Mutual Info will be zero.")
+    in_dtype = predictions.dtype if predictions.dtype in (np.float32, np.float64) else np.float32
+    eng = _engine.get_engine()
+    m = eng.reduce(predictions.astype(np.float32, copy=False),
+                   metrics=("mean_pred", "pred_variance", "total_pred_entropy", "expected_aleatoric_entropy",
+                            "mutual_info"))
+    m = {k: v.astype(in_dtype, copy=False) for k, v in m.items()}
+    var = m["pred_variance"]
+    y = np.asarray(y_true)
+    is0, is1 = (y == 0), (y == 1)
+    m["overall_mean_variance"] = np.mean(var)
+    m["mean_variance_class_0"] = np.mean(var[is0]) if is0.any() else 0.0
+    m["mean_variance_class_1"] = np.mean(var[is1]) if is1.any() else 0.0
+    return m
+
+
+# ===================== confidence intervals =====================
+def _aggregate_row_to_dict(row) -> Dict[str, float]:
+    return {k: float(v) for k, v in zip(AGG_KEYS, row)}
+
+
+def bootstrap_metrics(uq_predictions: np.ndarray, y_true: np.ndarray,
+                      n_bootstrap: int = 100, random_state: Optional[int] = None) -> Optional[List[Dict]]:
+    """Bootstrap over windows of the six aggregate means (reference uq_techniques.py:116-172).
+
+    The reference resamples columns of the (T,N) tensor and recomputes every per-window metric; since those
+    metrics are functions of one column only, metrics(preds[:, idx]) == metrics(preds)[idx], so each iteration
+    is a gather-mean (K6 kernel).  The index stream is drawn on the host with the legacy NumPy generator in
+    exactly the reference's order (:130-131, :142), so CI values are reproducible against it."""
+    if random_state is not None:
+        np.random.seed(random_state)
+    preds = np.asarray(uq_predictions)
+    n_samples = preds.shape[1]
+    y = np.asarray(y_true)
+    print(f"Starting bootstrap with {n_bootstrap} iterations...")
+    results: List[Dict] = []
+    try:
+        base = uq_evaluation_dist(preds, y)
+        eng = _engine.get_engine()
+        chunk = max(1, min(n_bootstrap, (256 << 20) // max(8 * n_samples, 1)))
+        done = 0
+        while done < n_bootstrap:
+            b = min(chunk, n_bootstrap - done)
+            idx = np.empty((b, n_samples), dtype=np.int64)
+            for i in range(b):
+                if (done + i + 1) % 10 == 0:
+                    print(f"  Bootstrap iteration {done+i+1}/{n_bootstrap}")
+                idx[i] = np.random.choice(n_samples, n_samples, replace=True)
+            rows = eng.bootstrap(base, y, idx)
+            results.extend(_aggregate_row_to_dict(r) for r in rows)
+            done += b
+    except Exception as e:  # the reference tolerates per-iteration failures (:162-165)
+        print(f"Error during bootstrap: {e}")
+    if not results:
+        print("Error: No bootstrap results generated.")
+        return None
+    print("Bootstrap finished.")
+    return results
+
+
+def compute_confidence_intervals(bootstrap_results: List[Dict], alpha: float = 0.05) -> Dict[str, float]:
+    """Mean and percentile CI bounds per aggregate (reference uq_techniques.py:175-206; keys :200-202)."""
+    out: Dict[str, float] = {}
+    if not bootstrap_results:
+        return out
+    lo_q, hi_q = 100 * alpha / 2, 100 * (1 - alpha / 2)
+    for name in bootstrap_results[0].keys():
+        try:
+            vals = np.array([r[name] for r in bootstrap_results], dtype=np.float64)
+            out[f"{name}_mean"] = float(vals.mean())
+            out[f"{name}_ci_lower"] = float(np.percentile(vals, lo_q))
+            out[f"{name}_ci_upper"] = float(np.percentile(vals, hi_q))
+        except Exception as e:
+            print(f"Error calculating CI for metric '{name}': {e}")
+    return out
+
+
+# ===================== visualisation (off the hot path) =====================
+def _pyplot():
+    try:
+        import matplotlib
+        matplotlib.use("Agg")
+        import matplotlib.pyplot as plt
+        return plt
+    except Exception:
+        return None
+
+
+def _save_plot_data(output_dir: str, stem: str, **arrays):
+    """matplotlib is absent from this image: keep the data a figure would have shown."""
+    os.makedirs(output_dir, exist_ok=True)
+    np.savez_compressed(os.path.join(output_dir, stem + ".npz"), **arrays)
+
+
+def plot_uncertainty_metric(uncertainty_values: np.ndarray, uq_name: str, metric_name: str,
+                            output_dir: str = "./uq_plots", title: Optional[str] = None, max_samples: int = 5000):
+    """Line plot of a per-window metric, subsampled above max_samples (reference uq_techniques.py:210-239)."""
+    os.makedirs(output_dir, exist_ok=True)
+    vals = np.asarray(uncertainty_values)
+    pos = np.arange(len(vals))
+    sub = len(vals) > max_samples
+    if sub:
+        pos = np.sort(np.random.choice(len(vals), max_samples, replace=False))
+        vals = vals[pos]
+        print(f"Warning: Plotting line plot for {max_samples} random samples out of {len(uncertainty_values)}.")
+    plt = _pyplot()
+    stem = f"line_{metric_name}_{uq_name}"
+    if plt is None:
+        return _save_plot_data(output_dir, stem, index=pos, values=vals)
+    plt.figure(figsize=(15, 4))
+    plt.plot(pos, vals, alpha=0.7)
+    plt.title(title or f"{metric_name} over Samples - {uq_name}")
+    plt.xlabel("Sample Index (Subsampled)" if sub else "Sample Index")
+    plt.ylabel(metric_name)
+    plt.grid(True, alpha=0.3)
+    plt.tight_layout()
+    plt.savefig(os.path.join(output_dir, stem + ".png"), bbox_inches="tight")
+    plt.close()
+
+
+def plot_class_uncertainties(class0_unc: float, class1_unc: float, uq_name: str, output_dir: str = "./uq_plots"):
+    """Bar chart of the two class-conditional mean variances (reference uq_techniques.py:242-255)."""
+    os.makedirs(output_dir, exist_ok=True)
+    plt = _pyplot()
+    stem = f"bar_class_variance_{uq_name}"
+    if plt is None:
+        return _save_plot_data(output_dir, stem, values=np.array([class0_unc, class1_unc], dtype=np.float64))
+    plt.figure(figsize=(6, 5))
+    bars = plt.bar(["Normal (0)", "Apnea/Hypopnea (1)"], [class0_unc, class1_unc], color=["skyblue", "salmon"])
+    plt.bar_label(bars, fmt="%.6f")
+    plt.title(f"Mean Predictive Variance by True Class - {uq_name}")
+    plt.ylabel("Mean Predictive Variance")
+    plt.ylim(bottom=0)
+    plt.tight_layout()
+    plt.savefig(os.path.join(output_dir, stem + ".png"), bbox_inches="tight")
+    plt.close()
+
+
+def plot_metric_distribution(metric_values: np.ndarray, y_true: np.ndarray, uq_name: str, metric_name: str,
+                             output_dir: str = "./uq_plots", bins: int = 30):
+    """Per-class histograms of a per-window metric (reference uq_techniques.py:258-275)."""
+    os.makedirs(output_dir, exist_ok=True)
+    vals, y = np.asarray(metric_values), np.asarray(y_true)
+    plt = _pyplot()
+    stem = f"hist_{metric_name}_by_class_{uq_name}"
+    if plt is None:
+        data = {}
+        for cls in (0, 1):
+            if np.any(y == cls):
+                h, edges = np.histogram(vals[y == cls], bins=bins, density=True)
+                data[f"density_class{cls}"] = h
+                data[f"edges_class{cls}"] = edges
+        return _save_plot_data(output_dir, stem, **data)
+    plt.figure(figsize=(10, 6))
+    for cls, label in ((0, "True Normal (0)"), (1, "True Apnea/Hypopnea (1)")):
+        if np.any(y == cls):
+            plt.hist(vals[y == cls], bins=bins, alpha=0.6, label=label, density=True)
+    plt.title(f"{metric_name} Distribution by True Class - {uq_name}")
+    plt.xlabel(f"{metric_name} Value")
+    plt.ylabel("Density")
+    plt.legend()
+    plt.grid(True, alpha=0.3)
+    plt.tight_layout()
+    plt.savefig(os.path.join(output_dir, stem + ".png"), bbox_inches="tight")
+    plt.close()
+
+
+# ===================== orchestrator =====================
+def evaluate_uq_methods(predictions: np.ndarray, y_test: np.ndarray, evaluation_label: str = "UQ Evaluation",
+                        n_bootstrap: int = 100, random_state: Optional[int] = None,
+                        output_plot_dir: str = "./uq_plots") -> Optional[Dict]:
+    """Metrics + bootstrap CIs + figures; returns the aggregated dict (reference uq_techniques.py:278-391;
+    keys :200-202 and :350-355; None-in -> None-out :309-311; length mismatch -> ValueError :312-313)."""
+    print(f"\n=== Evaluating Uncertainty: {evaluation_label} ===")
+    if predictions is None or y_test is None:
+        print("Error: Input predictions or labels are None.")
+        return None
+    print(f"Input prediction shape: {predictions.shape}, Samples: {len(y_test)}")
+    if len(y_test) != predictions.shape[1]:
+        raise ValueError(f"Mismatch between prediction samples ({predictions.shape[1]}) and label samples ({len(y_test)})")
+    if predictions.ndim == 3 and predictions.shape[-1] == 1:
+        predictions = predictions[..., 0]
+    if predictions.ndim == 1:
+        predictions = predictions.reshape(1, -1)
+
+    print("\nCalculating base UQ metrics...")
+    per_window = uq_evaluation_dist(predictions, y_test)
+    if per_window is None:
+        print("Error: Failed to calculate base UQ metrics.")
+        return None
+    point = {
+        "overall_mean_variance": per_window["overall_mean_variance"],
+        "mean_variance_class_0": per_window["mean_variance_class_0"],
+        "mean_variance_class_1": per_window["mean_variance_class_1"],
+        "mean_total_pred_entropy": np.mean(per_window["total_pred_entropy"]),
+        "mean_expected_aleatoric_entropy": np.mean(per_window["expected_aleatoric_entropy"]),
+        "mean_mutual_info": np.mean(per_window["mutual_info"]),
+    }
+    print(f"- Overall Mean Variance: {point['overall_mean_variance']:.6f}")
+    print(f"- Mean Variance Class 0: {point['mean_variance_class_0']:.6f}")
+    print(f"- Mean Variance Class 1: {point['mean_variance_class_1']:.6f}")
+    print(f"- Mean Predictive Entropy (Total): {point['mean_total_pred_entropy']:.4f}")
+    print(f"- Mean Expected Entropy (Aleatoric): {point['mean_expected_aleatoric_entropy']:.4f}")
+    print(f"- Mean Mutual Info (Epistemic): {point['mean_mutual_info']:.6f}")
+
+    print(f"\nComputing CIs (n_bootstrap={n_bootstrap})...")
+    t0 = time.time()
+    aggregated: Dict = {}
+    boot = bootstrap_metrics(predictions, y_test, n_bootstrap, random_state)
+    if boot:
+        aggregated.update(compute_confidence_intervals(boot))
+        print(f"CIs computed in {time.time()-t0:.2f}s")
+    else:
+        print("Warning: Bootstrap failed, CIs not computed.")
+    aggregated.update(point)
+
+    print("\nGenerating visualizations...")
+    for key, name in (("pred_variance", "Predictive Variance"), ("total_pred_entropy", "Predictive Entropy"),
+                      ("mutual_info", "Mutual Information")):
+        plot_metric_distribution(per_window[key], y_test, evaluation_label, name, output_dir=output_plot_dir)
+    plot_class_uncertainties(aggregated["mean_variance_class_0"], aggregated["mean_variance_class_1"],
+                             evaluation_label, output_dir=output_plot_dir)
+    print("\n=== Evaluation Complete ===")
+    return aggregated
