@@ -33,7 +33,7 @@ def test_reduce_matches_reference_golden(golden_dir):
     assert np.all(m1["pred_variance"] == 0) and np.all(m1["mutual_info"] <= 1e-6)
 
 
-@pytest.mark.parametrize("t,n", [(1, 1), (5, 1000), (50, 4096), (50, 4099), (100, 777), (25, 128), (700, 300)])
+@pytest.mark.parametrize("t,n", [(1, 2), (3, 2), (5, 1000), (50, 4096), (50, 4099), (100, 777), (25, 128), (700, 300)])
 def test_reduce_matches_oracle_shapes(t, n):
     rng = np.random.default_rng(t * 1000 + n)
     p = rng.random((t, n)).astype(np.float32)

@@ -301,7 +301,10 @@ fused_forward_kernel(const FusedArgs a) {
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
 
-  const bool swap_lbo_sbo = (a.variant & 1) != 0;
+  // perf-decomposition switches (tests/tools only): results are WRONG when any is set
+  const bool dbg_no_copy = (a.variant & 2) != 0;   // producer does not fetch weights
+  const bool dbg_raw_epi = (a.variant & 4) != 0;   // epilogue skips bias/ReLU/BN/dropout math
+  const bool dbg_no_mma = (a.variant & 8) != 0;    // issuer skips the MMAs
 
   if (warp == 0) {
     // =========================== weight producer (one thread) ===========================
@@ -319,9 +322,12 @@ fused_forward_kernel(const FusedArgs a) {
               mbar_wait(bar_empty + 8 * slot, ph ^ 1, a.err_flag, 1);
               const int nst = min(fl.sps, fl.nsteps - step);
               const uint32_t bytes = (uint32_t)nst * fl.step_bytes;
-              mbar_arrive_expect_tx(bar_full + 8 * slot, bytes);
-              bulk_g2s(s_base + Cfg::oRing + slot * kSlotBytes, wmem + fl.w_off + (size_t)step * fl.step_bytes, bytes,
-                       bar_full + 8 * slot);
+              if (dbg_no_copy) { mbar_arrive(bar_full + 8 * slot); }
+              else {
+                mbar_arrive_expect_tx(bar_full + 8 * slot, bytes);
+                bulk_g2s(s_base + Cfg::oRing + slot * kSlotBytes, wmem + fl.w_off + (size_t)step * fl.step_bytes, bytes,
+                         bar_full + 8 * slot);
+              }
               step += nst;
             }
           }
@@ -356,12 +362,12 @@ fused_forward_kernel(const FusedArgs a) {
                 else { a_off = (uint32_t)(2 * slab) * kPlaneBytes + (uint32_t)(tap - fl.halo + 4) * 16u; a_lbo = kPlaneBytes; }
                 const uint32_t b_addr = bslot + (uint32_t)sl * fl.step_bytes;
                 const uint32_t b_lbo = (uint32_t)fl.cout * 16u;
-                const uint64_t bdesc = swap_lbo_sbo ? umma_desc(b_addr, 128u, b_lbo) : umma_desc(b_addr, b_lbo, 128u);
+                const uint64_t bdesc = umma_desc(b_addr, b_lbo, 128u);
 #pragma unroll
                 for (int tl = 0; tl < TILES; ++tl) {
                   const uint32_t a_addr = s_base + Cfg::oAct + tl * kActBytes + a_off;
-                  const uint64_t adesc = swap_lbo_sbo ? umma_desc(a_addr, 128u, a_lbo) : umma_desc(a_addr, a_lbo, 128u);
-                  umma_bf16(tmem_base + tl * 256, adesc, bdesc, idesc, step > 0 ? 1u : 0u);
+                  const uint64_t adesc = umma_desc(a_addr, a_lbo, 128u);
+                  if (!dbg_no_mma) umma_bf16(tmem_base + tl * 256, adesc, bdesc, idesc, step > 0 ? 1u : 0u);
                 }
                 if (++slab == slabs) { slab = 0; ++tap; }
               }
@@ -444,6 +450,13 @@ fused_forward_kernel(const FusedArgs a) {
             tmem_ld_wait();
             uint32_t mword = 0xFFFFFFFFu;
             if (a.dropout && a.mask_bits) mword = mrow ? __ldg(mrow + (c0 >> 5)) : 0u;
+            if (dbg_raw_epi) {
+#pragma unroll
+              for (int q = 0; q < 4; ++q)
+                st_shared_v4(act_row + (uint32_t)((c0 >> 3) + q) * kPlaneBytes, v[8 * q] & 0x3F803F80u, v[8 * q + 2] & 0x3F803F80u,
+                             v[8 * q + 4] & 0x3F803F80u, v[8 * q + 6] & 0x3F803F80u);
+              continue;
+            }
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
               const int cb = c0 + 8 * q;
