@@ -12,7 +12,7 @@ from gpu_common import engine_with_members, members, twin_masks
 from oracle import network, reductions
 
 pytestmark = pytest.mark.gpu
-VARIANTS = [0, 16]     # 0: one tile per CTA, two CTAs per SM; 16: two tiles per CTA sharing the weight ring
+VARIANTS = [0, 16]     # 0 (default): two tiles per CTA sharing the weight ring; 16: one tile per CTA, two CTAs per SM
 
 
 def _x(uqk, n, seed=31):
@@ -111,7 +111,7 @@ def test_shard_invariance_and_fp32_agreement(uqk, eng):
     hi = eng.mcd(x[13:], n_passes=3, seed=11, bn_mode="inference", return_probs=True, window_base=13)["probs"]
     np.testing.assert_array_equal(np.concatenate([lo, hi], axis=1), full)
     fp32 = eng.mcd(x, n_passes=3, seed=11, bn_mode="inference", precision="fp32", return_probs=True)["probs"]
-    assert np.abs(fp32 - full).max() < 4e-2
+    assert np.abs(fp32 - full).max() < 6e-2     # bf16 chain vs fp32 chain, same masks
 
 
 def test_native_rng_statistics(uqk, eng):

@@ -572,8 +572,8 @@ static int launch_variant(const FusedParams& p, cudaStream_t s) {
 int fused_launch(const FusedParams& p, cudaStream_t s) {
   if (p.n == 0) return UQK_OK;
   switch (p.variant >> 4) {
-    case 1: return launch_variant<2, 4>(p, s);
-    default: return launch_variant<1, 2>(p, s);
+    case 1: return launch_variant<1, 2>(p, s);    // one tile per CTA, two CTAs per SM
+    default: return launch_variant<2, 4>(p, s);   // two tiles per CTA share one weight stream
   }
 }
 

@@ -85,6 +85,56 @@ def deep_ensembles_predict(ensemble_models: List, x_test_data: np.ndarray) -> np
     return de_predictions
 
 
+# ===================== fused entry points (additive; no counterpart in the reference) =====================
+def _finish_uq(out: Dict, y_true) -> Dict:
+    res = {k: out[k] for k in ("mean_pred", "pred_variance", "total_pred_entropy", "expected_aleatoric_entropy",
+                               "mutual_info") if k in out}
+    res["predictive_entropy_bits"] = out.get("entropy_bits")      # CSV column Predictive_Entropy (log2 form)
+    res["predicted_label"] = out.get("label")                     # CSV column Predicted_Label (mean > 0.5)
+    if "probs" in out:
+        res["probs"] = out["probs"]
+    if y_true is not None and "pred_variance" in out and not hasattr(out["pred_variance"], "is_cuda"):
+        y = np.asarray(y_true)
+        var = out["pred_variance"]
+        is0, is1 = (y == 0), (y == 1)
+        res["overall_mean_variance"] = np.mean(var)
+        res["mean_variance_class_0"] = np.mean(var[is0]) if is0.any() else 0.0
+        res["mean_variance_class_1"] = np.mean(var[is1]) if is1.any() else 0.0
+    return res
+
+
+def mc_dropout_uq(model, x_test_data, n_pred: int = 50, *, y_true=None, return_probs: bool = False,
+                  bn_mode: str = "calibrated", precision: str = "bf16", seed: Optional[int] = None, masks=None,
+                  calib_windows: int = 4096, calib_passes: int = 2, recalibrate: bool = True,
+                  device_out: bool = False) -> Dict:
+    """mc_dropout_predict + uq_evaluation_dist + the drivers' inline CSV metrics in ONE fused call: the
+    (T,N) probability tensor is never written to HBM unless ``return_probs``.  Returns the per-window arrays of
+    uq_techniques.py:103-108 plus ``predictive_entropy_bits`` / ``predicted_label``
+    (analyze_mcd_patient_level.py:113-117).  ``bn_mode='calibrated'`` first estimates the batch statistics on
+    ``calib_windows`` windows with the exact layer-synchronous path (inside this call when ``recalibrate``)."""
+    eng = _engine.get_engine()
+    eng.ensure_members(lambda: _model.weights_of(model)[None], key=("mcd", id(model)))
+    seed = _seed() if seed is None else int(seed)
+    if bn_mode == "batch":
+        precision = "fp32"
+    if bn_mode == "calibrated" and (recalibrate or not eng.calibrated):
+        eng.calibrate(x_test_data, n_windows=calib_windows, n_passes=calib_passes, seed=seed)
+    out = eng.mcd(x_test_data, n_passes=int(n_pred), seed=seed, bn_mode=bn_mode, precision=precision, masks=masks,
+                  return_probs=return_probs, device_out=device_out)
+    return _finish_uq(out, y_true)
+
+
+def deep_ensemble_uq(ensemble_models: List, x_test_data, *, y_true=None, return_probs: bool = False,
+                     precision: str = "bf16", device_out: bool = False) -> Dict:
+    """deep_ensembles_predict + uq_evaluation_dist + inline CSV metrics in one fused call (see mc_dropout_uq)."""
+    eng = _engine.get_engine()
+    models = list(ensemble_models)
+    eng.ensure_members(lambda: np.stack([_model.weights_of(m) for m in models]), key=("de",) + _members_key(models))
+    out = eng.de(x_test_data, n_members=len(models), precision=precision, return_probs=return_probs,
+                 device_out=device_out)
+    return _finish_uq(out, y_true)
+
+
 # ===================== uncertainty metrics =====================
 def safe_entropy(probs: np.ndarray, axis: int = 1, epsilon: float = 1e-10) -> np.ndarray:
     """Entropy (nats) of clipped, renormalised probability rows -- scipy.stats.entropy semantics
