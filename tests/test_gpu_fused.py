@@ -116,18 +116,24 @@ def test_shard_invariance_and_fp32_agreement(uqk, eng):
 
 def test_native_rng_statistics(uqk, eng):
     """Statistical agreement of the UQ metrics under the native RNG (no masks shared with the oracle):
-    cohort means of variance / entropy / MI from the fused kernel vs the oracle driven by an independent
-    NumPy generator, within 15 % relative at T=16, N=96."""
-    n, T = 96, 16
+    cohort means of variance / entropy / MI / mean probability from the fused kernel (in-kernel Philox) vs the
+    oracle driven by three independent NumPy generators.  The kernel's value must lie within 4 standard
+    deviations of the spread between the independent oracle streams (floor: 5 % relative)."""
+    n, T, K = 128, 12, 3
     x = _x(uqk, n, seed=36)
     out = eng.mcd(x, n_passes=T, seed=424242, bn_mode="inference", return_probs=True)
-    rng = np.random.default_rng(5)
-    ref = []
-    for t in range(T):
-        masks = [rng.random((n, 60, b.cout)) >= b.rate for b in uqk.arch.BLOCKS]
-        ref.append(network.forward_f64(members()[0], x, training=True, masks=masks, bn_mode="inference")[:, 0])
-    rm = reductions.uq_evaluation_dist(np.stack(ref).astype(np.float32), None)
-    for k in ("pred_variance", "total_pred_entropy", "mutual_info"):
-        a, b = float(np.mean(out[k])), float(np.mean(rm[k]))
-        assert abs(a - b) <= 0.15 * abs(b) + 1e-4, (k, a, b)
-    assert abs(float(out["mean_pred"].mean()) - float(rm["mean_pred"].mean())) < 0.03
+    keys = ("pred_variance", "total_pred_entropy", "mutual_info", "mean_pred")
+    est = {k: [] for k in keys}
+    for s in range(K):
+        rng = np.random.default_rng(100 + s)
+        ref = []
+        for t in range(T):
+            masks = [rng.random((n, 60, b.cout)) >= b.rate for b in uqk.arch.BLOCKS]
+            ref.append(network.forward_f64(members()[0], x, training=True, masks=masks, bn_mode="inference")[:, 0])
+        rm = reductions.uq_evaluation_dist(np.stack(ref).astype(np.float32), None)
+        for k in keys:
+            est[k].append(float(np.mean(rm[k])))
+    for k in keys:
+        mu, sd = float(np.mean(est[k])), float(np.std(est[k], ddof=1))
+        a = float(np.mean(out[k]))
+        assert abs(a - mu) <= 4 * max(sd, 0.05 * abs(mu)), (k, a, est[k])

@@ -21,7 +21,7 @@ def main():
     res = []
     for v in variants:
         eng.option("variant", v)
-        for mode in ("mcd", "det"):
+        for mode in (sys.argv[4].split(",") if len(sys.argv) > 4 else ("mcd", "det")):
             def run():
                 if mode == "mcd":
                     eng.mcd(x, n_passes=T, bn_mode="inference", device_out=True, metrics=("mean_pred",))

@@ -88,7 +88,7 @@ static int run_layersync(Handle* h, const void* x, int x_dtype, int64_t n, int n
     for (int64_t c0 = 0; c0 < n; c0 += chunk) {
       const int64_t cn = std::min(chunk, n - c0);
       LsPassParams p{};
-      p.blob_dev = h->d_blobs + (size_t)(de ? g : 0) * kBlobFloats;
+      p.blob_dev = h->d_blobs + (size_t)(de ? g : 0) * kBlobStride;
       p.x_f32 = h->d_x32 + (size_t)c0 * kL * kF;
       p.act0 = h->d_act[0]; p.act1 = h->d_act[1];
       p.n = cn; p.bn_mode = bn_mode; p.dropout = dropout ? 1 : 0; p.seed = seed; p.pass = g;
@@ -193,15 +193,16 @@ int uqk_set_model(uqk_handle* hh, int n_members, const float* blobs_host, size_t
   for (void* p : {(void*)h->d_blobs, (void*)h->d_packed, (void*)h->d_tables_inf}) if (p) cudaFree(p);
   h->d_blobs = nullptr; h->d_packed = nullptr; h->d_tables_inf = nullptr; h->n_members = 0;
   const size_t pb = fused_packed_bytes();
-  UQK_CUDA(cudaMalloc(&h->d_blobs, sizeof(float) * kBlobFloats * n_members));
+  UQK_CUDA(cudaMalloc(&h->d_blobs, sizeof(float) * kBlobStride * n_members));
   UQK_CUDA(cudaMalloc(&h->d_packed, pb * n_members));
   UQK_CUDA(cudaMalloc(&h->d_tables_inf, sizeof(float) * kTableFloats * n_members));
-  UQK_CUDA(cudaMemcpy(h->d_blobs, blobs_host, sizeof(float) * kBlobFloats * n_members, cudaMemcpyHostToDevice));
+  UQK_CUDA(cudaMemcpy2D(h->d_blobs, sizeof(float) * kBlobStride, blobs_host, sizeof(float) * kBlobFloats,
+                        sizeof(float) * kBlobFloats, n_members, cudaMemcpyHostToDevice));
   std::vector<uint16_t> packed(pb / 2);
   for (int m = 0; m < n_members; ++m) {
     fused_pack_member(blobs_host + (size_t)m * kBlobFloats, packed.data());
     UQK_CUDA(cudaMemcpy(reinterpret_cast<uint8_t*>(h->d_packed) + (size_t)m * pb, packed.data(), pb, cudaMemcpyHostToDevice));
-    int rc = build_tables(h->d_blobs + (size_t)m * kBlobFloats, nullptr, nullptr, 0, h->d_tables_inf + (size_t)m * kTableFloats, 0);
+    int rc = build_tables(h->d_blobs + (size_t)m * kBlobStride, nullptr, nullptr, 0, h->d_tables_inf + (size_t)m * kTableFloats, 0);
     if (rc) return rc;
   }
   UQK_CUDA(cudaDeviceSynchronize());
@@ -224,7 +225,7 @@ int uqk_forward_det(uqk_handle* hh, int member, const void* x_dev, int x_dtype, 
   if (precision == UQK_PREC_FP32) {
     // a one-member "ensemble" starting at `member`
     Handle view = *h;
-    view.d_blobs = h->d_blobs + (size_t)member * kBlobFloats;
+    view.d_blobs = h->d_blobs + (size_t)member * kBlobStride;
     rc = run_layersync(&view, x_dev, x_dtype, n, 1, true, false, UQK_BN_INFERENCE, 0, 0, nullptr, probs_dev, nullptr,
                        nullptr, s);
     h->d_x32 = view.d_x32; h->x32_cap = view.x32_cap; h->d_act[0] = view.d_act[0]; h->d_act[1] = view.d_act[1];

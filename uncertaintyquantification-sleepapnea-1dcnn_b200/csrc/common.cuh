@@ -54,6 +54,7 @@ inline BlobOffsets blob_offsets() {
   return o;
 }
 constexpr size_t kBlobFloats = 853441;
+constexpr size_t kBlobStride = 853444;   // device stride between members: keeps every member 16-byte aligned (float4 loads)
 
 // Per-layer channel offsets into the per-member affine tables (sum of Cout = 992).
 __host__ __device__ constexpr int ch_off(int l) {

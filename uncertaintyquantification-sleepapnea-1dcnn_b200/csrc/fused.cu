@@ -32,7 +32,8 @@ namespace uqk {
 // ---- geometry ---------------------------------------------------------------------------------------------------
 constexpr int kRowsPad = 136;                      // rows -4 .. 131 of a tile (4 zero rows above and below)
 constexpr int kPlaneBytes = kRowsPad * 16;         // one 8-channel chunk, all rows: 2176 B
-constexpr int kActBytes = (kMaxCh / 8) * kPlaneBytes;  // 69632 B per tile
+constexpr int kOnesPlane = kMaxCh / 8;             // plane 32: constant [1, 1, 0, ...] rows -> bias added by the MMA
+constexpr int kActBytes = (kMaxCh / 8 + 1) * kPlaneBytes;  // 71808 B per tile
 constexpr int kSlotBytes = 16384;                  // weight ring slot
 
 struct FusedLayer {
@@ -40,23 +41,27 @@ struct FusedLayer {
   int cout;
   int taps;
   int halo;
-  int nsteps;      // K=16 MMA steps per tile
+  int nconv;       // K=16 MMA steps of the convolution per tile
+  int nsteps;      // nconv + 1: the last step multiplies the ones-plane with the bias row
   int step_bytes;  // bytes of weights per step = cout * 32
   int sps;         // steps per ring stage
   int nstages;
   uint32_t w_off;  // byte offset of the layer inside one member's packed image
 };
 
+__host__ __device__ constexpr int fl_cout(int l) { return l == 0 ? 128 : l == 1 ? 192 : l == 2 ? 224 : l == 3 ? 96 : l == 4 ? 256 : 96; }
+__host__ __device__ constexpr int fl_nconv(int l) { return l == 0 ? 4 : l == 1 ? 40 : l == 2 ? 36 : l == 3 ? 98 : l == 4 ? 54 : 144; }
+__host__ __device__ constexpr uint32_t fl_bytes(int l) { return (uint32_t)(fl_nconv(l) + 1) * (uint32_t)fl_cout(l) * 32u; }
+__host__ __device__ constexpr uint32_t fl_off(int l) { return l == 0 ? 0u : fl_off(l - 1) + fl_bytes(l - 1); }
 __host__ __device__ constexpr FusedLayer fused_layer(int l) {
-  // nsteps: layer 1 = 4 tap pairs; others taps * cin / 16
-  return l == 0 ? FusedLayer{8, 128, 7, 3, 4, 4096, 4, 1, 0u}
-       : l == 1 ? FusedLayer{128, 192, 5, 2, 40, 6144, 2, 20, 16384u}
-       : l == 2 ? FusedLayer{192, 224, 3, 1, 36, 7168, 2, 18, 16384u + 245760u}
-       : l == 3 ? FusedLayer{224, 96, 7, 3, 98, 3072, 5, 20, 16384u + 245760u + 258048u}
-       : l == 4 ? FusedLayer{96, 256, 9, 4, 54, 8192, 2, 27, 16384u + 245760u + 258048u + 301056u}
-                : FusedLayer{256, 96, 9, 4, 144, 3072, 5, 29, 16384u + 245760u + 258048u + 301056u + 442368u};
+  const int cout = fl_cout(l), nsteps = fl_nconv(l) + 1, sb = cout * 32, sps = kSlotBytes / sb;
+  return FusedLayer{l == 0 ? 8 : l == 1 ? 128 : l == 2 ? 192 : l == 3 ? 224 : l == 4 ? 96 : 256,
+                    cout,
+                    l == 0 ? 7 : l == 1 ? 5 : l == 2 ? 3 : l == 3 ? 7 : 9,
+                    l == 0 ? 3 : l == 1 ? 2 : l == 2 ? 1 : l == 3 ? 3 : 4,
+                    fl_nconv(l), nsteps, sb, sps, (nsteps + sps - 1) / sps, fl_off(l)};
 }
-constexpr uint32_t kPackedBytes = 16384u + 245760u + 258048u + 301056u + 442368u + 442368u;  // 1,705,984
+constexpr uint32_t kPackedBytes = fl_off(5) + fl_bytes(5);
 
 size_t fused_packed_bytes() { return kPackedBytes; }
 
@@ -67,34 +72,46 @@ static inline uint16_t f32_to_bf16_rne(float f) {
   u += 0x7FFFu + ((u >> 16) & 1u);
   return (uint16_t)(u >> 16);
 }
+static inline float bf16_to_f32(uint16_t h) {
+  uint32_t u = (uint32_t)h << 16;
+  float f;
+  std::memcpy(&f, &u, 4);
+  return f;
+}
 
 // Host-side packing of one member into the shared-memory image the kernel streams:
 //   layer l, step s, plane p (K elements 8p..8p+7 of the step), output channel n, element kk:
 //   dst[(w_off/2) + ((s*2 + p)*cout + n)*8 + kk]
 //   layers 2..6: tap j = s / (cin/16), slab i = s % (cin/16), channel c = 16 i + 8 p + kk  -> W[j][c][n]
 //   layer 1    : tap j = 2 s + p, channel kk (<4)                                        -> W[j][kk][n], else 0
+//   bias step (s = nconv): plane 0, kk = 0 -> bf16(bias[n]), kk = 1 -> bf16(bias[n] - hi)  (hi + lo split: the MMA
+//   adds the bias with 16 mantissa bits because the A operand of this step is the constant [1, 1, 0, ...] plane)
 void fused_pack_member(const float* blob, uint16_t* dst) {
   const BlobOffsets off = blob_offsets();
   for (int l = 0; l < kBlocks; ++l) {
     const FusedLayer fl = fused_layer(l);
     const BlockDef b = block_def(l);
     const float* w = blob + off.conv_w[l];  // (k, cin, cout)
+    const float* bias = blob + off.conv_b[l];
     uint16_t* d = dst + fl.w_off / 2;
     for (int s = 0; s < fl.nsteps; ++s)
       for (int p = 0; p < 2; ++p)
         for (int n = 0; n < fl.cout; ++n)
           for (int kk = 0; kk < 8; ++kk) {
-            float v = 0.f;
-            if (l == 0) {
+            uint16_t o = 0;
+            if (s == fl.nconv) {
+              if (p == 0 && kk == 0) o = f32_to_bf16_rne(bias[n]);
+              if (p == 0 && kk == 1) o = f32_to_bf16_rne(bias[n] - bf16_to_f32(f32_to_bf16_rne(bias[n])));
+            } else if (l == 0) {
               const int j = 2 * s + p;
-              if (j < b.k && kk < b.cin) v = w[((size_t)j * b.cin + kk) * b.cout + n];
+              if (j < b.k && kk < b.cin) o = f32_to_bf16_rne(w[((size_t)j * b.cin + kk) * b.cout + n]);
             } else {
               const int slabs = b.cin / 16;
               const int j = s / slabs, i = s % slabs;
               const int c = 16 * i + 8 * p + kk;
-              v = w[((size_t)j * b.cin + c) * b.cout + n];
+              o = f32_to_bf16_rne(w[((size_t)j * b.cin + c) * b.cout + n]);
             }
-            d[((size_t)(s * 2 + p) * fl.cout + n) * 8 + kk] = f32_to_bf16_rne(v);
+            d[((size_t)(s * 2 + p) * fl.cout + n) * 8 + kk] = o;
           }
   }
 }
@@ -231,7 +248,6 @@ struct FusedArgs {
   long long n;
   int n_groups;
   int mode_de;
-  int dropout;
   uint32_t k0, k1;
   long long window_base;
   const uint32_t* mask_bits;
@@ -245,24 +261,283 @@ struct FusedArgs {
   long long n_units;
 };
 
+// dropout source of the epilogue
+constexpr int kDropNone = 0, kDropPhilox = 1, kDropBits = 2;
+
 template <int TILES, int NSLOTS>
 struct FusedCfg {
-  static constexpr int kWarps = 2 + 4 * TILES;
+  static constexpr int kEpiWarps = 8;                       // per tile: 2 warps per TMEM lane quarter
+  static constexpr int kEpiThreads = 32 * kEpiWarps;
+  static constexpr int kWarps = 2 + kEpiWarps * TILES;
   static constexpr int kThreads = 32 * kWarps;
   static constexpr int kWpu = 2 * TILES;  // windows per unit
   static constexpr int kTmemCols = 256 * TILES;
   // shared-memory map (bytes)
   static constexpr int oAct = 0;
   static constexpr int oRing = oAct + TILES * kActBytes;
-  static constexpr int oTab = oRing + NSLOTS * kSlotBytes;           // per tile: bias/scale/shift[256] + dense[100]
-  static constexpr int kTabBytes = (3 * 256 + 128) * 4;
-  static constexpr int oBar = oTab + TILES * kTabBytes;              // mbarriers
+  static constexpr int kTabFloats = 2 * 512 + 128;                   // 2 x (scale[256], shift[256]) + dense w[96] + b
+  static constexpr int oTab = oRing + NSLOTS * kSlotBytes;
+  static constexpr int oBar = oTab + TILES * kTabFloats * 4;         // mbarriers
   static constexpr int kNumBars = 2 * NSLOTS + 2 * TILES;
-  static constexpr int oMisc = oBar + 8 * kNumBars;                  // tmem ptr, zsum[TILES][2]
-  static constexpr int oProbs = oMisc + 16 + 8 * TILES;              // probs[kWpu][n_groups]
+  static constexpr int oMisc = oBar + 8 * kNumBars;                  // tmem ptr (16 B), zpart[TILES][2][4]
+  static constexpr int oAlo = oMisc + 16 + 32 * TILES;               // A-descriptor low words, one per (layer, step)
+  static constexpr int oProbs = oAlo + 4 * 392;                      // probs[kWpu][n_groups]
 };
 
-template <int TILES, int NSLOTS>
+// Bounded mbarrier wait.  `hint_ns` lets the hardware suspend the polling thread inside try_wait instead of
+// spinning; the watchdog turns a protocol bug into a trap (never a hung GPU).
+__device__ __forceinline__ void mbar_wait2(uint32_t bar, uint32_t parity, int* err_flag, int code) {
+  uint32_t spins = 0;
+  for (;;) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.b32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity), "r"(1000000u)
+        : "memory");
+    if (ok) return;
+    if (++spins > (1u << 22)) mbar_timeout(err_flag, code);
+  }
+}
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.b32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr)
+      : "memory");
+}
+// tcgen05.wait::ld with the loaded registers as in/out operands: every use of v[] depends on the wait.
+__device__ __forceinline__ void tmem_wait16(uint32_t (&v)[16]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]),
+                 "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15])
+               :
+               : "memory");
+}
+
+// Keep-bits of one 16-column chunk from two Philox4x32-10 calls (8 channels each): bit (8 q + e) = keep element e of
+// call q; 16-bit fields, keep iff field >= thr (low halves compared after a 16-bit shift, high halves in place).
+__device__ __forceinline__ uint32_t philox_keep16(uint32_t c0w, uint32_t pass, uint32_t c2, uint32_t chunk8,
+                                                  uint32_t k0, uint32_t k1, uint32_t thr_hi) {
+  uint32_t bits = 0;
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    const Philox4 r = philox4x32_10(c0w, pass, c2, chunk8 + q, k0, k1);
+    const uint32_t b = ((r.x << 16) >= thr_hi ? 1u : 0u) | (r.x >= thr_hi ? 2u : 0u) | ((r.y << 16) >= thr_hi ? 4u : 0u) |
+                       (r.y >= thr_hi ? 8u : 0u) | ((r.z << 16) >= thr_hi ? 16u : 0u) | (r.z >= thr_hi ? 32u : 0u) |
+                       ((r.w << 16) >= thr_hi ? 64u : 0u) | (r.w >= thr_hi ? 128u : 0u);
+    bits |= b << (8 * q);
+  }
+  return bits;
+}
+
+// One 16-column chunk of the epilogue: ReLU -> BatchNorm affine (dropout scale folded) -> dropout -> bf16 store
+// (layers 1-5) or dot with the dense kernel (layer 6).  The conv bias is already in the accumulator (bias MMA step).
+template <bool DROP, bool LAST, bool DBG>
+__device__ __forceinline__ void epi_chunk16(const uint32_t (&v)[16], int c0, const float* __restrict__ tab_s,
+                                            const float* __restrict__ tab_h, const float* __restrict__ tab_w,
+                                            uint32_t act_row, bool row_valid, uint32_t keep16, float& zacc, float* dbg) {
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    const int cb = c0 + 8 * q;
+    const float4 s0 = *reinterpret_cast<const float4*>(tab_s + cb), s1 = *reinterpret_cast<const float4*>(tab_s + cb + 4);
+    const float4 h0 = *reinterpret_cast<const float4*>(tab_h + cb), h1 = *reinterpret_cast<const float4*>(tab_h + cb + 4);
+    const float ss[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+    const float hh[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+    float y[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      y[e] = fmaf(fmaxf(__uint_as_float(v[8 * q + e]), 0.f), ss[e], hh[e]);
+      if (DROP) y[e] = (keep16 & (1u << (8 * q + e))) ? y[e] : 0.f;
+    }
+    if (DBG) {
+      if (dbg) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) dbg[cb + e] = row_valid ? y[e] : 0.f;
+      }
+    }
+    if (!LAST) {
+      uint32_t p0 = pack_bf16x2(y[0], y[1]), p1 = pack_bf16x2(y[2], y[3]), p2 = pack_bf16x2(y[4], y[5]),
+               p3 = pack_bf16x2(y[6], y[7]);
+      if (!row_valid) { p0 = 0u; p1 = 0u; p2 = 0u; p3 = 0u; }   // zero rows = the next layer's `same` padding
+      st_shared_v4(act_row + (uint32_t)(cb >> 3) * kPlaneBytes, p0, p1, p2, p3);
+    } else {
+      const float4 w0 = *reinterpret_cast<const float4*>(tab_w + cb), w1 = *reinterpret_cast<const float4*>(tab_w + cb + 4);
+      zacc = fmaf(y[0], w0.x, zacc); zacc = fmaf(y[1], w0.y, zacc); zacc = fmaf(y[2], w0.z, zacc); zacc = fmaf(y[3], w0.w, zacc);
+      zacc = fmaf(y[4], w1.x, zacc); zacc = fmaf(y[5], w1.y, zacc); zacc = fmaf(y[6], w1.z, zacc); zacc = fmaf(y[7], w1.w, zacc);
+    }
+  }
+}
+
+__host__ __device__ constexpr int fl_step_base(int l) { return l == 0 ? 0 : fl_step_base(l - 1) + fl_nconv(l - 1) + 1; }
+constexpr int kTotalSteps = fl_step_base(kBlocks);   // 382 convolution steps + 6 bias steps
+
+__device__ __forceinline__ uint64_t mk64(uint32_t lo, uint32_t hi) { return ((uint64_t)hi << 32) | (uint64_t)lo; }
+
+// ---- MMA issue of one layer (warp 1; the whole warp walks the schedule, one elected lane issues) -----------------
+// A-descriptor low words are precomputed per (layer, step) in shared memory (s_alo); the high word of every
+// descriptor is the constant SBO=128 | version=1.
+template <int L, int TILES, int NSLOTS, typename Cfg>
+__device__ __forceinline__ void issue_layer(uint32_t s_base, uint32_t tmem_base, const uint32_t* s_alo, uint32_t bar_full,
+                                            uint32_t bar_empty, uint32_t bar_acc, uint32_t bar_act, uint32_t& it,
+                                            uint32_t& n_act, int* err_flag, bool no_mma) {
+  constexpr FusedLayer fl = fused_layer(L);
+  constexpr uint32_t kHi = (128u >> 4) | (1u << 14);
+  constexpr uint32_t kBLbo = ((uint32_t)(fl.cout * 16) >> 4) << 16;
+  constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(fl.cout >> 3) << 17) | ((128u >> 4) << 24);
+  constexpr int kLast = fl.nsteps - (fl.nstages - 1) * fl.sps;
+  for (int tl = 0; tl < TILES; ++tl) mbar_wait2(bar_act + 8 * tl, n_act & 1, err_flag, 2);
+  ++n_act;
+  tc_fence_after();
+#pragma unroll 1
+  for (int st = 0; st < fl.nstages; ++st, ++it) {
+    const int slot = it % NSLOTS;
+    const uint32_t ph = (it / NSLOTS) & 1;
+    mbar_wait2(bar_full + 8 * slot, ph, err_flag, 3);
+    tc_fence_after();
+    const int nst = (st == fl.nstages - 1) ? kLast : fl.sps;
+    const uint32_t b_lo0 = (((s_base + Cfg::oRing + slot * kSlotBytes) >> 4) & 0x3FFFu) | kBLbo;
+    if (elect_one()) {
+      const uint32_t* alo = s_alo + fl_step_base(L) + st * fl.sps;
+      if (!no_mma) {
+#pragma unroll
+        for (int sl = 0; sl < fl.sps; ++sl) {
+          if (sl < nst) {
+            const uint32_t a0 = alo[sl];
+            const uint64_t bdesc = mk64(b_lo0 + (uint32_t)sl * (uint32_t)(fl.step_bytes >> 4), kHi);
+            const uint32_t acc = (st > 0 || sl > 0) ? 1u : 0u;
+            umma_bf16(tmem_base, mk64(a0, kHi), bdesc, kIdesc, acc);
+            if (TILES == 2) umma_bf16(tmem_base + 256, mk64(a0 + (uint32_t)(kActBytes >> 4), kHi), bdesc, kIdesc, acc);
+          }
+        }
+      }
+      umma_commit(bar_empty + 8 * slot);   // frees the ring slot when these MMAs have read it
+    }
+    __syncwarp();
+  }
+  if (elect_one()) {
+    for (int tl = 0; tl < TILES; ++tl) umma_commit(bar_acc + 8 * tl);   // accumulator(s) complete
+  }
+  __syncwarp();
+}
+
+// ---- epilogue of one layer (8 warps per tile) -----------------------------------------------------------------------
+struct EpiCtx {
+  uint32_t act_row, taddr, c0w, k0, k1, bar_acc, bar_act;
+  int t, colhalf, tid_t, we, lane, quarter, slot_w, tl;
+  bool row_valid;
+  float* tab;
+  float* tab_w;
+  float* zp;
+  int* err_flag;
+};
+
+template <int L, int DROP, bool DBG, int EPI_THREADS>
+__device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, const float* __restrict__ tab_g, int g,
+                                          long long win, uint32_t& n_acc, float* probs_s, float* dbg_base) {
+  constexpr int cout = fl_cout(L);
+  constexpr int my = cout / 32;            // 16-column chunks owned by this warp (chunks colhalf, colhalf+2, ...)
+  constexpr bool kLastLayer = (L == kBlocks - 1);
+  // stage this layer's scale / shift (double buffered) while the MMAs run
+  float* tab_s = c.tab + (L & 1) * 512;
+  float* tab_h = tab_s + 256;
+  for (int i = c.tid_t; i < cout; i += EPI_THREADS) {
+    tab_s[i] = __ldg(tab_g + kChTotal + ch_off(L) + i);
+    tab_h[i] = __ldg(tab_g + 2 * kChTotal + ch_off(L) + i);
+  }
+  if (kLastLayer && c.tid_t < kDenseIn + 1) c.tab_w[c.tid_t] = __ldg(tab_g + 3 * kChTotal + c.tid_t);
+
+  // dropout keep-bits of this thread's chunks, computed in the shadow of the layer's MMAs
+  uint32_t kb[(my + 1) / 2];
+#pragma unroll
+  for (int j = 0; j < (my + 1) / 2; ++j) kb[j] = 0u;
+  if (DROP == kDropPhilox) {
+    constexpr uint32_t thr_hi = drop_thr(L) << 16;
+    const uint32_t c2 = ((uint32_t)L << 16) | (uint32_t)c.t;
+#pragma unroll
+    for (int j = 0; j < my; ++j) {
+      const uint32_t k = (uint32_t)(c.colhalf + 2 * j);
+      kb[j >> 1] |= philox_keep16(c.c0w, (uint32_t)g, c2, 2u * k, c.k0, c.k1, thr_hi) << (16 * (j & 1));
+    }
+  } else if (DROP == kDropBits) {
+    const uint32_t* mrow = a.mask_bits + ((((size_t)g * a.n + (c.row_valid ? win : 0)) * kBlocks + L) * kL + (c.row_valid ? c.t : 0)) * 8;
+#pragma unroll
+    for (int j = 0; j < my; ++j) {
+      const int k = c.colhalf + 2 * j;
+      const uint32_t w = c.row_valid ? __ldg(mrow + (k >> 1)) : 0u;
+      kb[j >> 1] |= ((w >> (16 * (k & 1))) & 0xFFFFu) << (16 * (j & 1));
+    }
+  }
+
+  // one warp polls the accumulator barrier; the others sleep in the named barrier (no issue slots burnt)
+  if (c.we == 0) {
+    mbar_wait2(c.bar_acc, n_acc & 1, c.err_flag, 4);
+    tc_fence_after();
+    tc_fence_before();
+  }
+  ++n_acc;
+  named_bar_sync(1 + c.tl, EPI_THREADS);
+  tc_fence_after();
+
+  float* dbg = nullptr;
+  if (DBG) {
+    if (dbg_base) dbg = dbg_base + (size_t)L * 128 * 256;
+  }
+  float zacc = 0.f;
+  // software pipeline: the TMEM load of the next chunk is in flight while the current one is processed
+  uint32_t va[16], vb[16];
+  tmem_ld16(c.taddr + (uint32_t)(16 * c.colhalf), va);
+#pragma unroll
+  for (int j = 0; j < my; j += 2) {
+    tmem_wait16(va);
+    if (j + 1 < my) tmem_ld16(c.taddr + (uint32_t)(16 * (c.colhalf + 2 * (j + 1))), vb);
+    epi_chunk16<DROP != kDropNone, kLastLayer, DBG>(va, 16 * (c.colhalf + 2 * j), tab_s, tab_h, c.tab_w, c.act_row, c.row_valid,
+                                                   (kb[j >> 1] >> (16 * (j & 1))) & 0xFFFFu, zacc, dbg);
+    if (j + 1 < my) {
+      tmem_wait16(vb);
+      if (j + 2 < my) tmem_ld16(c.taddr + (uint32_t)(16 * (c.colhalf + 2 * (j + 2))), va);
+      epi_chunk16<DROP != kDropNone, kLastLayer, DBG>(vb, 16 * (c.colhalf + 2 * (j + 1)), tab_s, tab_h, c.tab_w, c.act_row,
+                                                     c.row_valid, (kb[(j + 1) >> 1] >> (16 * ((j + 1) & 1))) & 0xFFFFu, zacc, dbg);
+    }
+  }
+
+  if (!kLastLayer) {
+    // activations of the next layer are in place: publish to the tensor-core proxy, hand TMEM back
+    fence_proxy_async();
+    tc_fence_before();
+    mbar_arrive(c.bar_act);
+  } else {
+    // ---- head: GlobalAveragePooling1D + Dense(96->1) + sigmoid; one window = 2 lane quarters x 2 column halves
+    tc_fence_before();
+    if (!c.row_valid) zacc = 0.f;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) zacc += __shfl_xor_sync(0xffffffffu, zacc, o);
+    if (c.lane == 0) c.zp[c.slot_w * 4 + (c.quarter & 1) * 2 + c.colhalf] = zacc;
+    named_bar_sync(1 + c.tl, EPI_THREADS);
+    if (c.colhalf == 0 && c.t == 0 && (c.quarter & 1) == 0) {
+      const float* z4 = c.zp + c.slot_w * 4;
+      const float z = (((z4[0] + z4[1]) + z4[2]) + z4[3]) * (1.0f / (float)kL) + c.tab_w[kDenseIn];   // fixed order
+      const float p = 1.0f / (1.0f + expf(-z));
+      probs_s[(2 * c.tl + c.slot_w) * a.n_groups + g] = p;
+      if (a.probs && win < a.n) a.probs[(size_t)g * a.n + win] = p;
+    }
+  }
+}
+
+template <int TILES, int NSLOTS, int DROP, bool DBG>
 __global__ void __launch_bounds__(FusedCfg<TILES, NSLOTS>::kThreads, TILES == 1 ? 2 : 1)
 fused_forward_kernel(const FusedArgs a) {
   using Cfg = FusedCfg<TILES, NSLOTS>;
@@ -276,16 +551,30 @@ fused_forward_kernel(const FusedArgs a) {
   const uint32_t bar_acc = bar_empty + 8 * NSLOTS;              // [TILES]  accumulator complete (MMA -> epilogue)
   const uint32_t bar_act = bar_acc + 8 * TILES;                 // [TILES]  activations ready (epilogue -> MMA)
   volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(smem + Cfg::oMisc);
-  float* zsum = reinterpret_cast<float*>(smem + Cfg::oMisc + 16);  // [TILES][2]
-  float* probs_s = reinterpret_cast<float*>(smem + Cfg::oProbs);   // [kWpu][n_groups]
+  float* zpart = reinterpret_cast<float*>(smem + Cfg::oMisc + 16);  // [TILES][2 windows][4 partial sums]
+  uint32_t* s_alo = reinterpret_cast<uint32_t*>(smem + Cfg::oAlo);  // [kTotalSteps] A-descriptor low words (tile 0)
+  float* probs_s = reinterpret_cast<float*>(smem + Cfg::oProbs);    // [kWpu][n_groups]
 
   // ---- one-time set-up
   for (int i = threadIdx.x; i < (TILES * kActBytes) / 16; i += Cfg::kThreads)
     reinterpret_cast<uint4*>(smem + Cfg::oAct)[i] = make_uint4(0, 0, 0, 0);   // halo rows stay zero for ever
-  if (threadIdx.x < 2 * TILES) zsum[threadIdx.x] = 0.f;
+  for (int i = threadIdx.x; i < kTotalSteps; i += Cfg::kThreads) {
+    int l = 0, sidx = i;
+    while (sidx >= fl_nconv(l) + 1) { sidx -= fl_nconv(l) + 1; ++l; }
+    const FusedLayer fl = fused_layer(l);
+    uint32_t a_off, a_lbo;
+    if (sidx == fl.nconv) { a_off = (uint32_t)kOnesPlane * kPlaneBytes + 4u * 16u; a_lbo = 16u; }          // bias step
+    else if (l == 0) { a_off = (uint32_t)(2 * sidx + 1) * 16u; a_lbo = 16u; }                               // tap pair
+    else {
+      const int slabs = fl.cinp / 16, tap = sidx / slabs, slab = sidx % slabs;
+      a_off = (uint32_t)(2 * slab) * kPlaneBytes + (uint32_t)(tap - fl.halo + 4) * 16u;                     // shifted rows
+      a_lbo = kPlaneBytes;
+    }
+    s_alo[i] = (((s_base + Cfg::oAct + a_off) >> 4) & 0x3FFFu) | ((a_lbo >> 4) << 16);
+  }
   if (threadIdx.x == 0) {
     for (int i = 0; i < NSLOTS; ++i) { mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, 1); }
-    for (int i = 0; i < TILES; ++i) { mbar_init(bar_acc + 8 * i, 1); mbar_init(bar_act + 8 * i, 128); }
+    for (int i = 0; i < TILES; ++i) { mbar_init(bar_acc + 8 * i, 1); mbar_init(bar_act + 8 * i, Cfg::kEpiThreads); }
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -301,9 +590,8 @@ fused_forward_kernel(const FusedArgs a) {
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
 
-  // perf-decomposition switches (tests/tools only): results are WRONG when any is set
+  // perf-decomposition switches (tools only): results are WRONG when any is set
   const bool dbg_no_copy = (a.variant & 2) != 0;   // producer does not fetch weights
-  const bool dbg_raw_epi = (a.variant & 4) != 0;   // epilogue skips bias/ReLU/BN/dropout math
   const bool dbg_no_mma = (a.variant & 8) != 0;    // issuer skips the MMAs
 
   if (warp == 0) {
@@ -313,13 +601,14 @@ fused_forward_kernel(const FusedArgs a) {
       for (long long unit = blockIdx.x; unit < a.n_units; unit += gridDim.x) {
         for (int g = 0; g < a.n_groups; ++g) {
           const uint8_t* wmem = a.packed + (size_t)(a.mode_de ? g : 0) * kPackedBytes;
+#pragma unroll 1
           for (int l = 0; l < kBlocks; ++l) {
             const FusedLayer fl = fused_layer(l);
             int step = 0;
             for (int st = 0; st < fl.nstages; ++st, ++it) {
               const int slot = it % NSLOTS;
               const uint32_t ph = (it / NSLOTS) & 1;
-              mbar_wait(bar_empty + 8 * slot, ph ^ 1, a.err_flag, 1);
+              mbar_wait2(bar_empty + 8 * slot, ph ^ 1, a.err_flag, 1);
               const int nst = min(fl.sps, fl.nsteps - step);
               const uint32_t bytes = (uint32_t)nst * fl.step_bytes;
               if (dbg_no_copy) { mbar_arrive(bar_full + 8 * slot); }
@@ -335,198 +624,88 @@ fused_forward_kernel(const FusedArgs a) {
       }
     }
   } else if (warp == 1) {
-    // =========================== MMA issuer (one thread) ===========================
-    if (lane == 0) {
-      uint32_t it = 0, n_act = 0;
-      for (long long unit = blockIdx.x; unit < a.n_units; unit += gridDim.x) {
-        for (int g = 0; g < a.n_groups; ++g) {
-          for (int l = 0; l < kBlocks; ++l) {
-            const FusedLayer fl = fused_layer(l);
-            const uint32_t idesc = umma_idesc(fl.cout);
-            const int slabs = l == 0 ? 1 : fl.cinp / 16;
-            for (int tl = 0; tl < TILES; ++tl) mbar_wait(bar_act + 8 * tl, n_act & 1, a.err_flag, 2);
-            ++n_act;
-            tc_fence_after();
-            int step = 0, tap = 0, slab = 0;
-            for (int st = 0; st < fl.nstages; ++st, ++it) {
-              const int slot = it % NSLOTS;
-              const uint32_t ph = (it / NSLOTS) & 1;
-              mbar_wait(bar_full + 8 * slot, ph, a.err_flag, 3);
-              tc_fence_after();
-              const int nst = min(fl.sps, fl.nsteps - step);
-              const uint32_t bslot = s_base + Cfg::oRing + slot * kSlotBytes;
-              for (int sl = 0; sl < nst; ++sl, ++step) {
-                // A: rows shifted by the tap; B: this step's two K planes
-                uint32_t a_off, a_lbo;
-                if (l == 0) { a_off = (uint32_t)(2 * step + 1) * 16u; a_lbo = 16u; }
-                else { a_off = (uint32_t)(2 * slab) * kPlaneBytes + (uint32_t)(tap - fl.halo + 4) * 16u; a_lbo = kPlaneBytes; }
-                const uint32_t b_addr = bslot + (uint32_t)sl * fl.step_bytes;
-                const uint32_t b_lbo = (uint32_t)fl.cout * 16u;
-                const uint64_t bdesc = umma_desc(b_addr, b_lbo, 128u);
-#pragma unroll
-                for (int tl = 0; tl < TILES; ++tl) {
-                  const uint32_t a_addr = s_base + Cfg::oAct + tl * kActBytes + a_off;
-                  const uint64_t adesc = umma_desc(a_addr, a_lbo, 128u);
-                  if (!dbg_no_mma) umma_bf16(tmem_base + tl * 256, adesc, bdesc, idesc, step > 0 ? 1u : 0u);
-                }
-                if (++slab == slabs) { slab = 0; ++tap; }
-              }
-              umma_commit(bar_empty + 8 * slot);   // frees the ring slot when these MMAs have read it
-            }
-            for (int tl = 0; tl < TILES; ++tl) umma_commit(bar_acc + 8 * tl);   // accumulator(s) complete
-          }
-        }
+    // =========================== MMA issuer ===========================
+    uint32_t it = 0, n_act = 0;
+    for (long long unit = blockIdx.x; unit < a.n_units; unit += gridDim.x) {
+      for (int g = 0; g < a.n_groups; ++g) {
+        issue_layer<0, TILES, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_acc, bar_act, it, n_act, a.err_flag, dbg_no_mma);
+        issue_layer<1, TILES, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_acc, bar_act, it, n_act, a.err_flag, dbg_no_mma);
+        issue_layer<2, TILES, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_acc, bar_act, it, n_act, a.err_flag, dbg_no_mma);
+        issue_layer<3, TILES, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_acc, bar_act, it, n_act, a.err_flag, dbg_no_mma);
+        issue_layer<4, TILES, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_acc, bar_act, it, n_act, a.err_flag, dbg_no_mma);
+        issue_layer<5, TILES, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_acc, bar_act, it, n_act, a.err_flag, dbg_no_mma);
       }
     }
   } else {
-    // =========================== epilogue warps: 4 per tile ===========================
-    const int tl = (warp - 2) >> 2;
-    const int quarter = warp & 3;                 // TMEM lanes [32*quarter, +32) are accessible to this warp
-    const int row = quarter * 32 + lane;          // accumulator row = TMEM lane
-    const int slot_w = row >> 6;                  // which of the tile's two windows
-    const int t = row & 63;                       // time step (60..63 = zero rows)
-    const int tid_t = (warp - 2 - 4 * tl) * 32 + lane;  // 0..127 within the tile's epilogue group
-    float* tab = reinterpret_cast<float*>(smem + Cfg::oTab + tl * Cfg::kTabBytes);
-    const uint32_t act_row = s_base + Cfg::oAct + tl * kActBytes + (uint32_t)(row + 4) * 16u;
-    const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(tl * 256);
+    // =========================== epilogue warps: 8 per tile ===========================
+    const int ew = warp - 2;
+    EpiCtx c;
+    c.tl = ew >> 3;
+    c.we = ew & 7;
+    c.lane = lane;
+    c.quarter = warp & 3;                         // TMEM lanes [32*quarter, +32) are accessible to this warp
+    c.colhalf = c.we >> 2;                        // which half of the 16-column chunks this warp owns
+    const int row = c.quarter * 32 + lane;        // accumulator row = TMEM lane
+    c.slot_w = row >> 6;                          // which of the tile's two windows
+    c.t = row & 63;                               // time step (60..63 = zero rows)
+    c.tid_t = c.we * 32 + lane;                   // 0..255 within the tile's epilogue group
+    c.tab = reinterpret_cast<float*>(smem + Cfg::oTab) + c.tl * Cfg::kTabFloats;
+    c.tab_w = c.tab + 1024;
+    c.act_row = s_base + Cfg::oAct + c.tl * kActBytes + (uint32_t)(row + 4) * 16u;
+    c.taddr = tmem_base + ((uint32_t)(c.quarter * 32) << 16) + (uint32_t)(c.tl * 256);
+    c.zp = zpart + c.tl * 8;
+    c.bar_acc = bar_acc + 8 * c.tl;
+    c.bar_act = bar_act + 8 * c.tl;
+    c.k0 = a.k0; c.k1 = a.k1;
+    c.err_flag = a.err_flag;
     uint32_t n_acc = 0;
 
     for (long long unit = blockIdx.x; unit < a.n_units; unit += gridDim.x) {
-      const long long win = unit * Cfg::kWpu + 2 * tl + slot_w;
-      const bool row_valid = (t < kL) && (win < a.n);
+      const long long win = unit * Cfg::kWpu + 2 * c.tl + c.slot_w;
+      c.row_valid = (c.t < kL) && (win < a.n);
       // this row's 4 input features as bf16 (kept in registers for all groups of the unit)
       uint32_t xin0 = 0, xin1 = 0;
-      if (row_valid) {
-        float f0, f1, f2, f3;
-        if (a.x_f64) {
-          const double2* p = reinterpret_cast<const double2*>(static_cast<const double*>(a.x) + ((size_t)win * kL + t) * kF);
-          const double2 u = __ldg(p), v = __ldg(p + 1);
-          f0 = (float)u.x; f1 = (float)u.y; f2 = (float)v.x; f3 = (float)v.y;
-        } else {
-          const float4 u = __ldg(reinterpret_cast<const float4*>(static_cast<const float*>(a.x) + ((size_t)win * kL + t) * kF));
-          f0 = u.x; f1 = u.y; f2 = u.z; f3 = u.w;
+      if (c.colhalf == 0) {
+        if (c.row_valid) {
+          float f0, f1, f2, f3;
+          if (a.x_f64) {
+            const double2* p = reinterpret_cast<const double2*>(static_cast<const double*>(a.x) + ((size_t)win * kL + c.t) * kF);
+            const double2 u = __ldg(p), v = __ldg(p + 1);
+            f0 = (float)u.x; f1 = (float)u.y; f2 = (float)v.x; f3 = (float)v.y;
+          } else {
+            const float4 u = __ldg(reinterpret_cast<const float4*>(static_cast<const float*>(a.x) + ((size_t)win * kL + c.t) * kF));
+            f0 = u.x; f1 = u.y; f2 = u.z; f3 = u.w;
+          }
+          xin0 = pack_bf16x2(f0, f1);
+          xin1 = pack_bf16x2(f2, f3);
         }
-        xin0 = pack_bf16x2(f0, f1);
-        xin1 = pack_bf16x2(f2, f3);
+      } else {
+        // constant plane [1, 1, 0, ...] on valid rows: the bias step of every layer reads it as its A operand
+        st_shared_v4(c.act_row + (uint32_t)kOnesPlane * kPlaneBytes, c.row_valid ? 0x3F803F80u : 0u, 0u, 0u, 0u);
       }
-      const uint32_t c0w = (uint32_t)(a.window_base + win);
+      c.c0w = (uint32_t)(a.window_base + win);
+      float* dbg_base = nullptr;
+      if (DBG) {
+        if (a.dbg_act && blockIdx.x == 0 && unit == blockIdx.x && c.tl == 0) dbg_base = a.dbg_act + (size_t)row * 256;
+      }
 
       for (int g = 0; g < a.n_groups; ++g) {
         // ---- layer-1 input: channels 0..3 real, 4..7 zero, in plane 0
-        st_shared_v4(act_row, xin0, xin1, 0u, 0u);
+        if (c.colhalf == 0) st_shared_v4(c.act_row, xin0, xin1, 0u, 0u);
         fence_proxy_async();
-        mbar_arrive(bar_act + 8 * tl);
-
+        mbar_arrive(c.bar_act);
         const float* tab_g = a.tables + (size_t)(a.mode_de ? g : 0) * kTableFloats;
-        for (int l = 0; l < kBlocks; ++l) {
-          const FusedLayer fl = fused_layer(l);
-          const int cout = fl.cout;
-          // stage this layer's bias / scale / shift (and the dense layer for l == 5) while the MMAs run
-          named_bar_sync(1 + tl, 128);   // previous layer's readers of `tab` are done
-          for (int i = tid_t; i < cout; i += 128) {
-            tab[i] = __ldg(tab_g + ch_off(l) + i);
-            tab[256 + i] = __ldg(tab_g + kChTotal + ch_off(l) + i);
-            tab[512 + i] = __ldg(tab_g + 2 * kChTotal + ch_off(l) + i);
-          }
-          if (l == kBlocks - 1 && tid_t < kDenseIn + 1) tab[768 + tid_t] = __ldg(tab_g + 3 * kChTotal + tid_t);
-          named_bar_sync(1 + tl, 128);
-
-          mbar_wait(bar_acc + 8 * tl, n_acc & 1, a.err_flag, 4);
-          ++n_acc;
-          tc_fence_after();
-
-          const uint32_t thr = drop_thr(l);
-          const uint32_t* mrow = nullptr;
-          if (a.dropout && a.mask_bits && row_valid)
-            mrow = a.mask_bits + ((((size_t)g * a.n + win) * kBlocks + l) * kL + t) * 8;
-          float* dbg = nullptr;
-          if (a.dbg_act && blockIdx.x == 0 && unit == blockIdx.x && g == 0 && tl == 0)
-            dbg = a.dbg_act + ((size_t)l * 128 + row) * 256;
-          float zacc = 0.f;
-
-          for (int c0 = 0; c0 < cout; c0 += 32) {
-            uint32_t v[32];
-            tmem_ld32(taddr + (uint32_t)c0, v);
-            tmem_ld_wait();
-            uint32_t mword = 0xFFFFFFFFu;
-            if (a.dropout && a.mask_bits) mword = mrow ? __ldg(mrow + (c0 >> 5)) : 0u;
-            if (dbg_raw_epi) {
-#pragma unroll
-              for (int q = 0; q < 4; ++q)
-                st_shared_v4(act_row + (uint32_t)((c0 >> 3) + q) * kPlaneBytes, v[8 * q] & 0x3F803F80u, v[8 * q + 2] & 0x3F803F80u,
-                             v[8 * q + 4] & 0x3F803F80u, v[8 * q + 6] & 0x3F803F80u);
-              continue;
-            }
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              const int cb = c0 + 8 * q;
-              uint32_t keep = 0xFFu;
-              if (a.dropout) {
-                if (a.mask_bits) {
-                  keep = (mword >> (8 * q)) & 0xFFu;
-                } else {
-                  const Philox4 r = philox4x32_10(c0w, (uint32_t)g, ((uint32_t)l << 16) | (uint32_t)t,
-                                                  (uint32_t)(cb >> 3), a.k0, a.k1);
-                  keep = (uint32_t)((r.x & 0xFFFFu) >= thr) | ((uint32_t)((r.x >> 16) >= thr) << 1) |
-                         ((uint32_t)((r.y & 0xFFFFu) >= thr) << 2) | ((uint32_t)((r.y >> 16) >= thr) << 3) |
-                         ((uint32_t)((r.z & 0xFFFFu) >= thr) << 4) | ((uint32_t)((r.z >> 16) >= thr) << 5) |
-                         ((uint32_t)((r.w & 0xFFFFu) >= thr) << 6) | ((uint32_t)((r.w >> 16) >= thr) << 7);
-                }
-              }
-              if (!row_valid) keep = 0u;   // zero rows (the next layer's `same` padding) and out-of-range windows
-              const float4 b0 = *reinterpret_cast<const float4*>(tab + cb), b1 = *reinterpret_cast<const float4*>(tab + cb + 4);
-              const float4 s0 = *reinterpret_cast<const float4*>(tab + 256 + cb), s1 = *reinterpret_cast<const float4*>(tab + 256 + cb + 4);
-              const float4 h0 = *reinterpret_cast<const float4*>(tab + 512 + cb), h1 = *reinterpret_cast<const float4*>(tab + 512 + cb + 4);
-              const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-              const float ss[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
-              const float hh[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
-              float y[8];
-#pragma unroll
-              for (int e = 0; e < 8; ++e) {
-                const float r0 = fmaxf(__uint_as_float(v[8 * q + e]) + bb[e], 0.f);   // bias + ReLU
-                const float y0 = fmaf(r0, ss[e], hh[e]);                                // BatchNorm affine (* 1/keep)
-                y[e] = ((keep >> e) & 1u) ? y0 : 0.f;                                   // dropout
-              }
-              if (dbg) {
-#pragma unroll
-                for (int e = 0; e < 8; ++e) dbg[cb + e] = y[e];
-              }
-              if (l < kBlocks - 1) {
-                st_shared_v4(act_row + (uint32_t)(cb >> 3) * kPlaneBytes, pack_bf16x2(y[0], y[1]), pack_bf16x2(y[2], y[3]),
-                             pack_bf16x2(y[4], y[5]), pack_bf16x2(y[6], y[7]));
-              } else {
-                const float4 w0 = *reinterpret_cast<const float4*>(tab + 768 + cb), w1 = *reinterpret_cast<const float4*>(tab + 768 + cb + 4);
-                zacc = fmaf(y[0], w0.x, zacc); zacc = fmaf(y[1], w0.y, zacc); zacc = fmaf(y[2], w0.z, zacc); zacc = fmaf(y[3], w0.w, zacc);
-                zacc = fmaf(y[4], w1.x, zacc); zacc = fmaf(y[5], w1.y, zacc); zacc = fmaf(y[6], w1.z, zacc); zacc = fmaf(y[7], w1.w, zacc);
-              }
-            }
-          }
-
-          if (l < kBlocks - 1) {
-            // activations of the next layer are in place: publish to the tensor-core proxy, hand TMEM back
-            fence_proxy_async();
-            tc_fence_before();
-            mbar_arrive(bar_act + 8 * tl);
-          } else {
-            // ---- head: GlobalAveragePooling1D + Dense(96->1) + sigmoid; rows of one window = 2 warps
-            tc_fence_before();
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) zacc += __shfl_xor_sync(0xffffffffu, zacc, o);
-            if (lane == 0) atomicAdd(&zsum[tl * 2 + slot_w], zacc);
-            named_bar_sync(1 + tl, 128);
-            if ((row & 63) == 0) {
-              const float z = zsum[tl * 2 + slot_w] * (1.0f / (float)kL) + tab[768 + kDenseIn];
-              const float p = 1.0f / (1.0f + expf(-z));
-              probs_s[(2 * tl + slot_w) * a.n_groups + g] = p;
-              zsum[tl * 2 + slot_w] = 0.f;
-              if (a.probs && win < a.n) a.probs[(size_t)g * a.n + win] = p;
-            }
-          }
-        }
+        float* dbg_g = (DBG && g == 0) ? dbg_base : nullptr;
+        epi_layer<0, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
+        epi_layer<1, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
+        epi_layer<2, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
+        epi_layer<3, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
+        epi_layer<4, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
+        epi_layer<5, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
       }
       // ---- K3: per-window reductions over the T (or M) probabilities, in the reference's evaluation order
-      if ((row & 63) == 0 && win < a.n) {
-        const float* pw = probs_s + (2 * tl + slot_w) * a.n_groups;
+      if (c.colhalf == 0 && c.t == 0 && (c.quarter & 1) == 0 && win < a.n) {
+        const float* pw = probs_s + (2 * c.tl + c.slot_w) * a.n_groups;
         window_metrics([&](int tt) { return pw[tt]; }, a.n_groups, win, a.out);
       }
     }
@@ -543,38 +722,59 @@ fused_forward_kernel(const FusedArgs a) {
 }
 
 // ---- host launcher ----------------------------------------------------------------------------------------------
-template <int TILES, int NSLOTS>
+template <int TILES, int NSLOTS, int DROP, bool DBG>
 static int launch_variant(const FusedParams& p, cudaStream_t s) {
   using Cfg = FusedCfg<TILES, NSLOTS>;
   FusedArgs a{};
   a.x = p.x; a.x_f64 = p.x_dtype == UQK_F64; a.n = p.n; a.n_groups = p.n_groups; a.mode_de = p.mode_de;
-  a.dropout = p.dropout; a.k0 = (uint32_t)(p.seed & 0xFFFFFFFFull); a.k1 = (uint32_t)(p.seed >> 32);
+  a.k0 = (uint32_t)(p.seed & 0xFFFFFFFFull); a.k1 = (uint32_t)(p.seed >> 32);
   a.window_base = p.window_base; a.mask_bits = p.mask_bits; a.packed = reinterpret_cast<const uint8_t*>(p.packed);
   a.tables = p.tables; a.probs = p.probs; a.out = p.out; a.dbg_act = p.dbg_act; a.err_flag = p.err_flag;
   a.variant = p.variant;
   a.n_units = (p.n + Cfg::kWpu - 1) / Cfg::kWpu;
   const size_t smem = (size_t)Cfg::oProbs + (size_t)Cfg::kWpu * p.n_groups * sizeof(float);
-  if (smem > 227 * 1024) { set_error("fused kernel: %d passes/members do not fit in shared memory", p.n_groups); return UQK_E_SHAPE; }
+  if (smem > 227 * 1024) return UQK_E_SHAPE;   // caller falls back to the smaller configuration
   int dev = 0, sms = 148;
   UQK_CUDA(cudaGetDevice(&dev));
   UQK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  UQK_CUDA(cudaFuncSetAttribute(fused_forward_kernel<TILES, NSLOTS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  auto kern = fused_forward_kernel<TILES, NSLOTS, DROP, DBG>;
+  UQK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 1;
-  UQK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fused_forward_kernel<TILES, NSLOTS>, Cfg::kThreads, smem));
+  UQK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, Cfg::kThreads, smem));
   if (per_sm < 1) { set_error("fused kernel does not fit on an SM (smem %zu)", smem); return UQK_E_CUDA; }
   if (per_sm * Cfg::kTmemCols > 512) per_sm = 512 / Cfg::kTmemCols;   // TMEM: 512 columns per SM
   const long long grid = std::min<long long>(a.n_units, (long long)sms * per_sm);
-  fused_forward_kernel<TILES, NSLOTS><<<(unsigned)grid, Cfg::kThreads, smem, s>>>(a);
+  kern<<<(unsigned)grid, Cfg::kThreads, smem, s>>>(a);
   UQK_LAUNCH_CHECK();
   return UQK_OK;
 }
 
+template <int TILES, int NSLOTS>
+static int launch_drop(const FusedParams& p, cudaStream_t s) {
+  const int drop = !p.dropout ? kDropNone : (p.mask_bits ? kDropBits : kDropPhilox);
+  if (p.dbg_act) {
+    switch (drop) {
+      case kDropNone: return launch_variant<TILES, NSLOTS, kDropNone, true>(p, s);
+      case kDropPhilox: return launch_variant<TILES, NSLOTS, kDropPhilox, true>(p, s);
+      default: return launch_variant<TILES, NSLOTS, kDropBits, true>(p, s);
+    }
+  }
+  switch (drop) {
+    case kDropNone: return launch_variant<TILES, NSLOTS, kDropNone, false>(p, s);
+    case kDropPhilox: return launch_variant<TILES, NSLOTS, kDropPhilox, false>(p, s);
+    default: return launch_variant<TILES, NSLOTS, kDropBits, false>(p, s);
+  }
+}
+
 int fused_launch(const FusedParams& p, cudaStream_t s) {
   if (p.n == 0) return UQK_OK;
-  switch (p.variant >> 4) {
-    case 1: return launch_variant<1, 2>(p, s);    // one tile per CTA, two CTAs per SM
-    default: return launch_variant<2, 4>(p, s);   // two tiles per CTA share one weight stream
+  if ((p.variant >> 4) != 1) {
+    const int rc = launch_drop<2, 4>(p, s);       // two tiles per CTA share one weight stream
+    if (rc != UQK_E_SHAPE) return rc;             // too many passes for its shared memory -> smaller configuration
   }
+  const int rc = launch_drop<1, 2>(p, s);         // one tile per CTA, two CTAs per SM
+  if (rc == UQK_E_SHAPE) set_error("fused kernel: %d passes/members do not fit in shared memory", p.n_groups);
+  return rc;
 }
 
 }  // namespace uqk
