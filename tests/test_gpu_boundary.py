@@ -106,7 +106,7 @@ def test_patient_reduce_matches_reference_script_output(golden_dir):
     np.testing.assert_array_equal(mine["num_windows"].values, ref["num_windows"].values)     # counts, exact
     for c in ref.columns[1:-1]:
         np.testing.assert_allclose(mine[c].values, ref[c].values.astype(float), rtol=1e-6, atol=1e-9, err_msg=c)
-    np.testing.assert_array_equal(mine["patient_accuracy"].values, ref["patient_accuracy"].values)
+    np.testing.assert_allclose(mine["patient_accuracy"].values, ref["patient_accuracy"].values, rtol=1e-12)
 
 
 def test_patient_reduce_cohort_scale_properties(uqk):
