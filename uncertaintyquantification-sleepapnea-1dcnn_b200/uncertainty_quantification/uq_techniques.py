@@ -106,12 +106,13 @@ def _finish_uq(out: Dict, y_true) -> Dict:
 def mc_dropout_uq(model, x_test_data, n_pred: int = 50, *, y_true=None, return_probs: bool = False,
                   bn_mode: str = "calibrated", precision: str = "bf16", seed: Optional[int] = None, masks=None,
                   calib_windows: int = 4096, calib_passes: int = 2, recalibrate: bool = True,
-                  device_out: bool = False) -> Dict:
+                  device_out: bool = False, window_base: int = 0) -> Dict:
     """mc_dropout_predict + uq_evaluation_dist + the drivers' inline CSV metrics in ONE fused call: the
     (T,N) probability tensor is never written to HBM unless ``return_probs``.  Returns the per-window arrays of
     uq_techniques.py:103-108 plus ``predictive_entropy_bits`` / ``predicted_label``
     (analyze_mcd_patient_level.py:113-117).  ``bn_mode='calibrated'`` first estimates the batch statistics on
-    ``calib_windows`` windows with the exact layer-synchronous path (inside this call when ``recalibrate``)."""
+    ``calib_windows`` windows with the exact layer-synchronous path (inside this call when ``recalibrate``).
+    ``window_base`` = global index of the first window (multi-GPU shards: masks are keyed by the global index)."""
     eng = _engine.get_engine()
     eng.ensure_members(lambda: _model.weights_of(model)[None], key=("mcd", id(model)))
     seed = _seed() if seed is None else int(seed)
@@ -120,7 +121,7 @@ def mc_dropout_uq(model, x_test_data, n_pred: int = 50, *, y_true=None, return_p
     if bn_mode == "calibrated" and (recalibrate or not eng.calibrated):
         eng.calibrate(x_test_data, n_windows=calib_windows, n_passes=calib_passes, seed=seed)
     out = eng.mcd(x_test_data, n_passes=int(n_pred), seed=seed, bn_mode=bn_mode, precision=precision, masks=masks,
-                  return_probs=return_probs, device_out=device_out)
+                  return_probs=return_probs, device_out=device_out, window_base=int(window_base))
     return _finish_uq(out, y_true)
 
 
