@@ -132,6 +132,21 @@ int uqk_bootstrap(const float* variance_dev, const float* total_entropy_dev, con
                   const float* mutual_info_dev, const int32_t* y_dev, const int64_t* idx_dev, int n_boot,
                   int64_t n_windows, double* out_dev, void* stream);
 
+/* Allocation-free variant of uqk_bootstrap (no counterpart in the reference: it exists for callers of THIS library).
+ * For processes that must not allocate device memory while running -- e.g. a server that gave the whole GPU to its
+ * own arena or to a framework's caching allocator at start-up, or a latency-critical loop where cudaMalloc/cudaFree
+ * are banned because they can synchronise the device.  Same arguments and results as uqk_bootstrap, but the
+ * (n_boot x 8 doubles) scratch lives in a fixed 64 KiB device array inside libuqk.so (held by every GPU that loads
+ * the library until the process exits); the call makes no cudaMalloc/cudaFree/cudaMallocAsync.
+ *   - n_boot <= 1024 per call; larger values are rejected with UQK_E_SHAPE (split the iterations over several calls).
+ *   - The first call on each device resolves the array's device address (cudaGetSymbolAddress); make that first
+ *     call before starting any stream capture.
+ *   - All calls on a device share the one array: it is cleared at the start of every call, and two calls that
+ *     overlap on the GPU (different streams / threads) race on it -- serialise them. */
+int uqk_bootstrap_noalloc(const float* variance_dev, const float* total_entropy_dev, const float* expected_entropy_dev,
+                          const float* mutual_info_dev, const int32_t* y_dev, const int64_t* idx_dev, int n_boot,
+                          int64_t n_windows, double* out_dev, void* stream);
+
 /* Diagnostics: number of kernel launches the library has issued on this handle since creation. */
 int64_t uqk_launch_count(uqk_handle* h);
 /* Diagnostics for tests: selects the fused-kernel variant (0 = default). */

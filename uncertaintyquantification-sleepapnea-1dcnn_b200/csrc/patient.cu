@@ -6,6 +6,8 @@
 #include "common.cuh"
 #include "internal.h"
 
+#include <mutex>
+
 namespace uqk {
 
 constexpr int kPatThreads = 256;
@@ -192,3 +194,56 @@ int uqk_bootstrap(const float* variance_dev, const float* total_entropy_dev, con
 }
 
 }  // extern "C"
+
+// ---- uqk_bootstrap_noalloc: the same gather-means with the per-iteration sums kept in a fixed device array ----------
+// Who needs this: a caller that must not allocate device memory while it runs.  Typical cases are a serving process
+// that hands the whole GPU to its own arena / a framework's caching allocator at start-up (so cudaMalloc fails or
+// fragments), and a latency-critical loop in which cudaMalloc/cudaFree are banned because they may synchronise the
+// device.  uqk_bootstrap() takes its (n_boot x 8 doubles) scratch from the stream-ordered allocator; this variant
+// keeps it in the file-scope array below instead: 64 KiB that every GPU which loads libuqk.so holds until exit.
+namespace uqk {
+constexpr int kBootStaticMax = 1024;                        // largest n_boot the fixed scratch can hold
+static __device__ __align__(256) double g_boot_scratch[kBootStaticMax * 8];
+constexpr int kMaxDevices = 64;
+static double* g_boot_scratch_addr[kMaxDevices] = {};       // device address of the array, per device
+static std::mutex g_boot_mu;
+}  // namespace uqk
+
+extern "C" int uqk_bootstrap_noalloc(const float* variance_dev, const float* total_entropy_dev,
+                                     const float* expected_entropy_dev, const float* mutual_info_dev,
+                                     const int32_t* y_dev, const int64_t* idx_dev, int n_boot, int64_t n_windows,
+                                     double* out_dev, void* stream) {
+  if (n_boot < 1 || n_windows < 1) { set_error("need n_boot >= 1 and n_windows >= 1"); return UQK_E_BADARG; }
+  if (n_boot > kBootStaticMax) {
+    set_error("uqk_bootstrap_noalloc: n_boot=%d exceeds the fixed scratch (max %d iterations per call); "
+              "split the call or use uqk_bootstrap", n_boot, kBootStaticMax);
+    return UQK_E_SHAPE;
+  }
+  if (!variance_dev || !total_entropy_dev || !expected_entropy_dev || !mutual_info_dev || !y_dev || !idx_dev || !out_dev) {
+    set_error("NULL argument"); return UQK_E_BADARG;
+  }
+  int dev = 0;
+  UQK_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) { set_error("device index %d not supported", dev); return UQK_E_BADARG; }
+  double* sums = nullptr;
+  {
+    // In host code `g_boot_scratch` is only a handle for the symbol, not a device address: resolve it once per
+    // device, with that device current (it is: we just asked which one is), and hand the result to the kernels.
+    std::lock_guard<std::mutex> lock(g_boot_mu);
+    sums = g_boot_scratch_addr[dev];
+    if (!sums) {
+      UQK_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&sums), g_boot_scratch));
+      g_boot_scratch_addr[dev] = sums;
+    }
+  }
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  // the array keeps the previous call's sums: clear the part this call accumulates into
+  UQK_CUDA(cudaMemsetAsync(sums, 0, sizeof(double) * 8 * (size_t)n_boot, s));
+  const int gx = (int)std::max<int64_t>(1, std::min<int64_t>((n_windows + kBootThreads * 8 - 1) / (kBootThreads * 8), 148));
+  bootstrap_kernel<<<dim3(gx, n_boot), kBootThreads, 0, s>>>(variance_dev, total_entropy_dev, expected_entropy_dev,
+                                                            mutual_info_dev, y_dev, idx_dev, n_windows, sums);
+  UQK_LAUNCH_CHECK();
+  bootstrap_finalize_kernel<<<(n_boot + 127) / 128, 128, 0, s>>>(sums, n_boot, n_windows, out_dev);
+  UQK_LAUNCH_CHECK();
+  return UQK_OK;
+}
