@@ -13,8 +13,8 @@ Counter mapping (must match csrc/philox.cuh):
     c2 = (layer << 16) | row          layer in 0..5, row in 0..59
     c3 = channel chunk q              (8 consecutive channels share one Philox call)
     key = (seed & 0xffffffff, seed >> 32)
-    element e in 0..7 of the chunk uses the 16-bit field  (out[e >> 1] >> (16 * (e & 1))) & 0xffff
-    keep  <=>  field >= round(rate * 65536)      (TF: keep iff u >= rate; kept values scaled by 1/(1-rate))
+    element e in 0..7 of the chunk uses the 15-bit field  (out[e >> 1] >> (16 * (e & 1))) & 0x7fff
+    keep  <=>  field >= round(rate * 32768)      (TF: keep iff u >= rate; kept values scaled by 1/(1-rate))
 """
 from __future__ import annotations
 
@@ -55,15 +55,15 @@ def dropout_keep_mask(seed: int, window_idx, t: int, layer: int, cout: int, rate
     window_idx = np.asarray(window_idx, dtype=np.uint64)
     n = window_idx.shape[0]
     nq = cout // 8
-    thr = int(round(rate * 65536.0))
+    thr = int(round(rate * 32768.0))
     c0 = (window_idx & MASK32).reshape(n, 1, 1)
     c1 = np.uint64(t)
     c2 = (np.uint64(layer << 16) | np.arange(rows, dtype=np.uint64)).reshape(1, rows, 1)
     c3 = np.arange(nq, dtype=np.uint64).reshape(1, 1, nq)
     out = philox4x32(c0, c1, c2, c3, seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)
     words = np.stack(out, axis=-1)                                  # (n, rows, nq, 4)
-    lo = words & np.uint32(0xFFFF)
-    hi = words >> np.uint32(16)
+    lo = words & np.uint32(0x7FFF)
+    hi = (words >> np.uint32(16)) & np.uint32(0x7FFF)
     fields = np.stack([lo, hi], axis=-1).reshape(n, rows, nq * 8)  # e = 2*word + half
     return fields >= thr
 

@@ -27,6 +27,7 @@ struct Handle {
   int n_members = 0;
   float* d_blobs = nullptr;       // n_members x kBlobFloats
   uint16_t* d_packed = nullptr;   // n_members x packed image (bf16)
+  uint16_t* d_packed_pair = nullptr;  // n_members x packed image, CTA-pair layout
   float* d_tables_inf = nullptr;  // n_members x kTableFloats: inference BN, no dropout (ensemble / deterministic)
   float* d_table_mcd = nullptr;   // kTableFloats: MC-Dropout table (dropout scale folded), rebuilt per call
   float* d_frozen = nullptr;      // 2 x 6 x 256: calibrated mean, var
@@ -109,7 +110,7 @@ static int run_fused(Handle* h, const void* x, int x_dtype, int64_t n, int n_gro
                      const MetricsOut& out, cudaStream_t s) {
   FusedParams p{};
   p.x = x; p.x_dtype = x_dtype; p.n = n; p.n_groups = n_groups; p.mode_de = de ? 1 : 0; p.dropout = dropout ? 1 : 0;
-  p.seed = seed; p.window_base = window_base; p.mask_bits = mask_bits; p.packed = h->d_packed; p.tables = tables;
+  p.seed = seed; p.window_base = window_base; p.mask_bits = mask_bits; p.packed = h->d_packed; p.packed_pair = h->d_packed_pair; p.tables = tables;
   p.probs = probs; p.out = out; p.err_flag = h->d_err; p.variant = h->variant;
   p.dbg_act = h->dbg_dump ? h->d_dbg : nullptr;
   return fused_launch(p, s);
@@ -163,7 +164,7 @@ int uqk_destroy(uqk_handle* hh) {
   Handle* h = reinterpret_cast<Handle*>(hh);
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
-  void* ptrs[] = {h->d_blobs, h->d_packed, h->d_tables_inf, h->d_table_mcd, h->d_frozen, h->d_stats, h->d_affine,
+  void* ptrs[] = {h->d_blobs, h->d_packed, h->d_packed_pair, h->d_tables_inf, h->d_table_mcd, h->d_frozen, h->d_stats, h->d_affine,
                   h->d_accum, h->d_err, h->d_x32, h->d_act[0], h->d_act[1], h->d_probs_tmp, h->d_dbg};
   for (void* p : ptrs) if (p) cudaFree(p);
   cudaGetLastError();
@@ -190,11 +191,12 @@ int uqk_set_model(uqk_handle* hh, int n_members, const float* blobs_host, size_t
   Handle* h = reinterpret_cast<Handle*>(hh);
   UQK_CUDA(cudaSetDevice(h->device));
   UQK_CUDA(cudaDeviceSynchronize());
-  for (void* p : {(void*)h->d_blobs, (void*)h->d_packed, (void*)h->d_tables_inf}) if (p) cudaFree(p);
-  h->d_blobs = nullptr; h->d_packed = nullptr; h->d_tables_inf = nullptr; h->n_members = 0;
+  for (void* p : {(void*)h->d_blobs, (void*)h->d_packed, (void*)h->d_packed_pair, (void*)h->d_tables_inf}) if (p) cudaFree(p);
+  h->d_blobs = nullptr; h->d_packed = nullptr; h->d_packed_pair = nullptr; h->d_tables_inf = nullptr; h->n_members = 0;
   const size_t pb = fused_packed_bytes();
   UQK_CUDA(cudaMalloc(&h->d_blobs, sizeof(float) * kBlobStride * n_members));
   UQK_CUDA(cudaMalloc(&h->d_packed, pb * n_members));
+  UQK_CUDA(cudaMalloc(&h->d_packed_pair, pb * n_members));
   UQK_CUDA(cudaMalloc(&h->d_tables_inf, sizeof(float) * kTableFloats * n_members));
   UQK_CUDA(cudaMemcpy2D(h->d_blobs, sizeof(float) * kBlobStride, blobs_host, sizeof(float) * kBlobFloats,
                         sizeof(float) * kBlobFloats, n_members, cudaMemcpyHostToDevice));
@@ -202,6 +204,8 @@ int uqk_set_model(uqk_handle* hh, int n_members, const float* blobs_host, size_t
   for (int m = 0; m < n_members; ++m) {
     fused_pack_member(blobs_host + (size_t)m * kBlobFloats, packed.data());
     UQK_CUDA(cudaMemcpy(reinterpret_cast<uint8_t*>(h->d_packed) + (size_t)m * pb, packed.data(), pb, cudaMemcpyHostToDevice));
+    fused_pack_member_pair(blobs_host + (size_t)m * kBlobFloats, packed.data());
+    UQK_CUDA(cudaMemcpy(reinterpret_cast<uint8_t*>(h->d_packed_pair) + (size_t)m * pb, packed.data(), pb, cudaMemcpyHostToDevice));
     int rc = build_tables(h->d_blobs + (size_t)m * kBlobStride, nullptr, nullptr, 0, h->d_tables_inf + (size_t)m * kTableFloats, 0);
     if (rc) return rc;
   }
@@ -235,6 +239,7 @@ int uqk_forward_det(uqk_handle* hh, int member, const void* x_dev, int x_dtype, 
   if (precision != UQK_PREC_BF16_TC) { set_error("unknown precision %d", precision); return UQK_E_BADARG; }
   Handle view = *h;
   view.d_packed = reinterpret_cast<uint16_t*>(reinterpret_cast<uint8_t*>(h->d_packed) + (size_t)member * fused_packed_bytes());
+  view.d_packed_pair = reinterpret_cast<uint16_t*>(reinterpret_cast<uint8_t*>(h->d_packed_pair) + (size_t)member * fused_packed_bytes());
   return run_fused(&view, x_dev, x_dtype, n, 1, true, false, 0, 0, nullptr, h->d_tables_inf + (size_t)member * kTableFloats,
                    probs_dev, MetricsOut{}, s);
 }

@@ -26,9 +26,10 @@ __host__ __device__ constexpr BlockDef block_def(int l) {
        : l == 4 ? BlockDef{96, 256, 9, 4, 0.3f}
                 : BlockDef{256, 96, 9, 4, 0.5f};
 }
-// 16-bit dropout threshold: keep iff draw >= thr (TF: keep iff u >= rate)
-__host__ __device__ constexpr uint32_t drop_thr(int l) {
-  return l == 0 ? 19661u : l == 1 ? 19661u : l == 2 ? 26214u : l == 3 ? 13107u : l == 4 ? 19661u : 32768u;
+// 15-bit dropout threshold round(rate * 32768): an element is kept iff its 15-bit uniform draw >= thr
+// (TF: keep iff u >= rate).  Rates 0.3, 0.3, 0.4, 0.2, 0.3, 0.5 (cnn_baseline_train.py:61,65,70,75,80,86).
+__host__ __device__ constexpr uint32_t drop_thr15(int l) {
+  return l == 0 ? 9830u : l == 1 ? 9830u : l == 2 ? 13107u : l == 3 ? 6554u : l == 4 ? 9830u : 16384u;
 }
 
 // Offsets (in floats) into one member's Keras-order blob.
@@ -104,10 +105,10 @@ __device__ __forceinline__ Philox4 philox4x32_10(uint32_t c0, uint32_t c1, uint3
   }
   return Philox4{c0, c1, c2, c3};
 }
-// 16-bit field e (0..7) of one Philox call: word e>>1, half e&1
-__device__ __forceinline__ uint32_t philox_field16(const Philox4& r, int e) {
+// 15-bit field e (0..7) of one Philox call: word e>>1, half e&1, low 15 bits of that half
+__device__ __forceinline__ uint32_t philox_field15(const Philox4& r, int e) {
   const uint32_t w = (e >> 1) == 0 ? r.x : (e >> 1) == 1 ? r.y : (e >> 1) == 2 ? r.z : r.w;
-  return (e & 1) ? (w >> 16) : (w & 0xFFFFu);
+  return ((e & 1) ? (w >> 16) : w) & 0x7FFFu;
 }
 
 // ---- per-window reductions, exact evaluation order of the reference's NumPy code ----------------------------

@@ -26,6 +26,8 @@
 
 #include <vector>
 #include <cstring>
+#include <cstdio>
+#include <cstdlib>
 
 namespace uqk {
 
@@ -62,6 +64,9 @@ __host__ __device__ constexpr FusedLayer fused_layer(int l) {
                     fl_nconv(l), nsteps, sb, sps, (nsteps + sps - 1) / sps, fl_off(l)};
 }
 constexpr uint32_t kPackedBytes = fl_off(5) + fl_bytes(5);
+// Run-time indexable copies (the constexpr helpers above recurse, which is only free at compile time).
+__constant__ FusedLayer c_layers[kBlocks] = {fused_layer(0), fused_layer(1), fused_layer(2),
+                                             fused_layer(3), fused_layer(4), fused_layer(5)};
 
 size_t fused_packed_bytes() { return kPackedBytes; }
 
@@ -114,6 +119,23 @@ void fused_pack_member(const float* blob, uint16_t* dst) {
             d[((size_t)(s * 2 + p) * fl.cout + n) * 8 + kk] = o;
           }
   }
+}
+
+// Pair layout (cta_group::2): CTA r of a pair holds output channels [r*N/2, (r+1)*N/2) of every step, i.e. each CTA
+// streams HALF of the weights and the tensor cores of the two SMs exchange the halves.  Image = [half 0][half 1], each
+// half laid out like the single-CTA image with N/2 rows per plane.
+void fused_pack_member_pair(const float* blob, uint16_t* dst) {
+  std::vector<uint16_t> full(kPackedBytes / 2);
+  fused_pack_member(blob, full.data());
+  for (int r = 0; r < 2; ++r)
+    for (int l = 0; l < kBlocks; ++l) {
+      const FusedLayer fl = fused_layer(l);
+      const int nh = fl.cout / 2;
+      const uint16_t* src = full.data() + fl.w_off / 2;
+      uint16_t* d = dst + (size_t)r * (kPackedBytes / 4) + fl.w_off / 4;
+      for (int sp = 0; sp < fl.nsteps * 2; ++sp)
+        std::memcpy(d + (size_t)sp * nh * 8, src + ((size_t)sp * fl.cout + (size_t)r * nh) * 8, (size_t)nh * 16);
+    }
 }
 
 // ---- tables builder ---------------------------------------------------------------------------------------------
@@ -241,6 +263,41 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
+// ---- cluster / CTA-pair helpers (cta_group::2 variant) -------------------------------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t mapa_shared(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_addr) {
+  // relaxed: a release at cluster scope costs a MEMBAR.ALL.GPU per arrive; the data this signal publishes lives in
+  // shared memory and was already fenced to the async proxy (fence.proxy.async) / written by TMA before the arrive
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void umma_bf16_2cta(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                               uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// commit of the pair's MMAs: arrives on the barrier at the same CTA-relative offset in BOTH CTAs (mask 0b11)
+__device__ __forceinline__ void umma_commit_2cta(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+               "h"((uint16_t)3)
+               : "memory");
+}
+
 // ---- the kernel -------------------------------------------------------------------------------------------------
 struct FusedArgs {
   const void* x;
@@ -288,6 +345,7 @@ struct FusedCfg {
 // spinning; the watchdog turns a protocol bug into a trap (never a hung GPU).
 __device__ __forceinline__ void mbar_wait2(uint32_t bar, uint32_t parity, int* err_flag, int code) {
   uint32_t spins = 0;
+  long long t0 = 0;
   for (;;) {
     uint32_t ok;
     asm volatile(
@@ -295,10 +353,14 @@ __device__ __forceinline__ void mbar_wait2(uint32_t bar, uint32_t parity, int* e
         "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
         "selp.b32 %0, 1, 0, p;\n\t}"
         : "=r"(ok)
-        : "r"(bar), "r"(parity), "r"(1000000u)
+        : "r"(bar), "r"(parity), "r"(20000u)
         : "memory");
     if (ok) return;
-    if (++spins > (1u << 22)) mbar_timeout(err_flag, code);
+    if ((++spins & 63u) == 0u) {                      // watchdog: ~2 s of waiting is a protocol bug
+      const long long now = clock64();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 4000000000ll) mbar_timeout(err_flag, code);
+    }
   }
 }
 __device__ __forceinline__ bool elect_one() {
@@ -328,28 +390,28 @@ __device__ __forceinline__ void tmem_wait16(uint32_t (&v)[16]) {
                : "memory");
 }
 
-// Keep-bits of one 16-column chunk from two Philox4x32-10 calls (8 channels each): bit (8 q + e) = keep element e of
-// call q; 16-bit fields, keep iff field >= thr (low halves compared after a 16-bit shift, high halves in place).
-__device__ __forceinline__ uint32_t philox_keep16(uint32_t c0w, uint32_t pass, uint32_t c2, uint32_t chunk8,
-                                                  uint32_t k0, uint32_t k1, uint32_t thr_hi) {
-  uint32_t bits = 0;
-#pragma unroll
-  for (int q = 0; q < 2; ++q) {
-    const Philox4 r = philox4x32_10(c0w, pass, c2, chunk8 + q, k0, k1);
-    const uint32_t b = ((r.x << 16) >= thr_hi ? 1u : 0u) | (r.x >= thr_hi ? 2u : 0u) | ((r.y << 16) >= thr_hi ? 4u : 0u) |
-                       (r.y >= thr_hi ? 8u : 0u) | ((r.z << 16) >= thr_hi ? 16u : 0u) | (r.z >= thr_hi ? 32u : 0u) |
-                       ((r.w << 16) >= thr_hi ? 64u : 0u) | (r.w >= thr_hi ? 128u : 0u);
-    bits |= b << (8 * q);
-  }
-  return bits;
+// bits 15 / 31 of d -> 0xFFFF / 0 per 16-bit half (prmt selector bit 3 = replicate the selected byte's sign bit;
+// the __byte_perm intrinsic ignores that bit, hence PTX)
+__device__ __forceinline__ uint32_t prmt_sign_halves(uint32_t d) {
+  uint32_t r;
+  asm("prmt.b32 %0, %1, %1, 0xBB99;" : "=r"(r) : "r"(d));
+  return r;
 }
 
 // One 16-column chunk of the epilogue: ReLU -> BatchNorm affine (dropout scale folded) -> dropout -> bf16 store
 // (layers 1-5) or dot with the dense kernel (layer 6).  The conv bias is already in the accumulator (bias MMA step).
-template <bool DROP, bool LAST, bool DBG>
+//
+// Dropout: one Philox4x32-10 call per 8 channels; element e uses 15-bit field (word e>>1, half e&1, low 15 bits) and
+// is kept iff field >= thr15 = round(rate * 32768) (TF: keep iff u >= rate).  For the stored layers the compare is
+// done on both halves of a word at once -- ((w & 0x7FFF7FFF) | 0x80008000) - thr15*0x00010001 leaves the keep flag in
+// bits 15 / 31, PRMT with sign replication turns it into a 0xFFFF / 0 mask per bf16 half, and one LOP3 applies the
+// mask (and the zero-row mask) to the packed pair: 4 ALU instructions per 2 elements, no predicates.
+template <int DROP, bool LAST, bool DBG>
 __device__ __forceinline__ void epi_chunk16(const uint32_t (&v)[16], int c0, const float* __restrict__ tab_s,
                                             const float* __restrict__ tab_h, const float* __restrict__ tab_w,
-                                            uint32_t act_row, bool row_valid, uint32_t keep16, float& zacc, float* dbg) {
+                                            uint32_t act_row, bool row_valid, uint32_t row_mask, uint32_t thr2,
+                                            uint32_t c0w, uint32_t pass, uint32_t c2, uint32_t k0, uint32_t k1,
+                                            uint32_t keep16, float& zacc, float* dbg) {
 #pragma unroll
   for (int q = 0; q < 2; ++q) {
     const int cb = c0 + 8 * q;
@@ -359,21 +421,39 @@ __device__ __forceinline__ void epi_chunk16(const uint32_t (&v)[16], int c0, con
     const float hh[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
     float y[8];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      y[e] = fmaf(fmaxf(__uint_as_float(v[8 * q + e]), 0.f), ss[e], hh[e]);
-      if (DROP) y[e] = (keep16 & (1u << (8 * q + e))) ? y[e] : 0.f;
+    for (int e = 0; e < 8; ++e) y[e] = fmaf(fmaxf(__uint_as_float(v[8 * q + e]), 0.f), ss[e], hh[e]);
+    uint32_t m[4] = {row_mask, row_mask, row_mask, row_mask};     // per bf16 pair: 0xFFFF per kept half
+    if (DROP == kDropPhilox) {
+      const Philox4 r = philox4x32_10(c0w, pass, c2, (uint32_t)(cb >> 3), k0, k1);
+      const uint32_t rw[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const uint32_t d = ((rw[i] & 0x7FFF7FFFu) | 0x80008000u) - thr2;
+        m[i] &= prmt_sign_halves(d);
+      }
+    } else if (DROP == kDropBits) {
+      const uint32_t kb = keep16 >> (8 * q);
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        m[i] &= (((kb >> (2 * i)) & 1u) ? 0x0000FFFFu : 0u) | (((kb >> (2 * i + 1)) & 1u) ? 0xFFFF0000u : 0u);
+    }
+    if (DBG || LAST) {
+      // float path (debug dump and the head): apply the same masks to the fp32 values
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        y[2 * i] = (m[i] & 0x0000FFFFu) ? y[2 * i] : 0.f;
+        y[2 * i + 1] = (m[i] & 0xFFFF0000u) ? y[2 * i + 1] : 0.f;
+      }
     }
     if (DBG) {
       if (dbg) {
 #pragma unroll
-        for (int e = 0; e < 8; ++e) dbg[cb + e] = row_valid ? y[e] : 0.f;
+        for (int e = 0; e < 8; ++e) dbg[cb + e] = y[e];
       }
     }
     if (!LAST) {
-      uint32_t p0 = pack_bf16x2(y[0], y[1]), p1 = pack_bf16x2(y[2], y[3]), p2 = pack_bf16x2(y[4], y[5]),
-               p3 = pack_bf16x2(y[6], y[7]);
-      if (!row_valid) { p0 = 0u; p1 = 0u; p2 = 0u; p3 = 0u; }   // zero rows = the next layer's `same` padding
-      st_shared_v4(act_row + (uint32_t)(cb >> 3) * kPlaneBytes, p0, p1, p2, p3);
+      st_shared_v4(act_row + (uint32_t)(cb >> 3) * kPlaneBytes, pack_bf16x2(y[0], y[1]) & m[0], pack_bf16x2(y[2], y[3]) & m[1],
+                   pack_bf16x2(y[4], y[5]) & m[2], pack_bf16x2(y[6], y[7]) & m[3]);
     } else {
       const float4 w0 = *reinterpret_cast<const float4*>(tab_w + cb), w1 = *reinterpret_cast<const float4*>(tab_w + cb + 4);
       zacc = fmaf(y[0], w0.x, zacc); zacc = fmaf(y[1], w0.y, zacc); zacc = fmaf(y[2], w0.z, zacc); zacc = fmaf(y[3], w0.w, zacc);
@@ -384,6 +464,8 @@ __device__ __forceinline__ void epi_chunk16(const uint32_t (&v)[16], int c0, con
 
 __host__ __device__ constexpr int fl_step_base(int l) { return l == 0 ? 0 : fl_step_base(l - 1) + fl_nconv(l - 1) + 1; }
 constexpr int kTotalSteps = fl_step_base(kBlocks);   // 382 convolution steps + 6 bias steps
+__constant__ int c_step_base[kBlocks + 1] = {fl_step_base(0), fl_step_base(1), fl_step_base(2), fl_step_base(3),
+                                             fl_step_base(4), fl_step_base(5), fl_step_base(6)};
 
 __device__ __forceinline__ uint64_t mk64(uint32_t lo, uint32_t hi) { return ((uint64_t)hi << 32) | (uint64_t)lo; }
 
@@ -437,6 +519,7 @@ __device__ __forceinline__ void issue_layer(uint32_t s_base, uint32_t tmem_base,
 // ---- epilogue of one layer (8 warps per tile) -----------------------------------------------------------------------
 struct EpiCtx {
   uint32_t act_row, taddr, c0w, k0, k1, bar_acc, bar_act;
+  uint32_t remote_act = 0;   // pair kernels, peer CTA: cluster address of the leader's "peer activations ready" barrier
   int t, colhalf, tid_t, we, lane, quarter, slot_w, tl;
   bool row_valid;
   float* tab;
@@ -444,6 +527,18 @@ struct EpiCtx {
   float* zp;
   int* err_flag;
 };
+
+// "this tile's activations are in place": local arrive (the issuer lives in this CTA), or -- peer CTA of a pair -- one
+// remote arrive on the leader's barrier after all 256 threads have fenced their stores.
+template <int EPI_THREADS>
+__device__ __forceinline__ void epi_signal_act(const EpiCtx& c) {
+  if (c.remote_act == 0) {
+    mbar_arrive(c.bar_act);
+  } else {
+    named_bar_sync(1 + c.tl, EPI_THREADS);
+    if (c.tid_t == 0) mbar_arrive_remote(c.remote_act);
+  }
+}
 
 template <int L, int DROP, bool DBG, int EPI_THREADS>
 __device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, const float* __restrict__ tab_g, int g,
@@ -460,19 +555,11 @@ __device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, c
   }
   if (kLastLayer && c.tid_t < kDenseIn + 1) c.tab_w[c.tid_t] = __ldg(tab_g + 3 * kChTotal + c.tid_t);
 
-  // dropout keep-bits of this thread's chunks, computed in the shadow of the layer's MMAs
+  // mask-injection mode (parity tests): this thread's keep-bits, fetched while the layer's MMAs run
   uint32_t kb[(my + 1) / 2];
 #pragma unroll
   for (int j = 0; j < (my + 1) / 2; ++j) kb[j] = 0u;
-  if (DROP == kDropPhilox) {
-    constexpr uint32_t thr_hi = drop_thr(L) << 16;
-    const uint32_t c2 = ((uint32_t)L << 16) | (uint32_t)c.t;
-#pragma unroll
-    for (int j = 0; j < my; ++j) {
-      const uint32_t k = (uint32_t)(c.colhalf + 2 * j);
-      kb[j >> 1] |= philox_keep16(c.c0w, (uint32_t)g, c2, 2u * k, c.k0, c.k1, thr_hi) << (16 * (j & 1));
-    }
-  } else if (DROP == kDropBits) {
+  if (DROP == kDropBits) {
     const uint32_t* mrow = a.mask_bits + ((((size_t)g * a.n + (c.row_valid ? win : 0)) * kBlocks + L) * kL + (c.row_valid ? c.t : 0)) * 8;
 #pragma unroll
     for (int j = 0; j < my; ++j) {
@@ -481,6 +568,9 @@ __device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, c
       kb[j >> 1] |= ((w >> (16 * (k & 1))) & 0xFFFFu) << (16 * (j & 1));
     }
   }
+  constexpr uint32_t thr2 = drop_thr15(L) * 0x00010001u;
+  const uint32_t c2 = ((uint32_t)L << 16) | (uint32_t)c.t;
+  const uint32_t row_mask = c.row_valid ? 0xFFFFFFFFu : 0u;   // zero rows = the next layer's `same` padding
 
   // one warp polls the accumulator barrier; the others sleep in the named barrier (no issue slots burnt)
   if (c.we == 0) {
@@ -504,13 +594,14 @@ __device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, c
   for (int j = 0; j < my; j += 2) {
     tmem_wait16(va);
     if (j + 1 < my) tmem_ld16(c.taddr + (uint32_t)(16 * (c.colhalf + 2 * (j + 1))), vb);
-    epi_chunk16<DROP != kDropNone, kLastLayer, DBG>(va, 16 * (c.colhalf + 2 * j), tab_s, tab_h, c.tab_w, c.act_row, c.row_valid,
-                                                   (kb[j >> 1] >> (16 * (j & 1))) & 0xFFFFu, zacc, dbg);
+    epi_chunk16<DROP, kLastLayer, DBG>(va, 16 * (c.colhalf + 2 * j), tab_s, tab_h, c.tab_w, c.act_row, c.row_valid, row_mask, thr2,
+                                       c.c0w, (uint32_t)g, c2, c.k0, c.k1, (kb[j >> 1] >> (16 * (j & 1))) & 0xFFFFu, zacc, dbg);
     if (j + 1 < my) {
       tmem_wait16(vb);
       if (j + 2 < my) tmem_ld16(c.taddr + (uint32_t)(16 * (c.colhalf + 2 * (j + 2))), va);
-      epi_chunk16<DROP != kDropNone, kLastLayer, DBG>(vb, 16 * (c.colhalf + 2 * (j + 1)), tab_s, tab_h, c.tab_w, c.act_row,
-                                                     c.row_valid, (kb[(j + 1) >> 1] >> (16 * ((j + 1) & 1))) & 0xFFFFu, zacc, dbg);
+      epi_chunk16<DROP, kLastLayer, DBG>(vb, 16 * (c.colhalf + 2 * (j + 1)), tab_s, tab_h, c.tab_w, c.act_row, c.row_valid, row_mask,
+                                         thr2, c.c0w, (uint32_t)g, c2, c.k0, c.k1,
+                                         (kb[(j + 1) >> 1] >> (16 * ((j + 1) & 1))) & 0xFFFFu, zacc, dbg);
     }
   }
 
@@ -518,11 +609,10 @@ __device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, c
     // activations of the next layer are in place: publish to the tensor-core proxy, hand TMEM back
     fence_proxy_async();
     tc_fence_before();
-    mbar_arrive(c.bar_act);
+    epi_signal_act<EPI_THREADS>(c);
   } else {
     // ---- head: GlobalAveragePooling1D + Dense(96->1) + sigmoid; one window = 2 lane quarters x 2 column halves
     tc_fence_before();
-    if (!c.row_valid) zacc = 0.f;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) zacc += __shfl_xor_sync(0xffffffffu, zacc, o);
     if (c.lane == 0) c.zp[c.slot_w * 4 + (c.quarter & 1) * 2 + c.colhalf] = zacc;
@@ -560,8 +650,8 @@ fused_forward_kernel(const FusedArgs a) {
     reinterpret_cast<uint4*>(smem + Cfg::oAct)[i] = make_uint4(0, 0, 0, 0);   // halo rows stay zero for ever
   for (int i = threadIdx.x; i < kTotalSteps; i += Cfg::kThreads) {
     int l = 0, sidx = i;
-    while (sidx >= fl_nconv(l) + 1) { sidx -= fl_nconv(l) + 1; ++l; }
-    const FusedLayer fl = fused_layer(l);
+    while (sidx >= c_layers[l].nsteps) { sidx -= c_layers[l].nsteps; ++l; }
+    const FusedLayer fl = c_layers[l];
     uint32_t a_off, a_lbo;
     if (sidx == fl.nconv) { a_off = (uint32_t)kOnesPlane * kPlaneBytes + 4u * 16u; a_lbo = 16u; }          // bias step
     else if (l == 0) { a_off = (uint32_t)(2 * sidx + 1) * 16u; a_lbo = 16u; }                               // tap pair
@@ -603,7 +693,7 @@ fused_forward_kernel(const FusedArgs a) {
           const uint8_t* wmem = a.packed + (size_t)(a.mode_de ? g : 0) * kPackedBytes;
 #pragma unroll 1
           for (int l = 0; l < kBlocks; ++l) {
-            const FusedLayer fl = fused_layer(l);
+            const FusedLayer fl = c_layers[l];
             int step = 0;
             for (int st = 0; st < fl.nstages; ++st, ++it) {
               const int slot = it % NSLOTS;
@@ -721,6 +811,739 @@ fused_forward_kernel(const FusedArgs a) {
   }
 }
 
+// =====================================================================================================================
+// CTA-pair variant (cta_group::2): a cluster of two CTAs on the two SMs of a TPC owns a unit of 4 windows; each CTA
+// holds ONE tile (its 2 windows) and HALF of every weight stage; the leader CTA issues M=256 MMAs that span both SMs.
+// Two pairs are co-resident per SM pair (2 CTAs / SM), so one pair's epilogue overlaps the other pair's MMAs, while
+// the weight traffic per SM stays that of the two-tile kernel (R = 4 window-passes per stream).
+// Peer -> leader signalling ("my half of stage s has landed", "my activations are ready") is relayed by the peer's
+// otherwise idle warp 1 with remote mbarrier arrives; leader -> both signalling uses tcgen05.commit multicast.
+// =====================================================================================================================
+template <int NSLOTS>
+struct PairCfg {
+  static constexpr int kEpiThreads = 256;
+  static constexpr int kWarps = 10;
+  static constexpr int kThreads = 32 * kWarps;
+  static constexpr int kWpu = 4;                   // windows per pair unit
+  static constexpr int kTmemCols = 256;
+  static constexpr int kSlot = kSlotBytes / 2;     // each CTA keeps half of a stage
+  static constexpr int oAct = 0;
+  static constexpr int oRing = oAct + kActBytes;
+  static constexpr int kTabFloats = 2 * 512 + 128;
+  static constexpr int oTab = oRing + NSLOTS * kSlot;
+  static constexpr int oBar = oTab + kTabFloats * 4;
+  static constexpr int kNumBars = 3 * NSLOTS + 3;  // full, empty, peer_full [NSLOTS]; acc, act, peer_act
+  static constexpr int oMisc = oBar + 8 * kNumBars;
+  static constexpr int oAlo = oMisc + 16 + 32;
+  static constexpr int oProbs = oAlo + 4 * 392;    // probs[2][n_groups]
+};
+
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity, int* err_flag, int code) {
+  uint32_t spins = 0;
+  long long t0 = 0;
+  for (;;) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.relaxed.cluster.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.b32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity), "r"(20000u)
+        : "memory");
+    if (ok) return;
+    if ((++spins & 63u) == 0u) {
+      const long long now = clock64();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 4000000000ll) mbar_timeout(err_flag, code);
+    }
+  }
+}
+
+template <int L, int NSLOTS, typename Cfg>
+__device__ __forceinline__ void issue_layer_pair(uint32_t s_base, uint32_t tmem_base, const uint32_t* s_alo,
+                                                 uint32_t bar_full, uint32_t bar_empty, uint32_t bar_peer_full,
+                                                 uint32_t bar_acc, uint32_t bar_act, uint32_t bar_peer_act, uint32_t& it,
+                                                 uint32_t& n_act, int* err_flag, bool no_mma) {
+  constexpr FusedLayer fl = fused_layer(L);
+  constexpr uint32_t kHi = (128u >> 4) | (1u << 14);
+  constexpr uint32_t kBLbo = ((uint32_t)((fl.cout / 2) * 16) >> 4) << 16;
+  constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(fl.cout >> 3) << 17) | ((256u >> 4) << 24);
+  constexpr int kLast = fl.nsteps - (fl.nstages - 1) * fl.sps;
+  mbar_wait2(bar_act, n_act & 1, err_flag, 2);
+  mbar_wait_cluster(bar_peer_act, n_act & 1, err_flag, 12);
+  ++n_act;
+  tc_fence_after();
+#pragma unroll 1
+  for (int st = 0; st < fl.nstages; ++st, ++it) {
+    const int slot = it % NSLOTS;
+    const uint32_t ph = (it / NSLOTS) & 1;
+    mbar_wait2(bar_full + 8 * slot, ph, err_flag, 3);
+    mbar_wait_cluster(bar_peer_full + 8 * slot, ph, err_flag, 13);
+    tc_fence_after();
+    const int nst = (st == fl.nstages - 1) ? kLast : fl.sps;
+    const uint32_t b_lo0 = (((s_base + Cfg::oRing + slot * Cfg::kSlot) >> 4) & 0x3FFFu) | kBLbo;
+    if (elect_one()) {
+      const uint32_t* alo = s_alo + fl_step_base(L) + st * fl.sps;
+      if (!no_mma) {
+#pragma unroll
+        for (int sl = 0; sl < fl.sps; ++sl) {
+          if (sl < nst) {
+            const uint64_t bdesc = mk64(b_lo0 + (uint32_t)sl * (uint32_t)(fl.step_bytes >> 5), kHi);
+            umma_bf16_2cta(tmem_base, mk64(alo[sl], kHi), bdesc, kIdesc, (st > 0 || sl > 0) ? 1u : 0u);
+          }
+        }
+      }
+      umma_commit_2cta(bar_empty + 8 * slot);   // both CTAs' ring slots are free once these MMAs have read them
+    }
+    __syncwarp();
+  }
+  if (elect_one()) umma_commit_2cta(bar_acc);   // both CTAs' accumulators complete
+  __syncwarp();
+}
+
+template <int L, int NSLOTS>
+__device__ __forceinline__ void relay_layer(uint32_t bar_full, uint32_t bar_act, uint32_t r_peer_full, uint32_t r_peer_act,
+                                            uint32_t& it, uint32_t& n_act, int* err_flag) {
+  constexpr FusedLayer fl = fused_layer(L);
+  mbar_wait2(bar_act, n_act & 1, err_flag, 22);
+  ++n_act;
+  mbar_arrive_remote(r_peer_act);
+#pragma unroll 1
+  for (int st = 0; st < fl.nstages; ++st, ++it) {
+    const int slot = it % NSLOTS;
+    mbar_wait2(bar_full + 8 * slot, (it / NSLOTS) & 1, err_flag, 23);
+    mbar_arrive_remote(r_peer_full + 8 * slot);
+  }
+}
+
+template <int NSLOTS, int DROP, bool DBG>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(PairCfg<NSLOTS>::kThreads, 2)
+fused_pair_kernel(const FusedArgs a) {
+  using Cfg = PairCfg<NSLOTS>;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const uint32_t s_base = smem_u32(smem);
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const long long pair_id = blockIdx.x >> 1;
+  const long long n_pairs = gridDim.x >> 1;
+
+  const uint32_t bar_full = s_base + Cfg::oBar;
+  const uint32_t bar_empty = bar_full + 8 * NSLOTS;
+  const uint32_t bar_peer_full = bar_empty + 8 * NSLOTS;        // used in the leader only
+  const uint32_t bar_acc = bar_peer_full + 8 * NSLOTS;
+  const uint32_t bar_act = bar_acc + 8;
+  const uint32_t bar_peer_act = bar_act + 8;                    // used in the leader only
+  volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(smem + Cfg::oMisc);
+  float* zpart = reinterpret_cast<float*>(smem + Cfg::oMisc + 16);
+  uint32_t* s_alo = reinterpret_cast<uint32_t*>(smem + Cfg::oAlo);
+  float* probs_s = reinterpret_cast<float*>(smem + Cfg::oProbs);
+
+  for (int i = threadIdx.x; i < kActBytes / 16; i += Cfg::kThreads)
+    reinterpret_cast<uint4*>(smem + Cfg::oAct)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = threadIdx.x; i < kTotalSteps; i += Cfg::kThreads) {
+    int l = 0, sidx = i;
+    while (sidx >= c_layers[l].nsteps) { sidx -= c_layers[l].nsteps; ++l; }
+    const FusedLayer fl = c_layers[l];
+    uint32_t a_off, a_lbo;
+    if (sidx == fl.nconv) { a_off = (uint32_t)kOnesPlane * kPlaneBytes + 4u * 16u; a_lbo = 16u; }
+    else if (l == 0) { a_off = (uint32_t)(2 * sidx + 1) * 16u; a_lbo = 16u; }
+    else {
+      const int slabs = fl.cinp / 16, tap = sidx / slabs, slab = sidx % slabs;
+      a_off = (uint32_t)(2 * slab) * kPlaneBytes + (uint32_t)(tap - fl.halo + 4) * 16u;
+      a_lbo = kPlaneBytes;
+    }
+    s_alo[i] = (((s_base + Cfg::oAct + a_off) >> 4) & 0x3FFFu) | ((a_lbo >> 4) << 16);
+  }
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < NSLOTS; ++i) {
+      mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, 1); mbar_init(bar_peer_full + 8 * i, 1);
+    }
+    mbar_init(bar_acc, 1); mbar_init(bar_act, Cfg::kEpiThreads); mbar_init(bar_peer_act, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32(const_cast<uint32_t*>(tmem_ptr))),
+                 "r"((uint32_t)Cfg::kTmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  fence_proxy_async();
+  tc_fence_before();
+  cluster_sync_all();          // barriers of BOTH CTAs are initialised before anyone signals across the pair
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+  const bool dbg_no_copy = (a.variant & 2) != 0;
+  const bool dbg_no_mma = (a.variant & 8) != 0;
+
+  if (warp == 0) {
+    // ---- weight producer: this CTA's half of every stage
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
+        for (int g = 0; g < a.n_groups; ++g) {
+          const uint8_t* wmem = a.packed + (size_t)(a.mode_de ? g : 0) * kPackedBytes + (size_t)rank * (kPackedBytes / 2);
+#pragma unroll 1
+          for (int l = 0; l < kBlocks; ++l) {
+            const FusedLayer fl = c_layers[l];
+            const uint32_t sb = (uint32_t)fl.step_bytes / 2;
+            int step = 0;
+            for (int st = 0; st < fl.nstages; ++st, ++it) {
+              const int slot = it % NSLOTS;
+              const uint32_t ph = (it / NSLOTS) & 1;
+              mbar_wait2(bar_empty + 8 * slot, ph ^ 1, a.err_flag, 1);
+              const int nst = min(fl.sps, fl.nsteps - step);
+              const uint32_t bytes = (uint32_t)nst * sb;
+              if (dbg_no_copy) { mbar_arrive(bar_full + 8 * slot); }
+              else {
+                mbar_arrive_expect_tx(bar_full + 8 * slot, bytes);
+                bulk_g2s(s_base + Cfg::oRing + slot * Cfg::kSlot, wmem + fl.w_off / 2 + (size_t)step * sb, bytes,
+                         bar_full + 8 * slot);
+              }
+              step += nst;
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    uint32_t it = 0, n_act = 0;
+    if (rank == 0) {
+      // ---- leader: MMA issuer for the pair
+      for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
+        for (int g = 0; g < a.n_groups; ++g) {
+          issue_layer_pair<0, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
+          issue_layer_pair<1, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
+          issue_layer_pair<2, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
+          issue_layer_pair<3, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
+          issue_layer_pair<4, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
+          issue_layer_pair<5, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
+        }
+      }
+    } else if (lane == 0) {
+      // ---- peer: relay "stage landed" / "activations ready" to the leader's barriers
+      const uint32_t r_peer_full = mapa_shared(bar_peer_full, 0);
+      const uint32_t r_peer_act = mapa_shared(bar_peer_act, 0);
+      for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
+        for (int g = 0; g < a.n_groups; ++g) {
+          relay_layer<0, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
+          relay_layer<1, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
+          relay_layer<2, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
+          relay_layer<3, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
+          relay_layer<4, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
+          relay_layer<5, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
+        }
+      }
+    }
+  } else {
+    // ---- epilogue: 8 warps, this CTA's tile
+    EpiCtx c;
+    c.tl = 0;
+    c.we = warp - 2;
+    c.lane = lane;
+    c.quarter = warp & 3;
+    c.colhalf = c.we >> 2;
+    const int row = c.quarter * 32 + lane;
+    c.slot_w = row >> 6;
+    c.t = row & 63;
+    c.tid_t = c.we * 32 + lane;
+    c.tab = reinterpret_cast<float*>(smem + Cfg::oTab);
+    c.tab_w = c.tab + 1024;
+    c.act_row = s_base + Cfg::oAct + (uint32_t)(row + 4) * 16u;
+    c.taddr = tmem_base + ((uint32_t)(c.quarter * 32) << 16);
+    c.zp = zpart;
+    c.bar_acc = bar_acc;
+    c.bar_act = bar_act;
+    c.k0 = a.k0; c.k1 = a.k1;
+    c.err_flag = a.err_flag;
+    uint32_t n_acc = 0;
+    for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
+      const long long win = unit * Cfg::kWpu + 2 * (long long)rank + c.slot_w;
+      c.row_valid = (c.t < kL) && (win < a.n);
+      uint32_t xin0 = 0, xin1 = 0;
+      if (c.colhalf == 0) {
+        if (c.row_valid) {
+          float f0, f1, f2, f3;
+          if (a.x_f64) {
+            const double2* p = reinterpret_cast<const double2*>(static_cast<const double*>(a.x) + ((size_t)win * kL + c.t) * kF);
+            const double2 u = __ldg(p), v = __ldg(p + 1);
+            f0 = (float)u.x; f1 = (float)u.y; f2 = (float)v.x; f3 = (float)v.y;
+          } else {
+            const float4 u = __ldg(reinterpret_cast<const float4*>(static_cast<const float*>(a.x) + ((size_t)win * kL + c.t) * kF));
+            f0 = u.x; f1 = u.y; f2 = u.z; f3 = u.w;
+          }
+          xin0 = pack_bf16x2(f0, f1);
+          xin1 = pack_bf16x2(f2, f3);
+        }
+      } else {
+        st_shared_v4(c.act_row + (uint32_t)kOnesPlane * kPlaneBytes, c.row_valid ? 0x3F803F80u : 0u, 0u, 0u, 0u);
+      }
+      c.c0w = (uint32_t)(a.window_base + win);
+      float* dbg_base = nullptr;
+      if (DBG) {
+        if (a.dbg_act && blockIdx.x == 0 && unit == pair_id) dbg_base = a.dbg_act + (size_t)row * 256;
+      }
+      for (int g = 0; g < a.n_groups; ++g) {
+        if (c.colhalf == 0) st_shared_v4(c.act_row, xin0, xin1, 0u, 0u);
+        fence_proxy_async();
+        mbar_arrive(c.bar_act);
+        const float* tab_g = a.tables + (size_t)(a.mode_de ? g : 0) * kTableFloats;
+        float* dbg_g = (DBG && g == 0) ? dbg_base : nullptr;
+        // probs_s rows are indexed by (2*tl + slot_w) = slot_w here
+        epi_layer<0, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
+        epi_layer<1, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
+        epi_layer<2, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
+        epi_layer<3, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
+        epi_layer<4, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
+        epi_layer<5, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
+      }
+      if (c.colhalf == 0 && c.t == 0 && (c.quarter & 1) == 0 && win < a.n) {
+        const float* pw = probs_s + c.slot_w * a.n_groups;
+        window_metrics([&](int tt) { return pw[tt]; }, a.n_groups, win, a.out);
+      }
+    }
+  }
+
+  // ---- teardown: nobody may leave while the pair can still touch its shared memory / TMEM
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)Cfg::kTmemCols)
+                 : "memory");
+  }
+}
+
+template <int NSLOTS, int DROP, bool DBG>
+static int launch_pair_variant(const FusedParams& p, cudaStream_t s) {
+  using Cfg = PairCfg<NSLOTS>;
+  FusedArgs a{};
+  a.x = p.x; a.x_f64 = p.x_dtype == UQK_F64; a.n = p.n; a.n_groups = p.n_groups; a.mode_de = p.mode_de;
+  a.k0 = (uint32_t)(p.seed & 0xFFFFFFFFull); a.k1 = (uint32_t)(p.seed >> 32);
+  a.window_base = p.window_base; a.mask_bits = p.mask_bits; a.packed = reinterpret_cast<const uint8_t*>(p.packed_pair);
+  a.tables = p.tables; a.probs = p.probs; a.out = p.out; a.dbg_act = p.dbg_act; a.err_flag = p.err_flag;
+  a.variant = p.variant;
+  a.n_units = (p.n + Cfg::kWpu - 1) / Cfg::kWpu;
+  const size_t smem = (size_t)Cfg::oProbs + (size_t)2 * p.n_groups * sizeof(float);
+  if (smem > 113 * 1024) return UQK_E_SHAPE;   // must leave room for two CTAs per SM
+  int dev = 0, sms = 148;
+  UQK_CUDA(cudaGetDevice(&dev));
+  UQK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  auto kern = fused_pair_kernel<NSLOTS, DROP, DBG>;
+  UQK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  UQK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+  int per_sm = 1;
+  UQK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, Cfg::kThreads, smem));
+  if (per_sm < 1) { set_error("pair kernel does not fit on an SM (smem %zu)", smem); return UQK_E_CUDA; }
+  // The occupancy API reports 1 block/SM for tcgen05 kernels on this driver although the hardware limits
+  // (registers, shared memory, 2 x 256 TMEM columns) admit two -- ncu's launch__occupancy_limit_* agree with two.
+  per_sm = (2 * (smem + 1024) <= 233472) ? 2 : 1;
+  const long long pairs = std::min<long long>(a.n_units, (long long)(sms / 2) * per_sm);
+  if (getenv("UQK_DEBUG")) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)(2 * pairs)); cfg.blockDim = dim3(Cfg::kThreads); cfg.dynamicSmemBytes = smem;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    int ncl = -1;
+    cudaError_t e = cudaOccupancyMaxActiveClusters(&ncl, kern, &cfg);
+    fprintf(stderr, "[uqk] pair kernel: smem=%zu per_sm=%d pairs=%lld maxActiveClusters=%d (%s)\n", smem, per_sm, pairs, ncl, cudaGetErrorString(e));
+    cudaFuncAttributes fa{};
+    cudaFuncGetAttributes(&fa, kern);
+    fprintf(stderr, "[uqk]   regs=%d static_smem=%zu local=%zu maxDyn=%d maxThreads=%d\n", fa.numRegs, fa.sharedSizeBytes, fa.localSizeBytes, fa.maxDynamicSharedSizeBytes, fa.maxThreadsPerBlock);
+    for (size_t sm : {(size_t)40000, (size_t)80000, (size_t)100000, (size_t)105000, (size_t)110000, (size_t)112000}) {
+      int b = -1;
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, kern, Cfg::kThreads, sm);
+      fprintf(stderr, "[uqk]   smem %zu -> blocks/SM %d\n", sm, b);
+    }
+    for (int th : {128, 192, 256, 320}) {
+      int b = -1;
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, kern, th, 40000);
+      fprintf(stderr, "[uqk]   threads %d smem 40000 -> blocks/SM %d\n", th, b);
+    }
+  }
+  kern<<<(unsigned)(2 * pairs), Cfg::kThreads, smem, s>>>(a);
+  UQK_LAUNCH_CHECK();
+  return UQK_OK;
+}
+
+template <int NSLOTS>
+static int launch_pair(const FusedParams& p, cudaStream_t s) {
+  const int drop = !p.dropout ? kDropNone : (p.mask_bits ? kDropBits : kDropPhilox);
+  if (p.dbg_act) {
+    switch (drop) {
+      case kDropNone: return launch_pair_variant<NSLOTS, kDropNone, true>(p, s);
+      case kDropPhilox: return launch_pair_variant<NSLOTS, kDropPhilox, true>(p, s);
+      default: return launch_pair_variant<NSLOTS, kDropBits, true>(p, s);
+    }
+  }
+  switch (drop) {
+    case kDropNone: return launch_pair_variant<NSLOTS, kDropNone, false>(p, s);
+    case kDropPhilox: return launch_pair_variant<NSLOTS, kDropPhilox, false>(p, s);
+    default: return launch_pair_variant<NSLOTS, kDropBits, false>(p, s);
+  }
+}
+
+// =====================================================================================================================
+// CTA-pair variant with TWO tiles per CTA and a dual-consumer issuer ("P2"): 1 CTA per SM, the pair owns a unit of 8
+// windows = tile-pairs A and B (each an M=256 accumulator spanning both SMs).  Both tile-pairs consume the SAME
+// weight stream (R = 8 window-passes per stream) through a ring of half-stages that is twice as deep in stage units
+// as the single-CTA ring.  The issuer gives tile-pair A priority: A runs ahead until the ring window stops it, B
+// trails by the window, so when A's accumulator completes, B still has several stages of MMAs to issue -- they cover
+// A's epilogue, and A's first stages of the next layer cover B's epilogue.  A ring slot is free when BOTH tile-pairs
+// have consumed it (mbarrier count 2, tcgen05.commit multicast to both CTAs).
+// =====================================================================================================================
+template <int NSLOTS>
+struct Pair2Cfg {
+  static constexpr int kEpiThreads = 256;
+  static constexpr int kWarps = 2 + 16;
+  static constexpr int kThreads = 32 * kWarps;
+  static constexpr int kWpu = 8;                   // windows per pair unit
+  static constexpr int kTmemCols = 512;
+  static constexpr int kSlot = kSlotBytes / 2;
+  static constexpr int oAct = 0;
+  static constexpr int oRing = oAct + 2 * kActBytes;
+  static constexpr int kTabFloats = 2 * 512 + 128;
+  static constexpr int oTab = oRing + NSLOTS * kSlot;
+  static constexpr int oBar = oTab + 2 * kTabFloats * 4;
+  static constexpr int kNumBars = 3 * NSLOTS + 6;  // full, empty, peer_full [NSLOTS]; acc[2], act[2], peer_act[2]
+  static constexpr int oMisc = oBar + 8 * kNumBars;
+  static constexpr int oAlo = oMisc + 16 + 64;
+  static constexpr int oProbs = oAlo + 4 * 392;    // probs[4][n_groups]
+};
+
+__device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.b32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ bool mbar_test_cluster(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.relaxed.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.b32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+
+// position of one tile-pair in the (unit, group, layer, stage) schedule
+struct TileCursor {
+  long long unit;
+  int g, l, st;
+  uint32_t q;        // global stage counter -> ring slot / phase
+  uint32_t n_act;    // activation-barrier phase counter
+  bool act_ok;       // this layer's activations already seen ready
+  bool done;
+};
+
+template <int NSLOTS, int DROP, bool DBG>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Pair2Cfg<NSLOTS>::kThreads, 1)
+fused_pair2_kernel(const FusedArgs a) {
+  using Cfg = Pair2Cfg<NSLOTS>;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const uint32_t s_base = smem_u32(smem);
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const long long pair_id = blockIdx.x >> 1;
+  const long long n_pairs = gridDim.x >> 1;
+
+  const uint32_t bar_full = s_base + Cfg::oBar;
+  const uint32_t bar_empty = bar_full + 8 * NSLOTS;
+  const uint32_t bar_peer_full = bar_empty + 8 * NSLOTS;        // leader only
+  const uint32_t bar_acc = bar_peer_full + 8 * NSLOTS;          // [2]
+  const uint32_t bar_act = bar_acc + 16;                        // [2] leader only: its own epilogue threads
+  const uint32_t bar_peer_act = bar_act + 16;                   // [2] leader only: one remote arrive per layer
+  volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(smem + Cfg::oMisc);
+  float* zpart = reinterpret_cast<float*>(smem + Cfg::oMisc + 16);
+  uint32_t* s_alo = reinterpret_cast<uint32_t*>(smem + Cfg::oAlo);
+  float* probs_s = reinterpret_cast<float*>(smem + Cfg::oProbs);
+
+  for (int i = threadIdx.x; i < (2 * kActBytes) / 16; i += Cfg::kThreads)
+    reinterpret_cast<uint4*>(smem + Cfg::oAct)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = threadIdx.x; i < kTotalSteps; i += Cfg::kThreads) {
+    int l = 0, sidx = i;
+    while (sidx >= c_layers[l].nsteps) { sidx -= c_layers[l].nsteps; ++l; }
+    const FusedLayer fl = c_layers[l];
+    uint32_t a_off, a_lbo;
+    if (sidx == fl.nconv) { a_off = (uint32_t)kOnesPlane * kPlaneBytes + 4u * 16u; a_lbo = 16u; }
+    else if (l == 0) { a_off = (uint32_t)(2 * sidx + 1) * 16u; a_lbo = 16u; }
+    else {
+      const int slabs = fl.cinp / 16, tap = sidx / slabs, slab = sidx % slabs;
+      a_off = (uint32_t)(2 * slab) * kPlaneBytes + (uint32_t)(tap - fl.halo + 4) * 16u;
+      a_lbo = kPlaneBytes;
+    }
+    s_alo[i] = (((s_base + Cfg::oAct + a_off) >> 4) & 0x3FFFu) | ((a_lbo >> 4) << 16);
+  }
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < NSLOTS; ++i) {
+      mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, 2); mbar_init(bar_peer_full + 8 * i, 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(bar_acc + 8 * i, 1); mbar_init(bar_act + 8 * i, Cfg::kEpiThreads); mbar_init(bar_peer_act + 8 * i, 1);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32(const_cast<uint32_t*>(tmem_ptr))),
+                 "r"((uint32_t)Cfg::kTmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  fence_proxy_async();
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+  const bool dbg_no_copy = (a.variant & 2) != 0;
+  const bool dbg_no_mma = (a.variant & 8) != 0;
+
+  if (warp == 0) {
+    // ---- weight producer: this CTA's half of every stage
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
+        for (int g = 0; g < a.n_groups; ++g) {
+          const uint8_t* wmem = a.packed + (size_t)(a.mode_de ? g : 0) * kPackedBytes + (size_t)rank * (kPackedBytes / 2);
+#pragma unroll 1
+          for (int l = 0; l < kBlocks; ++l) {
+            const FusedLayer fl = c_layers[l];
+            const uint32_t sb = (uint32_t)fl.step_bytes / 2;
+            int step = 0;
+            for (int st = 0; st < fl.nstages; ++st, ++it) {
+              const int slot = it % NSLOTS;
+              const uint32_t ph = (it / NSLOTS) & 1;
+              mbar_wait2(bar_empty + 8 * slot, ph ^ 1, a.err_flag, 1);
+              const int nst = min(fl.sps, fl.nsteps - step);
+              const uint32_t bytes = (uint32_t)nst * sb;
+              if (dbg_no_copy) { mbar_arrive(bar_full + 8 * slot); }
+              else {
+                mbar_arrive_expect_tx(bar_full + 8 * slot, bytes);
+                bulk_g2s(s_base + Cfg::oRing + slot * Cfg::kSlot, wmem + fl.w_off / 2 + (size_t)step * sb, bytes,
+                         bar_full + 8 * slot);
+              }
+              step += nst;
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (rank == 0) {
+      // ---- leader: dual-consumer MMA issuer (tile-pair 0 has priority, tile-pair 1 fills the gaps)
+      constexpr uint32_t kHi = (128u >> 4) | (1u << 14);
+      TileCursor cur[2];
+#pragma unroll
+      for (int tl = 0; tl < 2; ++tl) {
+        cur[tl].unit = pair_id; cur[tl].g = 0; cur[tl].l = 0; cur[tl].st = 0; cur[tl].q = 0; cur[tl].n_act = 0;
+        cur[tl].act_ok = false; cur[tl].done = pair_id >= a.n_units;
+      }
+      uint32_t idle = 0, landed_q = 0;   // stages [0, landed_q) are known to have landed in BOTH CTAs
+      long long t0 = 0;
+      while (!(cur[0].done && cur[1].done)) {
+        bool progressed = false;
+#pragma unroll
+        for (int tl = 0; tl < 2; ++tl) {
+          TileCursor& c = cur[tl];
+          if (c.done || progressed) continue;
+          if (!c.act_ok) {
+            if (!mbar_test(bar_act + 8 * tl, c.n_act & 1) || !mbar_test_cluster(bar_peer_act + 8 * tl, c.n_act & 1)) continue;
+            c.act_ok = true;
+          }
+          const int slot = c.q % NSLOTS;
+          if (c.q >= landed_q) {             // only the leading tile-pair ever polls the weight barriers
+            const uint32_t ph = (c.q / NSLOTS) & 1;
+            if (!mbar_test(bar_full + 8 * slot, ph) || !mbar_test_cluster(bar_peer_full + 8 * slot, ph)) continue;
+            landed_q = c.q + 1;
+          }
+          // ---- issue one stage of tile-pair tl
+          const FusedLayer fl = c_layers[c.l];
+          tc_fence_after();
+          const int step0 = c.st * fl.sps;
+          const int nst = min(fl.sps, fl.nsteps - step0);
+          const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(fl.cout >> 3) << 17) | ((256u >> 4) << 24);
+          const uint32_t b_lo0 = (((s_base + Cfg::oRing + slot * Cfg::kSlot) >> 4) & 0x3FFFu) | ((uint32_t)(fl.cout / 2) << 16);
+          const uint32_t b_step = (uint32_t)fl.step_bytes >> 5;
+          const bool last = (c.st == fl.nstages - 1);
+          if (elect_one()) {
+            const uint32_t* alo = s_alo + c_step_base[c.l] + step0;
+            const uint32_t a_tile = (uint32_t)tl * (uint32_t)(kActBytes >> 4);
+            if (!dbg_no_mma) {
+              for (int sl = 0; sl < nst; ++sl)
+                umma_bf16_2cta(tmem_base + (uint32_t)tl * 256u, mk64(alo[sl] + a_tile, kHi), mk64(b_lo0 + (uint32_t)sl * b_step, kHi),
+                               idesc, (step0 + sl) > 0 ? 1u : 0u);
+            }
+            umma_commit_2cta(bar_empty + 8 * slot);            // one of the two arrivals that free the slot
+            if (last) umma_commit_2cta(bar_acc + 8 * tl);       // accumulator of this tile-pair complete (both CTAs)
+          }
+          __syncwarp();
+          // ---- advance the cursor
+          ++c.q;
+          if (!last) { ++c.st; }
+          else {
+            c.st = 0; c.act_ok = false; ++c.n_act;
+            if (++c.l == kBlocks) {
+              c.l = 0;
+              if (++c.g == a.n_groups) { c.g = 0; c.unit += n_pairs; c.done = c.unit >= a.n_units; }
+            }
+          }
+          progressed = true;
+        }
+        if (progressed) { idle = 0; t0 = 0; }
+        else if ((++idle & 1023u) == 0u) {
+          const long long now = clock64();
+          if (t0 == 0) t0 = now;
+          else if (now - t0 > 4000000000ll) mbar_timeout(a.err_flag, 31);
+        }
+      }
+    } else if (lane == 0) {
+      // ---- peer: relay "my half of stage q has landed" to the leader, in stream order
+      const uint32_t r_peer_full = mapa_shared(bar_peer_full, 0);
+      uint32_t it = 0;
+      for (long long unit = pair_id; unit < a.n_units; unit += n_pairs)
+        for (int g = 0; g < a.n_groups; ++g)
+#pragma unroll 1
+          for (int l = 0; l < kBlocks; ++l) {
+            const int ns = c_layers[l].nstages;
+            for (int st = 0; st < ns; ++st, ++it) {
+              const int slot = it % NSLOTS;
+              mbar_wait2(bar_full + 8 * slot, (it / NSLOTS) & 1, a.err_flag, 23);
+              mbar_arrive_remote(r_peer_full + 8 * slot);
+            }
+          }
+    }
+  } else {
+    // ---- epilogue: 8 warps per tile
+    const int ew = warp - 2;
+    EpiCtx c;
+    c.tl = ew >> 3;
+    c.we = ew & 7;
+    c.lane = lane;
+    c.quarter = warp & 3;
+    c.colhalf = c.we >> 2;
+    const int row = c.quarter * 32 + lane;
+    c.slot_w = row >> 6;
+    c.t = row & 63;
+    c.tid_t = c.we * 32 + lane;
+    c.tab = reinterpret_cast<float*>(smem + Cfg::oTab) + c.tl * Cfg::kTabFloats;
+    c.tab_w = c.tab + 1024;
+    c.act_row = s_base + Cfg::oAct + c.tl * kActBytes + (uint32_t)(row + 4) * 16u;
+    c.taddr = tmem_base + ((uint32_t)(c.quarter * 32) << 16) + (uint32_t)(c.tl * 256);
+    c.zp = zpart + c.tl * 8;
+    c.bar_acc = bar_acc + 8 * c.tl;
+    c.bar_act = bar_act + 8 * c.tl;
+    c.remote_act = rank == 0 ? 0u : mapa_shared(bar_peer_act + 8 * c.tl, 0);
+    c.k0 = a.k0; c.k1 = a.k1;
+    c.err_flag = a.err_flag;
+    uint32_t n_acc = 0;
+    for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
+      // unit = 8 windows: tile-pair tl covers windows 4*tl .. 4*tl+3; this CTA (rank) takes 2 of them
+      const long long win = unit * Cfg::kWpu + 4 * c.tl + 2 * (long long)rank + c.slot_w;
+      c.row_valid = (c.t < kL) && (win < a.n);
+      uint32_t xin0 = 0, xin1 = 0;
+      if (c.colhalf == 0) {
+        if (c.row_valid) {
+          float f0, f1, f2, f3;
+          if (a.x_f64) {
+            const double2* p = reinterpret_cast<const double2*>(static_cast<const double*>(a.x) + ((size_t)win * kL + c.t) * kF);
+            const double2 u = __ldg(p), v = __ldg(p + 1);
+            f0 = (float)u.x; f1 = (float)u.y; f2 = (float)v.x; f3 = (float)v.y;
+          } else {
+            const float4 u = __ldg(reinterpret_cast<const float4*>(static_cast<const float*>(a.x) + ((size_t)win * kL + c.t) * kF));
+            f0 = u.x; f1 = u.y; f2 = u.z; f3 = u.w;
+          }
+          xin0 = pack_bf16x2(f0, f1);
+          xin1 = pack_bf16x2(f2, f3);
+        }
+      } else {
+        st_shared_v4(c.act_row + (uint32_t)kOnesPlane * kPlaneBytes, c.row_valid ? 0x3F803F80u : 0u, 0u, 0u, 0u);
+      }
+      c.c0w = (uint32_t)(a.window_base + win);
+      float* dbg_base = nullptr;
+      if (DBG) {
+        if (a.dbg_act && blockIdx.x == 0 && unit == pair_id && c.tl == 0) dbg_base = a.dbg_act + (size_t)row * 256;
+      }
+      for (int g = 0; g < a.n_groups; ++g) {
+        if (c.colhalf == 0) st_shared_v4(c.act_row, xin0, xin1, 0u, 0u);
+        fence_proxy_async();
+        epi_signal_act<Cfg::kEpiThreads>(c);
+        const float* tab_g = a.tables + (size_t)(a.mode_de ? g : 0) * kTableFloats;
+        float* dbg_g = (DBG && g == 0) ? dbg_base : nullptr;
+        epi_layer<0, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
+        epi_layer<1, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
+        epi_layer<2, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
+        epi_layer<3, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
+        epi_layer<4, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
+        epi_layer<5, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
+      }
+      if (c.colhalf == 0 && c.t == 0 && (c.quarter & 1) == 0 && win < a.n) {
+        const float* pw = probs_s + (2 * c.tl + c.slot_w) * a.n_groups;
+        window_metrics([&](int tt) { return pw[tt]; }, a.n_groups, win, a.out);
+      }
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)Cfg::kTmemCols)
+                 : "memory");
+  }
+}
+
+template <int NSLOTS, int DROP, bool DBG>
+static int launch_pair2_variant(const FusedParams& p, cudaStream_t s) {
+  using Cfg = Pair2Cfg<NSLOTS>;
+  FusedArgs a{};
+  a.x = p.x; a.x_f64 = p.x_dtype == UQK_F64; a.n = p.n; a.n_groups = p.n_groups; a.mode_de = p.mode_de;
+  a.k0 = (uint32_t)(p.seed & 0xFFFFFFFFull); a.k1 = (uint32_t)(p.seed >> 32);
+  a.window_base = p.window_base; a.mask_bits = p.mask_bits; a.packed = reinterpret_cast<const uint8_t*>(p.packed_pair);
+  a.tables = p.tables; a.probs = p.probs; a.out = p.out; a.dbg_act = p.dbg_act; a.err_flag = p.err_flag;
+  a.variant = p.variant;
+  a.n_units = (p.n + Cfg::kWpu - 1) / Cfg::kWpu;
+  const size_t smem = (size_t)Cfg::oProbs + (size_t)4 * p.n_groups * sizeof(float);
+  if (smem > 227 * 1024) return UQK_E_SHAPE;
+  int dev = 0, sms = 148;
+  UQK_CUDA(cudaGetDevice(&dev));
+  UQK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  auto kern = fused_pair2_kernel<NSLOTS, DROP, DBG>;
+  UQK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  UQK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+  const long long pairs = std::min<long long>(a.n_units, (long long)(sms / 2));
+  kern<<<(unsigned)(2 * pairs), Cfg::kThreads, smem, s>>>(a);
+  UQK_LAUNCH_CHECK();
+  return UQK_OK;
+}
+
+template <int NSLOTS>
+static int launch_pair2(const FusedParams& p, cudaStream_t s) {
+  const int drop = !p.dropout ? kDropNone : (p.mask_bits ? kDropBits : kDropPhilox);
+  if (p.dbg_act) {
+    switch (drop) {
+      case kDropNone: return launch_pair2_variant<NSLOTS, kDropNone, true>(p, s);
+      case kDropPhilox: return launch_pair2_variant<NSLOTS, kDropPhilox, true>(p, s);
+      default: return launch_pair2_variant<NSLOTS, kDropBits, true>(p, s);
+    }
+  }
+  switch (drop) {
+    case kDropNone: return launch_pair2_variant<NSLOTS, kDropNone, false>(p, s);
+    case kDropPhilox: return launch_pair2_variant<NSLOTS, kDropPhilox, false>(p, s);
+    default: return launch_pair2_variant<NSLOTS, kDropBits, false>(p, s);
+  }
+}
+
 // ---- host launcher ----------------------------------------------------------------------------------------------
 template <int TILES, int NSLOTS, int DROP, bool DBG>
 static int launch_variant(const FusedParams& p, cudaStream_t s) {
@@ -739,9 +1562,20 @@ static int launch_variant(const FusedParams& p, cudaStream_t s) {
   UQK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   auto kern = fused_forward_kernel<TILES, NSLOTS, DROP, DBG>;
   UQK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  UQK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
   int per_sm = 1;
   UQK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, Cfg::kThreads, smem));
   if (per_sm < 1) { set_error("fused kernel does not fit on an SM (smem %zu)", smem); return UQK_E_CUDA; }
+  if (getenv("UQK_DEBUG")) {
+    cudaFuncAttributes fa{};
+    cudaFuncGetAttributes(&fa, kern);
+    fprintf(stderr, "[uqk] fused<%d,%d>: smem=%zu threads=%d per_sm=%d regs=%d\n", TILES, NSLOTS, smem, Cfg::kThreads, per_sm, fa.numRegs);
+    for (size_t sm : {(size_t)40000, (size_t)100000, (size_t)112000}) {
+      int b = -1;
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, kern, Cfg::kThreads, sm);
+      fprintf(stderr, "[uqk]   smem %zu -> blocks/SM %d\n", sm, b);
+    }
+  }
   if (per_sm * Cfg::kTmemCols > 512) per_sm = 512 / Cfg::kTmemCols;   // TMEM: 512 columns per SM
   const long long grid = std::min<long long>(a.n_units, (long long)sms * per_sm);
   kern<<<(unsigned)grid, Cfg::kThreads, smem, s>>>(a);
@@ -768,6 +1602,14 @@ static int launch_drop(const FusedParams& p, cudaStream_t s) {
 
 int fused_launch(const FusedParams& p, cudaStream_t s) {
   if (p.n == 0) return UQK_OK;
+  if ((p.variant >> 4) == 2) {
+    const int rc = launch_pair<4>(p, s);          // CTA pairs (cta_group::2), two pairs co-resident per SM pair
+    if (rc != UQK_E_SHAPE) return rc;
+  }
+  if ((p.variant >> 4) == 3) {
+    const int rc = launch_pair2<9>(p, s);         // CTA pairs, two tiles per CTA, dual-consumer issuer
+    if (rc != UQK_E_SHAPE) return rc;
+  }
   if ((p.variant >> 4) != 1) {
     const int rc = launch_drop<2, 4>(p, s);       // two tiles per CTA share one weight stream
     if (rc != UQK_E_SHAPE) return rc;             // too many passes for its shared memory -> smaller configuration

@@ -35,6 +35,7 @@ constexpr int kTableFloats = 3 * kChTotal + kDenseIn + 4;
 // Packed bf16 weights of one member for the fused kernel (UMMA K-major, no swizzle), see fused.cu.
 size_t fused_packed_bytes();                      // bytes per member
 void fused_pack_member(const float* blob_host, uint16_t* packed_host);   // host-side packing
+void fused_pack_member_pair(const float* blob_host, uint16_t* packed_host);   // [half 0][half 1] for CTA pairs
 
 struct FusedParams {
   const void* x;              // (n,60,4) f32 or f64, device
@@ -47,6 +48,7 @@ struct FusedParams {
   int64_t window_base;
   const uint32_t* mask_bits;  // (T,N,6,60,8) or null
   const uint16_t* packed;     // n_members x packed bytes
+  const uint16_t* packed_pair;  // same, CTA-pair layout
   const float* tables;        // n_sets x kTableFloats
   float* probs;               // (n_groups, n) or null
   MetricsOut out;

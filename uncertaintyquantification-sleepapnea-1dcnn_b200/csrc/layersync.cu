@@ -132,7 +132,7 @@ __global__ void bn_dropout_kernel(float* __restrict__ act, const float* __restri
                                   const uint32_t* __restrict__ mask_bits /* (N,6,60,8) for this pass or null */) {
   const int nq = cout / 8;
   const int64_t total = n * kL * nq;
-  const uint32_t thr = drop_thr(layer);
+  const uint32_t thr = drop_thr15(layer);
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int q = (int)(i % nq);
     const int64_t wr = i / nq;
@@ -151,7 +151,7 @@ __global__ void bn_dropout_kernel(float* __restrict__ act, const float* __restri
                                         (uint32_t)q, k0, k1);
         keep = 0;
 #pragma unroll
-        for (int e = 0; e < 8; ++e) keep |= (philox_field16(r, e) >= thr ? 1u : 0u) << e;
+        for (int e = 0; e < 8; ++e) keep |= (philox_field15(r, e) >= thr ? 1u : 0u) << e;
       }
     }
 #pragma unroll
