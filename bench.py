@@ -234,10 +234,10 @@ def main():
     if os.path.isfile(tp):
         try:
             tj = json.load(open(tp))
-            traffic = tj.get("dram_bytes_per_window_pass", 0) * n * T
+            traffic = tj.get("dram_bytes_per_window", 0) * n
         except Exception:
             traffic = None
-    roofline = {"bound": "tensor", "kernel": "fused_forward_kernel (tcgen05 conv chain + Philox dropout + UQ epilogue)",
+    roofline = {"bound": "tensor", "kernel": "fused_pair_kernel (tcgen05 cta_group::2 conv chain + Philox dropout + UQ epilogue)",
                 "achieved": ach, "peak": peaks["sustained"], "unit": "TFLOP/s", "frac": ach / peaks["sustained"],
                 "peak_source": peaks["source"] + ", sustained bf16 (kernel timed inside a multi-second step)",
                 "frac_of_burst": ach / peaks["burst"], "achieved_dense_count": n * T * FLOP_DENSE / (ms_fused * 1e-3) / 1e12,
@@ -250,8 +250,8 @@ def main():
         k2 = max(1, min(args.steps, 2))
         ms_e2e, wall_e2e = timed(step_e2e, k2)
         t_e2e = max(ms_e2e * 1e-3, wall_e2e) / k2     # D2H reads are synchronous: wall clock covers them
-        e2e = {"value": world * n / t_e2e, "unit": "windows/s", "h2d_bytes_per_step": int(x_host.numel() * x_host.element_size()),
-               "d2h_bytes_per_step": int(n * 28), "api": "uq_techniques.mc_dropout_uq(model, x_host_pinned_float64, n_pred=50)"}
+        e2e = {"value": world * n / t_e2e, "unit": "windows/s", "h2d_bytes_per_step": int(world * x_host.numel() * x_host.element_size()),
+               "d2h_bytes_per_step": int(world * n * 28), "api": "uq_techniques.mc_dropout_uq(model, x_host_pinned_float64, n_pred=50)"}
 
     # ---- secondary: Deep Ensemble M=10 (configs[2]) device-resident, one step
     de_info = None

@@ -12,9 +12,9 @@ from gpu_common import engine_with_members, members, twin_masks
 from oracle import network, reductions
 
 pytestmark = pytest.mark.gpu
-# 0: two tiles per CTA sharing one weight stream; 16: one tile per CTA; 32: CTA pairs (cta_group::2), two pairs
-# co-resident per SM pair; 48: CTA pairs with two tiles per CTA and the dual-consumer issuer
-VARIANTS = [0, 16, 32, 48]
+# 0 (default): CTA pairs (cta_group::2), two pairs co-resident per SM pair; 16: one tile per CTA; 48: CTA pairs with
+# two tiles per CTA and the dual-consumer issuer; 64: two tiles per CTA sharing one weight stream
+VARIANTS = [0, 16, 48, 64]
 
 
 def _x(uqk, n, seed=31):

@@ -869,16 +869,14 @@ __device__ __forceinline__ void issue_layer_pair(uint32_t s_base, uint32_t tmem_
   constexpr uint32_t kBLbo = ((uint32_t)((fl.cout / 2) * 16) >> 4) << 16;
   constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(fl.cout >> 3) << 17) | ((256u >> 4) << 24);
   constexpr int kLast = fl.nsteps - (fl.nstages - 1) * fl.sps;
-  mbar_wait2(bar_act, n_act & 1, err_flag, 2);
-  mbar_wait_cluster(bar_peer_act, n_act & 1, err_flag, 12);
+  mbar_wait_cluster(bar_act, n_act & 1, err_flag, 2);      // 256 local arrivals + 1 relayed from the peer
   ++n_act;
   tc_fence_after();
 #pragma unroll 1
   for (int st = 0; st < fl.nstages; ++st, ++it) {
     const int slot = it % NSLOTS;
     const uint32_t ph = (it / NSLOTS) & 1;
-    mbar_wait2(bar_full + 8 * slot, ph, err_flag, 3);
-    mbar_wait_cluster(bar_peer_full + 8 * slot, ph, err_flag, 13);
+    mbar_wait_cluster(bar_full + 8 * slot, ph, err_flag, 3);   // own half landed (tx) + peer's half (relayed arrive)
     tc_fence_after();
     const int nst = (st == fl.nstages - 1) ? kLast : fl.sps;
     const uint32_t b_lo0 = (((s_base + Cfg::oRing + slot * Cfg::kSlot) >> 4) & 0x3FFFu) | kBLbo;
@@ -956,10 +954,12 @@ fused_pair_kernel(const FusedArgs a) {
     s_alo[i] = (((s_base + Cfg::oAct + a_off) >> 4) & 0x3FFFu) | ((a_lbo >> 4) << 16);
   }
   if (threadIdx.x == 0) {
+    // leader: every "full" / "act" barrier also counts one arrival relayed from the peer CTA
+    const uint32_t extra = rank == 0 ? 1u : 0u;
     for (int i = 0; i < NSLOTS; ++i) {
-      mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, 1); mbar_init(bar_peer_full + 8 * i, 1);
+      mbar_init(bar_full + 8 * i, 1 + extra); mbar_init(bar_empty + 8 * i, 1); mbar_init(bar_peer_full + 8 * i, 1);
     }
-    mbar_init(bar_acc, 1); mbar_init(bar_act, Cfg::kEpiThreads); mbar_init(bar_peer_act, 1);
+    mbar_init(bar_acc, 1); mbar_init(bar_act, Cfg::kEpiThreads + extra); mbar_init(bar_peer_act, 1);
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -1023,8 +1023,8 @@ fused_pair_kernel(const FusedArgs a) {
       }
     } else if (lane == 0) {
       // ---- peer: relay "stage landed" / "activations ready" to the leader's barriers
-      const uint32_t r_peer_full = mapa_shared(bar_peer_full, 0);
-      const uint32_t r_peer_act = mapa_shared(bar_peer_act, 0);
+      const uint32_t r_peer_full = mapa_shared(bar_full, 0);
+      const uint32_t r_peer_act = mapa_shared(bar_act, 0);
       for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
         for (int g = 0; g < a.n_groups; ++g) {
           relay_layer<0, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
@@ -1210,7 +1210,8 @@ struct Pair2Cfg {
   static constexpr int kNumBars = 3 * NSLOTS + 6;  // full, empty, peer_full [NSLOTS]; acc[2], act[2], peer_act[2]
   static constexpr int oMisc = oBar + 8 * kNumBars;
   static constexpr int oAlo = oMisc + 16 + 64;
-  static constexpr int oProbs = oAlo + 4 * 392;    // probs[4][n_groups]
+  static constexpr int oStage = (oAlo + 4 * 392 + 15) & ~15;   // per-stage issue table, 16 B per stage of a group
+  static constexpr int oProbs = oStage + 16 * 128; // probs[4][n_groups]
 };
 
 __device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
@@ -1268,6 +1269,7 @@ fused_pair2_kernel(const FusedArgs a) {
   float* zpart = reinterpret_cast<float*>(smem + Cfg::oMisc + 16);
   uint32_t* s_alo = reinterpret_cast<uint32_t*>(smem + Cfg::oAlo);
   float* probs_s = reinterpret_cast<float*>(smem + Cfg::oProbs);
+  uint4* s_stage = reinterpret_cast<uint4*>(smem + Cfg::oStage);   // {idesc, b_lo fields, first step index, flags}
 
   for (int i = threadIdx.x; i < (2 * kActBytes) / 16; i += Cfg::kThreads)
     reinterpret_cast<uint4*>(smem + Cfg::oAct)[i] = make_uint4(0, 0, 0, 0);
@@ -1284,6 +1286,22 @@ fused_pair2_kernel(const FusedArgs a) {
       a_lbo = kPlaneBytes;
     }
     s_alo[i] = (((s_base + Cfg::oAct + a_off) >> 4) & 0x3FFFu) | ((a_lbo >> 4) << 16);
+  }
+  if (threadIdx.x == 32) {
+    // issue table: one entry per weight stage of a group, in stream order
+    int e = 0;
+    for (int l = 0; l < kBlocks; ++l) {
+      const FusedLayer fl = c_layers[l];
+      for (int st = 0; st < fl.nstages; ++st, ++e) {
+        const int step0 = st * fl.sps;
+        const int nst = min(fl.sps, fl.nsteps - step0);
+        const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(fl.cout >> 3) << 17) | ((256u >> 4) << 24);
+        const uint32_t flags = (uint32_t)nst | ((uint32_t)(fl.step_bytes >> 5) << 8) | (st == 0 ? 1u << 24 : 0u) |
+                               (st == fl.nstages - 1 ? 1u << 25 : 0u);
+        s_stage[e] = make_uint4(idesc, (uint32_t)(fl.cout / 2) << 16, (uint32_t)(c_step_base[l] + step0), flags);
+      }
+    }
+    s_stage[127] = make_uint4((uint32_t)e, 0u, 0u, 0u);   // number of stages per group
   }
   if (threadIdx.x == 0) {
     for (int i = 0; i < NSLOTS; ++i) {
@@ -1341,63 +1359,60 @@ fused_pair2_kernel(const FusedArgs a) {
     }
   } else if (warp == 1) {
     if (rank == 0) {
-      // ---- leader: dual-consumer MMA issuer (tile-pair 0 has priority, tile-pair 1 fills the gaps)
+      // ---- leader: dual-consumer MMA issuer (tile-pair 0 leads by at most kMaxLead stages, tile-pair 1 fills the gaps)
       constexpr uint32_t kHi = (128u >> 4) | (1u << 14);
-      TileCursor cur[2];
-#pragma unroll
-      for (int tl = 0; tl < 2; ++tl) {
-        cur[tl].unit = pair_id; cur[tl].g = 0; cur[tl].l = 0; cur[tl].st = 0; cur[tl].q = 0; cur[tl].n_act = 0;
-        cur[tl].act_ok = false; cur[tl].done = pair_id >= a.n_units;
+      constexpr int kMaxLead = NSLOTS / 2;
+      const int stages_per_group = (int)s_stage[127].x;
+      const uint32_t ring_lo = ((s_base + Cfg::oRing) >> 4) & 0x3FFFu;
+      uint32_t q[2] = {0u, 0u};          // global stage counters -> ring slot / phase
+      int sidx[2] = {0, 0};              // stage index inside the group
+      uint32_t n_act[2] = {0u, 0u};
+      bool act_ok[2] = {false, false};
+      long long left[2];                 // groups still to process
+      {
+        const long long my_units = pair_id < a.n_units ? (a.n_units - pair_id + n_pairs - 1) / n_pairs : 0;
+        left[0] = left[1] = my_units * a.n_groups;
       }
       uint32_t idle = 0, landed_q = 0;   // stages [0, landed_q) are known to have landed in BOTH CTAs
       long long t0 = 0;
-      while (!(cur[0].done && cur[1].done)) {
+      while (left[0] > 0 || left[1] > 0) {
         bool progressed = false;
 #pragma unroll
         for (int tl = 0; tl < 2; ++tl) {
-          TileCursor& c = cur[tl];
-          if (c.done || progressed) continue;
-          if (!c.act_ok) {
-            if (!mbar_test(bar_act + 8 * tl, c.n_act & 1) || !mbar_test_cluster(bar_peer_act + 8 * tl, c.n_act & 1)) continue;
-            c.act_ok = true;
+          if (left[tl] <= 0 || progressed) continue;
+          // slots between the two cursors cannot be refilled: bound the lead so the ring keeps prefetching
+          if (left[tl ^ 1] > 0 && (int32_t)(q[tl] - q[tl ^ 1]) >= kMaxLead) continue;
+          const uint4 e = s_stage[sidx[tl]];
+          const bool first = (e.w >> 24) & 1u, last = (e.w >> 25) & 1u;
+          if (first && !act_ok[tl]) {
+            if (!mbar_test(bar_act + 8 * tl, n_act[tl] & 1) || !mbar_test_cluster(bar_peer_act + 8 * tl, n_act[tl] & 1)) continue;
+            act_ok[tl] = true;
           }
-          const int slot = c.q % NSLOTS;
-          if (c.q >= landed_q) {             // only the leading tile-pair ever polls the weight barriers
-            const uint32_t ph = (c.q / NSLOTS) & 1;
+          const uint32_t slot = q[tl] % NSLOTS;
+          if (q[tl] >= landed_q) {            // only the leading tile-pair ever polls the weight barriers
+            const uint32_t ph = (q[tl] / NSLOTS) & 1;
             if (!mbar_test(bar_full + 8 * slot, ph) || !mbar_test_cluster(bar_peer_full + 8 * slot, ph)) continue;
-            landed_q = c.q + 1;
+            landed_q = q[tl] + 1;
           }
-          // ---- issue one stage of tile-pair tl
-          const FusedLayer fl = c_layers[c.l];
           tc_fence_after();
-          const int step0 = c.st * fl.sps;
-          const int nst = min(fl.sps, fl.nsteps - step0);
-          const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(fl.cout >> 3) << 17) | ((256u >> 4) << 24);
-          const uint32_t b_lo0 = (((s_base + Cfg::oRing + slot * Cfg::kSlot) >> 4) & 0x3FFFu) | ((uint32_t)(fl.cout / 2) << 16);
-          const uint32_t b_step = (uint32_t)fl.step_bytes >> 5;
-          const bool last = (c.st == fl.nstages - 1);
           if (elect_one()) {
-            const uint32_t* alo = s_alo + c_step_base[c.l] + step0;
+            const uint32_t* alo = s_alo + e.z;
             const uint32_t a_tile = (uint32_t)tl * (uint32_t)(kActBytes >> 4);
+            const uint32_t b_lo0 = (ring_lo + slot * (uint32_t)(Cfg::kSlot >> 4)) | e.y;
+            const uint32_t b_step = (e.w >> 8) & 0xFFFFu;
+            const int nst = (int)(e.w & 0xFFu);
             if (!dbg_no_mma) {
               for (int sl = 0; sl < nst; ++sl)
                 umma_bf16_2cta(tmem_base + (uint32_t)tl * 256u, mk64(alo[sl] + a_tile, kHi), mk64(b_lo0 + (uint32_t)sl * b_step, kHi),
-                               idesc, (step0 + sl) > 0 ? 1u : 0u);
+                               e.x, (first && sl == 0) ? 0u : 1u);
             }
             umma_commit_2cta(bar_empty + 8 * slot);            // one of the two arrivals that free the slot
             if (last) umma_commit_2cta(bar_acc + 8 * tl);       // accumulator of this tile-pair complete (both CTAs)
           }
           __syncwarp();
-          // ---- advance the cursor
-          ++c.q;
-          if (!last) { ++c.st; }
-          else {
-            c.st = 0; c.act_ok = false; ++c.n_act;
-            if (++c.l == kBlocks) {
-              c.l = 0;
-              if (++c.g == a.n_groups) { c.g = 0; c.unit += n_pairs; c.done = c.unit >= a.n_units; }
-            }
-          }
+          ++q[tl];
+          if (last) { act_ok[tl] = false; ++n_act[tl]; }
+          if (++sidx[tl] == stages_per_group) { sidx[tl] = 0; --left[tl]; }
           progressed = true;
         }
         if (progressed) { idle = 0; t0 = 0; }
@@ -1602,19 +1617,15 @@ static int launch_drop(const FusedParams& p, cudaStream_t s) {
 
 int fused_launch(const FusedParams& p, cudaStream_t s) {
   if (p.n == 0) return UQK_OK;
-  if ((p.variant >> 4) == 2) {
-    const int rc = launch_pair<4>(p, s);          // CTA pairs (cta_group::2), two pairs co-resident per SM pair
-    if (rc != UQK_E_SHAPE) return rc;
-  }
-  if ((p.variant >> 4) == 3) {
-    const int rc = launch_pair2<9>(p, s);         // CTA pairs, two tiles per CTA, dual-consumer issuer
-    if (rc != UQK_E_SHAPE) return rc;
-  }
-  if ((p.variant >> 4) != 1) {
-    const int rc = launch_drop<2, 4>(p, s);       // two tiles per CTA share one weight stream
-    if (rc != UQK_E_SHAPE) return rc;             // too many passes for its shared memory -> smaller configuration
-  }
-  const int rc = launch_drop<1, 2>(p, s);         // one tile per CTA, two CTAs per SM
+  // variant >> 4: 0 / 2 = CTA pairs (default), 3 = CTA pairs with two tiles per CTA, 4 = two tiles per CTA,
+  // 1 = one tile per CTA.  Every configuration falls through to a smaller one when T (or M) probabilities per
+  // window do not fit its shared memory.
+  const int v = p.variant >> 4;
+  int rc = UQK_E_SHAPE;
+  if (v == 3) rc = launch_pair2<9>(p, s);
+  if (rc == UQK_E_SHAPE && (v == 0 || v == 2 || v == 3)) rc = launch_pair<4>(p, s);
+  if (rc == UQK_E_SHAPE && v != 1) rc = launch_drop<2, 4>(p, s);
+  if (rc == UQK_E_SHAPE) rc = launch_drop<1, 2>(p, s);
   if (rc == UQK_E_SHAPE) set_error("fused kernel: %d passes/members do not fit in shared memory", p.n_groups);
   return rc;
 }
