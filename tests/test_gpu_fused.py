@@ -139,3 +139,33 @@ def test_native_rng_statistics(uqk, eng):
         mu, sd = float(np.mean(est[k])), float(np.std(est[k], ddof=1))
         a = float(np.mean(out[k]))
         assert abs(a - mu) <= 4 * max(sd, 0.05 * abs(mu)), (k, a, est[k])
+
+
+def test_full_size_properties_mcd_and_de(uqk):
+    """BASELINE configs[1] / configs[2] sizes (1 M windows, T=50 / M=10): size-independent properties.
+    (i) any shard recomputed alone with its window_base reproduces the corresponding slice bit for bit,
+    (ii) duplicated windows give identical ensemble outputs, (iii) metric identities hold for every window."""
+    import torch
+    eng = engine_with_members(10) if False else engine_with_members()
+    eng.option("variant", 0)
+    n, T = 1_000_000, 50
+    xu = torch.from_numpy(uqk.synthetic.make_windows(1 << 15, seed=77))
+    x = xu.repeat(n // (1 << 15) + 1, 1, 1)[:n].contiguous().cuda()
+    out = eng.mcd(x, n_passes=T, seed=99, bn_mode="inference", device_out=True)
+    torch.cuda.synchronize()
+    for s in (0, 123_457, n - 1000):
+        part = eng.mcd(x[s:s + 1000], n_passes=T, seed=99, bn_mode="inference", device_out=True, window_base=s)
+        for k in ("mean_pred", "pred_variance", "mutual_info", "entropy_bits", "label"):
+            assert torch.equal(part[k], out[k][s:s + 1000]), (k, s)
+    m = out
+    assert float(m["mean_pred"].min()) >= 0.0 and float(m["mean_pred"].max()) <= 1.0
+    assert float(m["pred_variance"].min()) >= 0.0 and float(m["pred_variance"].max()) <= 0.25 + 1e-6
+    assert float(m["mutual_info"].min()) >= 0.0
+    assert float((m["total_pred_entropy"] - m["expected_aleatoric_entropy"] - m["mutual_info"]).abs().max()) < 1e-6
+    assert bool(((m["mean_pred"] > 0.5).int() == m["label"]).all())
+    # windows repeat with period 2^15 but have different global indices -> different dropout masks
+    assert not torch.equal(m["mean_pred"][: 1 << 15], m["mean_pred"][1 << 15: 1 << 16])
+    de = eng.de(x, n_members=3, device_out=True)
+    # the ensemble has no RNG: repeated windows must give identical results
+    assert torch.equal(de["mean_pred"][: 1 << 15], de["mean_pred"][1 << 15: 1 << 16])
+    assert torch.equal(de["pred_variance"][: 1 << 15], de["pred_variance"][(n // (1 << 15) - 1) << 15: (n // (1 << 15)) << 15])
