@@ -132,6 +132,12 @@ int uqk_bootstrap(const float* variance_dev, const float* total_entropy_dev, con
                   const float* mutual_info_dev, const int32_t* y_dev, const int64_t* idx_dev, int n_boot,
                   int64_t n_windows, double* out_dev, void* stream);
 
+/* Per-window standardisation (x - mean_t) / (std_t + 1e-8), population std over the 60 time steps of every
+ * (window, channel), computed in float64.  Replaces standardize_per_window
+ * (data_prepocessing/prepare_numpy_datasets.py:83-95), the step immediately before the hot path.
+ * x_dev / out_dev: (N,60,4) of x_dtype (out may alias x). */
+int uqk_standardize(const void* x_dev, int x_dtype, int64_t n_windows, void* out_dev, void* stream);
+
 /* Allocation-free variant of uqk_bootstrap (no counterpart in the reference: it exists for callers of THIS library).
  * For processes that must not allocate device memory while running -- e.g. a server that gave the whole GPU to its
  * own arena or to a framework's caching allocator at start-up, or a latency-critical loop where cudaMalloc/cudaFree

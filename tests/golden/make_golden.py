@@ -160,6 +160,34 @@ def main():
         out[f"mcd_batch_t{t}"] = network.forward_f64(ws, X, training=True, masks=masks)
         out[f"mcd_frozen_t{t}"] = network.forward_f64(ws, X, training=True, masks=masks, bn_mode="inference")
     np.savez_compressed(os.path.join(HERE, "forward_oracle_golden.npz"), **out)
+
+    # ---- 5. window standardisation: the reference's own standardize_per_window
+    #         (data_prepocessing/prepare_numpy_datasets.py:83-95; imblearn is absent and only used elsewhere -> stubbed)
+    import importlib.util, types
+    saved = {k: sys.modules.get(k) for k in ("imblearn", "imblearn.over_sampling", "imblearn.under_sampling")}
+    sys.modules["imblearn"] = types.ModuleType("imblearn")
+    sys.modules["imblearn.over_sampling"] = types.ModuleType("imblearn.over_sampling")
+    sys.modules["imblearn.over_sampling"].SMOTE = object
+    sys.modules["imblearn.under_sampling"] = types.ModuleType("imblearn.under_sampling")
+    sys.modules["imblearn.under_sampling"].RandomUnderSampler = object
+    try:
+        spec = importlib.util.spec_from_file_location(
+            "_ref_prepare", os.path.join(reference_loader.REFERENCE_ROOT, "data_prepocessing", "prepare_numpy_datasets.py"))
+        prep = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(prep)
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                sys.modules.pop(k, None)
+            else:
+                sys.modules[k] = v
+    rng = np.random.default_rng(4242)
+    raw = rng.standard_normal((24, 60, 4)) * np.array([3.0, 12.0, 0.5, 0.5]) + np.array([95.0, 70.0, 0.0, 0.0])
+    raw[3, :, 1] = 72.0                      # constant channel -> std = 0 -> (x - mean) / 1e-8 = 0
+    raw[5, :, 0] = raw[5, 0, 0]
+    with contextlib.redirect_stdout(sink):
+        std = prep.standardize_per_window(raw)
+    np.savez_compressed(os.path.join(HERE, "standardize_golden.npz"), raw=raw, out=std)
     print("golden vectors written to", HERE)
 
 

@@ -157,3 +157,16 @@ def test_reference_drivers_run_unchanged(tmp_path):
         sys.path[:] = saved
         for k in [k for k in sys.modules if k == "tensorflow" or k.startswith("tensorflow.") or k == "uq_techniques"]:
             del sys.modules[k]
+
+
+def test_standardize_matches_reference_golden(golden_dir):
+    """N3: uqk_standardize vs the reference's own standardize_per_window output (golden), float64 and float32."""
+    g = np.load(os.path.join(golden_dir, "standardize_golden.npz"))
+    eng = engine_with_members()
+    out = eng.standardize(g["raw"])
+    assert out.dtype == np.float64
+    np.testing.assert_allclose(out, g["out"], rtol=1e-11, atol=1e-9)
+    out32 = eng.standardize(g["raw"].astype(np.float32))
+    assert out32.dtype == np.float32
+    np.testing.assert_allclose(out32, g["out"], rtol=2e-3, atol=2e-3)     # float32 input quantisation of 95 +- 3 signals
+    assert eng.standardize(g["raw"][:0]).shape == (0, 60, 4)

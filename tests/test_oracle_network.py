@@ -52,3 +52,8 @@ def test_flop_counts(uqk):
     assert uqk.arch.flops_per_window_pass(False) == 101_806_272
     assert uqk.arch.flops_per_window_pass(True) == 98_844_864
     assert uqk.arch.blob_size() == 853_441
+
+
+def test_standardize_matches_reference_golden(uqk, golden_dir):
+    g = np.load(os.path.join(golden_dir, "standardize_golden.npz"))
+    np.testing.assert_allclose(uqk.synthetic.standardize_per_window(g["raw"]), g["out"], rtol=1e-13, atol=1e-13)

@@ -19,7 +19,7 @@ PREC_BF16_TC, PREC_FP32 = 0, 1
 EXPORTS = [
     "uqk_version", "uqk_last_error", "uqk_create", "uqk_destroy", "uqk_set_model", "uqk_forward_det",
     "uqk_calibrate", "uqk_get_bn_stats", "uqk_set_bn_stats", "uqk_mcd", "uqk_de", "uqk_reduce",
-    "uqk_patient_reduce", "uqk_bootstrap", "uqk_bootstrap_noalloc", "uqk_launch_count", "uqk_set_option",
+    "uqk_patient_reduce", "uqk_standardize", "uqk_bootstrap", "uqk_bootstrap_noalloc", "uqk_launch_count", "uqk_set_option",
 ]
 
 
@@ -61,6 +61,7 @@ def load() -> C.CDLL:
     lib.uqk_de.argtypes = [vp, vp, i32, i64, i32, i32, vp, C.POINTER(MetricsOut), vp]
     lib.uqk_reduce.argtypes = [vp, i32, i64, C.POINTER(MetricsOut), vp]
     lib.uqk_patient_reduce.argtypes = [vp, vp, vp, vp, vp, i64, vp, vp]
+    lib.uqk_standardize.argtypes = [vp, i32, i64, vp, vp]
     lib.uqk_bootstrap.argtypes = [vp, vp, vp, vp, vp, vp, i32, i64, vp, vp]
     lib.uqk_bootstrap_noalloc.argtypes = [vp, vp, vp, vp, vp, vp, i32, i64, vp, vp]
     lib.uqk_launch_count.argtypes = [vp]

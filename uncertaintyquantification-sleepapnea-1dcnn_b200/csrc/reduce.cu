@@ -7,6 +7,8 @@
 // its window's column in pass order (the evaluation order of np.mean/np.var(axis=0)).
 #include "common.cuh"
 
+#include <algorithm>
+
 namespace uqk {
 
 constexpr int kReduceThreads = 128;
@@ -72,3 +74,78 @@ int launch_reduce(const float* probs, int n_pass, int64_t n, const MetricsOut& o
 }
 
 }  // namespace uqk
+
+// ---- N3: per-window standardisation (reference data_prepocessing/prepare_numpy_datasets.py:83-95) -----------------
+// out = (x - mean_t) / (std_t + 1e-8), mean / population std over the 60 time steps of each (window, channel), in
+// float64 like NumPy on the float64 CSV data.  One warp per window: lane l owns rows l and l+32 (all 4 channels);
+// HBM-bound: 1920 B read + 1920 B written per float64 window.
+namespace uqk {
+template <typename T>
+__global__ void __launch_bounds__(256)
+standardize_kernel(const T* __restrict__ x, T* __restrict__ out, int64_t n, double eps) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t w = warp; w < n; w += nwarps) {
+    const T* xw = x + (size_t)w * kL * kF;
+    double v[2][kF];
+    double s[kF] = {0, 0, 0, 0};
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int r = lane + 32 * h;
+#pragma unroll
+      for (int c = 0; c < kF; ++c) {
+        v[h][c] = r < kL ? (double)xw[r * kF + c] : 0.0;
+        s[c] += v[h][c];
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < kF; ++c) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) s[c] += __shfl_xor_sync(0xffffffffu, s[c], o);
+      s[c] /= (double)kL;
+    }
+    double q[kF] = {0, 0, 0, 0};
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int r = lane + 32 * h;
+#pragma unroll
+      for (int c = 0; c < kF; ++c) {
+        const double d = r < kL ? v[h][c] - s[c] : 0.0;
+        q[c] += d * d;
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < kF; ++c) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) q[c] += __shfl_xor_sync(0xffffffffu, q[c], o);
+      q[c] = sqrt(q[c] / (double)kL) + eps;
+    }
+    T* ow = out + (size_t)w * kL * kF;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int r = lane + 32 * h;
+      if (r < kL) {
+#pragma unroll
+        for (int c = 0; c < kF; ++c) ow[r * kF + c] = (T)((v[h][c] - s[c]) / q[c]);
+      }
+    }
+  }
+}
+}  // namespace uqk
+
+extern "C" int uqk_standardize(const void* x_dev, int x_dtype, int64_t n_windows, void* out_dev, void* stream) {
+  using namespace uqk;
+  if (n_windows < 0) { set_error("n_windows must be >= 0"); return UQK_E_BADARG; }
+  if (n_windows == 0) return UQK_OK;
+  if (!x_dev || !out_dev) { set_error("NULL argument"); return UQK_E_BADARG; }
+  if (x_dtype != UQK_F32 && x_dtype != UQK_F64) { set_error("x_dtype must be UQK_F32 or UQK_F64"); return UQK_E_BADARG; }
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int grid = (int)std::min<int64_t>((n_windows * 32 + 255) / 256, 148 * 16);
+  if (x_dtype == UQK_F64)
+    standardize_kernel<double><<<grid, 256, 0, s>>>((const double*)x_dev, (double*)out_dev, n_windows, 1e-8);
+  else
+    standardize_kernel<float><<<grid, 256, 0, s>>>((const float*)x_dev, (float*)out_dev, n_windows, 1e-8);
+  UQK_LAUNCH_CHECK();
+  return UQK_OK;
+}

@@ -239,6 +239,15 @@ class Engine:
                        "uqk_patient_reduce")
             return out.cpu().numpy()
 
+    def standardize(self, x_raw, device_out: bool = False):
+        """Per-window z-score of raw (N,60,4) windows (prepare_numpy_datasets.py:83-95), same dtype out."""
+        with torch.cuda.device(self.device):
+            xt, dt = self.to_device(x_raw)
+            out = torch.empty_like(xt)
+            _lib.check(self.lib.uqk_standardize(xt.data_ptr(), dt, xt.shape[0], out.data_ptr(), self._stream()),
+                       "uqk_standardize")
+            return out if device_out else out.cpu().numpy()
+
     def debug_dump(self) -> np.ndarray:
         out = np.zeros((arch.N_BLOCKS, 128, 256), dtype=np.float32)
         _lib.check(self.lib.uqk_debug_read_dump(self._h, out.ctypes.data_as(C.c_void_p)), "uqk_debug_read_dump")
