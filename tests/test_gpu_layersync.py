@@ -89,3 +89,22 @@ def test_calibration_statistics(uqk):
         rv = (vs[0][l] + vs[1][l]) / 2
         np.testing.assert_allclose(mean[l, :b.cout], rm, rtol=2e-4, atol=2e-5)
         np.testing.assert_allclose(var[l, :b.cout], rv, rtol=2e-3, atol=2e-5)
+
+
+def test_calibration_is_bit_reproducible(uqk):
+    """Batch statistics are accumulated in fixed point (integer atomics), so two calibrations -- and therefore a
+    sharded multi-GPU run and a single-GPU run -- give bit-identical statistics and outputs."""
+    eng = engine_with_members()
+    x = _x(uqk, 300, seed=22)
+    eng.calibrate(x, n_windows=300, n_passes=2, seed=4)
+    m1, v1 = eng.get_bn_stats()
+    p1 = eng.mcd(x, n_passes=2, seed=4, bn_mode="calibrated", return_probs=True)["probs"]
+    eng.calibrate(x, n_windows=300, n_passes=2, seed=4)
+    m2, v2 = eng.get_bn_stats()
+    p2 = eng.mcd(x, n_passes=2, seed=4, bn_mode="calibrated", return_probs=True)["probs"]
+    np.testing.assert_array_equal(m1, m2)
+    np.testing.assert_array_equal(v1, v2)
+    np.testing.assert_array_equal(p1, p2)
+    b1 = eng.mcd(x, n_passes=2, seed=4, bn_mode="batch", precision="fp32", return_probs=True)["probs"]
+    b2 = eng.mcd(x, n_passes=2, seed=4, bn_mode="batch", precision="fp32", return_probs=True)["probs"]
+    np.testing.assert_array_equal(b1, b2)

@@ -23,6 +23,7 @@ __global__ void cast_input_kernel(const T* __restrict__ x, float* __restrict__ o
 // One block per window. 128 threads = 8 channel-quads x 16 row-quads; output tile 60 rows x 32 channels per
 // iteration; the whole input window (+ zero halo) is staged in shared memory once.
 constexpr int kConvThreads = 128;
+constexpr double kStatScale = 16777216.0;   // 2^24 fixed point of the batch-statistic accumulators
 
 template <int CIN, int COUT, int K>
 __global__ void __launch_bounds__(kConvThreads)
@@ -33,7 +34,9 @@ conv_relu_kernel(const float* __restrict__ in, const float* __restrict__ w, cons
   constexpr int XS = CIN + 1;
   extern __shared__ float smem[];
   float* xs = smem;               // [ROWS][XS]
-  float* ssum = xs + ROWS * XS;   // [32][2]
+  // per-channel (sum, sum of squares) of the block, 2^-24 fixed point: integer accumulation is associative, so the
+  // batch statistics -- and everything computed from them -- are bit-reproducible run to run and across GPUs
+  unsigned long long* ssum = reinterpret_cast<unsigned long long*>(xs + ((ROWS * XS + 1) & ~1));   // [32][2]
   const int tx = threadIdx.x & 7;   // channel quad within the 32-channel tile
   const int ty = threadIdx.x >> 3;  // row quad: rows 4*ty .. 4*ty+3
 
@@ -81,15 +84,16 @@ conv_relu_kernel(const float* __restrict__ in, const float* __restrict__ w, cons
         }
       }
       if (stats != nullptr) {
-        if (threadIdx.x < 64) ssum[threadIdx.x] = 0.f;
+        if (threadIdx.x < 64) ssum[threadIdx.x] = 0ull;
         __syncthreads();
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-          atomicAdd(&ssum[(tx * 4 + q) * 2 + 0], s[q]);
-          atomicAdd(&ssum[(tx * 4 + q) * 2 + 1], s2[q]);
+          atomicAdd(&ssum[(tx * 4 + q) * 2 + 0], (unsigned long long)__double2ll_rn((double)s[q] * kStatScale));
+          atomicAdd(&ssum[(tx * 4 + q) * 2 + 1], (unsigned long long)__double2ll_rn((double)s2[q] * kStatScale));
         }
         __syncthreads();
-        if (threadIdx.x < 64) atomicAdd(&stats[(size_t)(ct * 32) * 2 + threadIdx.x], (double)ssum[threadIdx.x]);
+        if (threadIdx.x < 64)
+          atomicAdd(reinterpret_cast<unsigned long long*>(stats) + (size_t)(ct * 32) * 2 + threadIdx.x, ssum[threadIdx.x]);
         __syncthreads();
       }
     }
@@ -104,8 +108,9 @@ __global__ void bn_finalize_kernel(const double* __restrict__ stats, double coun
                                    double* __restrict__ accum_mean, double* __restrict__ accum_var) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= cout) return;
-  const double mu = stats[2 * c] / count;
-  double var = stats[2 * c + 1] / count - mu * mu;  // biased variance (Keras training mode)
+  const long long* q = reinterpret_cast<const long long*>(stats);
+  const double mu = (double)q[2 * c] / kStatScale / count;
+  double var = (double)q[2 * c + 1] / kStatScale / count - mu * mu;  // biased variance (Keras training mode)
   if (var < 0) var = 0;
   const float inv = (float)((double)gamma[c] / sqrt(var + (double)kBnEps));
   scale[c] = inv * inv_keep;
@@ -192,7 +197,7 @@ template <int CIN, int COUT, int K>
 static int launch_conv(const float* in, const float* w, const float* b, float* out, double* stats, int64_t n,
                        cudaStream_t s) {
   constexpr int H = (K - 1) / 2;
-  const size_t smem = ((size_t)(kL + 2 * H + 4) * (CIN + 1) + 64) * sizeof(float);
+  const size_t smem = ((size_t)(kL + 2 * H + 4) * (CIN + 1) + 2 + 128) * sizeof(float);
   if (smem > 48 * 1024)
     UQK_CUDA(cudaFuncSetAttribute(conv_relu_kernel<CIN, COUT, K>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)smem));

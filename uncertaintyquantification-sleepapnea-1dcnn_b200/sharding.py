@@ -67,15 +67,21 @@ def gather_metrics(local: Dict[str, torch.Tensor], shards: List[Tuple[int, int]]
 
 
 def sharded_mc_dropout_uq(uq_module, model, x, n_pred: int = 50, patient_ids=None, seed: Optional[int] = None,
-                          bn_mode: str = "calibrated", group=None, **kw) -> Dict[str, np.ndarray]:
-    """Each rank runs the fused MC-Dropout path on its shard of ``x`` (host array, identical on all ranks, or
-    already the local shard when ``x_is_local``) and the per-window metrics are gathered on every rank."""
+                          bn_mode: str = "calibrated", calib_windows: int = 4096, group=None, **kw) -> Dict[str, np.ndarray]:
+    """Each rank runs the fused MC-Dropout path on its shard of ``x`` (host array, identical on all ranks) and the
+    per-window metrics are gathered on every rank.  The calibrated BatchNorm statistics are estimated by every rank on
+    the SAME global windows ``x[:calib_windows]`` and the dropout masks are keyed by the global window index, so the
+    gathered result is bit-identical to a single-GPU run."""
     rank, world = _world(group)
     n = len(x)
     shards = patient_aligned_shards(patient_ids, world) if patient_ids is not None else window_shards(n, world)
     s, e = shards[rank]
-    out = uq_module.mc_dropout_uq(model, x[s:e], n_pred=n_pred, seed=seed, bn_mode=bn_mode, device_out=True,
-                                  window_base=s, **kw)
+    if bn_mode == "calibrated":
+        uq_module.mc_dropout_uq(model, x[:min(n, calib_windows)][:0], n_pred=1, seed=seed, bn_mode="inference")  # uploads the model
+        uq_module._engine.get_engine().calibrate(x, n_windows=calib_windows, n_passes=2,
+                                                 seed=uq_module._seed() if seed is None else int(seed))
+    out = uq_module.mc_dropout_uq(model, x[s:e], n_pred=n_pred, seed=seed, bn_mode=bn_mode, recalibrate=False,
+                                  device_out=True, window_base=s, **kw)
     local = {k: v for k, v in out.items() if isinstance(v, torch.Tensor)}
     full = gather_metrics(local, shards, group)
     return {k: v.cpu().numpy() for k, v in full.items()}
