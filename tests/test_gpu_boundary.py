@@ -165,7 +165,13 @@ def test_standardize_matches_reference_golden(golden_dir):
     eng = engine_with_members()
     out = eng.standardize(g["raw"])
     assert out.dtype == np.float64
-    np.testing.assert_allclose(out, g["out"], rtol=1e-11, atol=1e-9)
+    # windows 3 and 5 hold a constant channel: std = 0, so (x - mean) / 1e-8 amplifies the last-bit rounding of the
+    # mean by 1e8 (NumPy's own value there is summation-order noise of ~1e-6); everything else must agree tightly
+    const = np.zeros(g["raw"].shape, dtype=bool)
+    const[3, :, 1] = True
+    const[5, :, 0] = True
+    np.testing.assert_allclose(out[~const], g["out"][~const], rtol=1e-11, atol=1e-9)
+    assert np.abs(out[const] - g["out"][const]).max() < 1e-4
     out32 = eng.standardize(g["raw"].astype(np.float32))
     assert out32.dtype == np.float32
     np.testing.assert_allclose(out32, g["out"], rtol=2e-3, atol=2e-3)     # float32 input quantisation of 95 +- 3 signals

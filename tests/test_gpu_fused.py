@@ -169,3 +169,19 @@ def test_full_size_properties_mcd_and_de(uqk):
     # the ensemble has no RNG: repeated windows must give identical results
     assert torch.equal(de["mean_pred"][: 1 << 15], de["mean_pred"][1 << 15: 1 << 16])
     assert torch.equal(de["pred_variance"][: 1 << 15], de["pred_variance"][(n // (1 << 15) - 1) << 15: (n // (1 << 15)) << 15])
+
+
+def test_many_passes_fall_back_to_reduction_kernel(uqk):
+    """T beyond the shared-memory probability buffer (T > 256): probabilities go through HBM and K4 reduces them;
+    results must equal the fused path on the common passes (masks depend on (window, pass) only)."""
+    eng = engine_with_members()
+    eng.option("variant", 0)
+    x = _x(uqk, 21, seed=40)
+    big = eng.mcd(x, n_passes=300, seed=3, bn_mode="inference", return_probs=True)
+    small = eng.mcd(x, n_passes=20, seed=3, bn_mode="inference", return_probs=True)
+    np.testing.assert_array_equal(big["probs"][:20], small["probs"])
+    m = eng.reduce(big["probs"])
+    for k in ("mean_pred", "pred_variance", "mutual_info", "label"):
+        np.testing.assert_array_equal(big[k], m[k], err_msg=k)
+    only = eng.mcd(x, n_passes=300, seed=3, bn_mode="inference")          # metrics only, scratch probabilities
+    np.testing.assert_array_equal(only["mean_pred"], big["mean_pred"])

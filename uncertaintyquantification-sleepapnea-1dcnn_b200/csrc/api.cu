@@ -73,7 +73,7 @@ static int check_x(const void* x, int dtype, int64_t n) {
 }
 
 // Layer-synchronous T passes (or M members) over all windows into probs (n_groups, n).
-static int run_layersync(Handle* h, const void* x, int x_dtype, int64_t n, int n_groups, bool de, bool dropout,
+static int run_layersync(Handle* h, int member0, const void* x, int x_dtype, int64_t n, int n_groups, bool de, bool dropout,
                          int bn_mode, uint64_t seed, int64_t window_base, const uint32_t* mask_bits, float* probs,
                          double* accum_mean, double* accum_var, cudaStream_t s) {
   if (n == 0) return UQK_OK;
@@ -89,7 +89,7 @@ static int run_layersync(Handle* h, const void* x, int x_dtype, int64_t n, int n
     for (int64_t c0 = 0; c0 < n; c0 += chunk) {
       const int64_t cn = std::min(chunk, n - c0);
       LsPassParams p{};
-      p.blob_dev = h->d_blobs + (size_t)(de ? g : 0) * kBlobStride;
+      p.blob_dev = h->d_blobs + (size_t)(member0 + (de ? g : 0)) * kBlobStride;
       p.x_f32 = h->d_x32 + (size_t)c0 * kL * kF;
       p.act0 = h->d_act[0]; p.act1 = h->d_act[1];
       p.n = cn; p.bn_mode = bn_mode; p.dropout = dropout ? 1 : 0; p.seed = seed; p.pass = g;
@@ -105,15 +105,33 @@ static int run_layersync(Handle* h, const void* x, int x_dtype, int64_t n, int n
   return UQK_OK;
 }
 
-static int run_fused(Handle* h, const void* x, int x_dtype, int64_t n, int n_groups, bool de, bool dropout,
+// Passes (or members) per window that still fit the fused kernel's shared-memory probability buffer in its default
+// configuration; beyond it the probabilities go through HBM and the stand-alone reduction kernel (K4).
+constexpr int kMaxFusedGroups = 256;
+
+static int run_fused(Handle* h, int member0, const void* x, int x_dtype, int64_t n, int n_groups, bool de, bool dropout,
                      uint64_t seed, int64_t window_base, const uint32_t* mask_bits, const float* tables, float* probs,
-                     const MetricsOut& out, cudaStream_t s) {
+                     const MetricsOut& out, bool want_metrics, cudaStream_t s) {
   FusedParams p{};
+  const size_t pb = fused_packed_bytes();
   p.x = x; p.x_dtype = x_dtype; p.n = n; p.n_groups = n_groups; p.mode_de = de ? 1 : 0; p.dropout = dropout ? 1 : 0;
-  p.seed = seed; p.window_base = window_base; p.mask_bits = mask_bits; p.packed = h->d_packed; p.packed_pair = h->d_packed_pair; p.tables = tables;
-  p.probs = probs; p.out = out; p.err_flag = h->d_err; p.variant = h->variant;
+  p.seed = seed; p.window_base = window_base; p.mask_bits = mask_bits;
+  p.packed = reinterpret_cast<const uint16_t*>(reinterpret_cast<const uint8_t*>(h->d_packed) + (size_t)member0 * pb);
+  p.packed_pair = reinterpret_cast<const uint16_t*>(reinterpret_cast<const uint8_t*>(h->d_packed_pair) + (size_t)member0 * pb);
+  p.tables = tables; p.err_flag = h->d_err; p.variant = h->variant;
   p.dbg_act = h->dbg_dump ? h->d_dbg : nullptr;
-  return fused_launch(p, s);
+  if (n_groups <= kMaxFusedGroups) {
+    p.probs = probs; p.out = out;
+    return fused_launch(p, s);
+  }
+  int rc;
+  if (!probs) {
+    if ((rc = ensure(&h->d_probs_tmp, &h->probs_cap, (size_t)n * n_groups))) return rc;
+    probs = h->d_probs_tmp;
+  }
+  p.probs = probs; p.out = MetricsOut{}; p.no_smem_probs = 1;
+  if ((rc = fused_launch(p, s))) return rc;
+  return want_metrics ? launch_reduce(probs, n_groups, n, out, s) : UQK_OK;
 }
 
 }  // namespace uqk
@@ -226,22 +244,12 @@ int uqk_forward_det(uqk_handle* hh, int member, const void* x_dev, int x_dtype, 
   if (n > 0 && !probs_dev) { set_error("probs_dev is NULL"); return UQK_E_BADARG; }
   UQK_CUDA(cudaSetDevice(h->device));
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  if (precision == UQK_PREC_FP32) {
-    // a one-member "ensemble" starting at `member`
-    Handle view = *h;
-    view.d_blobs = h->d_blobs + (size_t)member * kBlobStride;
-    rc = run_layersync(&view, x_dev, x_dtype, n, 1, true, false, UQK_BN_INFERENCE, 0, 0, nullptr, probs_dev, nullptr,
-                       nullptr, s);
-    h->d_x32 = view.d_x32; h->x32_cap = view.x32_cap; h->d_act[0] = view.d_act[0]; h->d_act[1] = view.d_act[1];
-    h->act_cap = view.act_cap;
-    return rc;
-  }
+  if (precision == UQK_PREC_FP32)
+    return run_layersync(h, member, x_dev, x_dtype, n, 1, true, false, UQK_BN_INFERENCE, 0, 0, nullptr, probs_dev, nullptr,
+                         nullptr, s);
   if (precision != UQK_PREC_BF16_TC) { set_error("unknown precision %d", precision); return UQK_E_BADARG; }
-  Handle view = *h;
-  view.d_packed = reinterpret_cast<uint16_t*>(reinterpret_cast<uint8_t*>(h->d_packed) + (size_t)member * fused_packed_bytes());
-  view.d_packed_pair = reinterpret_cast<uint16_t*>(reinterpret_cast<uint8_t*>(h->d_packed_pair) + (size_t)member * fused_packed_bytes());
-  return run_fused(&view, x_dev, x_dtype, n, 1, true, false, 0, 0, nullptr, h->d_tables_inf + (size_t)member * kTableFloats,
-                   probs_dev, MetricsOut{}, s);
+  return run_fused(h, member, x_dev, x_dtype, n, 1, true, false, 0, 0, nullptr, h->d_tables_inf + (size_t)member * kTableFloats,
+                   probs_dev, MetricsOut{}, false, s);
 }
 
 int uqk_calibrate(uqk_handle* hh, const void* x_dev, int x_dtype, int64_t n, int n_passes, uint64_t seed, void* stream) {
@@ -255,7 +263,7 @@ int uqk_calibrate(uqk_handle* hh, const void* x_dev, int x_dtype, int64_t n, int
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if ((rc = ensure(&h->d_probs_tmp, &h->probs_cap, (size_t)n * n_passes))) return rc;
   UQK_CUDA(cudaMemsetAsync(h->d_accum, 0, sizeof(double) * 2 * kBlocks * kMaxCh, s));
-  rc = run_layersync(h, x_dev, x_dtype, n, n_passes, false, true, UQK_BN_BATCH, seed, 0, nullptr, h->d_probs_tmp,
+  rc = run_layersync(h, 0, x_dev, x_dtype, n, n_passes, false, true, UQK_BN_BATCH, seed, 0, nullptr, h->d_probs_tmp,
                      h->d_accum, h->d_accum + kBlocks * kMaxCh, s);
   if (rc) return rc;
   average_stats_kernel<<<(2 * kBlocks * kMaxCh + 255) / 256, 256, 0, s>>>(h->d_accum, n_passes, h->d_frozen);
@@ -313,8 +321,8 @@ int uqk_mcd(uqk_handle* hh, const void* x_dev, int x_dtype, int64_t n, int n_pas
     const float* mean = bn_mode == UQK_BN_CALIBRATED ? h->d_frozen : nullptr;
     const float* var = bn_mode == UQK_BN_CALIBRATED ? h->d_frozen + kBlocks * kMaxCh : nullptr;
     if ((rc = build_tables(h->d_blobs, mean, var, 1, h->d_table_mcd, s))) return rc;
-    return run_fused(h, x_dev, x_dtype, n, n_passes, false, true, seed, window_base, mask_bits_dev, h->d_table_mcd,
-                     probs_dev, mo, s);
+    return run_fused(h, 0, x_dev, x_dtype, n, n_passes, false, true, seed, window_base, mask_bits_dev, h->d_table_mcd,
+                     probs_dev, mo, out != nullptr, s);
   }
   if (precision != UQK_PREC_FP32) { set_error("unknown precision %d", precision); return UQK_E_BADARG; }
   float* probs = probs_dev;
@@ -322,7 +330,7 @@ int uqk_mcd(uqk_handle* hh, const void* x_dev, int x_dtype, int64_t n, int n_pas
     if ((rc = ensure(&h->d_probs_tmp, &h->probs_cap, (size_t)n * n_passes))) return rc;
     probs = h->d_probs_tmp;
   }
-  rc = run_layersync(h, x_dev, x_dtype, n, n_passes, false, true, bn_mode, seed, window_base, mask_bits_dev, probs,
+  rc = run_layersync(h, 0, x_dev, x_dtype, n, n_passes, false, true, bn_mode, seed, window_base, mask_bits_dev, probs,
                      nullptr, nullptr, s);
   if (rc) return rc;
   if (out) return launch_reduce(probs, n_passes, n, mo, s);
@@ -343,14 +351,14 @@ int uqk_de(uqk_handle* hh, const void* x_dev, int x_dtype, int64_t n, int n_memb
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const MetricsOut mo = to_metrics(out);
   if (precision == UQK_PREC_BF16_TC)
-    return run_fused(h, x_dev, x_dtype, n, n_members, true, false, 0, 0, nullptr, h->d_tables_inf, probs_dev, mo, s);
+    return run_fused(h, 0, x_dev, x_dtype, n, n_members, true, false, 0, 0, nullptr, h->d_tables_inf, probs_dev, mo, out != nullptr, s);
   if (precision != UQK_PREC_FP32) { set_error("unknown precision %d", precision); return UQK_E_BADARG; }
   float* probs = probs_dev;
   if (!probs) {
     if ((rc = ensure(&h->d_probs_tmp, &h->probs_cap, (size_t)n * n_members))) return rc;
     probs = h->d_probs_tmp;
   }
-  rc = run_layersync(h, x_dev, x_dtype, n, n_members, true, false, UQK_BN_INFERENCE, 0, 0, nullptr, probs, nullptr,
+  rc = run_layersync(h, 0, x_dev, x_dtype, n, n_members, true, false, UQK_BN_INFERENCE, 0, 0, nullptr, probs, nullptr,
                      nullptr, s);
   if (rc) return rc;
   if (out) return launch_reduce(probs, n_members, n, mo, s);

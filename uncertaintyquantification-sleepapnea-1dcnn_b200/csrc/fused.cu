@@ -315,6 +315,7 @@ struct FusedArgs {
   float* dbg_act;
   int* err_flag;
   int variant;
+  int smem_probs;   // 1: per-window probabilities are kept in shared memory for the fused K3 reductions
   long long n_units;
 };
 
@@ -621,7 +622,7 @@ __device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, c
       const float* z4 = c.zp + c.slot_w * 4;
       const float z = (((z4[0] + z4[1]) + z4[2]) + z4[3]) * (1.0f / (float)kL) + c.tab_w[kDenseIn];   // fixed order
       const float p = 1.0f / (1.0f + expf(-z));
-      probs_s[(2 * c.tl + c.slot_w) * a.n_groups + g] = p;
+      if (a.smem_probs) probs_s[(2 * c.tl + c.slot_w) * a.n_groups + g] = p;
       if (a.probs && win < a.n) a.probs[(size_t)g * a.n + win] = p;
     }
   }
@@ -794,7 +795,7 @@ fused_forward_kernel(const FusedArgs a) {
         epi_layer<5, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
       }
       // ---- K3: per-window reductions over the T (or M) probabilities, in the reference's evaluation order
-      if (c.colhalf == 0 && c.t == 0 && (c.quarter & 1) == 0 && win < a.n) {
+      if (a.smem_probs && c.colhalf == 0 && c.t == 0 && (c.quarter & 1) == 0 && win < a.n) {
         const float* pw = probs_s + (2 * c.tl + c.slot_w) * a.n_groups;
         window_metrics([&](int tt) { return pw[tt]; }, a.n_groups, win, a.out);
       }
@@ -1098,7 +1099,7 @@ fused_pair_kernel(const FusedArgs a) {
         epi_layer<4, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
         epi_layer<5, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
       }
-      if (c.colhalf == 0 && c.t == 0 && (c.quarter & 1) == 0 && win < a.n) {
+      if (a.smem_probs && c.colhalf == 0 && c.t == 0 && (c.quarter & 1) == 0 && win < a.n) {
         const float* pw = probs_s + c.slot_w * a.n_groups;
         window_metrics([&](int tt) { return pw[tt]; }, a.n_groups, win, a.out);
       }
@@ -1125,7 +1126,8 @@ static int launch_pair_variant(const FusedParams& p, cudaStream_t s) {
   a.tables = p.tables; a.probs = p.probs; a.out = p.out; a.dbg_act = p.dbg_act; a.err_flag = p.err_flag;
   a.variant = p.variant;
   a.n_units = (p.n + Cfg::kWpu - 1) / Cfg::kWpu;
-  const size_t smem = (size_t)Cfg::oProbs + (size_t)2 * p.n_groups * sizeof(float);
+  a.smem_probs = p.no_smem_probs ? 0 : 1;
+  const size_t smem = (size_t)Cfg::oProbs + (p.no_smem_probs ? 0 : (size_t)2 * p.n_groups * sizeof(float));
   if (smem > 113 * 1024) return UQK_E_SHAPE;   // must leave room for two CTAs per SM
   int dev = 0, sms = 148;
   UQK_CUDA(cudaGetDevice(&dev));
@@ -1502,7 +1504,7 @@ fused_pair2_kernel(const FusedArgs a) {
         epi_layer<4, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
         epi_layer<5, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
       }
-      if (c.colhalf == 0 && c.t == 0 && (c.quarter & 1) == 0 && win < a.n) {
+      if (a.smem_probs && c.colhalf == 0 && c.t == 0 && (c.quarter & 1) == 0 && win < a.n) {
         const float* pw = probs_s + (2 * c.tl + c.slot_w) * a.n_groups;
         window_metrics([&](int tt) { return pw[tt]; }, a.n_groups, win, a.out);
       }
@@ -1528,7 +1530,8 @@ static int launch_pair2_variant(const FusedParams& p, cudaStream_t s) {
   a.tables = p.tables; a.probs = p.probs; a.out = p.out; a.dbg_act = p.dbg_act; a.err_flag = p.err_flag;
   a.variant = p.variant;
   a.n_units = (p.n + Cfg::kWpu - 1) / Cfg::kWpu;
-  const size_t smem = (size_t)Cfg::oProbs + (size_t)4 * p.n_groups * sizeof(float);
+  a.smem_probs = p.no_smem_probs ? 0 : 1;
+  const size_t smem = (size_t)Cfg::oProbs + (p.no_smem_probs ? 0 : (size_t)4 * p.n_groups * sizeof(float));
   if (smem > 227 * 1024) return UQK_E_SHAPE;
   int dev = 0, sms = 148;
   UQK_CUDA(cudaGetDevice(&dev));
@@ -1570,7 +1573,8 @@ static int launch_variant(const FusedParams& p, cudaStream_t s) {
   a.tables = p.tables; a.probs = p.probs; a.out = p.out; a.dbg_act = p.dbg_act; a.err_flag = p.err_flag;
   a.variant = p.variant;
   a.n_units = (p.n + Cfg::kWpu - 1) / Cfg::kWpu;
-  const size_t smem = (size_t)Cfg::oProbs + (size_t)Cfg::kWpu * p.n_groups * sizeof(float);
+  a.smem_probs = p.no_smem_probs ? 0 : 1;
+  const size_t smem = (size_t)Cfg::oProbs + (p.no_smem_probs ? 0 : (size_t)Cfg::kWpu * p.n_groups * sizeof(float));
   if (smem > 227 * 1024) return UQK_E_SHAPE;   // caller falls back to the smaller configuration
   int dev = 0, sms = 148;
   UQK_CUDA(cudaGetDevice(&dev));

@@ -55,6 +55,7 @@ struct FusedParams {
   float* dbg_act;             // optional debug dump (6,128,256) floats of unit 0 / group 0 / tile 0
   int* err_flag;              // device int: set !=0 by the in-kernel watchdog
   int variant;                // kernel variant selector (tests)
+  int no_smem_probs;          // 1: too many passes for shared memory: probabilities go to `probs` only (K4 reduces them)
 };
 int fused_launch(const FusedParams& p, cudaStream_t s);
 
