@@ -131,8 +131,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--windows", type=int, default=1_000_000, help="windows per GPU (configs[1]: 1M)")
     ap.add_argument("--passes", type=int, default=50)
-    ap.add_argument("--ref-windows", type=int, default=128, help="windows per step of the CPU reference arm")
-    ap.add_argument("--cpu-sample", type=int, default=192, help="windows of the cpu_baseline sample (0 = skip)")
+    ap.add_argument("--ref-windows", type=int, default=512, help="windows per step of the CPU reference arm")
+    ap.add_argument("--cpu-sample", type=int, default=768, help="windows of the cpu_baseline sample (0 = skip)")
     ap.add_argument("--variant", type=int, default=None)
     ap.add_argument("--skip-e2e", action="store_true")
     args = ap.parse_args()

@@ -80,6 +80,12 @@ def test_model_container_and_shim(tmp_path, uqk):
         for k in [k for k in sys.modules if k == "tensorflow" or k.startswith("tensorflow.")]:
             del sys.modules[k]
         model.UQModel._global_seed = 2025
+    # the engine's upload cache is keyed by weight content, not object identity
+    fp = model.fingerprint(m.blob())
+    ws = m.get_weights()
+    ws[1] = ws[1] + 1.0
+    m.set_weights(ws)
+    assert model.fingerprint(m.blob()) != fp and model.fingerprint(model.synthetic_model(1).blob()) == fp
     with pytest.raises(ValueError):
         model.UQModel(m.get_weights()[:-1])
     bad = tmp_path / "bad.keras"

@@ -61,7 +61,7 @@ class UQModel:
     def __call__(self, x, training: bool = False):
         from . import engine as _engine
         eng = _engine.get_engine()
-        eng.ensure_members(lambda: self._blob[None], key=("single", id(self), self._blob.ctypes.data))
+        eng.ensure_members(lambda: self._blob[None], key=("single", fingerprint(self._blob)))
         x = np.asarray(x)
         if training:
             # ONE stochastic pass with exact Keras semantics (batch-statistic BN + dropout); every call draws
@@ -83,6 +83,13 @@ class UQModel:
 def _default_precision() -> str:
     import os
     return os.environ.get("UQK_PRECISION", "bf16")
+
+
+def fingerprint(blob: np.ndarray) -> int:
+    """Content hash of a weight blob: the engine re-uploads a model when this changes (object identity is not a safe
+    cache key -- ids are reused after garbage collection and weights can be changed with ``set_weights``)."""
+    import zlib
+    return zlib.crc32(memoryview(np.ascontiguousarray(blob)).cast("B"))
 
 
 def weights_of(model) -> np.ndarray:

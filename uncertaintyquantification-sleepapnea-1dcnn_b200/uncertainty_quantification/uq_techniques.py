@@ -45,8 +45,8 @@ def _seed() -> int:
     return int(s) if s is not None else int(_model.UQModel._global_seed)
 
 
-def _members_key(models):
-    return tuple(id(m) for m in models)
+def _members_key(blobs):
+    return tuple(_model.fingerprint(b) for b in blobs)
 
 
 # ===================== forward passes =====================
@@ -55,7 +55,8 @@ def mc_dropout_predict(model, x_test_data: np.ndarray, n_pred: int = 50) -> np.n
     (reference uq_techniques.py:12-24: ``np.stack([model(x, training=True) for _ in range(n_pred)])``)."""
     t0 = time.time()
     eng = _engine.get_engine()
-    eng.ensure_members(lambda: _model.weights_of(model)[None], key=("mcd", id(model)))
+    blob = _model.weights_of(model)
+    eng.ensure_members(lambda: blob[None], key=("mcd",) + _members_key([blob]))
     x = np.asarray(x_test_data)
     n = x.shape[0]
     mode = _env("UQK_BN_MODE", "auto")
@@ -77,7 +78,8 @@ def deep_ensembles_predict(ensemble_models: List, x_test_data: np.ndarray) -> np
     t0 = time.time()
     eng = _engine.get_engine()
     models = list(ensemble_models)
-    eng.ensure_members(lambda: np.stack([_model.weights_of(m) for m in models]), key=("de",) + _members_key(models))
+    blobs = [_model.weights_of(m) for m in models]
+    eng.ensure_members(lambda: np.stack(blobs), key=("de",) + _members_key(blobs))
     x = np.asarray(x_test_data)
     out = eng.de(x, n_members=len(models), precision=_env("UQK_PRECISION", "bf16"), return_probs=True, metrics=())
     de_predictions = out["probs"].reshape(len(models), x.shape[0], 1)
@@ -114,7 +116,8 @@ def mc_dropout_uq(model, x_test_data, n_pred: int = 50, *, y_true=None, return_p
     ``calib_windows`` windows with the exact layer-synchronous path (inside this call when ``recalibrate``).
     ``window_base`` = global index of the first window (multi-GPU shards: masks are keyed by the global index)."""
     eng = _engine.get_engine()
-    eng.ensure_members(lambda: _model.weights_of(model)[None], key=("mcd", id(model)))
+    blob = _model.weights_of(model)
+    eng.ensure_members(lambda: blob[None], key=("mcd",) + _members_key([blob]))
     seed = _seed() if seed is None else int(seed)
     if bn_mode == "batch":
         precision = "fp32"
@@ -130,7 +133,8 @@ def deep_ensemble_uq(ensemble_models: List, x_test_data, *, y_true=None, return_
     """deep_ensembles_predict + uq_evaluation_dist + inline CSV metrics in one fused call (see mc_dropout_uq)."""
     eng = _engine.get_engine()
     models = list(ensemble_models)
-    eng.ensure_members(lambda: np.stack([_model.weights_of(m) for m in models]), key=("de",) + _members_key(models))
+    blobs = [_model.weights_of(m) for m in models]
+    eng.ensure_members(lambda: np.stack(blobs), key=("de",) + _members_key(blobs))
     out = eng.de(x_test_data, n_members=len(models), precision=precision, return_probs=return_probs,
                  device_out=device_out)
     return _finish_uq(out, y_true)
