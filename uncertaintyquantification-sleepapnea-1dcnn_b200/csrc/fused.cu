@@ -465,6 +465,8 @@ __device__ __forceinline__ void epi_chunk16(const uint32_t (&v)[16], int c0, con
 
 __host__ __device__ constexpr int fl_step_base(int l) { return l == 0 ? 0 : fl_step_base(l - 1) + fl_nconv(l - 1) + 1; }
 constexpr int kTotalSteps = fl_step_base(kBlocks);   // 382 convolution steps + 6 bias steps
+constexpr int kStagesPerGroup = fused_layer(0).nstages + fused_layer(1).nstages + fused_layer(2).nstages +
+                                fused_layer(3).nstages + fused_layer(4).nstages + fused_layer(5).nstages;
 __constant__ int c_step_base[kBlocks + 1] = {fl_step_base(0), fl_step_base(1), fl_step_base(2), fl_step_base(3),
                                              fl_step_base(4), fl_step_base(5), fl_step_base(6)};
 
@@ -864,7 +866,9 @@ template <int L, int NSLOTS, typename Cfg>
 __device__ __forceinline__ void issue_layer_pair(uint32_t s_base, uint32_t tmem_base, const uint32_t* s_alo,
                                                  uint32_t bar_full, uint32_t bar_empty, uint32_t bar_peer_full,
                                                  uint32_t bar_acc, uint32_t bar_act, uint32_t bar_peer_act, uint32_t& it,
-                                                 uint32_t& n_act, int* err_flag, bool no_mma) {
+                                                 uint32_t& n_act, int* err_flag, bool no_mma, uint32_t a_tile = 0u,
+                                                 volatile uint32_t* progress = nullptr, int lag_role = 0, uint32_t lag = 0u,
+                                                 uint32_t total_stages = 0u) {
   constexpr FusedLayer fl = fused_layer(L);
   constexpr uint32_t kHi = (128u >> 4) | (1u << 14);
   constexpr uint32_t kBLbo = ((uint32_t)((fl.cout / 2) * 16) >> 4) << 16;
@@ -877,6 +881,15 @@ __device__ __forceinline__ void issue_layer_pair(uint32_t s_base, uint32_t tmem_
   for (int st = 0; st < fl.nstages; ++st, ++it) {
     const int slot = it % NSLOTS;
     const uint32_t ph = (it / NSLOTS) & 1;
+    if (lag_role == 2) {
+      // trailing tile-pair: stay `lag` stages behind the leading one, so that its last stages of a layer cover the
+      // leader's epilogue and the leader's first stages of the next layer cover this one's
+      const uint32_t need = min(it + lag, total_stages);
+      uint32_t spins = 0;
+      while (*progress < need) {
+        if (++spins > (1u << 28)) mbar_timeout(err_flag, 41);
+      }
+    }
     mbar_wait_cluster(bar_full + 8 * slot, ph, err_flag, 3);   // own half landed (tx) + peer's half (relayed arrive)
     tc_fence_after();
     const int nst = (st == fl.nstages - 1) ? kLast : fl.sps;
@@ -888,11 +901,12 @@ __device__ __forceinline__ void issue_layer_pair(uint32_t s_base, uint32_t tmem_
         for (int sl = 0; sl < fl.sps; ++sl) {
           if (sl < nst) {
             const uint64_t bdesc = mk64(b_lo0 + (uint32_t)sl * (uint32_t)(fl.step_bytes >> 5), kHi);
-            umma_bf16_2cta(tmem_base, mk64(alo[sl], kHi), bdesc, kIdesc, (st > 0 || sl > 0) ? 1u : 0u);
+            umma_bf16_2cta(tmem_base, mk64(alo[sl] + a_tile, kHi), bdesc, kIdesc, (st > 0 || sl > 0) ? 1u : 0u);
           }
         }
       }
       umma_commit_2cta(bar_empty + 8 * slot);   // both CTAs' ring slots are free once these MMAs have read them
+      if (lag_role == 1) *progress = it + 1;    // leading tile-pair publishes how far it has issued
     }
     __syncwarp();
   }
@@ -1188,18 +1202,18 @@ static int launch_pair(const FusedParams& p, cudaStream_t s) {
 }
 
 // =====================================================================================================================
-// CTA-pair variant with TWO tiles per CTA and a dual-consumer issuer ("P2"): 1 CTA per SM, the pair owns a unit of 8
-// windows = tile-pairs A and B (each an M=256 accumulator spanning both SMs).  Both tile-pairs consume the SAME
-// weight stream (R = 8 window-passes per stream) through a ring of half-stages that is twice as deep in stage units
-// as the single-CTA ring.  The issuer gives tile-pair A priority: A runs ahead until the ring window stops it, B
-// trails by the window, so when A's accumulator completes, B still has several stages of MMAs to issue -- they cover
-// A's epilogue, and A's first stages of the next layer cover B's epilogue.  A ring slot is free when BOTH tile-pairs
-// have consumed it (mbarrier count 2, tcgen05.commit multicast to both CTAs).
+// CTA-pair variant with TWO tiles per CTA ("P2"): 1 CTA per SM, the pair owns a unit of 8 windows = tile-pairs A and B
+// (each an M=256 accumulator spanning both SMs).  Both tile-pairs consume the SAME weight stream (R = 8 window-passes
+// per stream, half the L2->SM traffic of the default pair kernel) through a 9-slot ring of half-stages.  The leader CTA
+// runs ONE MMA-ISSUER WARP PER TILE-PAIR: each walks the schedule on its own, blocks only on its own activations,
+// and the two drift apart at layer boundaries so one tile-pair's MMAs cover the other's epilogue.  A ring slot is
+// free when BOTH tile-pairs have consumed it (mbarrier count 2, tcgen05.commit multicast to both CTAs).
 // =====================================================================================================================
 template <int NSLOTS>
 struct Pair2Cfg {
   static constexpr int kEpiThreads = 256;
-  static constexpr int kWarps = 2 + 16;
+  static constexpr int kCtrlWarps = 3;             // producer, issuer of tile-pair 0 (peer: relay), issuer of tile-pair 1
+  static constexpr int kWarps = kCtrlWarps + 16;
   static constexpr int kThreads = 32 * kWarps;
   static constexpr int kWpu = 8;                   // windows per pair unit
   static constexpr int kTmemCols = 512;
@@ -1212,41 +1226,7 @@ struct Pair2Cfg {
   static constexpr int kNumBars = 3 * NSLOTS + 6;  // full, empty, peer_full [NSLOTS]; acc[2], act[2], peer_act[2]
   static constexpr int oMisc = oBar + 8 * kNumBars;
   static constexpr int oAlo = oMisc + 16 + 64;
-  static constexpr int oStage = (oAlo + 4 * 392 + 15) & ~15;   // per-stage issue table, 16 B per stage of a group
-  static constexpr int oProbs = oStage + 16 * 128; // probs[4][n_groups]
-};
-
-__device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-      "selp.b32 %0, 1, 0, p;\n\t}"
-      : "=r"(ok)
-      : "r"(bar), "r"(parity)
-      : "memory");
-  return ok != 0;
-}
-__device__ __forceinline__ bool mbar_test_cluster(uint32_t bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "mbarrier.test_wait.parity.relaxed.cluster.shared::cta.b64 p, [%1], %2;\n\t"
-      "selp.b32 %0, 1, 0, p;\n\t}"
-      : "=r"(ok)
-      : "r"(bar), "r"(parity)
-      : "memory");
-  return ok != 0;
-}
-
-// position of one tile-pair in the (unit, group, layer, stage) schedule
-struct TileCursor {
-  long long unit;
-  int g, l, st;
-  uint32_t q;        // global stage counter -> ring slot / phase
-  uint32_t n_act;    // activation-barrier phase counter
-  bool act_ok;       // this layer's activations already seen ready
-  bool done;
+  static constexpr int oProbs = (oAlo + 4 * 392 + 15) & ~15;   // probs[4][n_groups]
 };
 
 template <int NSLOTS, int DROP, bool DBG>
@@ -1271,7 +1251,6 @@ fused_pair2_kernel(const FusedArgs a) {
   float* zpart = reinterpret_cast<float*>(smem + Cfg::oMisc + 16);
   uint32_t* s_alo = reinterpret_cast<uint32_t*>(smem + Cfg::oAlo);
   float* probs_s = reinterpret_cast<float*>(smem + Cfg::oProbs);
-  uint4* s_stage = reinterpret_cast<uint4*>(smem + Cfg::oStage);   // {idesc, b_lo fields, first step index, flags}
 
   for (int i = threadIdx.x; i < (2 * kActBytes) / 16; i += Cfg::kThreads)
     reinterpret_cast<uint4*>(smem + Cfg::oAct)[i] = make_uint4(0, 0, 0, 0);
@@ -1289,28 +1268,16 @@ fused_pair2_kernel(const FusedArgs a) {
     }
     s_alo[i] = (((s_base + Cfg::oAct + a_off) >> 4) & 0x3FFFu) | ((a_lbo >> 4) << 16);
   }
-  if (threadIdx.x == 32) {
-    // issue table: one entry per weight stage of a group, in stream order
-    int e = 0;
-    for (int l = 0; l < kBlocks; ++l) {
-      const FusedLayer fl = c_layers[l];
-      for (int st = 0; st < fl.nstages; ++st, ++e) {
-        const int step0 = st * fl.sps;
-        const int nst = min(fl.sps, fl.nsteps - step0);
-        const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(fl.cout >> 3) << 17) | ((256u >> 4) << 24);
-        const uint32_t flags = (uint32_t)nst | ((uint32_t)(fl.step_bytes >> 5) << 8) | (st == 0 ? 1u << 24 : 0u) |
-                               (st == fl.nstages - 1 ? 1u << 25 : 0u);
-        s_stage[e] = make_uint4(idesc, (uint32_t)(fl.cout / 2) << 16, (uint32_t)(c_step_base[l] + step0), flags);
-      }
-    }
-    s_stage[127] = make_uint4((uint32_t)e, 0u, 0u, 0u);   // number of stages per group
-  }
   if (threadIdx.x == 0) {
+    *reinterpret_cast<volatile uint32_t*>(smem + Cfg::oMisc + 8) = 0u;   // progress counter of the leading tile-pair
+    // leader: every "full" / "act" barrier also counts one arrival relayed from the peer CTA; a ring slot is free when
+    // BOTH tile-pairs have consumed it (two commits)
+    const uint32_t extra = rank == 0 ? 1u : 0u;
     for (int i = 0; i < NSLOTS; ++i) {
-      mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, 2); mbar_init(bar_peer_full + 8 * i, 1);
+      mbar_init(bar_full + 8 * i, 1 + extra); mbar_init(bar_empty + 8 * i, 2); mbar_init(bar_peer_full + 8 * i, 1);
     }
     for (int i = 0; i < 2; ++i) {
-      mbar_init(bar_acc + 8 * i, 1); mbar_init(bar_act + 8 * i, Cfg::kEpiThreads); mbar_init(bar_peer_act + 8 * i, 1);
+      mbar_init(bar_acc + 8 * i, 1); mbar_init(bar_act + 8 * i, Cfg::kEpiThreads + extra); mbar_init(bar_peer_act + 8 * i, 1);
     }
     fence_barrier_init();
   }
@@ -1359,74 +1326,33 @@ fused_pair2_kernel(const FusedArgs a) {
         }
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == 1 || warp == 2) {
+    const int tl = warp - 1;
     if (rank == 0) {
-      // ---- leader: dual-consumer MMA issuer (tile-pair 0 leads by at most kMaxLead stages, tile-pair 1 fills the gaps)
-      constexpr uint32_t kHi = (128u >> 4) | (1u << 14);
-      constexpr int kMaxLead = NSLOTS / 2;
-      const int stages_per_group = (int)s_stage[127].x;
-      const uint32_t ring_lo = ((s_base + Cfg::oRing) >> 4) & 0x3FFFu;
-      uint32_t q[2] = {0u, 0u};          // global stage counters -> ring slot / phase
-      int sidx[2] = {0, 0};              // stage index inside the group
-      uint32_t n_act[2] = {0u, 0u};
-      bool act_ok[2] = {false, false};
-      long long left[2];                 // groups still to process
-      {
-        const long long my_units = pair_id < a.n_units ? (a.n_units - pair_id + n_pairs - 1) / n_pairs : 0;
-        left[0] = left[1] = my_units * a.n_groups;
-      }
-      uint32_t idle = 0, landed_q = 0;   // stages [0, landed_q) are known to have landed in BOTH CTAs
-      long long t0 = 0;
-      while (left[0] > 0 || left[1] > 0) {
-        bool progressed = false;
-#pragma unroll
-        for (int tl = 0; tl < 2; ++tl) {
-          if (left[tl] <= 0 || progressed) continue;
-          // slots between the two cursors cannot be refilled: bound the lead so the ring keeps prefetching
-          if (left[tl ^ 1] > 0 && (int32_t)(q[tl] - q[tl ^ 1]) >= kMaxLead) continue;
-          const uint4 e = s_stage[sidx[tl]];
-          const bool first = (e.w >> 24) & 1u, last = (e.w >> 25) & 1u;
-          if (first && !act_ok[tl]) {
-            if (!mbar_test(bar_act + 8 * tl, n_act[tl] & 1) || !mbar_test_cluster(bar_peer_act + 8 * tl, n_act[tl] & 1)) continue;
-            act_ok[tl] = true;
-          }
-          const uint32_t slot = q[tl] % NSLOTS;
-          if (q[tl] >= landed_q) {            // only the leading tile-pair ever polls the weight barriers
-            const uint32_t ph = (q[tl] / NSLOTS) & 1;
-            if (!mbar_test(bar_full + 8 * slot, ph) || !mbar_test_cluster(bar_peer_full + 8 * slot, ph)) continue;
-            landed_q = q[tl] + 1;
-          }
-          tc_fence_after();
-          if (elect_one()) {
-            const uint32_t* alo = s_alo + e.z;
-            const uint32_t a_tile = (uint32_t)tl * (uint32_t)(kActBytes >> 4);
-            const uint32_t b_lo0 = (ring_lo + slot * (uint32_t)(Cfg::kSlot >> 4)) | e.y;
-            const uint32_t b_step = (e.w >> 8) & 0xFFFFu;
-            const int nst = (int)(e.w & 0xFFu);
-            if (!dbg_no_mma) {
-              for (int sl = 0; sl < nst; ++sl)
-                umma_bf16_2cta(tmem_base + (uint32_t)tl * 256u, mk64(alo[sl] + a_tile, kHi), mk64(b_lo0 + (uint32_t)sl * b_step, kHi),
-                               e.x, (first && sl == 0) ? 0u : 1u);
-            }
-            umma_commit_2cta(bar_empty + 8 * slot);            // one of the two arrivals that free the slot
-            if (last) umma_commit_2cta(bar_acc + 8 * tl);       // accumulator of this tile-pair complete (both CTAs)
-          }
-          __syncwarp();
-          ++q[tl];
-          if (last) { act_ok[tl] = false; ++n_act[tl]; }
-          if (++sidx[tl] == stages_per_group) { sidx[tl] = 0; --left[tl]; }
-          progressed = true;
-        }
-        if (progressed) { idle = 0; t0 = 0; }
-        else if ((++idle & 1023u) == 0u) {
-          const long long now = clock64();
-          if (t0 == 0) t0 = now;
-          else if (now - t0 > 4000000000ll) mbar_timeout(a.err_flag, 31);
+      // ---- leader: one MMA-issuer warp per tile-pair.  Both walk the same weight stream; they drift apart at layer
+      //      boundaries (one waits for its epilogue while the other keeps the tensor pipe busy), bounded by the ring.
+      uint32_t it = 0, n_act = 0;
+      const uint32_t tm = tmem_base + (uint32_t)tl * 256u;
+      const uint32_t a_tile = (uint32_t)tl * (uint32_t)(kActBytes >> 4);
+      const uint32_t b_acc = bar_acc + 8 * tl, b_act = bar_act + 8 * tl;
+      volatile uint32_t* progress = reinterpret_cast<volatile uint32_t*>(smem + Cfg::oMisc + 8);
+      const int role = (a.variant & 1) ? 1 + tl : 0;          // variant bit 0 enforces a lag between the tile-pairs (measured: no gain)
+      const uint32_t lag = (uint32_t)(NSLOTS / 3);
+      const long long my_units = pair_id < a.n_units ? (a.n_units - pair_id + n_pairs - 1) / n_pairs : 0;
+      const uint32_t total = (uint32_t)(my_units * a.n_groups * (long long)kStagesPerGroup);
+      for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
+        for (int g = 0; g < a.n_groups; ++g) {
+          issue_layer_pair<0, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile, progress, role, lag, total);
+          issue_layer_pair<1, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile, progress, role, lag, total);
+          issue_layer_pair<2, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile, progress, role, lag, total);
+          issue_layer_pair<3, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile, progress, role, lag, total);
+          issue_layer_pair<4, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile, progress, role, lag, total);
+          issue_layer_pair<5, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile, progress, role, lag, total);
         }
       }
-    } else if (lane == 0) {
-      // ---- peer: relay "my half of stage q has landed" to the leader, in stream order
-      const uint32_t r_peer_full = mapa_shared(bar_peer_full, 0);
+    } else if (warp == 1 && lane == 0) {
+      // ---- peer: relay "my half of stage q has landed" to the leader's full barriers, in stream order
+      const uint32_t r_full = mapa_shared(bar_full, 0);
       uint32_t it = 0;
       for (long long unit = pair_id; unit < a.n_units; unit += n_pairs)
         for (int g = 0; g < a.n_groups; ++g)
@@ -1436,13 +1362,13 @@ fused_pair2_kernel(const FusedArgs a) {
             for (int st = 0; st < ns; ++st, ++it) {
               const int slot = it % NSLOTS;
               mbar_wait2(bar_full + 8 * slot, (it / NSLOTS) & 1, a.err_flag, 23);
-              mbar_arrive_remote(r_peer_full + 8 * slot);
+              mbar_arrive_remote(r_full + 8 * slot);
             }
           }
     }
   } else {
     // ---- epilogue: 8 warps per tile
-    const int ew = warp - 2;
+    const int ew = warp - Cfg::kCtrlWarps;
     EpiCtx c;
     c.tl = ew >> 3;
     c.we = ew & 7;
@@ -1460,7 +1386,7 @@ fused_pair2_kernel(const FusedArgs a) {
     c.zp = zpart + c.tl * 8;
     c.bar_acc = bar_acc + 8 * c.tl;
     c.bar_act = bar_act + 8 * c.tl;
-    c.remote_act = rank == 0 ? 0u : mapa_shared(bar_peer_act + 8 * c.tl, 0);
+    c.remote_act = rank == 0 ? 0u : mapa_shared(bar_act + 8 * c.tl, 0);
     c.k0 = a.k0; c.k1 = a.k1;
     c.err_flag = a.err_flag;
     uint32_t n_acc = 0;
