@@ -93,6 +93,21 @@ int uqk_calibrate(uqk_handle* h, const void* x_dev, int x_dtype, int64_t n_windo
 int uqk_get_bn_stats(uqk_handle* h, float* mean_host, float* var_host);
 int uqk_set_bn_stats(uqk_handle* h, const float* mean_host, const float* var_host);
 
+/* Exact batch-statistic BatchNorm over windows that are sharded across GPUs ("the exception").
+ * Keras normalises `model(x, training=True)` (uq_techniques.py:22) with the statistics of the WHOLE call, so when
+ * the windows of one call live on several GPUs every layer of every pass needs the per-channel sums of all ranks.
+ * With an exchange installed, every UQK_BN_BATCH pass of this handle (uqk_mcd with UQK_PREC_FP32, uqk_calibrate)
+ * calls, once per layer and on the host thread of that call,
+ *       fn(user, stats_dev, count, stream)
+ * after the layer's convolution has been enqueued: stats_dev holds count = 2*Cout int64 values on the device
+ * ((sum, sum of squares) per channel in 2^-24 fixed point) and fn must enqueue on `stream` an in-place SUM
+ * all-reduce over the ranks (e.g. ncclAllReduce(ncclInt64, ncclSum) / torch.distributed.all_reduce) and return 0.
+ * Integer sums are order-independent, so the sharded result is bit-identical to one GPU holding all windows.
+ * global_windows = number of windows of the whole call (the divisor of the statistics); every rank must make the
+ * same sequence of calls, including ranks whose shard is empty.  fn == NULL removes the exchange. */
+typedef int (*uqk_stats_exchange_fn)(void* user, long long* stats_dev, int count, void* stream);
+int uqk_set_stats_exchange(uqk_handle* h, uqk_stats_exchange_fn fn, void* user, int64_t global_windows);
+
 /* MC-Dropout: n_passes stochastic passes of member 0 over all windows + the per-window reductions.
  * Replaces mc_dropout_predict (uq_techniques.py:12-24) fused with uq_evaluation_dist (:40-112).
  *   seed              Philox4x32-10 key; masks are a pure function of (seed, window_index_base + n, pass,

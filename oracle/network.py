@@ -42,7 +42,8 @@ def _conv1d_same(x: np.ndarray, w: np.ndarray, b: np.ndarray) -> np.ndarray:
 
 def forward_f64(weights: Sequence[np.ndarray], x: np.ndarray, training: bool = False,
                 masks: Optional[List[np.ndarray]] = None, bn_mode: Optional[str] = None,
-                bn_stats: Optional[List] = None, return_stats: bool = False, return_acts: bool = False):
+                bn_stats: Optional[List] = None, return_stats: bool = False, return_acts: bool = False,
+                stats_exchange=None, global_windows: Optional[int] = None):
     """One forward pass of all N windows as ONE batch.
 
     training=False : BN uses moving statistics, dropout is the identity (uq_techniques.py:29,
@@ -51,6 +52,9 @@ def forward_f64(weights: Sequence[np.ndarray], x: np.ndarray, training: bool = F
                      batch mean / biased variance over axes (N, L) (uq_techniques.py:22) unless
                      ``bn_mode='inference'`` (frozen moving stats) or ``bn_stats`` (list of six
                      (mean, var) pairs, the calibrated mode) overrides it.
+    stats_exchange : host model of windows sharded over ranks (exact batch statistics): a callable
+                     ``(sum, sum_sq) -> (sum, sum_sq)`` over all ranks; ``x`` is then this rank's shard and
+                     ``global_windows`` the window count of the whole call.
     Returns probabilities (N, 1) float64 (and the per-layer batch (mean, var) if return_stats).
     """
     a = np.asarray(x, dtype=np.float64)
@@ -63,6 +67,11 @@ def forward_f64(weights: Sequence[np.ndarray], x: np.ndarray, training: bool = F
         a = np.maximum(_conv1d_same(a, w, b), 0.0)                       # Conv1D + ReLU
         if bn_stats is not None:
             mu, var = bn_stats[i]
+        elif bn_mode == "batch" and stats_exchange is not None:
+            ssum, ssq = stats_exchange(a.sum(axis=(0, 1)), (a * a).sum(axis=(0, 1)))
+            cnt = float(global_windows) * a.shape[1]
+            mu = ssum / cnt
+            var = np.maximum(ssq / cnt - mu * mu, 0.0)                    # biased, from the exchanged moments
         elif bn_mode == "batch":
             mu = a.mean(axis=(0, 1))
             var = a.var(axis=(0, 1))                                      # biased

@@ -57,3 +57,40 @@ def test_gather_metrics_world2_gloo(tmp_path):
         got = torch.load(os.path.join(str(tmp_path), f"rank{r}.pt"))
         assert torch.equal(got["mean_pred"], want_mean)
         assert torch.equal(got["label"], want_label)
+
+
+def _bn_worker(rank, world, port, n, tmp):
+    """Exact batch-statistic MC-Dropout pass with the windows sharded over `world` ranks: every layer's moments go
+    through sharding.StatsExchange (int64 fixed point, gloo all-reduce); the float64 oracle does the arithmetic."""
+    import sys
+    sys.path.insert(0, ROOT)
+    sh = importlib.import_module(PKG_NAME + ".sharding")
+    pkg = importlib.import_module(PKG_NAME)
+    from oracle import network, philox
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    x = pkg.synthetic.make_windows(n, seed=11)
+    w = pkg.synthetic.make_member_weights(0)
+    s, e = [(0, 0), (0, n)][rank] if n < 4 else sh.window_shards(n, world)[rank]      # n < 4: rank 0 holds nothing
+    masks = [philox.dropout_keep_mask(77, np.arange(s, e), 0, i, b.cout, b.rate) for i, b in enumerate(pkg.arch.BLOCKS)]
+    ex = sh.StatsExchange()
+    p = network.forward_f64(w, x[s:e], training=True, masks=masks, stats_exchange=ex.exchange_moments, global_windows=n)
+    assert ex.calls == len(pkg.arch.BLOCKS)
+    np.save(os.path.join(tmp, f"p{rank}.npy"), p[:, 0])
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n,port", [(12, 29541), (3, 29543)])
+def test_exact_batch_stats_exchange_world2_gloo(uqk, tmp_path, n, port):
+    from oracle import network, philox
+    mp.spawn(_bn_worker, args=(2, port, n, str(tmp_path)), nprocs=2, join=True)
+    x = uqk.synthetic.make_windows(n, seed=11)
+    w = uqk.synthetic.make_member_weights(0)
+    masks = [philox.dropout_keep_mask(77, np.arange(n), 0, i, b.cout, b.rate) for i, b in enumerate(uqk.arch.BLOCKS)]
+    want = network.forward_f64(w, x, training=True, masks=masks)[:, 0]          # one rank holding all windows
+    got = np.concatenate([np.load(os.path.join(str(tmp_path), f"p{r}.npy")) for r in range(2)])
+    assert got.shape == want.shape
+    # the exchanged moments are quantised to 2^-24 per rank and the variance comes from E[x^2]-mu^2
+    assert np.abs(got - want).max() < 1e-6

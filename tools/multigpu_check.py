@@ -1,7 +1,8 @@
 #!/usr/bin/env python
 """N>1 invariance on real GPUs (torchrun, one rank per GPU): the sharded MC-Dropout result gathered over NCCL must be
 bit-identical to the same call on one GPU (masks keyed by global window index, statistics calibrated on the same
-global windows).  Prints one JSON line on rank 0."""
+global windows).  Also checks exact batch-statistic BatchNorm with the per-layer statistics all-reduced over NCCL
+(sharding.StatsExchange) against one GPU holding all windows.  Prints one JSON line on rank 0."""
 import importlib, json, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
@@ -32,6 +33,16 @@ def main():
         single = uq.mc_dropout_uq(model, x, n_pred=12, seed=77, bn_mode="calibrated", recalibrate=False)
         res["identical"] = {k: bool(np.array_equal(full[k], single[k])) for k in single if single[k] is not None and k in full}
         res["all_identical"] = all(res["identical"].values())
+    # exact batch statistics: sharded + all-reduced vs one GPU (fp32 layer-synchronous path, smaller problem)
+    nb = min(n, 3000)
+    xb, pb = x[:nb], pid[:nb]
+    fullb = sh.sharded_mc_dropout_uq(uq, model, xb, n_pred=3, patient_ids=pb, seed=78, bn_mode="batch")
+    if rank == 0:
+        singleb = uq.mc_dropout_uq(model, xb, n_pred=3, seed=78, bn_mode="batch")
+        res["batch_windows"] = nb
+        res["batch_identical"] = {k: bool(np.array_equal(fullb[k], singleb[k])) for k in singleb
+                                  if singleb[k] is not None and k in fullb}
+        res["batch_all_identical"] = all(res["batch_identical"].values())
         print(json.dumps(res), flush=True)
     if world > 1:
         dist.barrier()

@@ -43,6 +43,10 @@ struct Handle {
   float* d_dbg = nullptr;         // 6 x 128 x 256 debug dump of the fused kernel (tests)
   int variant = 0;
   int dbg_dump = 0;
+  // cross-rank exchange of batch statistics (uqk_set_stats_exchange)
+  uqk_stats_exchange_fn xchg = nullptr;
+  void* xchg_user = nullptr;
+  int64_t xchg_global_n = 0;
 };
 
 static int ensure(float** p, size_t* cap, size_t need_floats) {
@@ -76,8 +80,9 @@ static int check_x(const void* x, int dtype, int64_t n) {
 static int run_layersync(Handle* h, int member0, const void* x, int x_dtype, int64_t n, int n_groups, bool de, bool dropout,
                          int bn_mode, uint64_t seed, int64_t window_base, const uint32_t* mask_bits, float* probs,
                          double* accum_mean, double* accum_var, cudaStream_t s) {
-  if (n == 0) return UQK_OK;
-  const int64_t chunk = bn_mode == UQK_BN_BATCH ? n : std::min<int64_t>(n, 16384);
+  const bool exchanging = bn_mode == UQK_BN_BATCH && h->xchg != nullptr;
+  if (n == 0 && !exchanging) return UQK_OK;   // an empty shard still takes part in every exchange of the call
+  const int64_t chunk = bn_mode == UQK_BN_BATCH ? std::max<int64_t>(n, 1) : std::min<int64_t>(n, 16384);
   int rc;
   if ((rc = ensure(&h->d_x32, &h->x32_cap, (size_t)n * kL * kF))) return rc;
   size_t cap0 = h->act_cap, cap1 = h->act_cap;
@@ -86,7 +91,7 @@ static int run_layersync(Handle* h, int member0, const void* x, int x_dtype, int
   h->act_cap = std::min(cap0, cap1);
   if ((rc = ls_cast_input(x, x_dtype, h->d_x32, n, s))) return rc;
   for (int g = 0; g < n_groups; ++g) {
-    for (int64_t c0 = 0; c0 < n; c0 += chunk) {
+    for (int64_t c0 = 0; c0 < std::max<int64_t>(n, 1); c0 += chunk) {
       const int64_t cn = std::min(chunk, n - c0);
       LsPassParams p{};
       p.blob_dev = h->d_blobs + (size_t)(member0 + (de ? g : 0)) * kBlobStride;
@@ -99,6 +104,7 @@ static int run_layersync(Handle* h, int member0, const void* x, int x_dtype, int
       p.stats_scratch = h->d_stats; p.affine_scratch = h->d_affine;
       p.accum_mean = accum_mean; p.accum_var = accum_var;
       p.probs_out = probs + (size_t)g * n + c0;
+      if (exchanging) { p.exchange = h->xchg; p.exchange_user = h->xchg_user; p.global_n = h->xchg_global_n; }
       if ((rc = ls_forward_pass(p, s))) return rc;
     }
   }
@@ -291,6 +297,18 @@ int uqk_set_bn_stats(uqk_handle* hh, const float* mean_host, const float* var_ho
   UQK_CUDA(cudaMemcpy(h->d_frozen, mean_host, sizeof(float) * kBlocks * kMaxCh, cudaMemcpyHostToDevice));
   UQK_CUDA(cudaMemcpy(h->d_frozen + kBlocks * kMaxCh, var_host, sizeof(float) * kBlocks * kMaxCh, cudaMemcpyHostToDevice));
   h->have_frozen = true;
+  return UQK_OK;
+}
+
+int uqk_set_stats_exchange(uqk_handle* hh, uqk_stats_exchange_fn fn, void* user, int64_t global_windows) {
+  if (!hh) { set_error("handle is NULL"); return UQK_E_BADARG; }
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  if (fn != nullptr && global_windows < 1) {
+    set_error("global_windows must be >= 1 (the window count of the whole call over all ranks), got %lld",
+              (long long)global_windows);
+    return UQK_E_BADARG;
+  }
+  h->xchg = fn; h->xchg_user = fn ? user : nullptr; h->xchg_global_n = fn ? global_windows : 0;
   return UQK_OK;
 }
 

@@ -24,6 +24,10 @@ struct LsPassParams {
   double* accum_mean;         // optional 6 x 256 doubles: += batch mean (calibration)
   double* accum_var;
   float* probs_out;           // (n,)
+  // cross-rank exchange of the batch statistics (uqk_set_stats_exchange); null = this rank holds the whole batch
+  int (*exchange)(void* user, long long* stats_dev, int count, void* stream);
+  void* exchange_user;
+  int64_t global_n;           // windows of the whole call over all ranks (divisor of the statistics) when exchanging
 };
 int ls_cast_input(const void* x, int x_dtype, float* out, int64_t n_windows, cudaStream_t s);
 int ls_forward_pass(const LsPassParams& p, cudaStream_t s);

@@ -201,6 +201,7 @@ static int launch_conv(const float* in, const float* w, const float* b, float* o
   if (smem > 48 * 1024)
     UQK_CUDA(cudaFuncSetAttribute(conv_relu_kernel<CIN, COUT, K>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)smem));
+  if (n == 0) return UQK_OK;   // empty shard of a multi-GPU call: nothing to convolve, statistics stay zero
   const int grid = (int)std::min<int64_t>(n, 148 * 64);
   conv_relu_kernel<CIN, COUT, K><<<grid, kConvThreads, smem, s>>>(in, w, b, out, stats, n);
   UQK_LAUNCH_CHECK();
@@ -247,12 +248,21 @@ int ls_forward_pass(const LsPassParams& p, cudaStream_t s) {
     }
     int rc = launch_conv_layer(l, in, blob + off.conv_w[l], blob + off.conv_b[l], out, stats, p.n, s);
     if (rc) return rc;
+    int64_t stat_windows = p.n;
+    if (stats != nullptr && p.exchange != nullptr) {
+      // sum the fixed-point (sum, sum of squares) over the ranks that hold the other windows of this call
+      if (p.exchange(p.exchange_user, reinterpret_cast<long long*>(stats), 2 * b.cout, static_cast<void*>(s)) != 0) {
+        set_error("batch-statistics exchange callback failed at layer %d, pass %d", l, p.pass);
+        return UQK_E_STATE;
+      }
+      stat_windows = p.global_n;
+    }
     const float inv_keep = p.dropout ? 1.0f / (1.0f - b.rate) : 1.0f;
     float* scale = p.affine_scratch + (size_t)l * kMaxCh * 2;
     float* shift = scale + kMaxCh;
     const int tb = 128, gb = (b.cout + tb - 1) / tb;
     if (p.bn_mode == UQK_BN_BATCH) {
-      bn_finalize_kernel<<<gb, tb, 0, s>>>(stats, (double)p.n * kL, blob + off.gamma[l], blob + off.beta[l], inv_keep,
+      bn_finalize_kernel<<<gb, tb, 0, s>>>(stats, (double)stat_windows * kL, blob + off.gamma[l], blob + off.beta[l], inv_keep,
                                            b.cout, scale, shift,
                                            p.accum_mean ? p.accum_mean + (size_t)l * kMaxCh : nullptr,
                                            p.accum_var ? p.accum_var + (size_t)l * kMaxCh : nullptr);
@@ -263,16 +273,18 @@ int ls_forward_pass(const LsPassParams& p, cudaStream_t s) {
                                          shift);
     }
     UQK_LAUNCH_CHECK();
-    const int64_t total = p.n * kL * (b.cout / 8);
-    const int grid = (int)std::min<int64_t>((total + 255) / 256, 148 * 32);
-    bn_dropout_kernel<<<grid, 256, 0, s>>>(out, scale, shift, b.cout, p.n, l, p.dropout ? 1 : 0,
-                                           (uint32_t)(p.seed & 0xFFFFFFFFull), (uint32_t)(p.seed >> 32),
-                                           (uint32_t)p.pass, p.window_base, p.mask_bits);
-    UQK_LAUNCH_CHECK();
+    if (p.n > 0) {
+      const int64_t total = p.n * kL * (b.cout / 8);
+      const int grid = (int)std::min<int64_t>((total + 255) / 256, 148 * 32);
+      bn_dropout_kernel<<<grid, 256, 0, s>>>(out, scale, shift, b.cout, p.n, l, p.dropout ? 1 : 0,
+                                             (uint32_t)(p.seed & 0xFFFFFFFFull), (uint32_t)(p.seed >> 32),
+                                             (uint32_t)p.pass, p.window_base, p.mask_bits);
+      UQK_LAUNCH_CHECK();
+    }
     in = out;
     cur ^= 1;
   }
-  {
+  if (p.n > 0) {
     const int64_t threads = p.n * 32;
     const int grid = (int)std::min<int64_t>((threads + 255) / 256, 148 * 32);
     head_kernel<<<grid, 256, 0, s>>>(in, blob + off.dense_w, blob + off.dense_b, p.probs_out, p.n);

@@ -25,6 +25,18 @@ def _require_cuda():
         raise _lib.UqkError("no CUDA device: this package runs on B200 (sm_100a) only and has no CPU fallback")
 
 
+class _DevicePtr:
+    """Minimal ``__cuda_array_interface__`` carrier so torch can alias memory owned by libuqk (no copy)."""
+
+    def __init__(self, ptr: int, count: int):
+        self.__cuda_array_interface__ = {"shape": (int(count),), "typestr": "<i8", "data": (int(ptr), False),
+                                         "version": 2, "strides": None}
+
+
+def _device_view_i64(ptr: int, count: int, device: int) -> "torch.Tensor":
+    return torch.as_tensor(_DevicePtr(ptr, count), device=torch.device("cuda", device))
+
+
 class Engine:
     """One engine per GPU (wraps one ``uqk_handle``).  Not thread-safe."""
 
@@ -38,6 +50,8 @@ class Engine:
         self.n_members = 0
         self._model_key = None
         self.calibrated = False
+        self._xchg_cb = None
+        self._xchg_error = None
 
     def close(self):
         if getattr(self, "_h", None):
@@ -145,6 +159,33 @@ class Engine:
                                               C.c_uint64(seed & (2 ** 64 - 1)), self._stream()), "uqk_calibrate")
             self.calibrated = True
 
+    def set_stats_exchange(self, reduce_fn, global_windows: int = 0):
+        """Installs (``reduce_fn`` callable) or removes (``None``) the cross-rank exchange of the batch statistics
+        (include/uqk.h ``uqk_set_stats_exchange``).  ``reduce_fn(t)`` receives a 1-D int64 CUDA tensor aliasing the
+        library's (sum, sum of squares) accumulators of one layer and must SUM-all-reduce it in place over the ranks
+        on the current stream (``torch.distributed.all_reduce`` does).  ``global_windows`` = windows of the whole call."""
+        if reduce_fn is None:
+            _lib.check(self.lib.uqk_set_stats_exchange(self._h, C.cast(None, _lib.STATS_EXCHANGE_FN), None, 0), "uqk_set_stats_exchange")
+            self._xchg_cb = None
+            return
+        dev = self.device
+        self._xchg_error = None
+
+        def _cb(_user, ptr, count, stream):
+            try:
+                cur = torch.cuda.current_stream(dev).cuda_stream
+                if (stream or 0) != cur:
+                    raise RuntimeError("the exchange must run on the stream the pass was enqueued on")
+                reduce_fn(_device_view_i64(ptr, count, dev))
+                return 0
+            except Exception as e:       # never let an exception cross the C boundary
+                self._xchg_error = e
+                return 1
+
+        cb = _lib.STATS_EXCHANGE_FN(_cb)
+        _lib.check(self.lib.uqk_set_stats_exchange(self._h, cb, None, int(global_windows)), "uqk_set_stats_exchange")
+        self._xchg_cb = cb               # keep the ctypes thunk alive while the library holds its address
+
     def get_bn_stats(self):
         mean = np.empty((arch.N_BLOCKS, arch.MAX_CH), dtype=np.float32)
         var = np.empty_like(mean)
@@ -175,11 +216,15 @@ class Engine:
                 if tuple(mt.shape) != (n_passes, n, arch.N_BLOCKS, arch.WINDOW_LEN, 8):
                     raise ValueError(f"masks must have shape (T,N,6,60,8), got {tuple(mt.shape)}")
                 mt = mt.to(self._dev()).contiguous()
-            _lib.check(self.lib.uqk_mcd(self._h, xt.data_ptr(), dt, n, int(n_passes), C.c_uint64(seed & (2 ** 64 - 1)),
-                                        _BN[bn_mode], _PREC[precision], int(window_base),
-                                        mt.data_ptr() if mt is not None else None,
-                                        probs.data_ptr() if probs is not None else None,
-                                        C.byref(mo) if bufs else None, self._stream()), "uqk_mcd")
+            rc = self.lib.uqk_mcd(self._h, xt.data_ptr(), dt, n, int(n_passes), C.c_uint64(seed & (2 ** 64 - 1)),
+                                  _BN[bn_mode], _PREC[precision], int(window_base),
+                                  mt.data_ptr() if mt is not None else None,
+                                  probs.data_ptr() if probs is not None else None,
+                                  C.byref(mo) if bufs else None, self._stream())
+            if rc != 0 and getattr(self, "_xchg_error", None) is not None:
+                err, self._xchg_error = self._xchg_error, None
+                raise RuntimeError("batch-statistics exchange failed") from err
+            _lib.check(rc, "uqk_mcd")
             return self._finish(bufs, probs, device_out)
 
     def de(self, x, n_members: Optional[int] = None, precision: str = "bf16", return_probs: bool = False,

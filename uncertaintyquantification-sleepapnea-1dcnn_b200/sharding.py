@@ -66,16 +66,62 @@ def gather_metrics(local: Dict[str, torch.Tensor], shards: List[Tuple[int, int]]
     return out
 
 
+STAT_SCALE = float(1 << 24)   # fixed point of the batch-statistic accumulators (csrc/layersync.cu kStatScale)
+
+
+class StatsExchange:
+    """The one real exchange step of the path ("the exception"): exact batch-statistic BatchNorm
+    (Keras ``training=True``, uq_techniques.py:22) normalises with the statistics of ALL windows of the call, so with
+    the windows sharded every layer of every pass SUM-all-reduces its per-channel (sum, sum of squares).  The sums
+    travel as int64 fixed point (2^-24): integer addition is associative, so the result does not depend on the number
+    of ranks or on the reduction order.  Called by the library through ``Engine.set_stats_exchange`` with a CUDA
+    tensor (NCCL); the gloo test calls it with CPU tensors."""
+
+    def __init__(self, group=None):
+        self.group = group
+        self.calls = 0
+
+    def __call__(self, t: torch.Tensor) -> torch.Tensor:
+        if t.dtype != torch.int64:
+            raise TypeError("batch statistics are exchanged as int64 fixed point")
+        self.calls += 1
+        if _world(self.group)[1] > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+        return t
+
+    # host model of what the library does around the exchange (used by the CPU tests with the float64 oracle)
+    def exchange_moments(self, ssum: np.ndarray, ssq: np.ndarray):
+        """(sum, sum of squares) per channel of this rank's windows -> the same over all ranks, via fixed point."""
+        q = torch.from_numpy(np.concatenate([np.rint(np.asarray(ssum, np.float64) * STAT_SCALE),
+                                             np.rint(np.asarray(ssq, np.float64) * STAT_SCALE)]).astype(np.int64))
+        q = self(q).numpy().astype(np.float64) / STAT_SCALE
+        c = len(q) // 2
+        return q[:c], q[c:]
+
+
 def sharded_mc_dropout_uq(uq_module, model, x, n_pred: int = 50, patient_ids=None, seed: Optional[int] = None,
                           bn_mode: str = "calibrated", calib_windows: int = 4096, group=None, **kw) -> Dict[str, np.ndarray]:
-    """Each rank runs the fused MC-Dropout path on its shard of ``x`` (host array, identical on all ranks) and the
-    per-window metrics are gathered on every rank.  The calibrated BatchNorm statistics are estimated by every rank on
-    the SAME global windows ``x[:calib_windows]`` and the dropout masks are keyed by the global window index, so the
-    gathered result is bit-identical to a single-GPU run."""
+    """Each rank runs the MC-Dropout path on its shard of ``x`` (host array, identical on all ranks) and the
+    per-window metrics are gathered on every rank.  The dropout masks are keyed by the global window index.
+    ``bn_mode='calibrated'``: every rank estimates the frozen statistics on the SAME global windows
+    ``x[:calib_windows]`` (no data-path collective).  ``bn_mode='batch'``: exact Keras semantics -- the per-layer
+    statistics are all-reduced over the ranks (``StatsExchange``).  Either way the gathered result is bit-identical
+    to a single-GPU run over all of ``x``."""
     rank, world = _world(group)
     n = len(x)
     shards = patient_aligned_shards(patient_ids, world) if patient_ids is not None else window_shards(n, world)
     s, e = shards[rank]
+    if bn_mode == "batch":
+        uq_module.mc_dropout_uq(model, x[:0], n_pred=1, seed=seed, bn_mode="inference")   # uploads the model
+        eng = uq_module._engine.get_engine()
+        eng.set_stats_exchange(StatsExchange(group), global_windows=n)
+        try:
+            out = uq_module.mc_dropout_uq(model, x[s:e], n_pred=n_pred, seed=seed, bn_mode="batch", device_out=True,
+                                          window_base=s, **kw)
+        finally:
+            eng.set_stats_exchange(None)
+        local = {k: v for k, v in out.items() if isinstance(v, torch.Tensor)}
+        return {k: v.cpu().numpy() for k, v in gather_metrics(local, shards, group).items()}
     if bn_mode == "calibrated":
         uq_module.mc_dropout_uq(model, x[:min(n, calib_windows)][:0], n_pred=1, seed=seed, bn_mode="inference")  # uploads the model
         uq_module._engine.get_engine().calibrate(x, n_windows=calib_windows, n_passes=2,
