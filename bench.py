@@ -263,6 +263,17 @@ def main():
         de_info = {"metric": "uq_windows_per_sec_de_M10", "value": nd / (ms_de * 1e-3), "windows": nd,
                    "tflops_valid": nd * 10 * FLOP_VALID / (ms_de * 1e-3) / 1e12}
 
+    # ---- secondary: the same MC-Dropout workload with EXACT batch-statistic BatchNorm (Keras training=True semantics:
+    # six statistics sweeps + the final run of the tensor-core kernel), device-resident, on a quarter of the windows
+    exact_info = None
+    if world == 1:
+        ne = min(n, 250_000)
+        run_exact = lambda: uq.mc_dropout_uq(model, x_dev[:ne], n_pred=T, seed=seed, bn_mode="batch", device_out=True)
+        run_exact()
+        ms_ex, _ = timed(run_exact, 1)
+        exact_info = {"metric": "uq_windows_per_sec_mcd_T%d_exact_batch_bn" % T, "value": ne / (ms_ex * 1e-3), "windows": ne,
+                      "kernel_runs_per_step": 7, "flops_vs_one_run": 3.67}
+
     cpu = None
     if rank == 0 and world == 1 and args.cpu_sample > 0:
         v, dt, cores = cpu_mcd_sample(args.cpu_sample, T)
@@ -279,7 +290,7 @@ def main():
                            "rng": "Philox4x32-10 in-kernel", "input": "float64 (N,60,4), 1.92 GB per GPU > L2, no L2 flush needed",
                            "unique_windows": n_unique, "collective": "nccl all_gather of per-window metrics" if world > 1 else "none"},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
-                "also": de_info}
+                "also": de_info, "also_exact_bn": exact_info}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -42,7 +42,10 @@ extern "C" {
 /* BatchNormalization statistics used by the stochastic (training=True) passes */
 #define UQK_BN_INFERENCE 0  /* moving statistics (frozen BN; what model.predict uses, uq_techniques.py:29) */
 #define UQK_BN_BATCH 1      /* exact Keras training=True semantics: batch mean / biased variance over (N,L) of the
-                               whole call, per pass (uq_techniques.py:22); layer-synchronous fp32 path */
+                               whole call, per pass (uq_techniques.py:22).  UQK_PREC_FP32: layer-synchronous kernels
+                               (activations of the call in HBM).  UQK_PREC_BF16_TC: the fused kernel is swept once
+                               per layer to collect that layer's statistics of every pass, then run normally
+                               (3.67x the flops of one run, no activation traffic) */
 #define UQK_BN_CALIBRATED 2 /* batch statistics estimated once by uqk_calibrate() and frozen for all passes */
 
 /* arithmetic of the forward passes */
@@ -96,11 +99,13 @@ int uqk_set_bn_stats(uqk_handle* h, const float* mean_host, const float* var_hos
 /* Exact batch-statistic BatchNorm over windows that are sharded across GPUs ("the exception").
  * Keras normalises `model(x, training=True)` (uq_techniques.py:22) with the statistics of the WHOLE call, so when
  * the windows of one call live on several GPUs every layer of every pass needs the per-channel sums of all ranks.
- * With an exchange installed, every UQK_BN_BATCH pass of this handle (uqk_mcd with UQK_PREC_FP32, uqk_calibrate)
- * calls, once per layer and on the host thread of that call,
+ * With an exchange installed, every UQK_BN_BATCH computation of this handle (uqk_mcd, uqk_calibrate) calls, on the
+ * host thread of that call,
  *       fn(user, stats_dev, count, stream)
- * after the layer's convolution has been enqueued: stats_dev holds count = 2*Cout int64 values on the device
- * ((sum, sum of squares) per channel in 2^-24 fixed point) and fn must enqueue on `stream` an in-place SUM
+ * after a layer's statistics have been enqueued -- once per layer and pass with count = 2*Cout on the
+ * layer-synchronous path, once per layer with count = n_passes*512 on the swept tensor-core path.  stats_dev holds
+ * `count` int64 values on the device ((sum, sum of squares) per channel in 2^-24 fixed point) and fn must enqueue on
+ * `stream` an in-place SUM
  * all-reduce over the ranks (e.g. ncclAllReduce(ncclInt64, ncclSum) / torch.distributed.all_reduce) and return 0.
  * Integer sums are order-independent, so the sharded result is bit-identical to one GPU holding all windows.
  * global_windows = number of windows of the whole call (the divisor of the statistics); every rank must make the

@@ -96,6 +96,26 @@ def test_predict_functions_shapes_and_semantics(uq, uqk):
     assert fused["mean_variance_class_1"] == 0.0
 
 
+def test_mc_dropout_predict_keeps_exact_semantics_above_the_fp32_limit(uq, uqk, monkeypatch):
+    """`mc_dropout_predict` in its default mode always normalises with the statistics of the whole call
+    (uq_techniques.py:22): fp32 kernels for small calls, the swept tensor-core kernel above the limit."""
+    model = importlib.import_module(PKG_NAME + ".model")
+    n = 70
+    x = uqk.synthetic.make_windows(n, seed=17)
+    m0 = model.UQModel(members()[0])
+    monkeypatch.setenv("UQK_SEED", "123")
+    with contextlib.redirect_stdout(io.StringIO()):
+        small = uq.mc_dropout_predict(m0, x, n_pred=2)                     # n <= limit: fp32 layer-synchronous
+        monkeypatch.setenv("UQK_EXACT_MAX_WINDOWS", "16")
+        big = uq.mc_dropout_predict(m0, x, n_pred=2)                       # n > limit: bf16 sweeps, same semantics
+    assert small.shape == big.shape == (2, n, 1)
+    d = np.abs(small - big)
+    assert 0 < d.max() < 4e-2 and d.mean() < 5e-3
+    from gpu_common import twin_masks
+    ref = np.stack([network.forward_f64(members()[0], x, training=True, masks=twin_masks(123, n, t)) for t in range(2)])
+    assert np.abs(small - ref).max() < 1e-4 and np.abs(big - ref).max() < 4e-2
+
+
 def test_patient_reduce_matches_reference_script_output(golden_dir):
     patient = importlib.import_module(PKG_NAME + ".patient")
     df = pd.read_csv(os.path.join(golden_dir, "patient_detail_fixture.csv"))

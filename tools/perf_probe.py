@@ -25,15 +25,17 @@ def main():
             def run():
                 if mode == "mcd":
                     eng.mcd(x, n_passes=T, bn_mode="inference", device_out=True, metrics=("mean_pred",))
+                elif mode == "exact":     # exact batch-statistic BatchNorm: 6 statistics sweeps + the final run
+                    eng.mcd(x, n_passes=T, bn_mode="batch", device_out=True, metrics=("mean_pred",))
                 else:
                     eng.de(x, n_members=1, device_out=True, metrics=("mean_pred",))
             run(); torch.cuda.synchronize()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record(); run(); e1.record(); torch.cuda.synchronize()
             ms = e0.elapsed_time(e1)
-            passes = T if mode == "mcd" else 1
+            passes = T if mode in ("mcd", "exact") else 1
             tf = n * passes * 98844864 / (ms * 1e-3) / 1e12
-            res.append({"variant": v, "mode": mode, "ms": ms, "tflops": tf})
+            res.append({"variant": v, "mode": mode, "ms": ms, "tflops": tf, "windows_per_s": n / (ms * 1e-3)})
             print(json.dumps(res[-1]), flush=True)
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
     json.dump(res, open(os.path.join(ROOT, "gpurun_out", "perf_probe.json"), "w"), indent=1)

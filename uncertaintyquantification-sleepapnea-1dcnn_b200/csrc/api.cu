@@ -40,6 +40,8 @@ struct Handle {
   float* d_x32 = nullptr; size_t x32_cap = 0;
   float* d_act[2] = {nullptr, nullptr}; size_t act_cap = 0;
   float* d_probs_tmp = nullptr; size_t probs_cap = 0;
+  float* d_tables_pass = nullptr; size_t tables_pass_cap = 0;   // exact batch-statistic mode: one epilogue table per pass
+  float* d_stats_pass = nullptr; size_t stats_pass_cap = 0;     // ... and n_passes x 2 x 256 int64 statistics (as floats x2)
   float* d_dbg = nullptr;         // 6 x 128 x 256 debug dump of the fused kernel (tests)
   int variant = 0;
   int dbg_dump = 0;
@@ -140,6 +142,56 @@ static int run_fused(Handle* h, int member0, const void* x, int x_dtype, int64_t
   return want_metrics ? launch_reduce(probs, n_groups, n, out, s) : UQK_OK;
 }
 
+// Exact Keras `training=True` semantics on the tensor-core kernel (uq_techniques.py:22: BatchNormalization uses the
+// statistics of the whole call).  The statistics of layer k depend on the normalised output of layers < k over ALL
+// windows, so the passes are swept k = 1..6 times through layers [0, k) -- sweep k accumulates layer k's per-pass
+// (sum, sum of squares) with the earlier layers already normalised exactly -- and a 7th, ordinary run produces the
+// probabilities with all six layers' statistics in place.  Cost: 3.67x the flops of one run (layers are recomputed
+// instead of spilling N x T x 60 x Cout activations to HBM); all T passes share each sweep.
+static int run_fused_exact(Handle* h, const void* x, int x_dtype, int64_t n, int n_passes, uint64_t seed, int64_t window_base,
+                           const uint32_t* mask_bits, float* probs, const MetricsOut& out, bool want_metrics, cudaStream_t s) {
+  int rc;
+  if ((rc = ensure(&h->d_tables_pass, &h->tables_pass_cap, (size_t)n_passes * kTableFloats))) return rc;
+  if ((rc = ensure(&h->d_stats_pass, &h->stats_pass_cap, (size_t)n_passes * 2 * kMaxCh * 2))) return rc;
+  unsigned long long* stats = reinterpret_cast<unsigned long long*>(h->d_stats_pass);
+  // bias / dense rows of every pass's table; the scale / shift rows are filled layer by layer below
+  if ((rc = build_tables(h->d_blobs, nullptr, nullptr, 1, h->d_table_mcd, s))) return rc;
+  if ((rc = exact_replicate_tables(h->d_table_mcd, n_passes, h->d_tables_pass, s))) return rc;
+  const bool exchanging = h->xchg != nullptr;
+  const int64_t stat_windows = exchanging ? h->xchg_global_n : n;
+  if (stat_windows < 1) return UQK_OK;
+  const size_t pb = fused_packed_bytes();
+  FusedParams p{};
+  p.x = x; p.x_dtype = x_dtype; p.n = n; p.n_groups = n_passes; p.mode_de = 0; p.dropout = 1;
+  p.seed = seed; p.window_base = window_base; p.mask_bits = mask_bits;
+  p.packed = h->d_packed; p.packed_pair = h->d_packed_pair; (void)pb;
+  p.tables = h->d_tables_pass; p.tab_per_group = 1; p.err_flag = h->d_err; p.variant = h->variant;
+  for (int k = 0; k < kBlocks; ++k) {
+    UQK_CUDA(cudaMemsetAsync(stats, 0, sizeof(unsigned long long) * (size_t)n_passes * 2 * kMaxCh, s));
+    p.stats = stats; p.n_layers = k + 1;
+    if ((rc = fused_launch(p, s))) return rc;           // n == 0 (empty shard): no launch, statistics stay zero
+    if (exchanging &&
+        h->xchg(h->xchg_user, reinterpret_cast<long long*>(stats), n_passes * 2 * kMaxCh, static_cast<void*>(s)) != 0) {
+      set_error("batch-statistics exchange callback failed at layer %d", k);
+      return UQK_E_STATE;
+    }
+    if ((rc = exact_layer_tables(h->d_blobs, stats, (double)stat_windows * kL, k, n_passes, h->d_tables_pass, s))) return rc;
+  }
+  p.stats = nullptr; p.n_layers = 0;
+  p.dbg_act = h->dbg_dump ? h->d_dbg : nullptr;
+  if (n_passes <= kMaxFusedGroups) {
+    p.probs = probs; p.out = out;
+    return fused_launch(p, s);
+  }
+  if (!probs) {
+    if ((rc = ensure(&h->d_probs_tmp, &h->probs_cap, (size_t)n * n_passes))) return rc;
+    probs = h->d_probs_tmp;
+  }
+  p.probs = probs; p.out = MetricsOut{}; p.no_smem_probs = 1;
+  if ((rc = fused_launch(p, s))) return rc;
+  return want_metrics ? launch_reduce(probs, n_passes, n, out, s) : UQK_OK;
+}
+
 }  // namespace uqk
 
 using namespace uqk;
@@ -189,7 +241,7 @@ int uqk_destroy(uqk_handle* hh) {
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
   void* ptrs[] = {h->d_blobs, h->d_packed, h->d_packed_pair, h->d_tables_inf, h->d_table_mcd, h->d_frozen, h->d_stats, h->d_affine,
-                  h->d_accum, h->d_err, h->d_x32, h->d_act[0], h->d_act[1], h->d_probs_tmp, h->d_dbg};
+                  h->d_accum, h->d_err, h->d_x32, h->d_act[0], h->d_act[1], h->d_probs_tmp, h->d_dbg, h->d_tables_pass, h->d_stats_pass};
   for (void* p : ptrs) if (p) cudaFree(p);
   cudaGetLastError();
   delete h;
@@ -331,11 +383,9 @@ int uqk_mcd(uqk_handle* hh, const void* x_dev, int x_dtype, int64_t n, int n_pas
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const MetricsOut mo = to_metrics(out);
   if (precision == UQK_PREC_BF16_TC) {
-    if (bn_mode == UQK_BN_BATCH) {
-      set_error("exact batch-statistic BatchNorm couples all windows of a layer; it runs on the layer-synchronous "
-                "path only (precision = UQK_PREC_FP32). Use UQK_BN_CALIBRATED with the fused kernel.");
-      return UQK_E_BADARG;
-    }
+    if (bn_mode == UQK_BN_BATCH)
+      return run_fused_exact(h, x_dev, x_dtype, n, n_passes, seed, window_base, mask_bits_dev, probs_dev, mo,
+                             out != nullptr, s);
     const float* mean = bn_mode == UQK_BN_CALIBRATED ? h->d_frozen : nullptr;
     const float* var = bn_mode == UQK_BN_CALIBRATED ? h->d_frozen + kBlocks * kMaxCh : nullptr;
     if ((rc = build_tables(h->d_blobs, mean, var, 1, h->d_table_mcd, s))) return rc;

@@ -159,10 +159,50 @@ __global__ void build_tables_kernel(const float* __restrict__ blob, BlobOffsets 
   if (i == 0) table[3 * kChTotal + kDenseIn] = blob[off.dense_b];
 }
 
+constexpr double kFusedStatScale = 16777216.0;   // 2^24 fixed point of batch statistics, as in layersync.cu
+
 int build_tables(const float* blob_dev, const float* mean, const float* var, int fold_dropout, float* table_dev,
                  cudaStream_t s) {
   build_tables_kernel<<<(kChTotal + 127) / 128, 128, 0, s>>>(blob_dev, blob_offsets(), mean, var, fold_dropout,
                                                              table_dev);
+  UQK_LAUNCH_CHECK();
+  return UQK_OK;
+}
+
+// Exact batch-statistic mode: after the statistics sweep of `layer`, turn the fixed-point (sum, sum of squares) of every
+// pass g into that pass's BatchNorm affine (dropout scale folded) inside its epilogue table.  Same arithmetic as
+// bn_finalize_kernel of the layer-synchronous path.  grid = n_groups, block >= cout.
+__global__ void exact_layer_tables_kernel(const float* __restrict__ blob, BlobOffsets off,
+                                          const unsigned long long* __restrict__ stats, double count, int layer,
+                                          float* __restrict__ tables) {
+  const int g = blockIdx.x, c = threadIdx.x;
+  const BlockDef b = block_def(layer);
+  if (c >= b.cout) return;
+  const long long* q = reinterpret_cast<const long long*>(stats) + (size_t)g * 2 * kMaxCh;
+  const double mu = (double)q[2 * c] / kFusedStatScale / count;
+  double var = (double)q[2 * c + 1] / kFusedStatScale / count - mu * mu;   // biased variance (Keras training mode)
+  if (var < 0) var = 0;
+  const float inv_keep = 1.0f / (1.0f - b.rate);
+  const float inv = (float)((double)blob[off.gamma[layer] + c] / sqrt(var + (double)kBnEps));
+  float* t = tables + (size_t)g * kTableFloats;
+  t[kChTotal + ch_off(layer) + c] = inv * inv_keep;
+  t[2 * kChTotal + ch_off(layer) + c] = (blob[off.beta[layer] + c] - (float)mu * inv) * inv_keep;
+}
+
+__global__ void replicate_table_kernel(const float* __restrict__ base, float* __restrict__ tables) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < kTableFloats) tables[(size_t)blockIdx.y * kTableFloats + i] = base[i];
+}
+
+int exact_replicate_tables(const float* base_table, int n_groups, float* tables, cudaStream_t s) {
+  replicate_table_kernel<<<dim3((kTableFloats + 255) / 256, n_groups), 256, 0, s>>>(base_table, tables);
+  UQK_LAUNCH_CHECK();
+  return UQK_OK;
+}
+
+int exact_layer_tables(const float* blob_dev, const unsigned long long* stats, double count, int layer, int n_groups,
+                       float* tables, cudaStream_t s) {
+  exact_layer_tables_kernel<<<n_groups, kMaxCh, 0, s>>>(blob_dev, blob_offsets(), stats, count, layer, tables);
   UQK_LAUNCH_CHECK();
   return UQK_OK;
 }
@@ -317,6 +357,11 @@ struct FusedArgs {
   int variant;
   int smem_probs;   // 1: per-window probabilities are kept in shared memory for the fused K3 reductions
   long long n_units;
+  // statistics sweep of the exact batch-statistic mode (pair kernel, STAT instantiation): run layers [0, n_layers) and
+  // accumulate the per-channel (sum, sum of squares) of layer n_layers-1's post-ReLU output into stats[g][2*256]
+  int n_layers;
+  int tab_per_group;              // 1: epilogue tables of group g are tables[g] although the weights are member 0's
+  unsigned long long* stats;
 };
 
 // dropout source of the epilogue
@@ -630,6 +675,87 @@ __device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, c
   }
 }
 
+// ---- statistics epilogue (exact batch-statistic mode) -------------------------------------------------------------
+// Sum of 16 per-lane values over the 32 lanes of a warp by recursive halving: after the xor-16/8/4/2 exchanges a lane
+// holds ONE of the 16 columns -- column (lane >> 1) & 15 -- summed over 16 lanes, and the xor-1 step completes it.
+// 16 shuffles instead of 80, and a fixed summation tree (the result does not depend on scheduling).
+__device__ __forceinline__ float warp_halve16(const float (&v)[16], int lane) {
+  float t8[8], t4[4], t2[2];
+  const bool b4 = (lane & 16) != 0, b3 = (lane & 8) != 0, b2 = (lane & 4) != 0, b1 = (lane & 2) != 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float keep = b4 ? v[8 + i] : v[i], send = b4 ? v[i] : v[8 + i];
+    t8[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float keep = b3 ? t8[4 + i] : t8[i], send = b3 ? t8[i] : t8[4 + i];
+    t4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+  }
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const float keep = b2 ? t4[2 + i] : t4[i], send = b2 ? t4[i] : t4[2 + i];
+    t2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+  }
+  const float keep = b1 ? t2[1] : t2[0], send = b1 ? t2[0] : t2[1];
+  float r = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+  r += __shfl_xor_sync(0xffffffffu, r, 1);
+  return r;
+}
+
+
+// Layer L is the last layer of a statistics sweep: ReLU of the accumulator (bias already added by the MMA), then the
+// per-channel sum / sum of squares over the valid rows.  One warp's partial covers 32 rows of one window; it is
+// converted to fixed point BEFORE it meets any other partial, so the totals are sums of integers that depend only on
+// (window, row half, channel) -- independent of the grid, of scheduling and of how windows are sharded over GPUs.
+template <int L, int EPI_THREADS>
+__device__ __forceinline__ void epi_stats(const EpiCtx& c, uint32_t& n_acc, unsigned long long* s_stats) {
+  constexpr int cout = fl_cout(L);
+  constexpr int my = cout / 32;
+  if (c.we == 0) {
+    mbar_wait2(c.bar_acc, n_acc & 1, c.err_flag, 4);
+    tc_fence_after();
+    tc_fence_before();
+  }
+  ++n_acc;
+  named_bar_sync(1 + c.tl, EPI_THREADS);
+  tc_fence_after();
+  uint32_t va[16];
+#pragma unroll 1
+  for (int j = 0; j < my; ++j) {
+    const int col0 = 16 * (c.colhalf + 2 * j);
+    tmem_ld16(c.taddr + (uint32_t)col0, va);
+    tmem_wait16(va);
+    float sv[16], qv[16];
+#pragma unroll
+    for (int e = 0; e < 16; ++e) {
+      const float r = c.row_valid ? fmaxf(__uint_as_float(va[e]), 0.f) : 0.f;
+      sv[e] = r;
+      qv[e] = r * r;
+    }
+    const float rs = warp_halve16(sv, c.lane);
+    const float rq = warp_halve16(qv, c.lane);
+    const int ch = col0 + ((c.lane >> 1) & 15);
+    const float mine = (c.lane & 1) ? rq : rs;      // even lane adds the sum, odd lane the sum of squares
+    atomicAdd(&s_stats[2 * ch + (c.lane & 1)], (unsigned long long)__double2ll_rn((double)mine * kFusedStatScale));
+  }
+  tc_fence_before();   // TMEM reads are complete before this thread lets the next unit's MMAs start
+}
+
+// Epilogue chain of a statistics sweep: normal epilogues for layers < n_layers-1, statistics for layer n_layers-1.
+template <int L, int DROP, int EPI_THREADS>
+__device__ __forceinline__ void epi_sweep(const EpiCtx& c, const FusedArgs& a, const float* __restrict__ tab_g, int g,
+                                          long long win, uint32_t& n_acc, unsigned long long* s_stats) {
+  if (a.n_layers == L + 1) {
+    epi_stats<L, EPI_THREADS>(c, n_acc, s_stats);
+    return;
+  }
+  if constexpr (L + 1 < kBlocks) {
+    epi_layer<L, DROP, false, EPI_THREADS>(c, a, tab_g, g, win, n_acc, nullptr, nullptr);
+    epi_sweep<L + 1, DROP, EPI_THREADS>(c, a, tab_g, g, win, n_acc, s_stats);
+  }
+}
+
 template <int TILES, int NSLOTS, int DROP, bool DBG>
 __global__ void __launch_bounds__(FusedCfg<TILES, NSLOTS>::kThreads, TILES == 1 ? 2 : 1)
 fused_forward_kernel(const FusedArgs a) {
@@ -787,7 +913,7 @@ fused_forward_kernel(const FusedArgs a) {
         if (c.colhalf == 0) st_shared_v4(c.act_row, xin0, xin1, 0u, 0u);
         fence_proxy_async();
         mbar_arrive(c.bar_act);
-        const float* tab_g = a.tables + (size_t)(a.mode_de ? g : 0) * kTableFloats;
+        const float* tab_g = a.tables + (size_t)((a.mode_de || a.tab_per_group) ? g : 0) * kTableFloats;
         float* dbg_g = (DBG && g == 0) ? dbg_base : nullptr;
         epi_layer<0, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
         epi_layer<1, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
@@ -929,7 +1055,9 @@ __device__ __forceinline__ void relay_layer(uint32_t bar_full, uint32_t bar_act,
   }
 }
 
-template <int NSLOTS, int DROP, bool DBG>
+// STAT = true: statistics sweep of the exact batch-statistic mode (see FusedArgs::n_layers); the epilogue warps then
+// walk passes in the OUTER loop so that one pass's statistics are accumulated in shared memory and flushed once.
+template <int NSLOTS, int DROP, bool DBG, bool STAT = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(PairCfg<NSLOTS>::kThreads, 2)
 fused_pair_kernel(const FusedArgs a) {
   using Cfg = PairCfg<NSLOTS>;
@@ -999,8 +1127,9 @@ fused_pair_kernel(const FusedArgs a) {
       for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
         for (int g = 0; g < a.n_groups; ++g) {
           const uint8_t* wmem = a.packed + (size_t)(a.mode_de ? g : 0) * kPackedBytes + (size_t)rank * (kPackedBytes / 2);
+          const int n_layers = STAT ? a.n_layers : kBlocks;
 #pragma unroll 1
-          for (int l = 0; l < kBlocks; ++l) {
+          for (int l = 0; l < n_layers; ++l) {
             const FusedLayer fl = c_layers[l];
             const uint32_t sb = (uint32_t)fl.step_bytes / 2;
             int step = 0;
@@ -1029,11 +1158,11 @@ fused_pair_kernel(const FusedArgs a) {
       for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
         for (int g = 0; g < a.n_groups; ++g) {
           issue_layer_pair<0, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
-          issue_layer_pair<1, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
-          issue_layer_pair<2, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
-          issue_layer_pair<3, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
-          issue_layer_pair<4, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
-          issue_layer_pair<5, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
+          if (!STAT || a.n_layers > 1) issue_layer_pair<1, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
+          if (!STAT || a.n_layers > 2) issue_layer_pair<2, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
+          if (!STAT || a.n_layers > 3) issue_layer_pair<3, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
+          if (!STAT || a.n_layers > 4) issue_layer_pair<4, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
+          if (!STAT || a.n_layers > 5) issue_layer_pair<5, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
         }
       }
     } else if (lane == 0) {
@@ -1043,11 +1172,11 @@ fused_pair_kernel(const FusedArgs a) {
       for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
         for (int g = 0; g < a.n_groups; ++g) {
           relay_layer<0, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
-          relay_layer<1, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
-          relay_layer<2, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
-          relay_layer<3, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
-          relay_layer<4, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
-          relay_layer<5, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
+          if (!STAT || a.n_layers > 1) relay_layer<1, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
+          if (!STAT || a.n_layers > 2) relay_layer<2, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
+          if (!STAT || a.n_layers > 3) relay_layer<3, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
+          if (!STAT || a.n_layers > 4) relay_layer<4, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
+          if (!STAT || a.n_layers > 5) relay_layer<5, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
         }
       }
     }
@@ -1073,10 +1202,11 @@ fused_pair_kernel(const FusedArgs a) {
     c.k0 = a.k0; c.k1 = a.k1;
     c.err_flag = a.err_flag;
     uint32_t n_acc = 0;
-    for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
-      const long long win = unit * Cfg::kWpu + 2 * (long long)rank + c.slot_w;
+    // per-unit prologue: which window this thread's row belongs to, its input row (bf16), the ones-plane row
+    auto unit_prologue = [&](long long unit, long long& win, uint32_t& xin0, uint32_t& xin1) {
+      win = unit * Cfg::kWpu + 2 * (long long)rank + c.slot_w;
       c.row_valid = (c.t < kL) && (win < a.n);
-      uint32_t xin0 = 0, xin1 = 0;
+      xin0 = 0; xin1 = 0;
       if (c.colhalf == 0) {
         if (c.row_valid) {
           float f0, f1, f2, f3;
@@ -1095,6 +1225,33 @@ fused_pair_kernel(const FusedArgs a) {
         st_shared_v4(c.act_row + (uint32_t)kOnesPlane * kPlaneBytes, c.row_valid ? 0x3F803F80u : 0u, 0u, 0u, 0u);
       }
       c.c0w = (uint32_t)(a.window_base + win);
+    };
+    if (STAT) {
+      unsigned long long* s_stats = reinterpret_cast<unsigned long long*>(smem + Cfg::oProbs);   // [2 * 256], no probs here
+      for (int i = c.tid_t; i < 2 * kMaxCh; i += Cfg::kEpiThreads) s_stats[i] = 0ull;
+      named_bar_sync(1, Cfg::kEpiThreads);
+      for (int g = 0; g < a.n_groups; ++g) {
+        const float* tab_g = a.tables + (size_t)g * kTableFloats;
+        for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
+          long long win; uint32_t xin0, xin1;
+          unit_prologue(unit, win, xin0, xin1);
+          if (c.colhalf == 0) st_shared_v4(c.act_row, xin0, xin1, 0u, 0u);
+          fence_proxy_async();
+          mbar_arrive(c.bar_act);
+          epi_sweep<0, DROP, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, s_stats);
+        }
+        // this pass is complete in this CTA: add its fixed-point sums to the global accumulators of pass g
+        named_bar_sync(1, Cfg::kEpiThreads);
+        for (int i = c.tid_t; i < 2 * kMaxCh; i += Cfg::kEpiThreads) {
+          const unsigned long long v = s_stats[i];
+          if (v != 0ull) { atomicAdd(a.stats + (size_t)g * 2 * kMaxCh + i, v); s_stats[i] = 0ull; }
+        }
+        named_bar_sync(1, Cfg::kEpiThreads);
+      }
+    } else {
+    for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
+      long long win; uint32_t xin0, xin1;
+      unit_prologue(unit, win, xin0, xin1);
       float* dbg_base = nullptr;
       if (DBG) {
         if (a.dbg_act && blockIdx.x == 0 && unit == pair_id) dbg_base = a.dbg_act + (size_t)row * 256;
@@ -1103,7 +1260,7 @@ fused_pair_kernel(const FusedArgs a) {
         if (c.colhalf == 0) st_shared_v4(c.act_row, xin0, xin1, 0u, 0u);
         fence_proxy_async();
         mbar_arrive(c.bar_act);
-        const float* tab_g = a.tables + (size_t)(a.mode_de ? g : 0) * kTableFloats;
+        const float* tab_g = a.tables + (size_t)((a.mode_de || a.tab_per_group) ? g : 0) * kTableFloats;
         float* dbg_g = (DBG && g == 0) ? dbg_base : nullptr;
         // probs_s rows are indexed by (2*tl + slot_w) = slot_w here
         epi_layer<0, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
@@ -1118,6 +1275,7 @@ fused_pair_kernel(const FusedArgs a) {
         window_metrics([&](int tt) { return pw[tt]; }, a.n_groups, win, a.out);
       }
     }
+    }
   }
 
   // ---- teardown: nobody may leave while the pair can still touch its shared memory / TMEM
@@ -1130,23 +1288,29 @@ fused_pair_kernel(const FusedArgs a) {
   }
 }
 
-template <int NSLOTS, int DROP, bool DBG>
+template <int NSLOTS, int DROP, bool DBG, bool STAT = false>
 static int launch_pair_variant(const FusedParams& p, cudaStream_t s) {
   using Cfg = PairCfg<NSLOTS>;
   FusedArgs a{};
-  a.x = p.x; a.x_f64 = p.x_dtype == UQK_F64; a.n = p.n; a.n_groups = p.n_groups; a.mode_de = p.mode_de;
+  a.x = p.x; a.x_f64 = p.x_dtype == UQK_F64; a.n = p.n; a.n_groups = p.n_groups; a.mode_de = p.mode_de; a.tab_per_group = p.tab_per_group;
   a.k0 = (uint32_t)(p.seed & 0xFFFFFFFFull); a.k1 = (uint32_t)(p.seed >> 32);
   a.window_base = p.window_base; a.mask_bits = p.mask_bits; a.packed = reinterpret_cast<const uint8_t*>(p.packed_pair);
   a.tables = p.tables; a.probs = p.probs; a.out = p.out; a.dbg_act = p.dbg_act; a.err_flag = p.err_flag;
   a.variant = p.variant;
   a.n_units = (p.n + Cfg::kWpu - 1) / Cfg::kWpu;
-  a.smem_probs = p.no_smem_probs ? 0 : 1;
-  const size_t smem = (size_t)Cfg::oProbs + (p.no_smem_probs ? 0 : (size_t)2 * p.n_groups * sizeof(float));
+  a.smem_probs = (p.no_smem_probs || STAT) ? 0 : 1;
+  a.n_layers = STAT ? p.n_layers : kBlocks; a.stats = p.stats;
+  if (STAT && (p.n_layers < 1 || p.n_layers > kBlocks || p.stats == nullptr)) {
+    set_error("statistics sweep needs 1 <= n_layers <= 6 and a statistics buffer"); return UQK_E_BADARG;
+  }
+  // the probability buffer of the fused reductions doubles as the statistics accumulator [2 x 256] u64 of a sweep
+  const size_t smem = (size_t)Cfg::oProbs + (STAT ? (size_t)2 * kMaxCh * sizeof(unsigned long long)
+                                                  : (p.no_smem_probs ? 0 : (size_t)2 * p.n_groups * sizeof(float)));
   if (smem > 113 * 1024) return UQK_E_SHAPE;   // must leave room for two CTAs per SM
   int dev = 0, sms = 148;
   UQK_CUDA(cudaGetDevice(&dev));
   UQK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  auto kern = fused_pair_kernel<NSLOTS, DROP, DBG>;
+  auto kern = fused_pair_kernel<NSLOTS, DROP, DBG, STAT>;
   UQK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   UQK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
   int per_sm = 1;
@@ -1187,6 +1351,11 @@ static int launch_pair_variant(const FusedParams& p, cudaStream_t s) {
 template <int NSLOTS>
 static int launch_pair(const FusedParams& p, cudaStream_t s) {
   const int drop = !p.dropout ? kDropNone : (p.mask_bits ? kDropBits : kDropPhilox);
+  if (p.stats) {   // statistics sweep of the exact batch-statistic mode (training=True: dropout is always on)
+    if (drop == kDropNone) { set_error("statistics sweeps exist for the dropout (training=True) passes only"); return UQK_E_BADARG; }
+    return drop == kDropPhilox ? launch_pair_variant<NSLOTS, kDropPhilox, false, true>(p, s)
+                               : launch_pair_variant<NSLOTS, kDropBits, false, true>(p, s);
+  }
   if (p.dbg_act) {
     switch (drop) {
       case kDropNone: return launch_pair_variant<NSLOTS, kDropNone, true>(p, s);
@@ -1421,7 +1590,7 @@ fused_pair2_kernel(const FusedArgs a) {
         if (c.colhalf == 0) st_shared_v4(c.act_row, xin0, xin1, 0u, 0u);
         fence_proxy_async();
         epi_signal_act<Cfg::kEpiThreads>(c);
-        const float* tab_g = a.tables + (size_t)(a.mode_de ? g : 0) * kTableFloats;
+        const float* tab_g = a.tables + (size_t)((a.mode_de || a.tab_per_group) ? g : 0) * kTableFloats;
         float* dbg_g = (DBG && g == 0) ? dbg_base : nullptr;
         epi_layer<0, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
         epi_layer<1, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
@@ -1450,7 +1619,7 @@ template <int NSLOTS, int DROP, bool DBG>
 static int launch_pair2_variant(const FusedParams& p, cudaStream_t s) {
   using Cfg = Pair2Cfg<NSLOTS>;
   FusedArgs a{};
-  a.x = p.x; a.x_f64 = p.x_dtype == UQK_F64; a.n = p.n; a.n_groups = p.n_groups; a.mode_de = p.mode_de;
+  a.x = p.x; a.x_f64 = p.x_dtype == UQK_F64; a.n = p.n; a.n_groups = p.n_groups; a.mode_de = p.mode_de; a.tab_per_group = p.tab_per_group;
   a.k0 = (uint32_t)(p.seed & 0xFFFFFFFFull); a.k1 = (uint32_t)(p.seed >> 32);
   a.window_base = p.window_base; a.mask_bits = p.mask_bits; a.packed = reinterpret_cast<const uint8_t*>(p.packed_pair);
   a.tables = p.tables; a.probs = p.probs; a.out = p.out; a.dbg_act = p.dbg_act; a.err_flag = p.err_flag;
@@ -1493,7 +1662,7 @@ template <int TILES, int NSLOTS, int DROP, bool DBG>
 static int launch_variant(const FusedParams& p, cudaStream_t s) {
   using Cfg = FusedCfg<TILES, NSLOTS>;
   FusedArgs a{};
-  a.x = p.x; a.x_f64 = p.x_dtype == UQK_F64; a.n = p.n; a.n_groups = p.n_groups; a.mode_de = p.mode_de;
+  a.x = p.x; a.x_f64 = p.x_dtype == UQK_F64; a.n = p.n; a.n_groups = p.n_groups; a.mode_de = p.mode_de; a.tab_per_group = p.tab_per_group;
   a.k0 = (uint32_t)(p.seed & 0xFFFFFFFFull); a.k1 = (uint32_t)(p.seed >> 32);
   a.window_base = p.window_base; a.mask_bits = p.mask_bits; a.packed = reinterpret_cast<const uint8_t*>(p.packed);
   a.tables = p.tables; a.probs = p.probs; a.out = p.out; a.dbg_act = p.dbg_act; a.err_flag = p.err_flag;
@@ -1551,6 +1720,7 @@ int fused_launch(const FusedParams& p, cudaStream_t s) {
   // 1 = one tile per CTA.  Every configuration falls through to a smaller one when T (or M) probabilities per
   // window do not fit its shared memory.
   const int v = p.variant >> 4;
+  if (p.stats) return launch_pair<4>(p, s);   // statistics sweeps exist in the CTA-pair kernel only
   int rc = UQK_E_SHAPE;
   if (v == 3) rc = launch_pair2<9>(p, s);
   if (rc == UQK_E_SHAPE && (v == 0 || v == 2 || v == 3)) rc = launch_pair<4>(p, s);

@@ -60,11 +60,20 @@ struct FusedParams {
   int* err_flag;              // device int: set !=0 by the in-kernel watchdog
   int variant;                // kernel variant selector (tests)
   int no_smem_probs;          // 1: too many passes for shared memory: probabilities go to `probs` only (K4 reduces them)
+  // exact batch-statistic mode (see run_fused_exact in api.cu)
+  int tab_per_group;          // 1: group g reads tables[g] (per-pass BatchNorm affine) with member 0's weights
+  int n_layers;               // statistics sweep: layers [0, n_layers) are computed ...
+  unsigned long long* stats;  // ... and (sum, sum of squares) of layer n_layers-1 go to stats[g][2*256]; null = normal run
 };
 int fused_launch(const FusedParams& p, cudaStream_t s);
 
 // tables builder: bias/scale/shift/dense for one set.  mean/var: 6x256 floats (frozen) or null -> moving stats.
 int build_tables(const float* blob_dev, const float* mean, const float* var, int fold_dropout, float* table_dev,
                  cudaStream_t s);
+
+// exact batch-statistic mode helpers (fused.cu)
+int exact_replicate_tables(const float* base_table, int n_groups, float* tables, cudaStream_t s);
+int exact_layer_tables(const float* blob_dev, const unsigned long long* stats, double count, int layer, int n_groups,
+                       float* tables, cudaStream_t s);
 
 }  // namespace uqk

@@ -9,9 +9,11 @@ reductions.
 
 Build-side knobs (the callers' positional signatures are frozen, so these are environment variables):
   UQK_BN_MODE    auto | batch | calibrated | inference      BatchNorm statistics of the MC-Dropout passes
-                 auto = exact Keras ``training=True`` semantics (batch statistics, fp32 layer-synchronous path)
-                 up to UQK_EXACT_MAX_WINDOWS windows, calibrated statistics + fused bf16 kernel above
-  UQK_PRECISION  bf16 | fp32
+                 auto = batch = exact Keras ``training=True`` semantics (statistics of the whole call): fp32
+                 layer-synchronous kernels up to UQK_EXACT_MAX_WINDOWS windows, above that the bf16 tensor-core
+                 kernel swept once per layer (same semantics, 3.7x the flops of one run).
+                 calibrated = statistics estimated once on UQK_CALIB_WINDOWS windows and frozen (fastest)
+  UQK_PRECISION  bf16 | fp32   (fp32 forces the layer-synchronous kernels at any size)
   UQK_SEED       Philox key of the dropout masks (default: the seed given to tf.random.set_seed, else 2025)
 """
 from __future__ import annotations
@@ -62,9 +64,12 @@ def mc_dropout_predict(model, x_test_data: np.ndarray, n_pred: int = 50) -> np.n
     mode = _env("UQK_BN_MODE", "auto")
     prec = _env("UQK_PRECISION", "bf16")
     if mode == "auto":
-        mode = "batch" if n <= int(_env("UQK_EXACT_MAX_WINDOWS", "16384")) else "calibrated"
+        mode = "batch"
     if mode == "batch":
-        prec = "fp32"      # exact batch statistics couple all windows of a layer: layer-synchronous path
+        # exact batch statistics couple all windows of a layer: fp32 layer-synchronous kernels while the whole call's
+        # activations fit comfortably, the swept tensor-core kernel above
+        if n <= int(_env("UQK_EXACT_MAX_WINDOWS", "16384")) and "UQK_PRECISION" not in os.environ:
+            prec = "fp32"
     elif mode == "calibrated" and not eng.calibrated:
         eng.calibrate(x, n_windows=int(_env("UQK_CALIB_WINDOWS", "4096")), n_passes=2, seed=_seed())
     out = eng.mcd(x, n_passes=int(n_pred), seed=_seed(), bn_mode=mode, precision=prec, return_probs=True, metrics=())
@@ -113,14 +118,14 @@ def mc_dropout_uq(model, x_test_data, n_pred: int = 50, *, y_true=None, return_p
     (T,N) probability tensor is never written to HBM unless ``return_probs``.  Returns the per-window arrays of
     uq_techniques.py:103-108 plus ``predictive_entropy_bits`` / ``predicted_label``
     (analyze_mcd_patient_level.py:113-117).  ``bn_mode='calibrated'`` first estimates the batch statistics on
-    ``calib_windows`` windows with the exact layer-synchronous path (inside this call when ``recalibrate``).
+    ``calib_windows`` windows with the exact layer-synchronous path (inside this call when ``recalibrate``);
+    ``bn_mode='batch'`` is the exact Keras ``training=True`` behaviour (statistics of all windows of this call):
+    ``precision='bf16'`` sweeps the tensor-core kernel once per layer, ``'fp32'`` uses the layer-synchronous kernels.
     ``window_base`` = global index of the first window (multi-GPU shards: masks are keyed by the global index)."""
     eng = _engine.get_engine()
     blob = _model.weights_of(model)
     eng.ensure_members(lambda: blob[None], key=("mcd",) + _members_key([blob]))
     seed = _seed() if seed is None else int(seed)
-    if bn_mode == "batch":
-        precision = "fp32"
     if bn_mode == "calibrated" and (recalibrate or not eng.calibrated):
         eng.calibrate(x_test_data, n_windows=calib_windows, n_passes=calib_passes, seed=seed)
     out = eng.mcd(x_test_data, n_passes=int(n_pred), seed=seed, bn_mode=bn_mode, precision=precision, masks=masks,
