@@ -175,6 +175,29 @@ int uqk_bootstrap_noalloc(const float* variance_dev, const float* total_entropy_
 
 /* Diagnostics: number of kernel launches the library has issued on this handle since creation. */
 int64_t uqk_launch_count(uqk_handle* h);
+/* N2 -- the per-window detail CSV (analyze_mcd_patient_level.py:134-152 builds the DataFrame and calls
+ * to_csv(path, index=False); analyze_de_patient_level.py does the same).  HOST function: writes, byte for byte, what
+ * pandas writes for int64 Patient_ID / Window_Index / True_Label, int Predicted_Label and float32 Predicted_Probability,
+ * Predictive_Variance, Predictive_Entropy (NumPy float32 repr: shortest round-trip digits, scientific below 1e-4 and
+ * from 1e6, NaN -> empty field), formatting row blocks on n_threads host threads (0 = all cores, at most 32).
+ * Window_Index = window_index_base + row.  write_header = 0 appends rows to an existing file (shards written in turn).
+ * All pointers are HOST arrays of n elements. */
+int uqk_write_detail_csv(const char* path, int64_t n, const int64_t* patient_id, int64_t window_index_base,
+                         const int64_t* true_label, const int32_t* pred_label, const float* prob, const float* variance,
+                         const float* entropy, int write_header, int n_threads);
+
+/* N2 -- GPU twin of analyze_window_level_uncertainty.py:30-64 on the device arrays the hot path produced: overall
+ * accuracy, pandas describe() (count, mean, std ddof=1, min, 25%, 50%, 75%, max) of Predictive_Entropy and
+ * Predictive_Variance for correctly / incorrectly classified windows, and the accuracy-vs-entropy table over
+ * n_bins (<= 64) equal-width bins [np.linspace(min, max + 1e-9, n_bins + 1), right-open].  Float64 arithmetic.
+ * out_dev: 35 + 3*n_bins doubles on the device:
+ *   [0] windows  [1] accuracy
+ *   [2 + 16*c + 8*m + k]   c: 0 correct, 1 incorrect;  m: 0 entropy, 1 variance;  k: the eight describe() rows
+ *   [34 .. 34+n_bins]      bin edges;  then n_bins window counts;  then n_bins accuracies (NaN for an empty bin)
+ * Stream-ordered scratch (cudaMallocAsync); enqueued on stream. */
+int uqk_window_summary(const float* entropy_dev, const float* variance_dev, const int32_t* true_label_dev,
+                       const int32_t* pred_label_dev, int64_t n_windows, int n_bins, double* out_dev, void* stream);
+
 /* Diagnostics for tests: selects the fused-kernel variant (0 = default). */
 int uqk_set_option(uqk_handle* h, const char* key, int64_t value);
 

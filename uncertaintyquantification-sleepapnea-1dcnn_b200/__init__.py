@@ -17,7 +17,7 @@ __all__ = ["arch", "synthetic"]
 
 def __getattr__(name):
     # Lazy so that host-only users (oracle, fixtures) do not need the CUDA library.
-    if name in ("model", "engine", "_lib", "sharding", "patient", "tf_shim"):
+    if name in ("model", "engine", "_lib", "sharding", "patient", "tf_shim", "emit"):
         import importlib
         return importlib.import_module(f"{__name__}.{name}")
     raise AttributeError(name)

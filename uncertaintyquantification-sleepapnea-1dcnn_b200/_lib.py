@@ -20,7 +20,7 @@ EXPORTS = [
     "uqk_version", "uqk_last_error", "uqk_create", "uqk_destroy", "uqk_set_model", "uqk_forward_det",
     "uqk_calibrate", "uqk_get_bn_stats", "uqk_set_bn_stats", "uqk_mcd", "uqk_de", "uqk_reduce",
     "uqk_patient_reduce", "uqk_standardize", "uqk_bootstrap", "uqk_bootstrap_noalloc", "uqk_launch_count", "uqk_set_option",
-    "uqk_set_stats_exchange",
+    "uqk_set_stats_exchange", "uqk_write_detail_csv", "uqk_window_summary",
 ]
 
 # int fn(void* user, long long* stats_dev, int count, void* stream)  -- include/uqk.h uqk_stats_exchange_fn
@@ -72,6 +72,8 @@ def load() -> C.CDLL:
     lib.uqk_launch_count.restype = i64
     lib.uqk_set_option.argtypes = [vp, C.c_char_p, i64]
     lib.uqk_set_stats_exchange.argtypes = [vp, STATS_EXCHANGE_FN, vp, i64]
+    lib.uqk_write_detail_csv.argtypes = [C.c_char_p, i64, vp, i64, vp, vp, vp, vp, vp, i32, i32]
+    lib.uqk_window_summary.argtypes = [vp, vp, vp, vp, i64, i32, vp, vp]
     if hasattr(lib, "uqk_debug_read_dump"):
         lib.uqk_debug_read_dump.argtypes = [vp, vp]
     for name in EXPORTS:
