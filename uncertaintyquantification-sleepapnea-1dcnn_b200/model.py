@@ -92,11 +92,76 @@ def fingerprint(blob: np.ndarray) -> int:
     return zlib.crc32(memoryview(np.ascontiguousarray(blob)).cast("B"))
 
 
+def _cfg(layer, name, default=None):
+    """Attribute of a Keras layer, falling back to ``get_config()`` (both exist on real layers)."""
+    if hasattr(layer, name):
+        return getattr(layer, name)
+    if hasattr(layer, "get_config"):
+        return layer.get_config().get(name, default)
+    return default
+
+
+def _first(v):
+    return v[0] if isinstance(v, (tuple, list)) else v
+
+
+def _act_name(a) -> str:
+    return a if isinstance(a, str) else getattr(a, "__name__", str(a))
+
+
+def validate_keras_model(model) -> None:
+    """Checks that a genuine Keras model has exactly the architecture the kernels implement
+    (models/cnn_baseline_train.py:55-94): layer classes in order, filters / kernel_size / padding / activation of
+    every Conv1D, BatchNormalization epsilon, Dropout rates, the pooling layer and the sigmoid Dense(1).  The weight
+    SHAPES are validated separately by ``weights_to_blob``; this catches what shapes cannot (a different dropout rate,
+    epsilon, activation or padding would silently change the numbers).  Raises ValueError with the first mismatch."""
+    layers = [l for l in getattr(model, "layers", []) if type(l).__name__ != "InputLayer"]
+    want = []
+    for b in arch.BLOCKS:
+        want += [("Conv1D", b), ("BatchNormalization", b), ("Dropout", b)]
+    want += [("GlobalAveragePooling1D", None), ("Dense", None)]
+    names = [type(l).__name__ for l in layers]
+    if names != [w[0] for w in want]:
+        raise ValueError(f"layer sequence {names} is not the Alarcon 1D-CNN ({[w[0] for w in want]})")
+    for i, (layer, (kind, b)) in enumerate(zip(layers, want)):
+        where = f"layer {i} ({getattr(layer, 'name', kind)})"
+        if kind == "Conv1D":
+            got = (int(_cfg(layer, "filters")), int(_first(_cfg(layer, "kernel_size"))), str(_cfg(layer, "padding")).lower(),
+                   _act_name(_cfg(layer, "activation")), int(_first(_cfg(layer, "strides", 1))),
+                   int(_first(_cfg(layer, "dilation_rate", 1))), bool(_cfg(layer, "use_bias", True)))
+            exp = (b.cout, b.k, "same", "relu", 1, 1, True)
+            if got != exp:
+                raise ValueError(f"{where}: Conv1D (filters, kernel, padding, activation, stride, dilation, bias) = {got}, need {exp}")
+        elif kind == "BatchNormalization":
+            eps = float(_cfg(layer, "epsilon"))
+            if abs(eps - arch.BN_EPS) > 1e-12:
+                raise ValueError(f"{where}: BatchNormalization epsilon {eps}, need {arch.BN_EPS}")
+            axis = _cfg(layer, "axis", -1)
+            axis = _first(list(axis) if isinstance(axis, (list, tuple)) else [axis])
+            if axis not in (-1, 2):
+                raise ValueError(f"{where}: BatchNormalization axis {axis}, need the channel axis")
+            if not (_cfg(layer, "center", True) and _cfg(layer, "scale", True)):
+                raise ValueError(f"{where}: BatchNormalization needs center=True and scale=True")
+        elif kind == "Dropout":
+            rate = float(_cfg(layer, "rate"))
+            if abs(rate - b.rate) > 1e-9:
+                raise ValueError(f"{where}: Dropout rate {rate}, need {b.rate}")
+            if _cfg(layer, "noise_shape", None) is not None:
+                raise ValueError(f"{where}: Dropout noise_shape is not supported (masks are per element)")
+        elif kind == "Dense":
+            got = (int(_cfg(layer, "units")), _act_name(_cfg(layer, "activation")), bool(_cfg(layer, "use_bias", True)))
+            if got != (1, "sigmoid", True):
+                raise ValueError(f"{where}: Dense (units, activation, bias) = {got}, need (1, 'sigmoid', True)")
+
+
 def weights_of(model) -> np.ndarray:
-    """Blob (853441,) float32 of a ``UQModel`` or of any object with Keras' ``get_weights()``."""
+    """Blob (853441,) float32 of a ``UQModel`` or of any object with Keras' ``get_weights()`` (a genuine Keras model,
+    whose layer list is validated first when it exposes one)."""
     if isinstance(model, UQModel):
         return model.blob()
     if hasattr(model, "get_weights"):
+        if hasattr(model, "layers"):
+            validate_keras_model(model)
         return synthetic.weights_to_blob(model.get_weights())
     raise TypeError(f"cannot extract weights from {type(model).__name__}: need UQModel or a Keras model")
 
