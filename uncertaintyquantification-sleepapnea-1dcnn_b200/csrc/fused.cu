@@ -581,7 +581,10 @@ struct EpiCtx {
 template <int EPI_THREADS>
 __device__ __forceinline__ void epi_signal_act(const EpiCtx& c) {
   if (c.remote_act == 0) {
-    mbar_arrive(c.bar_act);
+    // one arrival per warp (the barrier counts EPI_THREADS / 32): every lane has fenced its own stores, __syncwarp
+    // orders them before lane 0's release-arrive -- 8 mbarrier operations per hand-off instead of 256
+    __syncwarp();
+    if (c.lane == 0) mbar_arrive(c.bar_act);
   } else {
     named_bar_sync(1 + c.tl, EPI_THREADS);
     if (c.tid_t == 0) mbar_arrive_remote(c.remote_act);
@@ -793,7 +796,7 @@ fused_forward_kernel(const FusedArgs a) {
   }
   if (threadIdx.x == 0) {
     for (int i = 0; i < NSLOTS; ++i) { mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, 1); }
-    for (int i = 0; i < TILES; ++i) { mbar_init(bar_acc + 8 * i, 1); mbar_init(bar_act + 8 * i, Cfg::kEpiThreads); }
+    for (int i = 0; i < TILES; ++i) { mbar_init(bar_acc + 8 * i, 1); mbar_init(bar_act + 8 * i, Cfg::kEpiThreads / 32); }
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -912,7 +915,7 @@ fused_forward_kernel(const FusedArgs a) {
         // ---- layer-1 input: channels 0..3 real, 4..7 zero, in plane 0
         if (c.colhalf == 0) st_shared_v4(c.act_row, xin0, xin1, 0u, 0u);
         fence_proxy_async();
-        mbar_arrive(c.bar_act);
+        epi_signal_act<Cfg::kEpiThreads>(c);
         const float* tab_g = a.tables + (size_t)((a.mode_de || a.tab_per_group) ? g : 0) * kTableFloats;
         float* dbg_g = (DBG && g == 0) ? dbg_base : nullptr;
         epi_layer<0, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
@@ -1000,7 +1003,7 @@ __device__ __forceinline__ void issue_layer_pair(uint32_t s_base, uint32_t tmem_
   constexpr uint32_t kBLbo = ((uint32_t)((fl.cout / 2) * 16) >> 4) << 16;
   constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(fl.cout >> 3) << 17) | ((256u >> 4) << 24);
   constexpr int kLast = fl.nsteps - (fl.nstages - 1) * fl.sps;
-  mbar_wait_cluster(bar_act, n_act & 1, err_flag, 2);      // 256 local arrivals + 1 relayed from the peer
+  mbar_wait_cluster(bar_act, n_act & 1, err_flag, 2);      // 8 local warp arrivals + 1 relayed from the peer
   ++n_act;
   tc_fence_after();
 #pragma unroll 1
@@ -1102,7 +1105,7 @@ fused_pair_kernel(const FusedArgs a) {
     for (int i = 0; i < NSLOTS; ++i) {
       mbar_init(bar_full + 8 * i, 1 + extra); mbar_init(bar_empty + 8 * i, 1); mbar_init(bar_peer_full + 8 * i, 1);
     }
-    mbar_init(bar_acc, 1); mbar_init(bar_act, Cfg::kEpiThreads + extra); mbar_init(bar_peer_act, 1);
+    mbar_init(bar_acc, 1); mbar_init(bar_act, Cfg::kEpiThreads / 32 + extra); mbar_init(bar_peer_act, 1);
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -1237,7 +1240,7 @@ fused_pair_kernel(const FusedArgs a) {
           unit_prologue(unit, win, xin0, xin1);
           if (c.colhalf == 0) st_shared_v4(c.act_row, xin0, xin1, 0u, 0u);
           fence_proxy_async();
-          mbar_arrive(c.bar_act);
+          epi_signal_act<Cfg::kEpiThreads>(c);
           epi_sweep<0, DROP, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, s_stats);
         }
         // this pass is complete in this CTA: add its fixed-point sums to the global accumulators of pass g
@@ -1259,7 +1262,7 @@ fused_pair_kernel(const FusedArgs a) {
       for (int g = 0; g < a.n_groups; ++g) {
         if (c.colhalf == 0) st_shared_v4(c.act_row, xin0, xin1, 0u, 0u);
         fence_proxy_async();
-        mbar_arrive(c.bar_act);
+        epi_signal_act<Cfg::kEpiThreads>(c);
         const float* tab_g = a.tables + (size_t)((a.mode_de || a.tab_per_group) ? g : 0) * kTableFloats;
         float* dbg_g = (DBG && g == 0) ? dbg_base : nullptr;
         // probs_s rows are indexed by (2*tl + slot_w) = slot_w here
@@ -1446,7 +1449,7 @@ fused_pair2_kernel(const FusedArgs a) {
       mbar_init(bar_full + 8 * i, 1 + extra); mbar_init(bar_empty + 8 * i, 2); mbar_init(bar_peer_full + 8 * i, 1);
     }
     for (int i = 0; i < 2; ++i) {
-      mbar_init(bar_acc + 8 * i, 1); mbar_init(bar_act + 8 * i, Cfg::kEpiThreads + extra); mbar_init(bar_peer_act + 8 * i, 1);
+      mbar_init(bar_acc + 8 * i, 1); mbar_init(bar_act + 8 * i, Cfg::kEpiThreads / 32 + extra); mbar_init(bar_peer_act + 8 * i, 1);
     }
     fence_barrier_init();
   }
