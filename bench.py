@@ -237,7 +237,7 @@ def main():
             traffic = tj.get("dram_bytes_per_window", 0) * n
         except Exception:
             traffic = None
-    roofline = {"bound": "tensor", "kernel": "fused_pair_kernel (tcgen05 cta_group::2 conv chain + Philox dropout + UQ epilogue)",
+    roofline = {"bound": "tensor", "kernel": "fused_pair2_kernel (tcgen05 cta_group::2 conv chain, two tile-pairs per CTA pair + Philox dropout + UQ epilogue)",
                 "achieved": ach, "peak": peaks["sustained"], "unit": "TFLOP/s", "frac": ach / peaks["sustained"],
                 "peak_source": peaks["source"] + ", sustained bf16 (kernel timed inside a multi-second step)",
                 "frac_of_burst": ach / peaks["burst"], "achieved_dense_count": n * T * FLOP_DENSE / (ms_fused * 1e-3) / 1e12,

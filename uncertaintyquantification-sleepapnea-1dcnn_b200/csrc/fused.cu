@@ -444,6 +444,29 @@ __device__ __forceinline__ uint32_t prmt_sign_halves(uint32_t d) {
   return r;
 }
 
+template <uint32_t SEL>
+__device__ __forceinline__ uint32_t prmt_sign_bytes(uint32_t z) {
+  uint32_t r;
+  asm("prmt.b32 %0, %1, %1, %2;" : "=r"(r) : "r"(z), "n"(SEL));
+  return r;
+}
+
+// Keep-bits of 8 consecutive channels (one Philox4x32-10 call): bit e = 1 iff element e's 15-bit field >= thr15.
+// The compare runs on both halves of a word at once (see epi_chunk16); PRMT gathers the four bytes that carry the
+// result flags (bits 15 / 31 of each word) and a multiply packs their sign bits into 4 adjacent bits.
+__device__ __forceinline__ uint32_t philox_keep8(uint32_t c0w, uint32_t pass, uint32_t c2, uint32_t chunk8, uint32_t k0,
+                                                 uint32_t k1, uint32_t thr2) {
+  const Philox4 r = philox4x32_10(c0w, pass, c2, chunk8, k0, k1);
+  const uint32_t d0 = ((r.x & 0x7FFF7FFFu) | 0x80008000u) - thr2, d1 = ((r.y & 0x7FFF7FFFu) | 0x80008000u) - thr2;
+  const uint32_t d2 = ((r.z & 0x7FFF7FFFu) | 0x80008000u) - thr2, d3 = ((r.w & 0x7FFF7FFFu) | 0x80008000u) - thr2;
+  uint32_t g0, g1;
+  asm("prmt.b32 %0, %1, %2, 0x7531;" : "=r"(g0) : "r"(d0), "r"(d1));   // bytes: d0[15:8], d0[31:24], d1[15:8], d1[31:24]
+  asm("prmt.b32 %0, %1, %2, 0x7531;" : "=r"(g1) : "r"(d2), "r"(d3));
+  const uint32_t n0 = (((g0 >> 7) & 0x01010101u) * 0x01020408u) >> 24;    // sign of byte k -> bit k
+  const uint32_t n1 = (((g1 >> 7) & 0x01010101u) * 0x01020408u) >> 24;
+  return n0 | (n1 << 4);
+}
+
 // One 16-column chunk of the epilogue: ReLU -> BatchNorm affine (dropout scale folded) -> dropout -> bf16 store
 // (layers 1-5) or dot with the dense kernel (layer 6).  The conv bias is already in the accumulator (bias MMA step).
 //
@@ -469,19 +492,14 @@ __device__ __forceinline__ void epi_chunk16(const uint32_t (&v)[16], int c0, con
 #pragma unroll
     for (int e = 0; e < 8; ++e) y[e] = fmaf(fmaxf(__uint_as_float(v[8 * q + e]), 0.f), ss[e], hh[e]);
     uint32_t m[4] = {row_mask, row_mask, row_mask, row_mask};     // per bf16 pair: 0xFFFF per kept half
-    if (DROP == kDropPhilox) {
-      const Philox4 r = philox4x32_10(c0w, pass, c2, (uint32_t)(cb >> 3), k0, k1);
-      const uint32_t rw[4] = {r.x, r.y, r.z, r.w};
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const uint32_t d = ((rw[i] & 0x7FFF7FFFu) | 0x80008000u) - thr2;
-        m[i] &= prmt_sign_halves(d);
-      }
-    } else if (DROP == kDropBits) {
-      const uint32_t kb = keep16 >> (8 * q);
-#pragma unroll
-      for (int i = 0; i < 4; ++i)
-        m[i] &= (((kb >> (2 * i)) & 1u) ? 0x0000FFFFu : 0u) | (((kb >> (2 * i + 1)) & 1u) ? 0xFFFF0000u : 0u);
+    if (DROP != kDropNone) {
+      // keep16 holds this chunk's 16 keep-bits (already zero for padding rows).  A multiply spreads 4 bits into the
+      // sign bits of 4 bytes (bit k -> bit 8k+7; the partial products never collide), PRMT with sign replication
+      // widens two byte signs into the 0xFFFF / 0 masks of one bf16 pair: 1 IMAD + 2 PRMT per 4 elements.
+      const uint32_t kb8 = (keep16 >> (8 * q)) & 0xFFu;
+      const uint32_t z0 = (kb8 & 0xFu) * 0x10204080u, z1 = (kb8 >> 4) * 0x10204080u;
+      m[0] = prmt_sign_bytes<0x9988>(z0); m[1] = prmt_sign_bytes<0xBBAA>(z0);
+      m[2] = prmt_sign_bytes<0x9988>(z1); m[3] = prmt_sign_bytes<0xBBAA>(z1);
     }
     if (DBG || LAST) {
       // float path (debug dump and the head): apply the same masks to the fp32 values
@@ -622,6 +640,19 @@ __device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, c
   constexpr uint32_t thr2 = drop_thr15(L) * 0x00010001u;
   const uint32_t c2 = ((uint32_t)L << 16) | (uint32_t)c.t;
   const uint32_t row_mask = c.row_valid ? 0xFFFFFFFFu : 0u;   // zero rows = the next layer's `same` padding
+  if (DROP == kDropPhilox) {
+    // the dropout masks do not depend on the data: generate this thread's keep-bits now, while the layer's MMAs run
+    // and these warps would otherwise sleep on the accumulator barrier (10 Philox rounds per 8 channels leave the
+    // critical path of the epilogue)
+#pragma unroll
+    for (int j = 0; j < my; ++j) {
+      const uint32_t ch8 = (uint32_t)(2 * (c.colhalf + 2 * j));
+      uint32_t b16 = philox_keep8(c.c0w, (uint32_t)g, c2, ch8, c.k0, c.k1, thr2) |
+                     (philox_keep8(c.c0w, (uint32_t)g, c2, ch8 + 1u, c.k0, c.k1, thr2) << 8);
+      b16 = c.row_valid ? b16 : 0u;
+      kb[j >> 1] |= b16 << (16 * (j & 1));
+    }
+  }
 
   // one warp polls the accumulator barrier; the others sleep in the named barrier (no issue slots burnt)
   if (c.we == 0) {
@@ -1719,13 +1750,13 @@ static int launch_drop(const FusedParams& p, cudaStream_t s) {
 
 int fused_launch(const FusedParams& p, cudaStream_t s) {
   if (p.n == 0) return UQK_OK;
-  // variant >> 4: 0 / 2 = CTA pairs (default), 3 = CTA pairs with two tiles per CTA, 4 = two tiles per CTA,
-  // 1 = one tile per CTA.  Every configuration falls through to a smaller one when T (or M) probabilities per
-  // window do not fit its shared memory.
+  // variant >> 4: 0 / 3 = CTA pairs with two tiles per CTA (default), 2 = CTA pairs with one tile per CTA and two CTAs
+  // per SM, 4 = two tiles per CTA, 1 = one tile per CTA.  Every configuration falls through to a smaller one when T
+  // (or M) probabilities per window do not fit its shared memory.
   const int v = p.variant >> 4;
   if (p.stats) return launch_pair<4>(p, s);   // statistics sweeps exist in the CTA-pair kernel only
   int rc = UQK_E_SHAPE;
-  if (v == 3) rc = launch_pair2<9>(p, s);
+  if (v == 0 || v == 3) rc = launch_pair2<9>(p, s);
   if (rc == UQK_E_SHAPE && (v == 0 || v == 2 || v == 3)) rc = launch_pair<4>(p, s);
   if (rc == UQK_E_SHAPE && v != 1) rc = launch_drop<2, 4>(p, s);
   if (rc == UQK_E_SHAPE) rc = launch_drop<1, 2>(p, s);
