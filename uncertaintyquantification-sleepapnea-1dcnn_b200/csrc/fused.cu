@@ -451,20 +451,30 @@ __device__ __forceinline__ uint32_t prmt_sign_bytes(uint32_t z) {
   return r;
 }
 
-// Keep-bits of 8 consecutive channels (one Philox4x32-10 call): bit e = 1 iff element e's 15-bit field >= thr15.
-// The compare runs on both halves of a word at once (see epi_chunk16); PRMT gathers the four bytes that carry the
-// result flags (bits 15 / 31 of each word) and a multiply packs their sign bits into 4 adjacent bits.
-__device__ __forceinline__ uint32_t philox_keep8(uint32_t c0w, uint32_t pass, uint32_t c2, uint32_t chunk8, uint32_t k0,
-                                                 uint32_t k1, uint32_t thr2) {
+// Keep-flags of 8 consecutive channels (one Philox4x32-10 call): element e is kept iff its 15-bit field >= thr15.
+// The compare runs on both 16-bit halves of a word at once -- ((w & 0x7FFF7FFF) | 0x80008000) - thr15*0x00010001 leaves
+// the flag in bits 15 / 31 -- and a PRMT gathers the four flag bytes of two words: g0 carries elements 0..3 and g1
+// elements 4..7 in the SIGN BITS of their four bytes.
+__device__ __forceinline__ void philox_keep8(uint32_t c0w, uint32_t pass, uint32_t c2, uint32_t chunk8, uint32_t k0,
+                                             uint32_t k1, uint32_t thr2, uint32_t& g0, uint32_t& g1) {
   const Philox4 r = philox4x32_10(c0w, pass, c2, chunk8, k0, k1);
   const uint32_t d0 = ((r.x & 0x7FFF7FFFu) | 0x80008000u) - thr2, d1 = ((r.y & 0x7FFF7FFFu) | 0x80008000u) - thr2;
   const uint32_t d2 = ((r.z & 0x7FFF7FFFu) | 0x80008000u) - thr2, d3 = ((r.w & 0x7FFF7FFFu) | 0x80008000u) - thr2;
-  uint32_t g0, g1;
   asm("prmt.b32 %0, %1, %2, 0x7531;" : "=r"(g0) : "r"(d0), "r"(d1));   // bytes: d0[15:8], d0[31:24], d1[15:8], d1[31:24]
   asm("prmt.b32 %0, %1, %2, 0x7531;" : "=r"(g1) : "r"(d2), "r"(d3));
-  const uint32_t n0 = (((g0 >> 7) & 0x01010101u) * 0x01020408u) >> 24;    // sign of byte k -> bit k
-  const uint32_t n1 = (((g1 >> 7) & 0x01010101u) * 0x01020408u) >> 24;
-  return n0 | (n1 << 4);
+}
+
+// Keep-flag store of one thread and layer: the flags of 4 consecutive channels ("quad" t = channel_in_thread / 4) sit
+// in bit (t & 7) of the four bytes of word t >> 3 -- 32 flags per register, Cout/2 flags = at most 4 registers.
+// Insert = shift the byte-sign form into place (SHF + LOP3); extract = shift back to the byte signs (SHF), which is
+// what PRMT's sign replication reads when it widens a flag into the 0xFFFF / 0 mask of a bf16 half.
+__device__ __forceinline__ void keep_insert(uint32_t (&kb)[4], int t, uint32_t g) {   // t is a constant after unrolling
+  const int s = t & 7;
+  kb[t >> 3] |= (s == 7 ? g : (g >> (7 - s))) & (0x01010101u << s);
+}
+__device__ __forceinline__ uint32_t keep_extract(const uint32_t (&kb)[4], int t) {
+  const int s = t & 7;
+  return s == 7 ? kb[t >> 3] : (kb[t >> 3] << (7 - s));
 }
 
 // One 16-column chunk of the epilogue: ReLU -> BatchNorm affine (dropout scale folded) -> dropout -> bf16 store
@@ -480,7 +490,7 @@ __device__ __forceinline__ void epi_chunk16(const uint32_t (&v)[16], int c0, con
                                             const float* __restrict__ tab_h, const float* __restrict__ tab_w,
                                             uint32_t act_row, bool row_valid, uint32_t row_mask, uint32_t thr2,
                                             uint32_t c0w, uint32_t pass, uint32_t c2, uint32_t k0, uint32_t k1,
-                                            uint32_t keep16, float& zacc, float* dbg) {
+                                            const uint32_t (&zq)[4], float& zacc, float* dbg) {
 #pragma unroll
   for (int q = 0; q < 2; ++q) {
     const int cb = c0 + 8 * q;
@@ -493,13 +503,10 @@ __device__ __forceinline__ void epi_chunk16(const uint32_t (&v)[16], int c0, con
     for (int e = 0; e < 8; ++e) y[e] = fmaf(fmaxf(__uint_as_float(v[8 * q + e]), 0.f), ss[e], hh[e]);
     uint32_t m[4] = {row_mask, row_mask, row_mask, row_mask};     // per bf16 pair: 0xFFFF per kept half
     if (DROP != kDropNone) {
-      // keep16 holds this chunk's 16 keep-bits (already zero for padding rows).  A multiply spreads 4 bits into the
-      // sign bits of 4 bytes (bit k -> bit 8k+7; the partial products never collide), PRMT with sign replication
-      // widens two byte signs into the 0xFFFF / 0 masks of one bf16 pair: 1 IMAD + 2 PRMT per 4 elements.
-      const uint32_t kb8 = (keep16 >> (8 * q)) & 0xFFu;
-      const uint32_t z0 = (kb8 & 0xFu) * 0x10204080u, z1 = (kb8 >> 4) * 0x10204080u;
-      m[0] = prmt_sign_bytes<0x9988>(z0); m[1] = prmt_sign_bytes<0xBBAA>(z0);
-      m[2] = prmt_sign_bytes<0x9988>(z1); m[3] = prmt_sign_bytes<0xBBAA>(z1);
+      // zq[2q], zq[2q+1]: keep-flags of channels 0..3 / 4..7 of this half in the byte sign bits (zero for padding
+      // rows); PRMT with sign replication widens two byte signs into the 0xFFFF / 0 masks of one bf16 pair
+      m[0] = prmt_sign_bytes<0x9988>(zq[2 * q]); m[1] = prmt_sign_bytes<0xBBAA>(zq[2 * q]);
+      m[2] = prmt_sign_bytes<0x9988>(zq[2 * q + 1]); m[3] = prmt_sign_bytes<0xBBAA>(zq[2 * q + 1]);
     }
     if (DBG || LAST) {
       // float path (debug dump and the head): apply the same masks to the fp32 values
@@ -624,34 +631,41 @@ __device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, c
   }
   if (kLastLayer && c.tid_t < kDenseIn + 1) c.tab_w[c.tid_t] = __ldg(tab_g + 3 * kChTotal + c.tid_t);
 
-  // mask-injection mode (parity tests): this thread's keep-bits, fetched while the layer's MMAs run
-  uint32_t kb[(my + 1) / 2];
-#pragma unroll
-  for (int j = 0; j < (my + 1) / 2; ++j) kb[j] = 0u;
+  // keep-flags of this thread's row for this layer (see keep_insert): produced while the layer's MMAs run
+  uint32_t kb[4] = {0u, 0u, 0u, 0u};
+  constexpr uint32_t thr2 = drop_thr15(L) * 0x00010001u;
+  const uint32_t c2 = ((uint32_t)L << 16) | (uint32_t)c.t;
+  const uint32_t row_mask = c.row_valid ? 0xFFFFFFFFu : 0u;   // zero rows = the next layer's `same` padding
   if (DROP == kDropBits) {
+    // mask-injection mode (parity tests): explicit keep-bits from global memory, bit c%32 of word c/32
     const uint32_t* mrow = a.mask_bits + ((((size_t)g * a.n + (c.row_valid ? win : 0)) * kBlocks + L) * kL + (c.row_valid ? c.t : 0)) * 8;
 #pragma unroll
     for (int j = 0; j < my; ++j) {
       const int k = c.colhalf + 2 * j;
-      const uint32_t w = c.row_valid ? __ldg(mrow + (k >> 1)) : 0u;
-      kb[j >> 1] |= ((w >> (16 * (k & 1))) & 0xFFFFu) << (16 * (j & 1));
+      const uint32_t w16 = (__ldg(mrow + (k >> 1)) >> (16 * (k & 1))) & 0xFFFFu;
+#pragma unroll
+      for (int u = 0; u < 4; ++u)      // 4 bits -> bit 7 of 4 bytes (bit k lands on 8k + 7; the partial products never collide)
+        keep_insert(kb, 4 * j + u, (((w16 >> (4 * u)) & 0xFu) * 0x10204080u) & 0x80808080u);
     }
   }
-  constexpr uint32_t thr2 = drop_thr15(L) * 0x00010001u;
-  const uint32_t c2 = ((uint32_t)L << 16) | (uint32_t)c.t;
-  const uint32_t row_mask = c.row_valid ? 0xFFFFFFFFu : 0u;   // zero rows = the next layer's `same` padding
   if (DROP == kDropPhilox) {
-    // the dropout masks do not depend on the data: generate this thread's keep-bits now, while the layer's MMAs run
-    // and these warps would otherwise sleep on the accumulator barrier (10 Philox rounds per 8 channels leave the
-    // critical path of the epilogue)
+    // the dropout masks do not depend on the data: generate them now, while these warps would otherwise sleep on the
+    // accumulator barrier -- the 10 Philox rounds per 8 channels leave the critical path of the epilogue
 #pragma unroll
     for (int j = 0; j < my; ++j) {
       const uint32_t ch8 = (uint32_t)(2 * (c.colhalf + 2 * j));
-      uint32_t b16 = philox_keep8(c.c0w, (uint32_t)g, c2, ch8, c.k0, c.k1, thr2) |
-                     (philox_keep8(c.c0w, (uint32_t)g, c2, ch8 + 1u, c.k0, c.k1, thr2) << 8);
-      b16 = c.row_valid ? b16 : 0u;
-      kb[j >> 1] |= b16 << (16 * (j & 1));
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        uint32_t g0, g1;
+        philox_keep8(c.c0w, (uint32_t)g, c2, ch8 + (uint32_t)u, c.k0, c.k1, thr2, g0, g1);
+        keep_insert(kb, 4 * j + 2 * u, g0);
+        keep_insert(kb, 4 * j + 2 * u + 1, g1);
+      }
     }
+  }
+  if (DROP != kDropNone) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) kb[i] = c.row_valid ? kb[i] : 0u;   // padding rows keep nothing
   }
 
   // one warp polls the accumulator barrier; the others sleep in the named barrier (no issue slots burnt)
@@ -676,14 +690,17 @@ __device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, c
   for (int j = 0; j < my; j += 2) {
     tmem_wait16(va);
     if (j + 1 < my) tmem_ld16(c.taddr + (uint32_t)(16 * (c.colhalf + 2 * (j + 1))), vb);
-    epi_chunk16<DROP, kLastLayer, DBG>(va, 16 * (c.colhalf + 2 * j), tab_s, tab_h, c.tab_w, c.act_row, c.row_valid, row_mask, thr2,
-                                       c.c0w, (uint32_t)g, c2, c.k0, c.k1, (kb[j >> 1] >> (16 * (j & 1))) & 0xFFFFu, zacc, dbg);
+    {
+      const uint32_t zq[4] = {keep_extract(kb, 4 * j), keep_extract(kb, 4 * j + 1), keep_extract(kb, 4 * j + 2), keep_extract(kb, 4 * j + 3)};
+      epi_chunk16<DROP, kLastLayer, DBG>(va, 16 * (c.colhalf + 2 * j), tab_s, tab_h, c.tab_w, c.act_row, c.row_valid, row_mask, thr2,
+                                         c.c0w, (uint32_t)g, c2, c.k0, c.k1, zq, zacc, dbg);
+    }
     if (j + 1 < my) {
       tmem_wait16(vb);
       if (j + 2 < my) tmem_ld16(c.taddr + (uint32_t)(16 * (c.colhalf + 2 * (j + 2))), va);
+      const uint32_t zq[4] = {keep_extract(kb, 4 * j + 4), keep_extract(kb, 4 * j + 5), keep_extract(kb, 4 * j + 6), keep_extract(kb, 4 * j + 7)};
       epi_chunk16<DROP, kLastLayer, DBG>(vb, 16 * (c.colhalf + 2 * (j + 1)), tab_s, tab_h, c.tab_w, c.act_row, c.row_valid, row_mask,
-                                         thr2, c.c0w, (uint32_t)g, c2, c.k0, c.k1,
-                                         (kb[(j + 1) >> 1] >> (16 * ((j + 1) & 1))) & 0xFFFFu, zacc, dbg);
+                                         thr2, c.c0w, (uint32_t)g, c2, c.k0, c.k1, zq, zacc, dbg);
     }
   }
 
