@@ -5,7 +5,7 @@
   torchrun --nproc-per-node N ... bench.py --gpus N ...        (one rank per GPU, weak scaling)
 
 A "step" = one pass of the hot path over one batch of synthetic windows: calibration of the BatchNorm
-statistics (4096 windows x 2 passes, exact layer-synchronous path) + the fused tcgen05 kernel
+statistics (32768 windows x 2 passes, statistics sweeps of the tensor-core kernel) + the fused tcgen05 kernel
 (T stochastic passes + per-window reductions) [+ NCCL all-gather of the per-window metrics when N > 1].
 Prints ONE JSON line (rank 0).  Timing: CUDA events on the launching stream, barrier + synchronize on both
 sides, max over ranks; inputs (1.9 GB float64 per GPU) are larger than L2 (126 MB).
@@ -286,7 +286,7 @@ def main():
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
                 "config": {"workload": f"MC Dropout T={T} passes with entropy/MI/variance on {n} synthetic windows per GPU (BASELINE configs[1])",
-                           "windows_per_gpu": n, "passes": T, "bn_mode": "calibrated (4096 windows x 2 passes, inside the step)",
+                           "windows_per_gpu": n, "passes": T, "bn_mode": "calibrated (32768 windows x 2 passes, inside the step)",
                            "rng": "Philox4x32-10 in-kernel", "input": "float64 (N,60,4), 1.92 GB per GPU > L2, no L2 flush needed",
                            "unique_windows": n_unique, "collective": "nccl all_gather of per-window metrics" if world > 1 else "none"},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,

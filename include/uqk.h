@@ -87,8 +87,9 @@ int uqk_forward_det(uqk_handle* h, int member, const void* x_dev, int x_dtype, i
                     float* probs_dev, void* stream);
 
 /* Estimate the per-layer batch statistics that Keras training=True would use, on n_windows windows and
- * n_passes stochastic passes (exact layer-synchronous fp32 path), average them over the passes and freeze
- * them for UQK_BN_CALIBRATED.  Enqueued on stream. */
+ * n_passes stochastic passes, average them over the passes and freeze them for UQK_BN_CALIBRATED.  Up to 8192
+ * windows (option "calib_fp32_max") the exact fp32 layer-synchronous kernels compute them; larger sets go through
+ * the statistics sweeps of the tensor-core kernel (same definition, bf16 operands).  Enqueued on stream. */
 int uqk_calibrate(uqk_handle* h, const void* x_dev, int x_dtype, int64_t n_windows, int n_passes, uint64_t seed,
                   void* stream);
 /* Read back / install the frozen statistics: mean and var are host arrays of 6 x 256 floats (layer-major,

@@ -123,3 +123,28 @@ def test_exact_batch_large_t_goes_through_hbm(uqk):
     out = eng.mcd(x, n_passes=T, seed=3, bn_mode="batch", precision="bf16", return_probs=True)
     assert out["probs"].shape == (T, n) and np.isfinite(out["probs"]).all()
     np.testing.assert_array_equal(out["mean_pred"], eng.reduce(out["probs"])["mean_pred"])
+
+
+def test_tensor_core_calibration_matches_the_fp32_calibration(uqk):
+    """uqk_calibrate above `calib_fp32_max` windows runs the statistics sweeps: same definition (pass-averaged batch
+    mean / biased variance of the exact training=True forward, same Philox masks) as the fp32 path, bf16 operands."""
+    eng = engine_with_members()
+    n, passes, seed = 1500, 2, 12
+    x = _x(uqk, n, seed=15)
+    eng.calibrate(x, n_windows=n, n_passes=passes, seed=seed)
+    m32, v32 = eng.get_bn_stats()
+    eng.option("calib_fp32_max", 0)
+    try:
+        eng.calibrate(x, n_windows=n, n_passes=passes, seed=seed)
+        mtc, vtc = eng.get_bn_stats()
+        eng.calibrate(x, n_windows=n, n_passes=passes, seed=seed)
+        mtc2, vtc2 = eng.get_bn_stats()
+    finally:
+        eng.option("calib_fp32_max", 8192)
+    for l, b in enumerate(uqk.arch.BLOCKS):
+        a, c = m32[l, :b.cout], mtc[l, :b.cout]
+        assert np.abs(a - c).max() < 2e-2 * max(1.0, np.abs(a).max()), (l, np.abs(a - c).max())
+        a, c = v32[l, :b.cout], vtc[l, :b.cout]
+        assert np.abs(a - c).max() < 4e-2 * np.abs(a).max(), (l, np.abs(a - c).max())
+    np.testing.assert_array_equal(mtc, mtc2)          # integer statistics: bit-reproducible
+    np.testing.assert_array_equal(vtc, vtc2)

@@ -45,6 +45,7 @@ struct Handle {
   float* d_dbg = nullptr;         // 6 x 128 x 256 debug dump of the fused kernel (tests)
   int variant = 0;
   int dbg_dump = 0;
+  int64_t calib_fp32_max = 8192;  // calibration sets up to this size use the fp32 layer-synchronous kernels
   // cross-rank exchange of batch statistics (uqk_set_stats_exchange)
   uqk_stats_exchange_fn xchg = nullptr;
   void* xchg_user = nullptr;
@@ -148,8 +149,10 @@ static int run_fused(Handle* h, int member0, const void* x, int x_dtype, int64_t
 // (sum, sum of squares) with the earlier layers already normalised exactly -- and a 7th, ordinary run produces the
 // probabilities with all six layers' statistics in place.  Cost: 3.67x the flops of one run (layers are recomputed
 // instead of spilling N x T x 60 x Cout activations to HBM); all T passes share each sweep.
-static int run_fused_exact(Handle* h, const void* x, int x_dtype, int64_t n, int n_passes, uint64_t seed, int64_t window_base,
-                           const uint32_t* mask_bits, float* probs, const MetricsOut& out, bool want_metrics, cudaStream_t s) {
+// The six statistics sweeps: leaves every pass's BatchNorm affine in h->d_tables_pass and, when `frozen` is given, the
+// pass-averaged (mean, variance) of every layer there (tensor-core calibration).  Fills `p` for the caller's final run.
+static int run_exact_sweeps(Handle* h, const void* x, int x_dtype, int64_t n, int n_passes, uint64_t seed,
+                            int64_t window_base, const uint32_t* mask_bits, float* frozen, FusedParams& p, cudaStream_t s) {
   int rc;
   if ((rc = ensure(&h->d_tables_pass, &h->tables_pass_cap, (size_t)n_passes * kTableFloats))) return rc;
   if ((rc = ensure(&h->d_stats_pass, &h->stats_pass_cap, (size_t)n_passes * 2 * kMaxCh * 2))) return rc;
@@ -159,13 +162,12 @@ static int run_fused_exact(Handle* h, const void* x, int x_dtype, int64_t n, int
   if ((rc = exact_replicate_tables(h->d_table_mcd, n_passes, h->d_tables_pass, s))) return rc;
   const bool exchanging = h->xchg != nullptr;
   const int64_t stat_windows = exchanging ? h->xchg_global_n : n;
-  if (stat_windows < 1) return UQK_OK;
-  const size_t pb = fused_packed_bytes();
-  FusedParams p{};
+  p = FusedParams{};
   p.x = x; p.x_dtype = x_dtype; p.n = n; p.n_groups = n_passes; p.mode_de = 0; p.dropout = 1;
   p.seed = seed; p.window_base = window_base; p.mask_bits = mask_bits;
-  p.packed = h->d_packed; p.packed_pair = h->d_packed_pair; (void)pb;
+  p.packed = h->d_packed; p.packed_pair = h->d_packed_pair;
   p.tables = h->d_tables_pass; p.tab_per_group = 1; p.err_flag = h->d_err; p.variant = h->variant;
+  if (stat_windows < 1) return UQK_OK;
   for (int k = 0; k < kBlocks; ++k) {
     UQK_CUDA(cudaMemsetAsync(stats, 0, sizeof(unsigned long long) * (size_t)n_passes * 2 * kMaxCh, s));
     p.stats = stats; p.n_layers = k + 1;
@@ -176,8 +178,24 @@ static int run_fused_exact(Handle* h, const void* x, int x_dtype, int64_t n, int
       return UQK_E_STATE;
     }
     if ((rc = exact_layer_tables(h->d_blobs, stats, (double)stat_windows * kL, k, n_passes, h->d_tables_pass, s))) return rc;
+    if (frozen && (rc = exact_layer_average(stats, (double)stat_windows * kL, k, n_passes, frozen, s))) return rc;
   }
   p.stats = nullptr; p.n_layers = 0;
+  return UQK_OK;
+}
+
+// Exact Keras `training=True` semantics on the tensor-core kernel (uq_techniques.py:22: BatchNormalization uses the
+// statistics of the whole call).  The statistics of layer k depend on the normalised output of layers < k over ALL
+// windows, so the passes are swept k = 1..6 times through layers [0, k) -- sweep k accumulates layer k's per-pass
+// (sum, sum of squares) with the earlier layers already normalised exactly -- and a 7th, ordinary run produces the
+// probabilities with all six layers' statistics in place.  Cost: 3.67x the flops of one run (layers are recomputed
+// instead of spilling N x T x 60 x Cout activations to HBM); all T passes share each sweep.
+static int run_fused_exact(Handle* h, const void* x, int x_dtype, int64_t n, int n_passes, uint64_t seed, int64_t window_base,
+                           const uint32_t* mask_bits, float* probs, const MetricsOut& out, bool want_metrics, cudaStream_t s) {
+  FusedParams p{};
+  int rc = run_exact_sweeps(h, x, x_dtype, n, n_passes, seed, window_base, mask_bits, nullptr, p, s);
+  if (rc) return rc;
+  if (n == 0) return UQK_OK;
   p.dbg_act = h->dbg_dump ? h->d_dbg : nullptr;
   if (n_passes <= kMaxFusedGroups) {
     p.probs = probs; p.out = out;
@@ -253,6 +271,7 @@ int uqk_set_option(uqk_handle* hh, const char* key, int64_t value) {
   Handle* h = reinterpret_cast<Handle*>(hh);
   if (!strcmp(key, "variant")) { h->variant = (int)value; return UQK_OK; }
   if (!strcmp(key, "dbg_dump")) { h->dbg_dump = (int)value; return UQK_OK; }
+  if (!strcmp(key, "calib_fp32_max")) { h->calib_fp32_max = value; return UQK_OK; }   // see uqk_calibrate
   set_error("unknown option '%s'", key);
   return UQK_E_BADARG;
 }
@@ -319,6 +338,16 @@ int uqk_calibrate(uqk_handle* hh, const void* x_dev, int x_dtype, int64_t n, int
   if (rc) return rc;
   UQK_CUDA(cudaSetDevice(h->device));
   cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (n > h->calib_fp32_max) {
+    // larger calibration sets go through the statistics sweeps of the tensor-core kernel (same definition: per-pass
+    // batch statistics of the exact training=True forward, averaged over the passes)
+    if (n_passes > kMaxFusedGroups) { set_error("calibration on more than %lld windows takes at most %d passes",
+                                                (long long)h->calib_fp32_max, kMaxFusedGroups); return UQK_E_BADARG; }
+    FusedParams p{};
+    if ((rc = run_exact_sweeps(h, x_dev, x_dtype, n, n_passes, seed, 0, nullptr, h->d_frozen, p, s))) return rc;
+    h->have_frozen = true;
+    return UQK_OK;
+  }
   if ((rc = ensure(&h->d_probs_tmp, &h->probs_cap, (size_t)n * n_passes))) return rc;
   UQK_CUDA(cudaMemsetAsync(h->d_accum, 0, sizeof(double) * 2 * kBlocks * kMaxCh, s));
   rc = run_layersync(h, 0, x_dev, x_dtype, n, n_passes, false, true, UQK_BN_BATCH, seed, 0, nullptr, h->d_probs_tmp,

@@ -194,6 +194,31 @@ __global__ void replicate_table_kernel(const float* __restrict__ base, float* __
   if (i < kTableFloats) tables[(size_t)blockIdx.y * kTableFloats + i] = base[i];
 }
 
+// Calibration on the tensor-core sweeps: average the per-pass batch (mean, biased variance) of `layer` over the passes
+// into the frozen statistics (frozen[0..] = means 6 x 256, frozen[6*256..] = variances).  One thread per channel.
+__global__ void exact_layer_average_kernel(const unsigned long long* __restrict__ stats, double count, int layer, int cout,
+                                           int n_groups, float* __restrict__ frozen) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= cout) return;
+  double am = 0.0, av = 0.0;
+  for (int g = 0; g < n_groups; ++g) {
+    const long long* q = reinterpret_cast<const long long*>(stats) + (size_t)g * 2 * kMaxCh;
+    const double mu = (double)q[2 * c] / kFusedStatScale / count;
+    double var = (double)q[2 * c + 1] / kFusedStatScale / count - mu * mu;
+    if (var < 0) var = 0;
+    am += mu;
+    av += var;
+  }
+  frozen[layer * kMaxCh + c] = (float)(am / (double)n_groups);
+  frozen[(kBlocks + layer) * kMaxCh + c] = (float)(av / (double)n_groups);
+}
+
+int exact_layer_average(const unsigned long long* stats, double count, int layer, int n_groups, float* frozen, cudaStream_t s) {
+  exact_layer_average_kernel<<<1, kMaxCh, 0, s>>>(stats, count, layer, block_def(layer).cout, n_groups, frozen);
+  UQK_LAUNCH_CHECK();
+  return UQK_OK;
+}
+
 int exact_replicate_tables(const float* base_table, int n_groups, float* tables, cudaStream_t s) {
   replicate_table_kernel<<<dim3((kTableFloats + 255) / 256, n_groups), 256, 0, s>>>(base_table, tables);
   UQK_LAUNCH_CHECK();

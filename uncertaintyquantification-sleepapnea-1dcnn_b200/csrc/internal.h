@@ -76,4 +76,6 @@ int exact_replicate_tables(const float* base_table, int n_groups, float* tables,
 int exact_layer_tables(const float* blob_dev, const unsigned long long* stats, double count, int layer, int n_groups,
                        float* tables, cudaStream_t s);
 
+int exact_layer_average(const unsigned long long* stats, double count, int layer, int n_groups, float* frozen, cudaStream_t s);
+
 }  // namespace uqk

@@ -146,9 +146,10 @@ class Engine:
                                                 probs.data_ptr(), self._stream()), "uqk_forward_det")
             return probs if device_out else probs.cpu().numpy()
 
-    def calibrate(self, x, n_windows: int = 4096, n_passes: int = 2, seed: int = 2025):
+    def calibrate(self, x, n_windows: int = 32768, n_passes: int = 2, seed: int = 2025):
         """Freezes the batch statistics Keras ``training=True`` would use, estimated on the first
-        ``n_windows`` windows with the exact layer-synchronous path (BN modes)."""
+        ``n_windows`` windows (fp32 layer-synchronous kernels up to 8192 windows, the statistics sweeps of the
+        tensor-core kernel above; see DESIGN.md, BN modes)."""
         with torch.cuda.device(self.device):
             if isinstance(x, torch.Tensor):
                 xs = x[:n_windows]

@@ -100,7 +100,7 @@ class StatsExchange:
 
 
 def sharded_mc_dropout_uq(uq_module, model, x, n_pred: int = 50, patient_ids=None, seed: Optional[int] = None,
-                          bn_mode: str = "calibrated", calib_windows: int = 4096, group=None, **kw) -> Dict[str, np.ndarray]:
+                          bn_mode: str = "calibrated", calib_windows: int = 32768, group=None, **kw) -> Dict[str, np.ndarray]:
     """Each rank runs the MC-Dropout path on its shard of ``x`` (host array, identical on all ranks) and the
     per-window metrics are gathered on every rank.  The dropout masks are keyed by the global window index.
     ``bn_mode='calibrated'``: every rank estimates the frozen statistics on the SAME global windows

@@ -71,7 +71,7 @@ def mc_dropout_predict(model, x_test_data: np.ndarray, n_pred: int = 50) -> np.n
         if n <= int(_env("UQK_EXACT_MAX_WINDOWS", "16384")) and "UQK_PRECISION" not in os.environ:
             prec = "fp32"
     elif mode == "calibrated" and not eng.calibrated:
-        eng.calibrate(x, n_windows=int(_env("UQK_CALIB_WINDOWS", "4096")), n_passes=2, seed=_seed())
+        eng.calibrate(x, n_windows=int(_env("UQK_CALIB_WINDOWS", "32768")), n_passes=2, seed=_seed())
     out = eng.mcd(x, n_passes=int(n_pred), seed=_seed(), bn_mode=mode, precision=prec, return_probs=True, metrics=())
     mc_predictions = out["probs"].reshape(int(n_pred), n, 1)
     print(f"MC Dropout completed in {time.time()-t0:.1f}s ({n_pred} passes)")
@@ -112,13 +112,13 @@ def _finish_uq(out: Dict, y_true) -> Dict:
 
 def mc_dropout_uq(model, x_test_data, n_pred: int = 50, *, y_true=None, return_probs: bool = False,
                   bn_mode: str = "calibrated", precision: str = "bf16", seed: Optional[int] = None, masks=None,
-                  calib_windows: int = 4096, calib_passes: int = 2, recalibrate: bool = True,
+                  calib_windows: int = 32768, calib_passes: int = 2, recalibrate: bool = True,
                   device_out: bool = False, window_base: int = 0) -> Dict:
     """mc_dropout_predict + uq_evaluation_dist + the drivers' inline CSV metrics in ONE fused call: the
     (T,N) probability tensor is never written to HBM unless ``return_probs``.  Returns the per-window arrays of
     uq_techniques.py:103-108 plus ``predictive_entropy_bits`` / ``predicted_label``
     (analyze_mcd_patient_level.py:113-117).  ``bn_mode='calibrated'`` first estimates the batch statistics on
-    ``calib_windows`` windows with the exact layer-synchronous path (inside this call when ``recalibrate``);
+    ``calib_windows`` windows with the exact path (inside this call when ``recalibrate``);
     ``bn_mode='batch'`` is the exact Keras ``training=True`` behaviour (statistics of all windows of this call):
     ``precision='bf16'`` sweeps the tensor-core kernel once per layer, ``'fp32'`` uses the layer-synchronous kernels.
     ``window_base`` = global index of the first window (multi-GPU shards: masks are keyed by the global index)."""
