@@ -118,8 +118,12 @@ __device__ __forceinline__ float safe_entropy2(float p) {
   float q0 = fminf(fmaxf(1.0f - p, eps), 1.0f);
   float q1 = fminf(fmaxf(p, eps), 1.0f);
   const float s = q0 + q1;
-  q0 = q0 / s;
-  q1 = q1 / s;
+  // scipy renormalises the row; in float32 (1 - p) + p rounds to exactly 1 for almost every p, and x / 1 == x, so the
+  // two IEEE divisions run only for the rare rows whose sum is not 1 (same result bit for bit, ~20 % fewer instructions)
+  if (s != 1.0f) {
+    q0 = q0 / s;
+    q1 = q1 / s;
+  }
   return (-q0 * logf(q0)) + (-q1 * logf(q1));
 }
 // log2 entropy of the drivers (analyze_mcd_patient_level.py:113-115), float32 with NumPy-2 weak scalars
