@@ -129,6 +129,56 @@ bootstrap_kernel(const float* __restrict__ var, const float* __restrict__ tot, c
   }
 }
 
+// Array-of-structs staging for uqk_bootstrap: the five per-window values a resample needs share one 32-byte L2 sector,
+// so a random gather costs ONE sector instead of five (the gathers, not the index stream, bound this kernel: 5.7 MB
+// arrays stay in L2 and every 4-byte random access moves a whole sector).
+struct __align__(32) BootRow { float var, tot, expc, mi; int32_t y; int32_t pad[3]; };
+
+__global__ void bootstrap_pack_kernel(const float* __restrict__ var, const float* __restrict__ tot,
+                                      const float* __restrict__ expc, const float* __restrict__ mi,
+                                      const int32_t* __restrict__ y, int64_t n, BootRow* __restrict__ rows) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    BootRow r;
+    r.var = var[i]; r.tot = tot[i]; r.expc = expc[i]; r.mi = mi[i]; r.y = y[i]; r.pad[0] = r.pad[1] = r.pad[2] = 0;
+    rows[i] = r;
+  }
+}
+
+__global__ void __launch_bounds__(kBootThreads)
+bootstrap_rows_kernel(const BootRow* __restrict__ rows, const int64_t* __restrict__ idx, int64_t n,
+                      double* __restrict__ sums /* (n_boot, 8) */) {
+  const int b = blockIdx.y;
+  const int64_t* ib = idx + (size_t)b * n;
+  double a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (int64_t i = (int64_t)blockIdx.x * kBootThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kBootThreads) {
+    const int64_t j = __ldcs(ib + i);
+    const float4 f = __ldg(reinterpret_cast<const float4*>(rows + j));
+    const int yy = __ldg(&rows[j].y);
+    const double v = (double)f.x;
+    a[0] += v;
+    if (yy == 0) { a[1] += v; a[2] += 1.0; }
+    if (yy == 1) { a[3] += v; a[4] += 1.0; }
+    a[5] += (double)f.y;
+    a[6] += (double)f.z;
+    a[7] += (double)f.w;
+  }
+  __shared__ double red[8][kBootThreads / 32];
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    double v = a[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (l == 0) red[k][w] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < 8) {
+    double t = 0;
+    for (int i = 0; i < kBootThreads / 32; ++i) t += red[threadIdx.x][i];
+    atomicAdd(&sums[(size_t)b * 8 + threadIdx.x], t);
+  }
+}
+
 __global__ void bootstrap_finalize_kernel(const double* __restrict__ sums, int n_boot, int64_t n, double* __restrict__ out) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= n_boot) return;
@@ -181,14 +231,19 @@ int uqk_bootstrap(const float* variance_dev, const float* total_entropy_dev, con
   }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   double* sums = nullptr;
+  BootRow* rows = nullptr;
   UQK_CUDA(cudaMallocAsync(&sums, sizeof(double) * 8 * n_boot, s));
+  UQK_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&rows), sizeof(BootRow) * (size_t)n_windows, s));
   UQK_CUDA(cudaMemsetAsync(sums, 0, sizeof(double) * 8 * n_boot, s));
+  bootstrap_pack_kernel<<<(int)std::min<int64_t>((n_windows + 255) / 256, 148 * 8), 256, 0, s>>>(
+      variance_dev, total_entropy_dev, expected_entropy_dev, mutual_info_dev, y_dev, n_windows, rows);
+  UQK_LAUNCH_CHECK();
   const int gx = (int)std::max<int64_t>(1, std::min<int64_t>((n_windows + kBootThreads * 8 - 1) / (kBootThreads * 8), 148));
-  bootstrap_kernel<<<dim3(gx, n_boot), kBootThreads, 0, s>>>(variance_dev, total_entropy_dev, expected_entropy_dev,
-                                                            mutual_info_dev, y_dev, idx_dev, n_windows, sums);
+  bootstrap_rows_kernel<<<dim3(gx, n_boot), kBootThreads, 0, s>>>(rows, idx_dev, n_windows, sums);
   UQK_LAUNCH_CHECK();
   bootstrap_finalize_kernel<<<(n_boot + 127) / 128, 128, 0, s>>>(sums, n_boot, n_windows, out_dev);
   UQK_LAUNCH_CHECK();
+  UQK_CUDA(cudaFreeAsync(rows, s));
   UQK_CUDA(cudaFreeAsync(sums, s));
   return UQK_OK;
 }

@@ -80,6 +80,26 @@ int launch_reduce(const float* probs, int n_pass, int64_t n, const MetricsOut& o
 // float64 like NumPy on the float64 CSV data.  One warp per window: lane l owns rows l and l+32 (all 4 channels);
 // HBM-bound: 1920 B read + 1920 B written per float64 window.
 namespace uqk {
+__device__ __forceinline__ void load_row4(const double* p, bool ok, double (&v)[4]) {
+  if (ok) {
+    const double2 a = __ldcs(reinterpret_cast<const double2*>(p)), b = __ldcs(reinterpret_cast<const double2*>(p) + 1);
+    v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+  } else { v[0] = v[1] = v[2] = v[3] = 0.0; }
+}
+__device__ __forceinline__ void load_row4(const float* p, bool ok, double (&v)[4]) {
+  if (ok) {
+    const float4 a = __ldcs(reinterpret_cast<const float4*>(p));
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+  } else { v[0] = v[1] = v[2] = v[3] = 0.0; }
+}
+__device__ __forceinline__ void store_row4(double* p, const double (&z)[4]) {
+  __stcs(reinterpret_cast<double2*>(p), make_double2(z[0], z[1]));
+  __stcs(reinterpret_cast<double2*>(p) + 1, make_double2(z[2], z[3]));
+}
+__device__ __forceinline__ void store_row4(float* p, const double (&z)[4]) {
+  __stcs(reinterpret_cast<float4*>(p), make_float4((float)z[0], (float)z[1], (float)z[2], (float)z[3]));
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256)
 standardize_kernel(const T* __restrict__ x, T* __restrict__ out, int64_t n, double eps) {
@@ -93,11 +113,9 @@ standardize_kernel(const T* __restrict__ x, T* __restrict__ out, int64_t n, doub
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
       const int r = lane + 32 * h;
+      load_row4(xw + r * kF, r < kL, v[h]);     // one row = 4 channels = one 16 / 2 x 16 byte access
 #pragma unroll
-      for (int c = 0; c < kF; ++c) {
-        v[h][c] = r < kL ? (double)xw[r * kF + c] : 0.0;
-        s[c] += v[h][c];
-      }
+      for (int c = 0; c < kF; ++c) s[c] += v[h][c];
     }
 #pragma unroll
     for (int c = 0; c < kF; ++c) {
@@ -126,8 +144,10 @@ standardize_kernel(const T* __restrict__ x, T* __restrict__ out, int64_t n, doub
     for (int h = 0; h < 2; ++h) {
       const int r = lane + 32 * h;
       if (r < kL) {
+        double z[kF];
 #pragma unroll
-        for (int c = 0; c < kF; ++c) ow[r * kF + c] = (T)((v[h][c] - s[c]) / q[c]);
+        for (int c = 0; c < kF; ++c) z[c] = (v[h][c] - s[c]) / q[c];
+        store_row4(ow + r * kF, z);
       }
     }
   }
@@ -140,6 +160,9 @@ extern "C" int uqk_standardize(const void* x_dev, int x_dtype, int64_t n_windows
   if (n_windows == 0) return UQK_OK;
   if (!x_dev || !out_dev) { set_error("NULL argument"); return UQK_E_BADARG; }
   if (x_dtype != UQK_F32 && x_dtype != UQK_F64) { set_error("x_dtype must be UQK_F32 or UQK_F64"); return UQK_E_BADARG; }
+  if ((reinterpret_cast<uintptr_t>(x_dev) | reinterpret_cast<uintptr_t>(out_dev)) & 15) {
+    set_error("x_dev and out_dev must be 16-byte aligned (rows are moved with 16-byte accesses)"); return UQK_E_BADARG;
+  }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int grid = (int)std::min<int64_t>((n_windows * 32 + 255) / 256, 148 * 16);
   if (x_dtype == UQK_F64)
