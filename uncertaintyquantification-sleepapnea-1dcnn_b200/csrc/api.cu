@@ -42,6 +42,8 @@ struct Handle {
   float* d_probs_tmp = nullptr; size_t probs_cap = 0;
   float* d_tables_pass = nullptr; size_t tables_pass_cap = 0;   // exact batch-statistic mode: one epilogue table per pass
   float* d_stats_pass = nullptr; size_t stats_pass_cap = 0;     // ... and n_passes x 2 x 256 int64 statistics (as floats x2)
+  float* d_head_sum = nullptr; size_t head_sum_cap = 0;         // exact mode: head partials of one chunk of passes
+  float* d_head_cnt = nullptr; size_t head_cnt_cap = 0;         // ... kept-row counts (bytes, allocated in floats)
   float* d_dbg = nullptr;         // 6 x 128 x 256 debug dump of the fused kernel (tests)
   int variant = 0;
   int dbg_dump = 0;
@@ -143,16 +145,12 @@ static int run_fused(Handle* h, int member0, const void* x, int x_dtype, int64_t
   return want_metrics ? launch_reduce(probs, n_groups, n, out, s) : UQK_OK;
 }
 
-// Exact Keras `training=True` semantics on the tensor-core kernel (uq_techniques.py:22: BatchNormalization uses the
-// statistics of the whole call).  The statistics of layer k depend on the normalised output of layers < k over ALL
-// windows, so the passes are swept k = 1..6 times through layers [0, k) -- sweep k accumulates layer k's per-pass
-// (sum, sum of squares) with the earlier layers already normalised exactly -- and a 7th, ordinary run produces the
-// probabilities with all six layers' statistics in place.  Cost: 3.67x the flops of one run (layers are recomputed
-// instead of spilling N x T x 60 x Cout activations to HBM); all T passes share each sweep.
-// The six statistics sweeps: leaves every pass's BatchNorm affine in h->d_tables_pass and, when `frozen` is given, the
-// pass-averaged (mean, variance) of every layer there (tensor-core calibration).  Fills `p` for the caller's final run.
-static int run_exact_sweeps(Handle* h, const void* x, int x_dtype, int64_t n, int n_passes, uint64_t seed,
-                            int64_t window_base, const uint32_t* mask_bits, float* frozen, FusedParams& p, cudaStream_t s) {
+// The six statistics sweeps over passes [pass0, pass0 + n_passes): leaves every pass's BatchNorm affine in
+// h->d_tables_pass and, when `frozen` is given, the pass-averaged (mean, variance) of every layer there (tensor-core
+// calibration).  When head buffers are given the sixth sweep also emits the head partials (see exact_head_kernel).
+static int run_exact_sweeps(Handle* h, const void* x, int x_dtype, int64_t n, int pass0, int n_passes, uint64_t seed,
+                            int64_t window_base, const uint32_t* mask_bits, float* frozen, float* head_sum,
+                            unsigned char* head_cnt, cudaStream_t s) {
   int rc;
   if ((rc = ensure(&h->d_tables_pass, &h->tables_pass_cap, (size_t)n_passes * kTableFloats))) return rc;
   if ((rc = ensure(&h->d_stats_pass, &h->stats_pass_cap, (size_t)n_passes * 2 * kMaxCh * 2))) return rc;
@@ -162,15 +160,18 @@ static int run_exact_sweeps(Handle* h, const void* x, int x_dtype, int64_t n, in
   if ((rc = exact_replicate_tables(h->d_table_mcd, n_passes, h->d_tables_pass, s))) return rc;
   const bool exchanging = h->xchg != nullptr;
   const int64_t stat_windows = exchanging ? h->xchg_global_n : n;
-  p = FusedParams{};
+  FusedParams p{};
   p.x = x; p.x_dtype = x_dtype; p.n = n; p.n_groups = n_passes; p.mode_de = 0; p.dropout = 1;
-  p.seed = seed; p.window_base = window_base; p.mask_bits = mask_bits;
+  p.seed = seed; p.window_base = window_base; p.pass_base = pass0;
+  p.mask_bits = mask_bits ? mask_bits + (size_t)pass0 * n * kBlocks * kL * 8 : nullptr;
   p.packed = h->d_packed; p.packed_pair = h->d_packed_pair;
   p.tables = h->d_tables_pass; p.tab_per_group = 1; p.err_flag = h->d_err; p.variant = h->variant;
   if (stat_windows < 1) return UQK_OK;
   for (int k = 0; k < kBlocks; ++k) {
     UQK_CUDA(cudaMemsetAsync(stats, 0, sizeof(unsigned long long) * (size_t)n_passes * 2 * kMaxCh, s));
     p.stats = stats; p.n_layers = k + 1;
+    p.head_sum = k == kBlocks - 1 ? head_sum : nullptr;
+    p.head_cnt = k == kBlocks - 1 ? head_cnt : nullptr;
     if ((rc = fused_launch(p, s))) return rc;           // n == 0 (empty shard): no launch, statistics stay zero
     if (exchanging &&
         h->xchg(h->xchg_user, reinterpret_cast<long long*>(stats), n_passes * 2 * kMaxCh, static_cast<void*>(s)) != 0) {
@@ -180,33 +181,43 @@ static int run_exact_sweeps(Handle* h, const void* x, int x_dtype, int64_t n, in
     if ((rc = exact_layer_tables(h->d_blobs, stats, (double)stat_windows * kL, k, n_passes, h->d_tables_pass, s))) return rc;
     if (frozen && (rc = exact_layer_average(stats, (double)stat_windows * kL, k, n_passes, frozen, s))) return rc;
   }
-  p.stats = nullptr; p.n_layers = 0;
   return UQK_OK;
 }
 
 // Exact Keras `training=True` semantics on the tensor-core kernel (uq_techniques.py:22: BatchNormalization uses the
 // statistics of the whole call).  The statistics of layer k depend on the normalised output of layers < k over ALL
-// windows, so the passes are swept k = 1..6 times through layers [0, k) -- sweep k accumulates layer k's per-pass
-// (sum, sum of squares) with the earlier layers already normalised exactly -- and a 7th, ordinary run produces the
-// probabilities with all six layers' statistics in place.  Cost: 3.67x the flops of one run (layers are recomputed
-// instead of spilling N x T x 60 x Cout activations to HBM); all T passes share each sweep.
+// windows, so the passes are swept k = 1..6 times through layers [0, k): sweep k accumulates layer k's per-pass
+// (sum, sum of squares) with the earlier layers already normalised exactly.  The sixth sweep also leaves, per
+// (pass, window), the dropout-masked column sums of the layer-6 output; BatchNorm-6, GlobalAveragePooling and Dense are
+// linear in them, so a small kernel turns them into the probabilities once layer 6's statistics are known -- no seventh
+// pass over the network.  Cost: 2.67x the flops of one run (layers are recomputed instead of spilling
+// N x T x 60 x Cout activations to HBM); the passes are processed in chunks so that the head partials
+// (960 B per window-pass) stay within kExactHeadBudget.
+constexpr size_t kExactHeadBudget = (size_t)32 << 30;
+
 static int run_fused_exact(Handle* h, const void* x, int x_dtype, int64_t n, int n_passes, uint64_t seed, int64_t window_base,
                            const uint32_t* mask_bits, float* probs, const MetricsOut& out, bool want_metrics, cudaStream_t s) {
-  FusedParams p{};
-  int rc = run_exact_sweeps(h, x, x_dtype, n, n_passes, seed, window_base, mask_bits, nullptr, p, s);
-  if (rc) return rc;
+  int rc;
+  const bool exchanging = h->xchg != nullptr;
+  // every rank of a sharded call must cut the passes identically: size the chunks by the windows of the whole call
+  const int64_t n_for_chunks = std::max<int64_t>(1, exchanging ? h->xchg_global_n : n);
+  const size_t per_pass = (size_t)n_for_chunks * 2 * kDenseIn * 5;
+  const int chunk = (int)std::max<size_t>(1, std::min<size_t>((size_t)n_passes, std::min<size_t>(kExactHeadBudget / per_pass, kMaxFusedGroups)));
+  if (n > 0) {
+    if ((rc = ensure(&h->d_head_sum, &h->head_sum_cap, (size_t)chunk * n * 2 * kDenseIn))) return rc;
+    if ((rc = ensure(&h->d_head_cnt, &h->head_cnt_cap, ((size_t)chunk * n * 2 * kDenseIn + 3) / 4))) return rc;
+    if (!probs) {
+      if ((rc = ensure(&h->d_probs_tmp, &h->probs_cap, (size_t)n * n_passes))) return rc;
+      probs = h->d_probs_tmp;
+    }
+  }
+  unsigned char* head_cnt = reinterpret_cast<unsigned char*>(h->d_head_cnt);
+  for (int g0 = 0; g0 < n_passes; g0 += chunk) {
+    const int gc = std::min(chunk, n_passes - g0);
+    if ((rc = run_exact_sweeps(h, x, x_dtype, n, g0, gc, seed, window_base, mask_bits, nullptr, h->d_head_sum, head_cnt, s))) return rc;
+    if (n > 0 && (rc = exact_head(h->d_head_sum, head_cnt, h->d_tables_pass, gc, n, probs + (size_t)g0 * n, s))) return rc;
+  }
   if (n == 0) return UQK_OK;
-  p.dbg_act = h->dbg_dump ? h->d_dbg : nullptr;
-  if (n_passes <= kMaxFusedGroups) {
-    p.probs = probs; p.out = out;
-    return fused_launch(p, s);
-  }
-  if (!probs) {
-    if ((rc = ensure(&h->d_probs_tmp, &h->probs_cap, (size_t)n * n_passes))) return rc;
-    probs = h->d_probs_tmp;
-  }
-  p.probs = probs; p.out = MetricsOut{}; p.no_smem_probs = 1;
-  if ((rc = fused_launch(p, s))) return rc;
   return want_metrics ? launch_reduce(probs, n_passes, n, out, s) : UQK_OK;
 }
 
@@ -259,7 +270,7 @@ int uqk_destroy(uqk_handle* hh) {
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
   void* ptrs[] = {h->d_blobs, h->d_packed, h->d_packed_pair, h->d_tables_inf, h->d_table_mcd, h->d_frozen, h->d_stats, h->d_affine,
-                  h->d_accum, h->d_err, h->d_x32, h->d_act[0], h->d_act[1], h->d_probs_tmp, h->d_dbg, h->d_tables_pass, h->d_stats_pass};
+                  h->d_accum, h->d_err, h->d_x32, h->d_act[0], h->d_act[1], h->d_probs_tmp, h->d_dbg, h->d_tables_pass, h->d_stats_pass, h->d_head_sum, h->d_head_cnt};
   for (void* p : ptrs) if (p) cudaFree(p);
   cudaGetLastError();
   delete h;
@@ -343,8 +354,7 @@ int uqk_calibrate(uqk_handle* hh, const void* x_dev, int x_dtype, int64_t n, int
     // batch statistics of the exact training=True forward, averaged over the passes)
     if (n_passes > kMaxFusedGroups) { set_error("calibration on more than %lld windows takes at most %d passes",
                                                 (long long)h->calib_fp32_max, kMaxFusedGroups); return UQK_E_BADARG; }
-    FusedParams p{};
-    if ((rc = run_exact_sweeps(h, x_dev, x_dtype, n, n_passes, seed, 0, nullptr, h->d_frozen, p, s))) return rc;
+    if ((rc = run_exact_sweeps(h, x_dev, x_dtype, n, 0, n_passes, seed, 0, nullptr, h->d_frozen, nullptr, nullptr, s))) return rc;
     h->have_frozen = true;
     return UQK_OK;
   }

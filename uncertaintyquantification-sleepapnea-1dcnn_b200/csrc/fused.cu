@@ -219,6 +219,46 @@ int exact_layer_average(const unsigned long long* stats, double count, int layer
   return UQK_OK;
 }
 
+// Exact mode, last step: probabilities from the head partials of the sixth sweep.  With A = masked column sum and
+// B = kept-row count of a window's layer-6 output, GAP + Dense give z = (1/60) * sum_c w_c (scale_c A_c + shift_c B_c) + b
+// (scale / shift = this pass's BatchNorm affine with the dropout scale folded).  One warp per (pass, window).
+__global__ void __launch_bounds__(256)
+exact_head_kernel(const float* __restrict__ head_sum, const unsigned char* __restrict__ head_cnt,
+                  const float* __restrict__ tables, int n_groups, int64_t n, float* __restrict__ probs /* (n_groups, n) */) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  constexpr int kL6 = kBlocks - 1;
+  for (int64_t i = warp; i < (int64_t)n_groups * n; i += nwarps) {
+    const int g = (int)(i / n);
+    const float* t = tables + (size_t)g * kTableFloats;
+    const float* hs = head_sum + (size_t)i * 2 * kDenseIn;
+    const unsigned char* hc = head_cnt + (size_t)i * 2 * kDenseIn;
+    float z = 0.f;
+#pragma unroll
+    for (int k = 0; k < kDenseIn / 32; ++k) {
+      const int c = lane + 32 * k;
+      const float A = __ldcs(hs + c) + __ldcs(hs + kDenseIn + c);
+      const float B = (float)((int)hc[c] + (int)hc[kDenseIn + c]);
+      const float sc = __ldg(t + kChTotal + ch_off(kL6) + c), sh = __ldg(t + 2 * kChTotal + ch_off(kL6) + c);
+      z = fmaf(__ldg(t + 3 * kChTotal + c), fmaf(sc, A, sh * B), z);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) z += __shfl_xor_sync(0xffffffffu, z, o);
+    if (lane == 0) probs[i] = 1.0f / (1.0f + expf(-(z * (1.0f / (float)kL) + __ldg(t + 3 * kChTotal + kDenseIn))));
+  }
+}
+
+int exact_head(const float* head_sum, const unsigned char* head_cnt, const float* tables, int n_groups, int64_t n, float* probs,
+               cudaStream_t s) {
+  if (n == 0 || n_groups == 0) return UQK_OK;
+  const int64_t warps = (int64_t)n_groups * n;
+  exact_head_kernel<<<(int)std::min<int64_t>((warps * 32 + 255) / 256, 148 * 16), 256, 0, s>>>(head_sum, head_cnt, tables, n_groups,
+                                                                                              n, probs);
+  UQK_LAUNCH_CHECK();
+  return UQK_OK;
+}
+
 int exact_replicate_tables(const float* base_table, int n_groups, float* tables, cudaStream_t s) {
   replicate_table_kernel<<<dim3((kTableFloats + 255) / 256, n_groups), 256, 0, s>>>(base_table, tables);
   UQK_LAUNCH_CHECK();
@@ -387,6 +427,12 @@ struct FusedArgs {
   int n_layers;
   int tab_per_group;              // 1: epilogue tables of group g are tables[g] although the weights are member 0's
   unsigned long long* stats;
+  int pass_base;                  // Philox pass counter of group 0 (exact mode processes the passes in chunks)
+  // last statistics sweep (n_layers == 6): also emit, per (pass, window, row half, channel), the dropout-masked column
+  // sum of the post-ReLU layer-6 output and the number of kept rows -- BatchNorm + GlobalAveragePooling + Dense are
+  // linear in them, so the probabilities follow without another pass over the network (exact_head_kernel)
+  float* head_sum;                // (n_groups, n, 2, 96) float32, or null
+  unsigned char* head_cnt;        // (n_groups, n, 2, 96) uint8
 };
 
 // dropout source of the epilogue
@@ -652,6 +698,48 @@ __device__ __forceinline__ void epi_signal_act(const EpiCtx& c) {
   }
 }
 
+// Keep-flags of this thread's row for layer L (byte-lane layout of keep_insert), all zero for padding rows.
+//  - kDropPhilox: the dropout masks do not depend on the data, so they are generated while the layer's MMAs run and
+//    the epilogue warps would otherwise sleep on the accumulator barrier (10 Philox rounds per 8 channels leave the
+//    critical path of the epilogue);
+//  - kDropBits (mask injection, parity tests): explicit keep-bits from global memory, bit c%32 of word c/32.
+template <int L, int DROP>
+__device__ __forceinline__ void make_keep_flags(const EpiCtx& c, const FusedArgs& a, int g, long long win, uint32_t (&kb)[4]) {
+  constexpr int my = fl_cout(L) / 32;
+  kb[0] = kb[1] = kb[2] = kb[3] = 0u;
+  if (DROP == kDropBits) {
+    const uint32_t* mrow = a.mask_bits + ((((size_t)g * a.n + (c.row_valid ? win : 0)) * kBlocks + L) * kL + (c.row_valid ? c.t : 0)) * 8;
+#pragma unroll
+    for (int j = 0; j < my; ++j) {
+      const int k = c.colhalf + 2 * j;
+      const uint32_t w16 = (__ldg(mrow + (k >> 1)) >> (16 * (k & 1))) & 0xFFFFu;
+#pragma unroll
+      for (int u = 0; u < 4; ++u)      // 4 bits -> bit 7 of 4 bytes (bit k lands on 8k + 7; the partial products never collide)
+        keep_insert(kb, 4 * j + u, (((w16 >> (4 * u)) & 0xFu) * 0x10204080u) & 0x80808080u);
+    }
+  }
+  if (DROP == kDropPhilox) {
+    constexpr uint32_t thr2 = drop_thr15(L) * 0x00010001u;
+    const uint32_t c2 = ((uint32_t)L << 16) | (uint32_t)c.t;
+    const uint32_t pass = (uint32_t)(a.pass_base + g);
+#pragma unroll
+    for (int j = 0; j < my; ++j) {
+      const uint32_t ch8 = (uint32_t)(2 * (c.colhalf + 2 * j));
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        uint32_t g0, g1;
+        philox_keep8(c.c0w, pass, c2, ch8 + (uint32_t)u, c.k0, c.k1, thr2, g0, g1);
+        keep_insert(kb, 4 * j + 2 * u, g0);
+        keep_insert(kb, 4 * j + 2 * u + 1, g1);
+      }
+    }
+  }
+  if (DROP != kDropNone) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) kb[i] = c.row_valid ? kb[i] : 0u;   // padding rows keep nothing
+  }
+}
+
 template <int L, int DROP, bool DBG, int EPI_THREADS>
 __device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, const float* __restrict__ tab_g, int g,
                                           long long win, uint32_t& n_acc, float* probs_s, float* dbg_base) {
@@ -668,41 +756,11 @@ __device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, c
   if (kLastLayer && c.tid_t < kDenseIn + 1) c.tab_w[c.tid_t] = __ldg(tab_g + 3 * kChTotal + c.tid_t);
 
   // keep-flags of this thread's row for this layer (see keep_insert): produced while the layer's MMAs run
-  uint32_t kb[4] = {0u, 0u, 0u, 0u};
+  uint32_t kb[4];
+  make_keep_flags<L, DROP>(c, a, g, win, kb);
   constexpr uint32_t thr2 = drop_thr15(L) * 0x00010001u;
   const uint32_t c2 = ((uint32_t)L << 16) | (uint32_t)c.t;
   const uint32_t row_mask = c.row_valid ? 0xFFFFFFFFu : 0u;   // zero rows = the next layer's `same` padding
-  if (DROP == kDropBits) {
-    // mask-injection mode (parity tests): explicit keep-bits from global memory, bit c%32 of word c/32
-    const uint32_t* mrow = a.mask_bits + ((((size_t)g * a.n + (c.row_valid ? win : 0)) * kBlocks + L) * kL + (c.row_valid ? c.t : 0)) * 8;
-#pragma unroll
-    for (int j = 0; j < my; ++j) {
-      const int k = c.colhalf + 2 * j;
-      const uint32_t w16 = (__ldg(mrow + (k >> 1)) >> (16 * (k & 1))) & 0xFFFFu;
-#pragma unroll
-      for (int u = 0; u < 4; ++u)      // 4 bits -> bit 7 of 4 bytes (bit k lands on 8k + 7; the partial products never collide)
-        keep_insert(kb, 4 * j + u, (((w16 >> (4 * u)) & 0xFu) * 0x10204080u) & 0x80808080u);
-    }
-  }
-  if (DROP == kDropPhilox) {
-    // the dropout masks do not depend on the data: generate them now, while these warps would otherwise sleep on the
-    // accumulator barrier -- the 10 Philox rounds per 8 channels leave the critical path of the epilogue
-#pragma unroll
-    for (int j = 0; j < my; ++j) {
-      const uint32_t ch8 = (uint32_t)(2 * (c.colhalf + 2 * j));
-#pragma unroll
-      for (int u = 0; u < 2; ++u) {
-        uint32_t g0, g1;
-        philox_keep8(c.c0w, (uint32_t)g, c2, ch8 + (uint32_t)u, c.k0, c.k1, thr2, g0, g1);
-        keep_insert(kb, 4 * j + 2 * u, g0);
-        keep_insert(kb, 4 * j + 2 * u + 1, g1);
-      }
-    }
-  }
-  if (DROP != kDropNone) {
-#pragma unroll
-    for (int i = 0; i < 4; ++i) kb[i] = c.row_valid ? kb[i] : 0u;   // padding rows keep nothing
-  }
 
   // one warp polls the accumulator barrier; the others sleep in the named barrier (no issue slots burnt)
   if (c.we == 0) {
@@ -795,10 +853,17 @@ __device__ __forceinline__ float warp_halve16(const float (&v)[16], int lane) {
 // per-channel sum / sum of squares over the valid rows.  One warp's partial covers 32 rows of one window; it is
 // converted to fixed point BEFORE it meets any other partial, so the totals are sums of integers that depend only on
 // (window, row half, channel) -- independent of the grid, of scheduling and of how windows are sharded over GPUs.
-template <int L, int EPI_THREADS>
-__device__ __forceinline__ void epi_stats(const EpiCtx& c, uint32_t& n_acc, unsigned long long* s_stats) {
+template <int L, int DROP, int EPI_THREADS>
+__device__ __forceinline__ void epi_stats(const EpiCtx& c, const FusedArgs& a, int g, long long win, uint32_t& n_acc,
+                                          unsigned long long* s_stats) {
   constexpr int cout = fl_cout(L);
   constexpr int my = cout / 32;
+  constexpr bool kHead = (L == kBlocks - 1);
+  const bool head = kHead && a.head_sum != nullptr;
+  uint32_t kb[4] = {0u, 0u, 0u, 0u};
+  if (kHead) {
+    if (head) make_keep_flags<L, DROP>(c, a, g, win, kb);      // layer-6 dropout masks, in the MMA shadow
+  }
   if (c.we == 0) {
     mbar_wait2(c.bar_acc, n_acc & 1, c.err_flag, 4);
     tc_fence_after();
@@ -808,7 +873,9 @@ __device__ __forceinline__ void epi_stats(const EpiCtx& c, uint32_t& n_acc, unsi
   named_bar_sync(1 + c.tl, EPI_THREADS);
   tc_fence_after();
   uint32_t va[16];
-#pragma unroll 1
+  // (pass, window, row half) block of the head partials; this warp covers rows [32*(quarter&1), +32) of its window
+  const size_t head_row = (((size_t)g * a.n + (win < a.n ? win : 0)) * 2 + (size_t)(c.quarter & 1)) * kDenseIn;
+#pragma unroll
   for (int j = 0; j < my; ++j) {
     const int col0 = 16 * (c.colhalf + 2 * j);
     tmem_ld16(c.taddr + (uint32_t)col0, va);
@@ -825,6 +892,25 @@ __device__ __forceinline__ void epi_stats(const EpiCtx& c, uint32_t& n_acc, unsi
     const int ch = col0 + ((c.lane >> 1) & 15);
     const float mine = (c.lane & 1) ? rq : rs;      // even lane adds the sum, odd lane the sum of squares
     atomicAdd(&s_stats[2 * ch + (c.lane & 1)], (unsigned long long)__double2ll_rn((double)mine * kFusedStatScale));
+    if (kHead) {
+      if (head) {
+        // dropout-masked column sums and kept-row counts of this warp's 32 rows (flags are zero on padding rows)
+        float mv[16], fv[16];
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+          const uint32_t z = keep_extract(kb, 4 * j + (e >> 2));          // quad's flags in the byte sign bits
+          const bool keep = (z >> (8 * (e & 3) + 7)) & 1u;
+          mv[e] = keep ? sv[e] : 0.f;
+          fv[e] = keep ? 1.f : 0.f;
+        }
+        const float ra = warp_halve16(mv, c.lane);
+        const float rb = warp_halve16(fv, c.lane);
+        if (win < a.n) {
+          if (c.lane & 1) a.head_cnt[head_row + ch] = (unsigned char)__float2int_rn(rb);
+          else a.head_sum[head_row + ch] = ra;
+        }
+      }
+    }
   }
   tc_fence_before();   // TMEM reads are complete before this thread lets the next unit's MMAs start
 }
@@ -834,7 +920,7 @@ template <int L, int DROP, int EPI_THREADS>
 __device__ __forceinline__ void epi_sweep(const EpiCtx& c, const FusedArgs& a, const float* __restrict__ tab_g, int g,
                                           long long win, uint32_t& n_acc, unsigned long long* s_stats) {
   if (a.n_layers == L + 1) {
-    epi_stats<L, EPI_THREADS>(c, n_acc, s_stats);
+    epi_stats<L, DROP, EPI_THREADS>(c, a, g, win, n_acc, s_stats);
     return;
   }
   if constexpr (L + 1 < kBlocks) {
@@ -1386,7 +1472,7 @@ template <int NSLOTS, int DROP, bool DBG, bool STAT = false>
 static int launch_pair_variant(const FusedParams& p, cudaStream_t s) {
   using Cfg = PairCfg<NSLOTS>;
   FusedArgs a{};
-  a.x = p.x; a.x_f64 = p.x_dtype == UQK_F64; a.n = p.n; a.n_groups = p.n_groups; a.mode_de = p.mode_de; a.tab_per_group = p.tab_per_group;
+  a.x = p.x; a.x_f64 = p.x_dtype == UQK_F64; a.n = p.n; a.n_groups = p.n_groups; a.mode_de = p.mode_de; a.tab_per_group = p.tab_per_group; a.pass_base = p.pass_base;
   a.k0 = (uint32_t)(p.seed & 0xFFFFFFFFull); a.k1 = (uint32_t)(p.seed >> 32);
   a.window_base = p.window_base; a.mask_bits = p.mask_bits; a.packed = reinterpret_cast<const uint8_t*>(p.packed_pair);
   a.tables = p.tables; a.probs = p.probs; a.out = p.out; a.dbg_act = p.dbg_act; a.err_flag = p.err_flag;
@@ -1394,6 +1480,7 @@ static int launch_pair_variant(const FusedParams& p, cudaStream_t s) {
   a.n_units = (p.n + Cfg::kWpu - 1) / Cfg::kWpu;
   a.smem_probs = (p.no_smem_probs || STAT) ? 0 : 1;
   a.n_layers = STAT ? p.n_layers : kBlocks; a.stats = p.stats;
+  a.pass_base = p.pass_base; a.head_sum = STAT ? p.head_sum : nullptr; a.head_cnt = STAT ? p.head_cnt : nullptr;
   if (STAT && (p.n_layers < 1 || p.n_layers > kBlocks || p.stats == nullptr)) {
     set_error("statistics sweep needs 1 <= n_layers <= 6 and a statistics buffer"); return UQK_E_BADARG;
   }
@@ -1713,7 +1800,7 @@ template <int NSLOTS, int DROP, bool DBG>
 static int launch_pair2_variant(const FusedParams& p, cudaStream_t s) {
   using Cfg = Pair2Cfg<NSLOTS>;
   FusedArgs a{};
-  a.x = p.x; a.x_f64 = p.x_dtype == UQK_F64; a.n = p.n; a.n_groups = p.n_groups; a.mode_de = p.mode_de; a.tab_per_group = p.tab_per_group;
+  a.x = p.x; a.x_f64 = p.x_dtype == UQK_F64; a.n = p.n; a.n_groups = p.n_groups; a.mode_de = p.mode_de; a.tab_per_group = p.tab_per_group; a.pass_base = p.pass_base;
   a.k0 = (uint32_t)(p.seed & 0xFFFFFFFFull); a.k1 = (uint32_t)(p.seed >> 32);
   a.window_base = p.window_base; a.mask_bits = p.mask_bits; a.packed = reinterpret_cast<const uint8_t*>(p.packed_pair);
   a.tables = p.tables; a.probs = p.probs; a.out = p.out; a.dbg_act = p.dbg_act; a.err_flag = p.err_flag;
@@ -1756,7 +1843,7 @@ template <int TILES, int NSLOTS, int DROP, bool DBG>
 static int launch_variant(const FusedParams& p, cudaStream_t s) {
   using Cfg = FusedCfg<TILES, NSLOTS>;
   FusedArgs a{};
-  a.x = p.x; a.x_f64 = p.x_dtype == UQK_F64; a.n = p.n; a.n_groups = p.n_groups; a.mode_de = p.mode_de; a.tab_per_group = p.tab_per_group;
+  a.x = p.x; a.x_f64 = p.x_dtype == UQK_F64; a.n = p.n; a.n_groups = p.n_groups; a.mode_de = p.mode_de; a.tab_per_group = p.tab_per_group; a.pass_base = p.pass_base;
   a.k0 = (uint32_t)(p.seed & 0xFFFFFFFFull); a.k1 = (uint32_t)(p.seed >> 32);
   a.window_base = p.window_base; a.mask_bits = p.mask_bits; a.packed = reinterpret_cast<const uint8_t*>(p.packed);
   a.tables = p.tables; a.probs = p.probs; a.out = p.out; a.dbg_act = p.dbg_act; a.err_flag = p.err_flag;

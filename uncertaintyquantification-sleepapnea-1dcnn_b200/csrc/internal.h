@@ -64,6 +64,9 @@ struct FusedParams {
   int tab_per_group;          // 1: group g reads tables[g] (per-pass BatchNorm affine) with member 0's weights
   int n_layers;               // statistics sweep: layers [0, n_layers) are computed ...
   unsigned long long* stats;  // ... and (sum, sum of squares) of layer n_layers-1 go to stats[g][2*256]; null = normal run
+  int pass_base;              // Philox pass counter of group 0
+  float* head_sum;            // sixth sweep: (n_groups, n, 2, 96) masked column sums of the layer-6 output, or null
+  unsigned char* head_cnt;    // ... and kept-row counts
 };
 int fused_launch(const FusedParams& p, cudaStream_t s);
 
@@ -76,6 +79,8 @@ int exact_replicate_tables(const float* base_table, int n_groups, float* tables,
 int exact_layer_tables(const float* blob_dev, const unsigned long long* stats, double count, int layer, int n_groups,
                        float* tables, cudaStream_t s);
 
+int exact_head(const float* head_sum, const unsigned char* head_cnt, const float* tables, int n_groups, int64_t n, float* probs,
+               cudaStream_t s);
 int exact_layer_average(const unsigned long long* stats, double count, int layer, int n_groups, float* frozen, cudaStream_t s);
 
 }  // namespace uqk
