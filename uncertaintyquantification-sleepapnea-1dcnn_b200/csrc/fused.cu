@@ -433,10 +433,18 @@ struct FusedArgs {
   // linear in them, so the probabilities follow without another pass over the network (exact_head_kernel)
   float* head_sum;                // (n_groups, n, 2, 96) float32, or null
   unsigned char* head_cnt;        // (n_groups, n, 2, 96) uint8
+  // activation checkpoint between layers 4 and 5 (the narrowest interface, 96 channels): sweep 5 writes the bf16 planes
+  // of layer 5's input, sweep 6 resumes from them instead of recomputing layers 1-4
+  uint4* ckpt;                    // (n_groups, n, 12 planes, 64 rows) x 16 B, or null
+  int ckpt_write;                 // 1: this sweep writes the checkpoint
+  int first_layer;                // 0, or kCkptLayer: this sweep starts from the checkpoint
 };
 
 // dropout source of the epilogue
 constexpr int kDropNone = 0, kDropPhilox = 1, kDropBits = 2;
+// exact-mode checkpoint: input of layer index kCkptLayer (96 channels = 12 planes)
+constexpr int kCkptLayer = 4;
+constexpr int kCkptPlanes = 12;
 
 template <int TILES, int NSLOTS>
 struct FusedCfg {
@@ -567,12 +575,12 @@ __device__ __forceinline__ uint32_t keep_extract(const uint32_t (&kb)[4], int t)
 // done on both halves of a word at once -- ((w & 0x7FFF7FFF) | 0x80008000) - thr15*0x00010001 leaves the keep flag in
 // bits 15 / 31, PRMT with sign replication turns it into a 0xFFFF / 0 mask per bf16 half, and one LOP3 applies the
 // mask (and the zero-row mask) to the packed pair: 4 ALU instructions per 2 elements, no predicates.
-template <int DROP, bool LAST, bool DBG>
+template <int DROP, bool LAST, bool DBG, bool CKPT = false>
 __device__ __forceinline__ void epi_chunk16(const uint32_t (&v)[16], int c0, const float* __restrict__ tab_s,
                                             const float* __restrict__ tab_h, const float* __restrict__ tab_w,
                                             uint32_t act_row, bool row_valid, uint32_t row_mask, uint32_t thr2,
                                             uint32_t c0w, uint32_t pass, uint32_t c2, uint32_t k0, uint32_t k1,
-                                            const uint32_t (&zq)[4], float& zacc, float* dbg) {
+                                            const uint32_t (&zq)[4], float& zacc, float* dbg, uint4* ckpt = nullptr) {
 #pragma unroll
   for (int q = 0; q < 2; ++q) {
     const int cb = c0 + 8 * q;
@@ -605,8 +613,13 @@ __device__ __forceinline__ void epi_chunk16(const uint32_t (&v)[16], int c0, con
       }
     }
     if (!LAST) {
-      st_shared_v4(act_row + (uint32_t)(cb >> 3) * kPlaneBytes, pack_bf16x2(y[0], y[1]) & m[0], pack_bf16x2(y[2], y[3]) & m[1],
-                   pack_bf16x2(y[4], y[5]) & m[2], pack_bf16x2(y[6], y[7]) & m[3]);
+      const uint32_t p0 = pack_bf16x2(y[0], y[1]) & m[0], p1 = pack_bf16x2(y[2], y[3]) & m[1];
+      const uint32_t p2 = pack_bf16x2(y[4], y[5]) & m[2], p3 = pack_bf16x2(y[6], y[7]) & m[3];
+      st_shared_v4(act_row + (uint32_t)(cb >> 3) * kPlaneBytes, p0, p1, p2, p3);
+      if (CKPT) {
+        // exact-mode checkpoint: the same 8 channels of this row also go to HBM ([plane][row] x 16 B per window-pass)
+        if (ckpt) ckpt[(cb >> 3) * 64] = make_uint4(p0, p1, p2, p3);
+      }
     } else {
       const float4 w0 = *reinterpret_cast<const float4*>(tab_w + cb), w1 = *reinterpret_cast<const float4*>(tab_w + cb + 4);
       zacc = fmaf(y[0], w0.x, zacc); zacc = fmaf(y[1], w0.y, zacc); zacc = fmaf(y[2], w0.z, zacc); zacc = fmaf(y[3], w0.w, zacc);
@@ -740,9 +753,10 @@ __device__ __forceinline__ void make_keep_flags(const EpiCtx& c, const FusedArgs
   }
 }
 
-template <int L, int DROP, bool DBG, int EPI_THREADS>
+template <int L, int DROP, bool DBG, int EPI_THREADS, bool CKPT = false>
 __device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, const float* __restrict__ tab_g, int g,
-                                          long long win, uint32_t& n_acc, float* probs_s, float* dbg_base) {
+                                          long long win, uint32_t& n_acc, float* probs_s, float* dbg_base,
+                                          uint4* ckpt_row = nullptr) {
   constexpr int cout = fl_cout(L);
   constexpr int my = cout / 32;            // 16-column chunks owned by this warp (chunks colhalf, colhalf+2, ...)
   constexpr bool kLastLayer = (L == kBlocks - 1);
@@ -786,15 +800,15 @@ __device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, c
     if (j + 1 < my) tmem_ld16(c.taddr + (uint32_t)(16 * (c.colhalf + 2 * (j + 1))), vb);
     {
       const uint32_t zq[4] = {keep_extract(kb, 4 * j), keep_extract(kb, 4 * j + 1), keep_extract(kb, 4 * j + 2), keep_extract(kb, 4 * j + 3)};
-      epi_chunk16<DROP, kLastLayer, DBG>(va, 16 * (c.colhalf + 2 * j), tab_s, tab_h, c.tab_w, c.act_row, c.row_valid, row_mask, thr2,
-                                         c.c0w, (uint32_t)g, c2, c.k0, c.k1, zq, zacc, dbg);
+      epi_chunk16<DROP, kLastLayer, DBG, CKPT>(va, 16 * (c.colhalf + 2 * j), tab_s, tab_h, c.tab_w, c.act_row, c.row_valid, row_mask,
+                                               thr2, c.c0w, (uint32_t)g, c2, c.k0, c.k1, zq, zacc, dbg, ckpt_row);
     }
     if (j + 1 < my) {
       tmem_wait16(vb);
       if (j + 2 < my) tmem_ld16(c.taddr + (uint32_t)(16 * (c.colhalf + 2 * (j + 2))), va);
       const uint32_t zq[4] = {keep_extract(kb, 4 * j + 4), keep_extract(kb, 4 * j + 5), keep_extract(kb, 4 * j + 6), keep_extract(kb, 4 * j + 7)};
-      epi_chunk16<DROP, kLastLayer, DBG>(vb, 16 * (c.colhalf + 2 * (j + 1)), tab_s, tab_h, c.tab_w, c.act_row, c.row_valid, row_mask,
-                                         thr2, c.c0w, (uint32_t)g, c2, c.k0, c.k1, zq, zacc, dbg);
+      epi_chunk16<DROP, kLastLayer, DBG, CKPT>(vb, 16 * (c.colhalf + 2 * (j + 1)), tab_s, tab_h, c.tab_w, c.act_row, c.row_valid,
+                                               row_mask, thr2, c.c0w, (uint32_t)g, c2, c.k0, c.k1, zq, zacc, dbg, ckpt_row);
     }
   }
 
@@ -919,12 +933,25 @@ __device__ __forceinline__ void epi_stats(const EpiCtx& c, const FusedArgs& a, i
 template <int L, int DROP, int EPI_THREADS>
 __device__ __forceinline__ void epi_sweep(const EpiCtx& c, const FusedArgs& a, const float* __restrict__ tab_g, int g,
                                           long long win, uint32_t& n_acc, unsigned long long* s_stats) {
+  if (L < a.first_layer) {                    // resumed sweep: the earlier layers came from the checkpoint
+    if constexpr (L + 1 < kBlocks) epi_sweep<L + 1, DROP, EPI_THREADS>(c, a, tab_g, g, win, n_acc, s_stats);
+    return;
+  }
   if (a.n_layers == L + 1) {
     epi_stats<L, DROP, EPI_THREADS>(c, a, g, win, n_acc, s_stats);
     return;
   }
   if constexpr (L + 1 < kBlocks) {
-    epi_layer<L, DROP, false, EPI_THREADS>(c, a, tab_g, g, win, n_acc, nullptr, nullptr);
+    bool done = false;
+    if constexpr (L == kCkptLayer - 1) {
+      if (a.ckpt_write) {
+        // the output of this layer is the checkpointed activation: copy it to HBM on the way (rows 0..63 of the window)
+        uint4* row = win < a.n ? a.ckpt + (((size_t)g * a.n + win) * kCkptPlanes) * 64 + c.t : nullptr;
+        epi_layer<L, DROP, false, EPI_THREADS, true>(c, a, tab_g, g, win, n_acc, nullptr, nullptr, row);
+        done = true;
+      }
+    }
+    if (!done) epi_layer<L, DROP, false, EPI_THREADS>(c, a, tab_g, g, win, n_acc, nullptr, nullptr);
     epi_sweep<L + 1, DROP, EPI_THREADS>(c, a, tab_g, g, win, n_acc, s_stats);
   }
 }
@@ -1309,7 +1336,7 @@ fused_pair_kernel(const FusedArgs a) {
           const uint8_t* wmem = a.packed + (size_t)(a.mode_de ? g : 0) * kPackedBytes + (size_t)rank * (kPackedBytes / 2);
           const int n_layers = STAT ? a.n_layers : kBlocks;
 #pragma unroll 1
-          for (int l = 0; l < n_layers; ++l) {
+          for (int l = STAT ? a.first_layer : 0; l < n_layers; ++l) {
             const FusedLayer fl = c_layers[l];
             const uint32_t sb = (uint32_t)fl.step_bytes / 2;
             int step = 0;
@@ -1337,12 +1364,12 @@ fused_pair_kernel(const FusedArgs a) {
       // ---- leader: MMA issuer for the pair
       for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
         for (int g = 0; g < a.n_groups; ++g) {
-          issue_layer_pair<0, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
-          if (!STAT || a.n_layers > 1) issue_layer_pair<1, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
-          if (!STAT || a.n_layers > 2) issue_layer_pair<2, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
-          if (!STAT || a.n_layers > 3) issue_layer_pair<3, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
-          if (!STAT || a.n_layers > 4) issue_layer_pair<4, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
-          if (!STAT || a.n_layers > 5) issue_layer_pair<5, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
+          if (!STAT || a.first_layer <= 0) issue_layer_pair<0, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
+          if (!STAT || (a.n_layers > 1 && a.first_layer <= 1)) issue_layer_pair<1, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
+          if (!STAT || (a.n_layers > 2 && a.first_layer <= 2)) issue_layer_pair<2, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
+          if (!STAT || (a.n_layers > 3 && a.first_layer <= 3)) issue_layer_pair<3, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
+          if (!STAT || (a.n_layers > 4 && a.first_layer <= 4)) issue_layer_pair<4, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
+          if (!STAT || (a.n_layers > 5 && a.first_layer <= 5)) issue_layer_pair<5, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
         }
       }
     } else if (lane == 0) {
@@ -1351,12 +1378,12 @@ fused_pair_kernel(const FusedArgs a) {
       const uint32_t r_peer_act = mapa_shared(bar_act, 0);
       for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
         for (int g = 0; g < a.n_groups; ++g) {
-          relay_layer<0, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
-          if (!STAT || a.n_layers > 1) relay_layer<1, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
-          if (!STAT || a.n_layers > 2) relay_layer<2, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
-          if (!STAT || a.n_layers > 3) relay_layer<3, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
-          if (!STAT || a.n_layers > 4) relay_layer<4, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
-          if (!STAT || a.n_layers > 5) relay_layer<5, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
+          if (!STAT || a.first_layer <= 0) relay_layer<0, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
+          if (!STAT || (a.n_layers > 1 && a.first_layer <= 1)) relay_layer<1, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
+          if (!STAT || (a.n_layers > 2 && a.first_layer <= 2)) relay_layer<2, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
+          if (!STAT || (a.n_layers > 3 && a.first_layer <= 3)) relay_layer<3, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
+          if (!STAT || (a.n_layers > 4 && a.first_layer <= 4)) relay_layer<4, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
+          if (!STAT || (a.n_layers > 5 && a.first_layer <= 5)) relay_layer<5, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
         }
       }
     }
@@ -1415,7 +1442,18 @@ fused_pair_kernel(const FusedArgs a) {
         for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
           long long win; uint32_t xin0, xin1;
           unit_prologue(unit, win, xin0, xin1);
-          if (c.colhalf == 0) st_shared_v4(c.act_row, xin0, xin1, 0u, 0u);
+          if (a.first_layer == 0) {
+            if (c.colhalf == 0) st_shared_v4(c.act_row, xin0, xin1, 0u, 0u);
+          } else {
+            // resume from the checkpoint: this row's 12 planes of layer 5's input, six per column-half thread
+            const uint4* src = a.ckpt + (((size_t)g * a.n + (win < a.n ? win : 0)) * kCkptPlanes) * 64 + c.t;
+#pragma unroll
+            for (int q = 0; q < kCkptPlanes / 2; ++q) {
+              const int pl = c.colhalf * (kCkptPlanes / 2) + q;
+              const uint4 v = win < a.n ? __ldcs(src + (size_t)pl * 64) : make_uint4(0u, 0u, 0u, 0u);
+              st_shared_v4(c.act_row + (uint32_t)pl * kPlaneBytes, v.x, v.y, v.z, v.w);
+            }
+          }
           fence_proxy_async();
           epi_signal_act<Cfg::kEpiThreads>(c);
           epi_sweep<0, DROP, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, s_stats);
@@ -1481,6 +1519,7 @@ static int launch_pair_variant(const FusedParams& p, cudaStream_t s) {
   a.smem_probs = (p.no_smem_probs || STAT) ? 0 : 1;
   a.n_layers = STAT ? p.n_layers : kBlocks; a.stats = p.stats;
   a.pass_base = p.pass_base; a.head_sum = STAT ? p.head_sum : nullptr; a.head_cnt = STAT ? p.head_cnt : nullptr;
+  a.ckpt = STAT ? reinterpret_cast<uint4*>(p.ckpt) : nullptr; a.ckpt_write = STAT ? p.ckpt_write : 0; a.first_layer = STAT ? p.first_layer : 0;
   if (STAT && (p.n_layers < 1 || p.n_layers > kBlocks || p.stats == nullptr)) {
     set_error("statistics sweep needs 1 <= n_layers <= 6 and a statistics buffer"); return UQK_E_BADARG;
   }

@@ -67,7 +67,11 @@ struct FusedParams {
   int pass_base;              // Philox pass counter of group 0
   float* head_sum;            // sixth sweep: (n_groups, n, 2, 96) masked column sums of the layer-6 output, or null
   unsigned char* head_cnt;    // ... and kept-row counts
+  void* ckpt;                 // exact-mode activation checkpoint (n_groups, n, 12, 64) x 16 B between layers 4 and 5, or null
+  int ckpt_write;             // 1: this sweep (n_layers >= 5) writes it
+  int first_layer;            // 4: this sweep resumes from it; 0: starts from the windows
 };
+constexpr size_t kCkptBytesPerWindowPass = 12 * 64 * 16;
 int fused_launch(const FusedParams& p, cudaStream_t s);
 
 // tables builder: bias/scale/shift/dense for one set.  mean/var: 6x256 floats (frozen) or null -> moving stats.
