@@ -68,7 +68,12 @@ class UQModel:
             # new masks: the call counter is folded into the Philox key.
             seed = (UQModel._global_seed * 0x9E3779B97F4A7C15 + self._stochastic_calls) & (2 ** 64 - 1)
             self._stochastic_calls += 1
-            out = eng.mcd(x, n_passes=1, seed=seed, bn_mode="batch", precision="fp32", return_probs=True, metrics=())
+            # fp32 layer-synchronous kernels while the call's activations fit comfortably in HBM, the swept tensor-core
+            # kernel above that (same semantics, bf16 operands) -- the threshold mc_dropout_predict uses
+            import os
+            small = len(x) <= int(os.environ.get("UQK_EXACT_MAX_WINDOWS", "16384"))
+            out = eng.mcd(x, n_passes=1, seed=seed, bn_mode="batch", precision="fp32" if small else "bf16",
+                          return_probs=True, metrics=())
             p = out["probs"].reshape(-1, 1)
         else:
             p = eng.forward_det(x, member=0, precision=_default_precision()).reshape(-1, 1)
