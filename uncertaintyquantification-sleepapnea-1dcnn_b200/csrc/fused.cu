@@ -1199,9 +1199,7 @@ template <int L, int NSLOTS, typename Cfg>
 __device__ __forceinline__ void issue_layer_pair(uint32_t s_base, uint32_t tmem_base, const uint32_t* s_alo,
                                                  uint32_t bar_full, uint32_t bar_empty, uint32_t bar_peer_full,
                                                  uint32_t bar_acc, uint32_t bar_act, uint32_t bar_peer_act, uint32_t& it,
-                                                 uint32_t& n_act, int* err_flag, bool no_mma, uint32_t a_tile = 0u,
-                                                 volatile uint32_t* progress = nullptr, int lag_role = 0, uint32_t lag = 0u,
-                                                 uint32_t total_stages = 0u) {
+                                                 uint32_t& n_act, int* err_flag, bool no_mma, uint32_t a_tile = 0u) {
   constexpr FusedLayer fl = fused_layer(L);
   constexpr uint32_t kHi = (128u >> 4) | (1u << 14);
   constexpr uint32_t kBLbo = ((uint32_t)((fl.cout / 2) * 16) >> 4) << 16;
@@ -1214,15 +1212,6 @@ __device__ __forceinline__ void issue_layer_pair(uint32_t s_base, uint32_t tmem_
   for (int st = 0; st < fl.nstages; ++st, ++it) {
     const int slot = it % NSLOTS;
     const uint32_t ph = (it / NSLOTS) & 1;
-    if (lag_role == 2) {
-      // trailing tile-pair: stay `lag` stages behind the leading one, so that its last stages of a layer cover the
-      // leader's epilogue and the leader's first stages of the next layer cover this one's
-      const uint32_t need = min(it + lag, total_stages);
-      uint32_t spins = 0;
-      while (*progress < need) {
-        if (++spins > (1u << 28)) mbar_timeout(err_flag, 41);
-      }
-    }
     mbar_wait_cluster(bar_full + 8 * slot, ph, err_flag, 3);   // own half landed (tx) + peer's half (relayed arrive)
     tc_fence_after();
     const int nst = (st == fl.nstages - 1) ? kLast : fl.sps;
@@ -1239,7 +1228,6 @@ __device__ __forceinline__ void issue_layer_pair(uint32_t s_base, uint32_t tmem_
         }
       }
       umma_commit_2cta(bar_empty + 8 * slot);   // both CTAs' ring slots are free once these MMAs have read them
-      if (lag_role == 1) *progress = it + 1;    // leading tile-pair publishes how far it has issued
     }
     __syncwarp();
   }
@@ -1658,7 +1646,6 @@ fused_pair2_kernel(const FusedArgs a) {
     s_alo[i] = (((s_base + Cfg::oAct + a_off) >> 4) & 0x3FFFu) | ((a_lbo >> 4) << 16);
   }
   if (threadIdx.x == 0) {
-    *reinterpret_cast<volatile uint32_t*>(smem + Cfg::oMisc + 8) = 0u;   // progress counter of the leading tile-pair
     // leader: every "full" / "act" barrier also counts one arrival relayed from the peer CTA; a ring slot is free when
     // BOTH tile-pairs have consumed it (two commits)
     const uint32_t extra = rank == 0 ? 1u : 0u;
@@ -1724,19 +1711,14 @@ fused_pair2_kernel(const FusedArgs a) {
       const uint32_t tm = tmem_base + (uint32_t)tl * 256u;
       const uint32_t a_tile = (uint32_t)tl * (uint32_t)(kActBytes >> 4);
       const uint32_t b_acc = bar_acc + 8 * tl, b_act = bar_act + 8 * tl;
-      volatile uint32_t* progress = reinterpret_cast<volatile uint32_t*>(smem + Cfg::oMisc + 8);
-      const int role = (a.variant & 1) ? 1 + tl : 0;          // variant bit 0 enforces a lag between the tile-pairs (measured: no gain)
-      const uint32_t lag = (uint32_t)(NSLOTS / 3);
-      const long long my_units = pair_id < a.n_units ? (a.n_units - pair_id + n_pairs - 1) / n_pairs : 0;
-      const uint32_t total = (uint32_t)(my_units * a.n_groups * (long long)kStagesPerGroup);
       for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
         for (int g = 0; g < a.n_groups; ++g) {
-          issue_layer_pair<0, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile, progress, role, lag, total);
-          issue_layer_pair<1, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile, progress, role, lag, total);
-          issue_layer_pair<2, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile, progress, role, lag, total);
-          issue_layer_pair<3, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile, progress, role, lag, total);
-          issue_layer_pair<4, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile, progress, role, lag, total);
-          issue_layer_pair<5, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile, progress, role, lag, total);
+          issue_layer_pair<0, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
+          issue_layer_pair<1, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
+          issue_layer_pair<2, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
+          issue_layer_pair<3, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
+          issue_layer_pair<4, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
+          issue_layer_pair<5, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
         }
       }
     } else if (warp == 1 && lane == 0) {
