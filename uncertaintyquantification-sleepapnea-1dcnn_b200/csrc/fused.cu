@@ -1528,29 +1528,6 @@ static int launch_pair_variant(const FusedParams& p, cudaStream_t s) {
   // (registers, shared memory, 2 x 256 TMEM columns) admit two -- ncu's launch__occupancy_limit_* agree with two.
   per_sm = (2 * (smem + 1024) <= 233472) ? 2 : 1;
   const long long pairs = std::min<long long>(a.n_units, (long long)(sms / 2) * per_sm);
-  if (getenv("UQK_DEBUG")) {
-    cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3((unsigned)(2 * pairs)); cfg.blockDim = dim3(Cfg::kThreads); cfg.dynamicSmemBytes = smem;
-    cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-    cfg.attrs = at; cfg.numAttrs = 1;
-    int ncl = -1;
-    cudaError_t e = cudaOccupancyMaxActiveClusters(&ncl, kern, &cfg);
-    fprintf(stderr, "[uqk] pair kernel: smem=%zu per_sm=%d pairs=%lld maxActiveClusters=%d (%s)\n", smem, per_sm, pairs, ncl, cudaGetErrorString(e));
-    cudaFuncAttributes fa{};
-    cudaFuncGetAttributes(&fa, kern);
-    fprintf(stderr, "[uqk]   regs=%d static_smem=%zu local=%zu maxDyn=%d maxThreads=%d\n", fa.numRegs, fa.sharedSizeBytes, fa.localSizeBytes, fa.maxDynamicSharedSizeBytes, fa.maxThreadsPerBlock);
-    for (size_t sm : {(size_t)40000, (size_t)80000, (size_t)100000, (size_t)105000, (size_t)110000, (size_t)112000}) {
-      int b = -1;
-      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, kern, Cfg::kThreads, sm);
-      fprintf(stderr, "[uqk]   smem %zu -> blocks/SM %d\n", sm, b);
-    }
-    for (int th : {128, 192, 256, 320}) {
-      int b = -1;
-      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, kern, th, 40000);
-      fprintf(stderr, "[uqk]   threads %d smem 40000 -> blocks/SM %d\n", th, b);
-    }
-  }
   kern<<<(unsigned)(2 * pairs), Cfg::kThreads, smem, s>>>(a);
   UQK_LAUNCH_CHECK();
   return UQK_OK;
@@ -1882,16 +1859,6 @@ static int launch_variant(const FusedParams& p, cudaStream_t s) {
   int per_sm = 1;
   UQK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, Cfg::kThreads, smem));
   if (per_sm < 1) { set_error("fused kernel does not fit on an SM (smem %zu)", smem); return UQK_E_CUDA; }
-  if (getenv("UQK_DEBUG")) {
-    cudaFuncAttributes fa{};
-    cudaFuncGetAttributes(&fa, kern);
-    fprintf(stderr, "[uqk] fused<%d,%d>: smem=%zu threads=%d per_sm=%d regs=%d\n", TILES, NSLOTS, smem, Cfg::kThreads, per_sm, fa.numRegs);
-    for (size_t sm : {(size_t)40000, (size_t)100000, (size_t)112000}) {
-      int b = -1;
-      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, kern, Cfg::kThreads, sm);
-      fprintf(stderr, "[uqk]   smem %zu -> blocks/SM %d\n", sm, b);
-    }
-  }
   if (per_sm * Cfg::kTmemCols > 512) per_sm = 512 / Cfg::kTmemCols;   // TMEM: 512 columns per SM
   const long long grid = std::min<long long>(a.n_units, (long long)sms * per_sm);
   kern<<<(unsigned)grid, Cfg::kThreads, smem, s>>>(a);
