@@ -171,11 +171,15 @@ static int run_exact_sweeps(Handle* h, const void* x, int x_dtype, int64_t n, in
   for (int k = 0; k < kBlocks; ++k) {
     UQK_CUDA(cudaMemsetAsync(stats, 0, sizeof(unsigned long long) * (size_t)n_passes * 2 * kMaxCh, s));
     p.stats = stats; p.n_layers = k + 1;
+    // nothing is random before the first BatchNorm: layer 1's statistics are the same for every pass, so its sweep runs
+    // one pass and the sums are copied to the other passes' rows
+    p.n_groups = k == 0 ? 1 : n_passes;
     p.head_sum = k == kBlocks - 1 ? head_sum : nullptr;
     p.head_cnt = k == kBlocks - 1 ? head_cnt : nullptr;
     // sweep 5 leaves layer 5's input in the checkpoint, sweep 6 resumes from it (layers 1-4 are not recomputed again)
     p.ckpt = ckpt; p.ckpt_write = (ckpt && k == kBlocks - 2) ? 1 : 0; p.first_layer = (ckpt && k == kBlocks - 1) ? 4 : 0;
     if ((rc = fused_launch(p, s))) return rc;           // n == 0 (empty shard): no launch, statistics stay zero
+    if (k == 0 && n_passes > 1 && (rc = exact_replicate_stats(stats, n_passes, s))) return rc;
     if (exchanging &&
         h->xchg(h->xchg_user, reinterpret_cast<long long*>(stats), n_passes * 2 * kMaxCh, static_cast<void*>(s)) != 0) {
       set_error("batch-statistics exchange callback failed at layer %d", k);

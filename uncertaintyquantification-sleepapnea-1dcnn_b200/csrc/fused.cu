@@ -259,6 +259,18 @@ int exact_head(const float* head_sum, const unsigned char* head_cnt, const float
   return UQK_OK;
 }
 
+__global__ void replicate_stats_kernel(unsigned long long* __restrict__ stats) {   // row 0 -> rows 1..gridDim.y
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < 2 * kMaxCh) stats[(size_t)(blockIdx.y + 1) * 2 * kMaxCh + i] = stats[i];
+}
+
+int exact_replicate_stats(unsigned long long* stats, int n_groups, cudaStream_t s) {
+  if (n_groups < 2) return UQK_OK;
+  replicate_stats_kernel<<<dim3(2, n_groups - 1), 256, 0, s>>>(stats);
+  UQK_LAUNCH_CHECK();
+  return UQK_OK;
+}
+
 int exact_replicate_tables(const float* base_table, int n_groups, float* tables, cudaStream_t s) {
   replicate_table_kernel<<<dim3((kTableFloats + 255) / 256, n_groups), 256, 0, s>>>(base_table, tables);
   UQK_LAUNCH_CHECK();

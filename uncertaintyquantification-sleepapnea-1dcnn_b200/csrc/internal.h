@@ -85,6 +85,7 @@ int exact_layer_tables(const float* blob_dev, const unsigned long long* stats, d
 
 int exact_head(const float* head_sum, const unsigned char* head_cnt, const float* tables, int n_groups, int64_t n, float* probs,
                cudaStream_t s);
+int exact_replicate_stats(unsigned long long* stats, int n_groups, cudaStream_t s);
 int exact_layer_average(const unsigned long long* stats, double count, int layer, int n_groups, float* frozen, cudaStream_t s);
 
 }  // namespace uqk
