@@ -272,7 +272,7 @@ def main():
         run_exact()
         ms_ex, _ = timed(run_exact, 1)
         exact_info = {"metric": "uq_windows_per_sec_mcd_T%d_exact_batch_bn" % T, "value": ne / (ms_ex * 1e-3), "windows": ne,
-                      "kernel_runs_per_step": 6, "flops_vs_one_run": 2.19}
+                      "kernel_runs_per_step": 6, "flops_vs_one_run": 1.89}
 
     cpu = None
     if rank == 0 and world == 1 and args.cpu_sample > 0:

@@ -46,7 +46,7 @@ extern "C" {
                                (activations of the call in HBM).  UQK_PREC_BF16_TC: the fused kernel is swept once
                                per layer to collect that layer's statistics of every pass; the sixth sweep also
                                leaves what the linear head needs and resumes from a checkpoint of layer 5's input
-                               (2.19x the flops of one run) */
+                               (1.89x the flops of one run) */
 #define UQK_BN_CALIBRATED 2 /* batch statistics estimated once by uqk_calibrate() and frozen for all passes */
 
 /* arithmetic of the forward passes */

@@ -44,7 +44,8 @@ struct Handle {
   float* d_stats_pass = nullptr; size_t stats_pass_cap = 0;     // ... and n_passes x 2 x 256 int64 statistics (as floats x2)
   float* d_head_sum = nullptr; size_t head_sum_cap = 0;         // exact mode: head partials of one chunk of passes
   float* d_head_cnt = nullptr; size_t head_cnt_cap = 0;         // ... kept-row counts (bytes, allocated in floats)
-  float* d_ckpt = nullptr; size_t ckpt_cap = 0;                 // ... and the layer-4/5 activation checkpoint
+  float* d_ckpt = nullptr; size_t ckpt_cap = 0;                 // ... the layer-4/5 activation checkpoint
+  float* d_ckpt2 = nullptr; size_t ckpt2_cap = 0;               // ... and the layer-2/3 activation checkpoint
   float* d_dbg = nullptr;         // 6 x 128 x 256 debug dump of the fused kernel (tests)
   int variant = 0;
   int dbg_dump = 0;
@@ -151,7 +152,7 @@ static int run_fused(Handle* h, int member0, const void* x, int x_dtype, int64_t
 // calibration).  When head buffers are given the sixth sweep also emits the head partials (see exact_head_kernel).
 static int run_exact_sweeps(Handle* h, const void* x, int x_dtype, int64_t n, int pass0, int n_passes, uint64_t seed,
                             int64_t window_base, const uint32_t* mask_bits, float* frozen, float* head_sum,
-                            unsigned char* head_cnt, void* ckpt, cudaStream_t s) {
+                            unsigned char* head_cnt, void* ckpt2, void* ckpt4, cudaStream_t s) {
   int rc;
   if ((rc = ensure(&h->d_tables_pass, &h->tables_pass_cap, (size_t)n_passes * kTableFloats))) return rc;
   if ((rc = ensure(&h->d_stats_pass, &h->stats_pass_cap, (size_t)n_passes * 2 * kMaxCh * 2))) return rc;
@@ -176,8 +177,15 @@ static int run_exact_sweeps(Handle* h, const void* x, int x_dtype, int64_t n, in
     p.n_groups = k == 0 ? 1 : n_passes;
     p.head_sum = k == kBlocks - 1 ? head_sum : nullptr;
     p.head_cnt = k == kBlocks - 1 ? head_cnt : nullptr;
-    // sweep 5 leaves layer 5's input in the checkpoint, sweep 6 resumes from it (layers 1-4 are not recomputed again)
-    p.ckpt = ckpt; p.ckpt_write = (ckpt && k == kBlocks - 2) ? 1 : 0; p.first_layer = (ckpt && k == kBlocks - 1) ? 4 : 0;
+    // checkpoints (both or none): sweep 3 leaves layer 3's input in ckpt2, sweeps 4 and 5 resume from it; sweep 5 leaves
+    // layer 5's input in ckpt4, sweep 6 resumes from it -- no layer is computed more than three times
+    p.ckpt_out = nullptr; p.ckpt_out_layer = 0; p.ckpt_in = nullptr; p.first_layer = 0;
+    if (ckpt2 && ckpt4) {
+      if (k == 2) { p.ckpt_out = ckpt2; p.ckpt_out_layer = 2; }
+      if (k == 3) { p.ckpt_in = ckpt2; p.first_layer = 2; }
+      if (k == 4) { p.ckpt_in = ckpt2; p.first_layer = 2; p.ckpt_out = ckpt4; p.ckpt_out_layer = 4; }
+      if (k == 5) { p.ckpt_in = ckpt4; p.first_layer = 4; }
+    }
     if ((rc = fused_launch(p, s))) return rc;           // n == 0 (empty shard): no launch, statistics stay zero
     if (k == 0 && n_passes > 1 && (rc = exact_replicate_stats(stats, n_passes, s))) return rc;
     if (exchanging &&
@@ -199,9 +207,10 @@ static int run_exact_sweeps(Handle* h, const void* x, int x_dtype, int64_t n, in
 // linear in them, so a small kernel turns them into the probabilities once layer 6's statistics are known -- no seventh
 // pass over the network.  Cost: 2.67x the flops of one run (layers are recomputed instead of spilling
 // N x T x 60 x Cout activations to HBM); the passes are processed in chunks so that the head partials
-// (960 B per window-pass) and the layer-4/5 activation checkpoint (12 KB per window-pass: sweep 6 resumes from it
-// instead of recomputing layers 1-4, 2.19x the flops of one run in total) stay within kExactScratchBudget.
-constexpr size_t kExactScratchBudget = (size_t)64 << 30;
+// (960 B per window-pass) and the two activation checkpoints (inputs of layers 3 and 5, 24 + 12 KB per window-pass:
+// later sweeps resume from them instead of recomputing the layers in front, 1.89x the flops of one run in total)
+// stay within kExactScratchBudget.
+constexpr size_t kExactScratchBudget = (size_t)80 << 30;
 
 static int run_fused_exact(Handle* h, const void* x, int x_dtype, int64_t n, int n_passes, uint64_t seed, int64_t window_base,
                            const uint32_t* mask_bits, float* probs, const MetricsOut& out, bool want_metrics, cudaStream_t s) {
@@ -209,12 +218,13 @@ static int run_fused_exact(Handle* h, const void* x, int x_dtype, int64_t n, int
   const bool exchanging = h->xchg != nullptr;
   // every rank of a sharded call must cut the passes identically: size the chunks by the windows of the whole call
   const int64_t n_for_chunks = std::max<int64_t>(1, exchanging ? h->xchg_global_n : n);
-  const size_t per_pass = (size_t)n_for_chunks * (2 * kDenseIn * 5 + kCkptBytesPerWindowPass);   // head partials + checkpoint
+  const size_t per_pass = (size_t)n_for_chunks * (2 * kDenseIn * 5 + kCkpt2BytesPerWindowPass + kCkpt4BytesPerWindowPass);   // head partials + checkpoints
   const int chunk = (int)std::max<size_t>(1, std::min<size_t>((size_t)n_passes, std::min<size_t>(kExactScratchBudget / per_pass, kMaxFusedGroups)));
   if (n > 0) {
     if ((rc = ensure(&h->d_head_sum, &h->head_sum_cap, (size_t)chunk * n * 2 * kDenseIn))) return rc;
     if ((rc = ensure(&h->d_head_cnt, &h->head_cnt_cap, ((size_t)chunk * n * 2 * kDenseIn + 3) / 4))) return rc;
-    if ((rc = ensure(&h->d_ckpt, &h->ckpt_cap, (size_t)chunk * n * (kCkptBytesPerWindowPass / 4)))) return rc;
+    if ((rc = ensure(&h->d_ckpt, &h->ckpt_cap, (size_t)chunk * n * (kCkpt4BytesPerWindowPass / 4)))) return rc;
+    if ((rc = ensure(&h->d_ckpt2, &h->ckpt2_cap, (size_t)chunk * n * (kCkpt2BytesPerWindowPass / 4)))) return rc;
     if (!probs) {
       if ((rc = ensure(&h->d_probs_tmp, &h->probs_cap, (size_t)n * n_passes))) return rc;
       probs = h->d_probs_tmp;
@@ -223,7 +233,7 @@ static int run_fused_exact(Handle* h, const void* x, int x_dtype, int64_t n, int
   unsigned char* head_cnt = reinterpret_cast<unsigned char*>(h->d_head_cnt);
   for (int g0 = 0; g0 < n_passes; g0 += chunk) {
     const int gc = std::min(chunk, n_passes - g0);
-    if ((rc = run_exact_sweeps(h, x, x_dtype, n, g0, gc, seed, window_base, mask_bits, nullptr, h->d_head_sum, head_cnt, h->d_ckpt, s))) return rc;
+    if ((rc = run_exact_sweeps(h, x, x_dtype, n, g0, gc, seed, window_base, mask_bits, nullptr, h->d_head_sum, head_cnt, h->d_ckpt2, h->d_ckpt, s))) return rc;
     if (n > 0 && (rc = exact_head(h->d_head_sum, head_cnt, h->d_tables_pass, gc, n, probs + (size_t)g0 * n, s))) return rc;
   }
   if (n == 0) return UQK_OK;
@@ -279,7 +289,7 @@ int uqk_destroy(uqk_handle* hh) {
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
   void* ptrs[] = {h->d_blobs, h->d_packed, h->d_packed_pair, h->d_tables_inf, h->d_table_mcd, h->d_frozen, h->d_stats, h->d_affine,
-                  h->d_accum, h->d_err, h->d_x32, h->d_act[0], h->d_act[1], h->d_probs_tmp, h->d_dbg, h->d_tables_pass, h->d_stats_pass, h->d_head_sum, h->d_head_cnt, h->d_ckpt};
+                  h->d_accum, h->d_err, h->d_x32, h->d_act[0], h->d_act[1], h->d_probs_tmp, h->d_dbg, h->d_tables_pass, h->d_stats_pass, h->d_head_sum, h->d_head_cnt, h->d_ckpt, h->d_ckpt2};
   for (void* p : ptrs) if (p) cudaFree(p);
   cudaGetLastError();
   delete h;
@@ -363,7 +373,7 @@ int uqk_calibrate(uqk_handle* hh, const void* x_dev, int x_dtype, int64_t n, int
     // batch statistics of the exact training=True forward, averaged over the passes)
     if (n_passes > kMaxFusedGroups) { set_error("calibration on more than %lld windows takes at most %d passes",
                                                 (long long)h->calib_fp32_max, kMaxFusedGroups); return UQK_E_BADARG; }
-    if ((rc = run_exact_sweeps(h, x_dev, x_dtype, n, 0, n_passes, seed, 0, nullptr, h->d_frozen, nullptr, nullptr, nullptr, s))) return rc;
+    if ((rc = run_exact_sweeps(h, x_dev, x_dtype, n, 0, n_passes, seed, 0, nullptr, h->d_frozen, nullptr, nullptr, nullptr, nullptr, s))) return rc;
     h->have_frozen = true;
     return UQK_OK;
   }

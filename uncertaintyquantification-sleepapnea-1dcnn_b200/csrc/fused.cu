@@ -445,18 +445,19 @@ struct FusedArgs {
   // linear in them, so the probabilities follow without another pass over the network (exact_head_kernel)
   float* head_sum;                // (n_groups, n, 2, 96) float32, or null
   unsigned char* head_cnt;        // (n_groups, n, 2, 96) uint8
-  // activation checkpoint between layers 4 and 5 (the narrowest interface, 96 channels): sweep 5 writes the bf16 planes
-  // of layer 5's input, sweep 6 resumes from them instead of recomputing layers 1-4
-  uint4* ckpt;                    // (n_groups, n, 12 planes, 64 rows) x 16 B, or null
-  int ckpt_write;                 // 1: this sweep writes the checkpoint
-  int first_layer;                // 0, or kCkptLayer: this sweep starts from the checkpoint
+  // activation checkpoints of the exact mode: the bf16 planes of a layer's input, (n_groups, n, Cin/8 planes, 64 rows)
+  // x 16 B, written by the sweep that first has them in final form and read by the later sweeps instead of recomputing
+  // the layers in front (layer index 2: 192 channels = 24 planes; layer index 4: 96 channels = 12 planes)
+  uint4* ckpt_out;                // checkpoint written by this sweep, or null
+  int ckpt_out_layer;             // ... it holds the input of this layer index (2 or 4)
+  const uint4* ckpt_in;           // checkpoint this sweep resumes from, or null
+  int first_layer;                // ... it holds the input of this layer index (2 or 4); 0 = start from the windows
 };
 
 // dropout source of the epilogue
 constexpr int kDropNone = 0, kDropPhilox = 1, kDropBits = 2;
-// exact-mode checkpoint: input of layer index kCkptLayer (96 channels = 12 planes)
-constexpr int kCkptLayer = 4;
-constexpr int kCkptPlanes = 12;
+// exact-mode checkpoints: planes (8-channel chunks) of the input of layer index l
+__host__ __device__ constexpr int ckpt_planes(int l) { return l == 2 ? 24 : 12; }
 
 template <int TILES, int NSLOTS>
 struct FusedCfg {
@@ -955,10 +956,10 @@ __device__ __forceinline__ void epi_sweep(const EpiCtx& c, const FusedArgs& a, c
   }
   if constexpr (L + 1 < kBlocks) {
     bool done = false;
-    if constexpr (L == kCkptLayer - 1) {
-      if (a.ckpt_write) {
-        // the output of this layer is the checkpointed activation: copy it to HBM on the way (rows 0..63 of the window)
-        uint4* row = win < a.n ? a.ckpt + (((size_t)g * a.n + win) * kCkptPlanes) * 64 + c.t : nullptr;
+    if constexpr (L == 1 || L == 3) {
+      if (a.ckpt_out_layer == L + 1) {
+        // the output of this layer is a checkpointed activation: copy it to HBM on the way (rows 0..63 of the window)
+        uint4* row = win < a.n ? a.ckpt_out + (((size_t)g * a.n + win) * ckpt_planes(L + 1)) * 64 + c.t : nullptr;
         epi_layer<L, DROP, false, EPI_THREADS, true>(c, a, tab_g, g, win, n_acc, nullptr, nullptr, row);
         done = true;
       }
@@ -1445,11 +1446,12 @@ fused_pair_kernel(const FusedArgs a) {
           if (a.first_layer == 0) {
             if (c.colhalf == 0) st_shared_v4(c.act_row, xin0, xin1, 0u, 0u);
           } else {
-            // resume from the checkpoint: this row's 12 planes of layer 5's input, six per column-half thread
-            const uint4* src = a.ckpt + (((size_t)g * a.n + (win < a.n ? win : 0)) * kCkptPlanes) * 64 + c.t;
-#pragma unroll
-            for (int q = 0; q < kCkptPlanes / 2; ++q) {
-              const int pl = c.colhalf * (kCkptPlanes / 2) + q;
+            // resume from a checkpoint: this row's planes of the first layer's input, half of them per column-half thread
+            const int planes = ckpt_planes(a.first_layer);
+            const uint4* src = a.ckpt_in + (((size_t)g * a.n + (win < a.n ? win : 0)) * planes) * 64 + c.t;
+#pragma unroll 4
+            for (int q = 0; q < planes / 2; ++q) {
+              const int pl = c.colhalf * (planes / 2) + q;
               const uint4 v = win < a.n ? __ldcs(src + (size_t)pl * 64) : make_uint4(0u, 0u, 0u, 0u);
               st_shared_v4(c.act_row + (uint32_t)pl * kPlaneBytes, v.x, v.y, v.z, v.w);
             }
@@ -1519,7 +1521,8 @@ static int launch_pair_variant(const FusedParams& p, cudaStream_t s) {
   a.smem_probs = (p.no_smem_probs || STAT) ? 0 : 1;
   a.n_layers = STAT ? p.n_layers : kBlocks; a.stats = p.stats;
   a.pass_base = p.pass_base; a.head_sum = STAT ? p.head_sum : nullptr; a.head_cnt = STAT ? p.head_cnt : nullptr;
-  a.ckpt = STAT ? reinterpret_cast<uint4*>(p.ckpt) : nullptr; a.ckpt_write = STAT ? p.ckpt_write : 0; a.first_layer = STAT ? p.first_layer : 0;
+  a.ckpt_out = STAT ? reinterpret_cast<uint4*>(p.ckpt_out) : nullptr; a.ckpt_out_layer = (STAT && p.ckpt_out) ? p.ckpt_out_layer : 0;
+  a.ckpt_in = STAT ? reinterpret_cast<const uint4*>(p.ckpt_in) : nullptr; a.first_layer = (STAT && p.ckpt_in) ? p.first_layer : 0;
   if (STAT && (p.n_layers < 1 || p.n_layers > kBlocks || p.stats == nullptr)) {
     set_error("statistics sweep needs 1 <= n_layers <= 6 and a statistics buffer"); return UQK_E_BADARG;
   }

@@ -67,11 +67,14 @@ struct FusedParams {
   int pass_base;              // Philox pass counter of group 0
   float* head_sum;            // sixth sweep: (n_groups, n, 2, 96) masked column sums of the layer-6 output, or null
   unsigned char* head_cnt;    // ... and kept-row counts
-  void* ckpt;                 // exact-mode activation checkpoint (n_groups, n, 12, 64) x 16 B between layers 4 and 5, or null
-  int ckpt_write;             // 1: this sweep (n_layers >= 5) writes it
-  int first_layer;            // 4: this sweep resumes from it; 0: starts from the windows
+  // exact-mode activation checkpoints (bf16 planes of a layer's input, (n_groups, n, Cin/8, 64) x 16 B)
+  void* ckpt_out;             // written by this sweep, or null
+  int ckpt_out_layer;         // ... input of this layer index (2 or 4)
+  const void* ckpt_in;        // this sweep resumes from it, or null
+  int first_layer;            // ... input of this layer index (2 or 4)
 };
-constexpr size_t kCkptBytesPerWindowPass = 12 * 64 * 16;
+constexpr size_t kCkpt4BytesPerWindowPass = 12 * 64 * 16;   // input of layer index 4 (96 channels)
+constexpr size_t kCkpt2BytesPerWindowPass = 24 * 64 * 16;   // input of layer index 2 (192 channels)
 int fused_launch(const FusedParams& p, cudaStream_t s);
 
 // tables builder: bias/scale/shift/dense for one set.  mean/var: 6x256 floats (frozen) or null -> moving stats.

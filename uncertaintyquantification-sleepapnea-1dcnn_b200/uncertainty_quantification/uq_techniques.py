@@ -11,7 +11,7 @@ Build-side knobs (the callers' positional signatures are frozen, so these are en
   UQK_BN_MODE    auto | batch | calibrated | inference      BatchNorm statistics of the MC-Dropout passes
                  auto = batch = exact Keras ``training=True`` semantics (statistics of the whole call): fp32
                  layer-synchronous kernels up to UQK_EXACT_MAX_WINDOWS windows, above that the bf16 tensor-core
-                 kernel swept once per layer (same semantics, 2.2x the flops of one run).
+                 kernel swept once per layer (same semantics, 1.9x the flops of one run).
                  calibrated = statistics estimated once on UQK_CALIB_WINDOWS windows and frozen (fastest)
   UQK_PRECISION  bf16 | fp32   (fp32 forces the layer-synchronous kernels at any size)
   UQK_SEED       Philox key of the dropout masks (default: the seed given to tf.random.set_seed, else 2025)
