@@ -45,8 +45,8 @@ extern "C" {
                                whole call, per pass (uq_techniques.py:22).  UQK_PREC_FP32: layer-synchronous kernels
                                (activations of the call in HBM).  UQK_PREC_BF16_TC: the fused kernel is swept once
                                per layer to collect that layer's statistics of every pass; the sixth sweep also
-                               leaves what the linear head needs and resumes from a checkpoint of layer 5's input
-                               (1.89x the flops of one run) */
+                               leaves what the linear head needs; later sweeps resume from bf16 checkpoints of
+                               the inputs of layers 3 and 5 (1.89x the flops of one run) */
 #define UQK_BN_CALIBRATED 2 /* batch statistics estimated once by uqk_calibrate() and frozen for all passes */
 
 /* arithmetic of the forward passes */
