@@ -80,3 +80,22 @@ def test_csv_round_trip_and_errors(tmp_path):
         emit.write_detailed_csv(path, pid, y[:-1], lab, mean, var, ent)
     with pytest.raises(Exception):
         emit.write_detailed_csv(os.path.join(str(tmp_path), "no_such_dir", "x.csv"), pid, y, lab, mean, var, ent)
+
+
+def test_csv_float_text_on_random_bit_patterns(tmp_path):
+    """Every float32 exponent range: 300k random bit patterns (NaNs included -> empty fields) format like pandas."""
+    emit = importlib.import_module(PKG_NAME + ".emit")
+    rng = np.random.default_rng(11)
+    n = 300_000
+    cols = [rng.integers(0, 2 ** 32, n, dtype=np.uint64).astype(np.uint32).view(np.float32) for _ in range(3)]
+    pid = np.full(n, 200001, dtype=np.int64)
+    y = np.zeros(n, dtype=np.int64)
+    lab = np.ones(n, dtype=int)
+    ref, got = str(tmp_path / "ref.csv"), str(tmp_path / "got.csv")
+    _reference_csv(ref, pid, y, lab, *cols)
+    emit.write_detailed_csv(got, pid, y, lab, *cols)
+    a, b = open(ref, "rb").read(), open(got, "rb").read()
+    if a != b:
+        la, lb = a.split(b"\n"), b.split(b"\n")
+        bad = [(i, x, z) for i, (x, z) in enumerate(zip(la, lb)) if x != z][:5]
+        raise AssertionError(f"{len(la)} vs {len(lb)} lines; first differences: {bad}")
