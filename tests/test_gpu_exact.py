@@ -148,3 +148,25 @@ def test_tensor_core_calibration_matches_the_fp32_calibration(uqk):
         assert np.abs(a - c).max() < 4e-2 * np.abs(a).max(), (l, np.abs(a - c).max())
     np.testing.assert_array_equal(mtc, mtc2)          # integer statistics: bit-reproducible
     np.testing.assert_array_equal(vtc, vtc2)
+
+
+def test_exact_batch_is_independent_of_the_pass_chunking(uqk):
+    """The exact mode processes the passes in chunks sized by a memory budget; Philox pass counters, injected masks and
+    output rows are offset per chunk, so the result must not depend on the chunk size."""
+    eng = engine_with_members()
+    n, T, seed = 23, 5, 17
+    x = _x(uqk, n, seed=19)
+    rng = np.random.default_rng(4)
+    bits = rng.integers(0, 2 ** 32, (T, n, 6, 60, 8), dtype=np.uint64).astype(np.uint32)
+    whole = eng.mcd(x, n_passes=T, seed=seed, bn_mode="batch", precision="bf16", return_probs=True)
+    whole_m = eng.mcd(x, n_passes=T, seed=seed, bn_mode="batch", precision="bf16", masks=bits, return_probs=True)
+    try:
+        for chunk in (1, 2):
+            eng.option("exact_chunk_max", chunk)
+            part = eng.mcd(x, n_passes=T, seed=seed, bn_mode="batch", precision="bf16", return_probs=True)
+            part_m = eng.mcd(x, n_passes=T, seed=seed, bn_mode="batch", precision="bf16", masks=bits, return_probs=True)
+            for k in ("probs", "mean_pred", "pred_variance", "label"):
+                np.testing.assert_array_equal(part[k], whole[k])
+                np.testing.assert_array_equal(part_m[k], whole_m[k])
+    finally:
+        eng.option("exact_chunk_max", 0)

@@ -50,6 +50,7 @@ struct Handle {
   int variant = 0;
   int dbg_dump = 0;
   int64_t calib_fp32_max = 8192;  // calibration sets up to this size use the fp32 layer-synchronous kernels
+  int exact_chunk_max = 0;        // tests: cap on the passes per chunk of the exact mode (0 = memory budget only)
   // cross-rank exchange of batch statistics (uqk_set_stats_exchange)
   uqk_stats_exchange_fn xchg = nullptr;
   void* xchg_user = nullptr;
@@ -219,7 +220,8 @@ static int run_fused_exact(Handle* h, const void* x, int x_dtype, int64_t n, int
   // every rank of a sharded call must cut the passes identically: size the chunks by the windows of the whole call
   const int64_t n_for_chunks = std::max<int64_t>(1, exchanging ? h->xchg_global_n : n);
   const size_t per_pass = (size_t)n_for_chunks * (2 * kDenseIn * 5 + kCkpt2BytesPerWindowPass + kCkpt4BytesPerWindowPass);   // head partials + checkpoints
-  const int chunk = (int)std::max<size_t>(1, std::min<size_t>((size_t)n_passes, std::min<size_t>(kExactScratchBudget / per_pass, kMaxFusedGroups)));
+  int chunk = (int)std::max<size_t>(1, std::min<size_t>((size_t)n_passes, std::min<size_t>(kExactScratchBudget / per_pass, kMaxFusedGroups)));
+  if (h->exact_chunk_max > 0) chunk = std::min(chunk, h->exact_chunk_max);
   if (n > 0) {
     if ((rc = ensure(&h->d_head_sum, &h->head_sum_cap, (size_t)chunk * n * 2 * kDenseIn))) return rc;
     if ((rc = ensure(&h->d_head_cnt, &h->head_cnt_cap, ((size_t)chunk * n * 2 * kDenseIn + 3) / 4))) return rc;
@@ -302,6 +304,7 @@ int uqk_set_option(uqk_handle* hh, const char* key, int64_t value) {
   if (!strcmp(key, "variant")) { h->variant = (int)value; return UQK_OK; }
   if (!strcmp(key, "dbg_dump")) { h->dbg_dump = (int)value; return UQK_OK; }
   if (!strcmp(key, "calib_fp32_max")) { h->calib_fp32_max = value; return UQK_OK; }   // see uqk_calibrate
+  if (!strcmp(key, "exact_chunk_max")) { h->exact_chunk_max = (int)value; return UQK_OK; }   // passes per chunk of the exact mode (0 = by memory budget)
   set_error("unknown option '%s'", key);
   return UQK_E_BADARG;
 }
