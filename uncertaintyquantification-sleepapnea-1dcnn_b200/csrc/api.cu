@@ -223,10 +223,17 @@ static int run_fused_exact(Handle* h, const void* x, int x_dtype, int64_t n, int
   int chunk = (int)std::max<size_t>(1, std::min<size_t>((size_t)n_passes, std::min<size_t>(kExactScratchBudget / per_pass, kMaxFusedGroups)));
   if (h->exact_chunk_max > 0) chunk = std::min(chunk, h->exact_chunk_max);
   if (n > 0) {
-    if ((rc = ensure(&h->d_head_sum, &h->head_sum_cap, (size_t)chunk * n * 2 * kDenseIn))) return rc;
-    if ((rc = ensure(&h->d_head_cnt, &h->head_cnt_cap, ((size_t)chunk * n * 2 * kDenseIn + 3) / 4))) return rc;
-    if ((rc = ensure(&h->d_ckpt, &h->ckpt_cap, (size_t)chunk * n * (kCkpt4BytesPerWindowPass / 4)))) return rc;
-    if ((rc = ensure(&h->d_ckpt2, &h->ckpt2_cap, (size_t)chunk * n * (kCkpt2BytesPerWindowPass / 4)))) return rc;
+    for (;;) {
+      // the result does not depend on the chunk size, so a GPU short of memory gets smaller chunks instead of an error
+      // (not when the passes are cut jointly with other ranks)
+      rc = ensure(&h->d_head_sum, &h->head_sum_cap, (size_t)chunk * n * 2 * kDenseIn);
+      if (!rc) rc = ensure(&h->d_head_cnt, &h->head_cnt_cap, ((size_t)chunk * n * 2 * kDenseIn + 3) / 4);
+      if (!rc) rc = ensure(&h->d_ckpt, &h->ckpt_cap, (size_t)chunk * n * (kCkpt4BytesPerWindowPass / 4));
+      if (!rc) rc = ensure(&h->d_ckpt2, &h->ckpt2_cap, (size_t)chunk * n * (kCkpt2BytesPerWindowPass / 4));
+      if (rc != UQK_E_NOMEM || chunk == 1 || exchanging) break;
+      chunk = (chunk + 1) / 2;
+    }
+    if (rc) return rc;
     if (!probs) {
       if ((rc = ensure(&h->d_probs_tmp, &h->probs_cap, (size_t)n * n_passes))) return rc;
       probs = h->d_probs_tmp;
