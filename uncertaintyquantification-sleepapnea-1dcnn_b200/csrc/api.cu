@@ -206,8 +206,8 @@ static int run_exact_sweeps(Handle* h, const void* x, int x_dtype, int64_t n, in
 // (sum, sum of squares) with the earlier layers already normalised exactly.  The sixth sweep also leaves, per
 // (pass, window), the dropout-masked column sums of the layer-6 output; BatchNorm-6, GlobalAveragePooling and Dense are
 // linear in them, so a small kernel turns them into the probabilities once layer 6's statistics are known -- no seventh
-// pass over the network.  Cost: 2.67x the flops of one run (layers are recomputed instead of spilling
-// N x T x 60 x Cout activations to HBM); the passes are processed in chunks so that the head partials
+// pass over the network.  Layers are recomputed instead of spilling all N x T x 60 x Cout activations to HBM (2.67x the
+// flops of one run without checkpoints); the passes are processed in chunks so that the head partials
 // (960 B per window-pass) and the two activation checkpoints (inputs of layers 3 and 5, 24 + 12 KB per window-pass:
 // later sweeps resume from them instead of recomputing the layers in front, 1.89x the flops of one run in total)
 // stay within kExactScratchBudget.

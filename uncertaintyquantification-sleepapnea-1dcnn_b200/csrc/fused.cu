@@ -18,9 +18,13 @@
 //    bias+ReLU -> BN affine -> Philox dropout -> bf16.  One 68 KB buffer per tile instead of two.
 //  * Weights (1.7 MB bf16 per member, L2 resident) stream through a shared-memory ring with cp.async.bulk (TMA
 //    bulk copies, mbarrier complete_tx); they are pre-packed on the host into the exact shared-memory image.
-//  * Warp roles: warp 0 = weight producer, warp 1 = TMEM allocator + MMA issuer (one thread), 4 warps per tile =
-//    epilogue (TMEM lane quarter = warp_id % 4).  Two CTAs are resident per SM (TILES=1), so one CTA's epilogue
-//    overlaps the other's MMAs.
+//  * Warp roles: warp 0 = weight producer, then one warp per accumulator = TMEM allocator / MMA issuer (one elected
+//    lane), 8 warps per tile = epilogue (TMEM lane quarter = warp_id % 4, two warps per quarter on alternate 16-column
+//    chunks).
+//  * Kernels in this file, all with this mapping: fused_forward_kernel<TILES,...> (one CTA per unit, no clusters),
+//    fused_pair_kernel (cta_group::2 CTA pairs, one tile per CTA, two CTAs per SM; its STAT instantiation runs the
+//    statistics sweeps of the exact batch-statistic mode) and fused_pair2_kernel (CTA pairs with two tile-pairs per
+//    pair sharing one weight stream -- the default).
 #include "common.cuh"
 #include "internal.h"
 
