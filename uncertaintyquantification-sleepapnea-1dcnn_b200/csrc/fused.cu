@@ -25,52 +25,9 @@
 //    fused_pair_kernel (cta_group::2 CTA pairs, one tile per CTA, two CTAs per SM; its STAT instantiation runs the
 //    statistics sweeps of the exact batch-statistic mode) and fused_pair2_kernel (CTA pairs with two tile-pairs per
 //    pair sharing one weight stream -- the default).
-#include "common.cuh"
-#include "internal.h"
-
-#include <vector>
-#include <cstring>
-#include <cstdio>
-#include <cstdlib>
+#include "fused_kernels.cuh"
 
 namespace uqk {
-
-// ---- geometry ---------------------------------------------------------------------------------------------------
-constexpr int kRowsPad = 136;                      // rows -4 .. 131 of a tile (4 zero rows above and below)
-constexpr int kPlaneBytes = kRowsPad * 16;         // one 8-channel chunk, all rows: 2176 B
-constexpr int kOnesPlane = kMaxCh / 8;             // plane 32: constant [1, 1, 0, ...] rows -> bias added by the MMA
-constexpr int kActBytes = (kMaxCh / 8 + 1) * kPlaneBytes;  // 71808 B per tile
-constexpr int kSlotBytes = 16384;                  // weight ring slot
-
-struct FusedLayer {
-  int cinp;        // input channels as seen by the MMA (layer 1: 4 real + 4 zero, two taps per K=16 step)
-  int cout;
-  int taps;
-  int halo;
-  int nconv;       // K=16 MMA steps of the convolution per tile
-  int nsteps;      // nconv + 1: the last step multiplies the ones-plane with the bias row
-  int step_bytes;  // bytes of weights per step = cout * 32
-  int sps;         // steps per ring stage
-  int nstages;
-  uint32_t w_off;  // byte offset of the layer inside one member's packed image
-};
-
-__host__ __device__ constexpr int fl_cout(int l) { return l == 0 ? 128 : l == 1 ? 192 : l == 2 ? 224 : l == 3 ? 96 : l == 4 ? 256 : 96; }
-__host__ __device__ constexpr int fl_nconv(int l) { return l == 0 ? 4 : l == 1 ? 40 : l == 2 ? 36 : l == 3 ? 98 : l == 4 ? 54 : 144; }
-__host__ __device__ constexpr uint32_t fl_bytes(int l) { return (uint32_t)(fl_nconv(l) + 1) * (uint32_t)fl_cout(l) * 32u; }
-__host__ __device__ constexpr uint32_t fl_off(int l) { return l == 0 ? 0u : fl_off(l - 1) + fl_bytes(l - 1); }
-__host__ __device__ constexpr FusedLayer fused_layer(int l) {
-  const int cout = fl_cout(l), nsteps = fl_nconv(l) + 1, sb = cout * 32, sps = kSlotBytes / sb;
-  return FusedLayer{l == 0 ? 8 : l == 1 ? 128 : l == 2 ? 192 : l == 3 ? 224 : l == 4 ? 96 : 256,
-                    cout,
-                    l == 0 ? 7 : l == 1 ? 5 : l == 2 ? 3 : l == 3 ? 7 : 9,
-                    l == 0 ? 3 : l == 1 ? 2 : l == 2 ? 1 : l == 3 ? 3 : 4,
-                    fl_nconv(l), nsteps, sb, sps, (nsteps + sps - 1) / sps, fl_off(l)};
-}
-constexpr uint32_t kPackedBytes = fl_off(5) + fl_bytes(5);
-// Run-time indexable copies (the constexpr helpers above recurse, which is only free at compile time).
-__constant__ FusedLayer c_layers[kBlocks] = {fused_layer(0), fused_layer(1), fused_layer(2),
-                                             fused_layer(3), fused_layer(4), fused_layer(5)};
 
 size_t fused_packed_bytes() { return kPackedBytes; }
 
@@ -163,7 +120,6 @@ __global__ void build_tables_kernel(const float* __restrict__ blob, BlobOffsets 
   if (i == 0) table[3 * kChTotal + kDenseIn] = blob[off.dense_b];
 }
 
-constexpr double kFusedStatScale = 16777216.0;   // 2^24 fixed point of batch statistics, as in layersync.cu
 
 int build_tables(const float* blob_dev, const float* mean, const float* var, int fold_dropout, float* table_dev,
                  cudaStream_t s) {
@@ -288,1632 +244,18 @@ int exact_layer_tables(const float* blob_dev, const unsigned long long* stats, d
   return UQK_OK;
 }
 
-// ---- PTX wrappers -----------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-      "selp.b32 %0, 1, 0, p;\n\t}"
-      : "=r"(ok)
-      : "r"(bar), "r"(parity)
-      : "memory");
-  return ok != 0;
-}
-// Bounded wait: a protocol bug must end the kernel with an error, never hang the GPU.
-__device__ __noinline__ void mbar_timeout(int* err_flag, int code) {
-  if (err_flag) atomicExch(err_flag, code);
-  __threadfence_system();
-  __trap();
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, int* err_flag, int code) {
-  if (mbar_try_wait(bar, parity)) return;
-  const long long t0 = clock64();
-  while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > 4000000000ll) mbar_timeout(err_flag, code);
-  }
-}
-__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-
-__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
-               "l"(src), "r"(bytes), "r"(bar)
-               : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
-                                          uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
-      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
-        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
-        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-      : "r"(taddr)
-      : "memory");
-}
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-
-// UMMA shared-memory descriptor, K-major, SWIZZLE_NONE (cute::UMMA::SmemDescriptor bit layout):
-//   [0,14) start>>4   [16,30) LBO>>4 (K-direction core-matrix stride)   [32,46) SBO>>4 (8-row group stride)
-//   [46,48) version = 1 (Blackwell)   [61,64) layout type = 0
-__device__ __forceinline__ uint64_t umma_desc(uint32_t addr, uint32_t lbo, uint32_t sbo) {
-  return (uint64_t)((addr >> 4) & 0x3FFFu) | ((uint64_t)((lbo >> 4) & 0x3FFFu) << 16) |
-         ((uint64_t)((sbo >> 4) & 0x3FFFu) << 32) | (1ull << 46);
-}
-// Instruction descriptor, kind::f16: D=f32 (bit 4), A=B=bf16 (bits 7,10), K-major A and B, N>>3 at 17, M>>4 at 24
-__device__ __forceinline__ uint32_t umma_idesc(int n) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-}
-
-__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
-  uint32_t r;
-  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
-  return r;
-}
-__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
-  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
-}
-__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
-  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
-}
-
-// ---- cluster / CTA-pair helpers (cta_group::2 variant) -------------------------------------------------------------------
-__device__ __forceinline__ uint32_t cluster_ctarank() {
-  uint32_t r;
-  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-  return r;
-}
-__device__ __forceinline__ void cluster_sync_all() {
-  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-__device__ __forceinline__ uint32_t mapa_shared(uint32_t addr, uint32_t rank) {
-  uint32_t r;
-  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
-  return r;
-}
-__device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_addr) {
-  // relaxed: a release at cluster scope costs a MEMBAR.ALL.GPU per arrive; the data this signal publishes lives in
-  // shared memory and was already fenced to the async proxy (fence.proxy.async) / written by TMA before the arrive
-  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
-}
-__device__ __forceinline__ void umma_bf16_2cta(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
-                                               uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
-      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-// commit of the pair's MMAs: arrives on the barrier at the same CTA-relative offset in BOTH CTAs (mask 0b11)
-__device__ __forceinline__ void umma_commit_2cta(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
-               "h"((uint16_t)3)
-               : "memory");
-}
-
-// ---- the kernel -------------------------------------------------------------------------------------------------
-struct FusedArgs {
-  const void* x;
-  int x_f64;
-  long long n;
-  int n_groups;
-  int mode_de;
-  uint32_t k0, k1;
-  long long window_base;
-  const uint32_t* mask_bits;
-  const uint8_t* packed;
-  const float* tables;
-  float* probs;
-  MetricsOut out;
-  float* dbg_act;
-  int* err_flag;
-  int variant;
-  int smem_probs;   // 1: per-window probabilities are kept in shared memory for the fused K3 reductions
-  long long n_units;
-  // statistics sweep of the exact batch-statistic mode (pair kernel, STAT instantiation): run layers [0, n_layers) and
-  // accumulate the per-channel (sum, sum of squares) of layer n_layers-1's post-ReLU output into stats[g][2*256]
-  int n_layers;
-  int tab_per_group;              // 1: epilogue tables of group g are tables[g] although the weights are member 0's
-  unsigned long long* stats;
-  int pass_base;                  // Philox pass counter of group 0 (exact mode processes the passes in chunks)
-  // last statistics sweep (n_layers == 6): also emit, per (pass, window, row half, channel), the dropout-masked column
-  // sum of the post-ReLU layer-6 output and the number of kept rows -- BatchNorm + GlobalAveragePooling + Dense are
-  // linear in them, so the probabilities follow without another pass over the network (exact_head_kernel)
-  float* head_sum;                // (n_groups, n, 2, 96) float32, or null
-  unsigned char* head_cnt;        // (n_groups, n, 2, 96) uint8
-  // activation checkpoints of the exact mode: the bf16 planes of a layer's input, (n_groups, n, Cin/8 planes, 64 rows)
-  // x 16 B, written by the sweep that first has them in final form and read by the later sweeps instead of recomputing
-  // the layers in front (layer index 2: 192 channels = 24 planes; layer index 4: 96 channels = 12 planes)
-  uint4* ckpt_out;                // checkpoint written by this sweep, or null
-  int ckpt_out_layer;             // ... it holds the input of this layer index (2 or 4)
-  const uint4* ckpt_in;           // checkpoint this sweep resumes from, or null
-  int first_layer;                // ... it holds the input of this layer index (2 or 4); 0 = start from the windows
-};
-
-// dropout source of the epilogue
-constexpr int kDropNone = 0, kDropPhilox = 1, kDropBits = 2;
-// exact-mode checkpoints: planes (8-channel chunks) of the input of layer index l
-__host__ __device__ constexpr int ckpt_planes(int l) { return l == 2 ? 24 : 12; }
-
-template <int TILES, int NSLOTS>
-struct FusedCfg {
-  static constexpr int kEpiWarps = 8;                       // per tile: 2 warps per TMEM lane quarter
-  static constexpr int kEpiThreads = 32 * kEpiWarps;
-  static constexpr int kWarps = 2 + kEpiWarps * TILES;
-  static constexpr int kThreads = 32 * kWarps;
-  static constexpr int kWpu = 2 * TILES;  // windows per unit
-  static constexpr int kTmemCols = 256 * TILES;
-  // shared-memory map (bytes)
-  static constexpr int oAct = 0;
-  static constexpr int oRing = oAct + TILES * kActBytes;
-  static constexpr int kTabFloats = 2 * 512 + 128;                   // 2 x (scale[256], shift[256]) + dense w[96] + b
-  static constexpr int oTab = oRing + NSLOTS * kSlotBytes;
-  static constexpr int oBar = oTab + TILES * kTabFloats * 4;         // mbarriers
-  static constexpr int kNumBars = 2 * NSLOTS + 2 * TILES;
-  static constexpr int oMisc = oBar + 8 * kNumBars;                  // tmem ptr (16 B), zpart[TILES][2][4]
-  static constexpr int oAlo = oMisc + 16 + 32 * TILES;               // A-descriptor low words, one per (layer, step)
-  static constexpr int oProbs = oAlo + 4 * 392;                      // probs[kWpu][n_groups]
-};
-
-// Bounded mbarrier wait.  `hint_ns` lets the hardware suspend the polling thread inside try_wait instead of
-// spinning; the watchdog turns a protocol bug into a trap (never a hung GPU).
-__device__ __forceinline__ void mbar_wait2(uint32_t bar, uint32_t parity, int* err_flag, int code) {
-  // The polling loop lives inside one asm block (try_wait, branch, counter: ~6 SASS instructions per wake-up instead
-  // of the ~15 the compiler emits around a C++ loop -- pollers are woken by every arrival / transaction update, and
-  // their instructions cost issue slots and power under the cap).  Every 2048 unsuccessful tries control returns to
-  // C++ for the watchdog.
-  long long t0 = 0;
-  for (;;) {
-    uint32_t ok;
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t.reg .b32 n;\n\t"
-        "mov.u32 n, 2048;\n"
-        "UQK_TRY:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
-        "@p bra UQK_DONE;\n\t"
-        "sub.u32 n, n, 1;\n\t"
-        "setp.ne.u32 p, n, 0;\n\t"
-        "@p bra UQK_TRY;\n\t"
-        "mov.u32 %0, 0;\n\t"
-        "bra UQK_END;\n"
-        "UQK_DONE:\n\t"
-        "mov.u32 %0, 1;\n"
-        "UQK_END:\n\t}"
-        : "=r"(ok)
-        : "r"(bar), "r"(parity), "r"(20000u)
-        : "memory");
-    if (ok) return;
-    const long long now = clock64();                  // watchdog: ~2 s of waiting is a protocol bug
-    if (t0 == 0) t0 = now;
-    else if (now - t0 > 4000000000ll) mbar_timeout(err_flag, code);
-  }
-}
-__device__ __forceinline__ bool elect_one() {
-  uint32_t pred;
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "elect.sync _|p, 0xffffffff;\n\t"
-      "selp.b32 %0, 1, 0, p;\n\t}"
-      : "=r"(pred));
-  return pred != 0;
-}
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-      : "r"(taddr)
-      : "memory");
-}
-// tcgen05.wait::ld with the loaded registers as in/out operands: every use of v[] depends on the wait.
-__device__ __forceinline__ void tmem_wait16(uint32_t (&v)[16]) {
-  asm volatile("tcgen05.wait::ld.sync.aligned;"
-               : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]),
-                 "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15])
-               :
-               : "memory");
-}
-
-// bits 15 / 31 of d -> 0xFFFF / 0 per 16-bit half (prmt selector bit 3 = replicate the selected byte's sign bit;
-// the __byte_perm intrinsic ignores that bit, hence PTX)
-__device__ __forceinline__ uint32_t prmt_sign_halves(uint32_t d) {
-  uint32_t r;
-  asm("prmt.b32 %0, %1, %1, 0xBB99;" : "=r"(r) : "r"(d));
-  return r;
-}
-
-template <uint32_t SEL>
-__device__ __forceinline__ uint32_t prmt_sign_bytes(uint32_t z) {
-  uint32_t r;
-  asm("prmt.b32 %0, %1, %1, %2;" : "=r"(r) : "r"(z), "n"(SEL));
-  return r;
-}
-
-// Keep-flags of 8 consecutive channels (one Philox4x32-10 call): element e is kept iff its 15-bit field >= thr15.
-// The compare runs on both 16-bit halves of a word at once -- ((w & 0x7FFF7FFF) | 0x80008000) - thr15*0x00010001 leaves
-// the flag in bits 15 / 31 -- and a PRMT gathers the four flag bytes of two words: g0 carries elements 0..3 and g1
-// elements 4..7 in the SIGN BITS of their four bytes.
-__device__ __forceinline__ void philox_keep8(uint32_t c0w, uint32_t pass, uint32_t c2, uint32_t chunk8, uint32_t k0,
-                                             uint32_t k1, uint32_t thr2, uint32_t& g0, uint32_t& g1) {
-  const Philox4 r = philox4x32_10(c0w, pass, c2, chunk8, k0, k1);
-  const uint32_t d0 = ((r.x & 0x7FFF7FFFu) | 0x80008000u) - thr2, d1 = ((r.y & 0x7FFF7FFFu) | 0x80008000u) - thr2;
-  const uint32_t d2 = ((r.z & 0x7FFF7FFFu) | 0x80008000u) - thr2, d3 = ((r.w & 0x7FFF7FFFu) | 0x80008000u) - thr2;
-  asm("prmt.b32 %0, %1, %2, 0x7531;" : "=r"(g0) : "r"(d0), "r"(d1));   // bytes: d0[15:8], d0[31:24], d1[15:8], d1[31:24]
-  asm("prmt.b32 %0, %1, %2, 0x7531;" : "=r"(g1) : "r"(d2), "r"(d3));
-}
-
-// Keep-flag store of one thread and layer: the flags of 4 consecutive channels ("quad" t = channel_in_thread / 4) sit
-// in bit (t & 7) of the four bytes of word t >> 3 -- 32 flags per register, Cout/2 flags = at most 4 registers.
-// Insert = shift the byte-sign form into place (SHF + LOP3); extract = shift back to the byte signs (SHF), which is
-// what PRMT's sign replication reads when it widens a flag into the 0xFFFF / 0 mask of a bf16 half.
-__device__ __forceinline__ void keep_insert(uint32_t (&kb)[4], int t, uint32_t g) {   // t is a constant after unrolling
-  const int s = t & 7;
-  kb[t >> 3] |= (s == 7 ? g : (g >> (7 - s))) & (0x01010101u << s);
-}
-__device__ __forceinline__ uint32_t keep_extract(const uint32_t (&kb)[4], int t) {
-  const int s = t & 7;
-  return s == 7 ? kb[t >> 3] : (kb[t >> 3] << (7 - s));
-}
-
-// One 16-column chunk of the epilogue: ReLU -> BatchNorm affine (dropout scale folded) -> dropout -> bf16 store
-// (layers 1-5) or dot with the dense kernel (layer 6).  The conv bias is already in the accumulator (bias MMA step).
-//
-// Dropout: one Philox4x32-10 call per 8 channels; element e uses 15-bit field (word e>>1, half e&1, low 15 bits) and
-// is kept iff field >= thr15 = round(rate * 32768) (TF: keep iff u >= rate).  For the stored layers the compare is
-// done on both halves of a word at once -- ((w & 0x7FFF7FFF) | 0x80008000) - thr15*0x00010001 leaves the keep flag in
-// bits 15 / 31, PRMT with sign replication turns it into a 0xFFFF / 0 mask per bf16 half, and one LOP3 applies the
-// mask (and the zero-row mask) to the packed pair: 4 ALU instructions per 2 elements, no predicates.
-template <int DROP, bool LAST, bool DBG, bool CKPT = false>
-__device__ __forceinline__ void epi_chunk16(const uint32_t (&v)[16], int c0, const float* __restrict__ tab_s,
-                                            const float* __restrict__ tab_h, const float* __restrict__ tab_w,
-                                            uint32_t act_row, bool row_valid, uint32_t row_mask, uint32_t thr2,
-                                            uint32_t c0w, uint32_t pass, uint32_t c2, uint32_t k0, uint32_t k1,
-                                            const uint32_t (&zq)[4], float& zacc, float* dbg, uint4* ckpt = nullptr) {
-#pragma unroll
-  for (int q = 0; q < 2; ++q) {
-    const int cb = c0 + 8 * q;
-    const float4 s0 = *reinterpret_cast<const float4*>(tab_s + cb), s1 = *reinterpret_cast<const float4*>(tab_s + cb + 4);
-    const float4 h0 = *reinterpret_cast<const float4*>(tab_h + cb), h1 = *reinterpret_cast<const float4*>(tab_h + cb + 4);
-    const float ss[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
-    const float hh[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
-    float y[8];
-#pragma unroll
-    for (int e = 0; e < 8; ++e) y[e] = fmaf(fmaxf(__uint_as_float(v[8 * q + e]), 0.f), ss[e], hh[e]);
-    uint32_t m[4] = {row_mask, row_mask, row_mask, row_mask};     // per bf16 pair: 0xFFFF per kept half
-    if (DROP != kDropNone) {
-      // zq[2q], zq[2q+1]: keep-flags of channels 0..3 / 4..7 of this half in the byte sign bits (zero for padding
-      // rows); PRMT with sign replication widens two byte signs into the 0xFFFF / 0 masks of one bf16 pair
-      m[0] = prmt_sign_bytes<0x9988>(zq[2 * q]); m[1] = prmt_sign_bytes<0xBBAA>(zq[2 * q]);
-      m[2] = prmt_sign_bytes<0x9988>(zq[2 * q + 1]); m[3] = prmt_sign_bytes<0xBBAA>(zq[2 * q + 1]);
-    }
-    if (DBG || LAST) {
-      // float path (debug dump and the head): apply the same masks to the fp32 values
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        y[2 * i] = (m[i] & 0x0000FFFFu) ? y[2 * i] : 0.f;
-        y[2 * i + 1] = (m[i] & 0xFFFF0000u) ? y[2 * i + 1] : 0.f;
-      }
-    }
-    if (DBG) {
-      if (dbg) {
-#pragma unroll
-        for (int e = 0; e < 8; ++e) dbg[cb + e] = y[e];
-      }
-    }
-    if (!LAST) {
-      const uint32_t p0 = pack_bf16x2(y[0], y[1]) & m[0], p1 = pack_bf16x2(y[2], y[3]) & m[1];
-      const uint32_t p2 = pack_bf16x2(y[4], y[5]) & m[2], p3 = pack_bf16x2(y[6], y[7]) & m[3];
-      st_shared_v4(act_row + (uint32_t)(cb >> 3) * kPlaneBytes, p0, p1, p2, p3);
-      if (CKPT) {
-        // exact-mode checkpoint: the same 8 channels of this row also go to HBM ([plane][row] x 16 B per window-pass)
-        if (ckpt) ckpt[(cb >> 3) * 64] = make_uint4(p0, p1, p2, p3);
-      }
-    } else {
-      const float4 w0 = *reinterpret_cast<const float4*>(tab_w + cb), w1 = *reinterpret_cast<const float4*>(tab_w + cb + 4);
-      zacc = fmaf(y[0], w0.x, zacc); zacc = fmaf(y[1], w0.y, zacc); zacc = fmaf(y[2], w0.z, zacc); zacc = fmaf(y[3], w0.w, zacc);
-      zacc = fmaf(y[4], w1.x, zacc); zacc = fmaf(y[5], w1.y, zacc); zacc = fmaf(y[6], w1.z, zacc); zacc = fmaf(y[7], w1.w, zacc);
-    }
-  }
-}
-
-__host__ __device__ constexpr int fl_step_base(int l) { return l == 0 ? 0 : fl_step_base(l - 1) + fl_nconv(l - 1) + 1; }
-constexpr int kTotalSteps = fl_step_base(kBlocks);   // 382 convolution steps + 6 bias steps
-constexpr int kStagesPerGroup = fused_layer(0).nstages + fused_layer(1).nstages + fused_layer(2).nstages +
-                                fused_layer(3).nstages + fused_layer(4).nstages + fused_layer(5).nstages;
-__constant__ int c_step_base[kBlocks + 1] = {fl_step_base(0), fl_step_base(1), fl_step_base(2), fl_step_base(3),
-                                             fl_step_base(4), fl_step_base(5), fl_step_base(6)};
-
-__device__ __forceinline__ uint64_t mk64(uint32_t lo, uint32_t hi) { return ((uint64_t)hi << 32) | (uint64_t)lo; }
-
-// ---- MMA issue of one layer (warp 1; the whole warp walks the schedule, one elected lane issues) -----------------
-// A-descriptor low words are precomputed per (layer, step) in shared memory (s_alo); the high word of every
-// descriptor is the constant SBO=128 | version=1.
-template <int L, int TILES, int NSLOTS, typename Cfg>
-__device__ __forceinline__ void issue_layer(uint32_t s_base, uint32_t tmem_base, const uint32_t* s_alo, uint32_t bar_full,
-                                            uint32_t bar_empty, uint32_t bar_acc, uint32_t bar_act, uint32_t& it,
-                                            uint32_t& n_act, int* err_flag, bool no_mma) {
-  constexpr FusedLayer fl = fused_layer(L);
-  constexpr uint32_t kHi = (128u >> 4) | (1u << 14);
-  constexpr uint32_t kBLbo = ((uint32_t)(fl.cout * 16) >> 4) << 16;
-  constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(fl.cout >> 3) << 17) | ((128u >> 4) << 24);
-  constexpr int kLast = fl.nsteps - (fl.nstages - 1) * fl.sps;
-  for (int tl = 0; tl < TILES; ++tl) mbar_wait2(bar_act + 8 * tl, n_act & 1, err_flag, 2);
-  ++n_act;
-  tc_fence_after();
-#pragma unroll 1
-  for (int st = 0; st < fl.nstages; ++st, ++it) {
-    const int slot = it % NSLOTS;
-    const uint32_t ph = (it / NSLOTS) & 1;
-    mbar_wait2(bar_full + 8 * slot, ph, err_flag, 3);
-    tc_fence_after();
-    const int nst = (st == fl.nstages - 1) ? kLast : fl.sps;
-    const uint32_t b_lo0 = (((s_base + Cfg::oRing + slot * kSlotBytes) >> 4) & 0x3FFFu) | kBLbo;
-    if (elect_one()) {
-      const uint32_t* alo = s_alo + fl_step_base(L) + st * fl.sps;
-      if (!no_mma) {
-#pragma unroll
-        for (int sl = 0; sl < fl.sps; ++sl) {
-          if (sl < nst) {
-            const uint32_t a0 = alo[sl];
-            const uint64_t bdesc = mk64(b_lo0 + (uint32_t)sl * (uint32_t)(fl.step_bytes >> 4), kHi);
-            const uint32_t acc = (st > 0 || sl > 0) ? 1u : 0u;
-            umma_bf16(tmem_base, mk64(a0, kHi), bdesc, kIdesc, acc);
-            if (TILES == 2) umma_bf16(tmem_base + 256, mk64(a0 + (uint32_t)(kActBytes >> 4), kHi), bdesc, kIdesc, acc);
-          }
-        }
-      }
-      umma_commit(bar_empty + 8 * slot);   // frees the ring slot when these MMAs have read it
-    }
-    __syncwarp();
-  }
-  if (elect_one()) {
-    for (int tl = 0; tl < TILES; ++tl) umma_commit(bar_acc + 8 * tl);   // accumulator(s) complete
-  }
-  __syncwarp();
-}
-
-// ---- epilogue of one layer (8 warps per tile) -----------------------------------------------------------------------
-struct EpiCtx {
-  uint32_t act_row, taddr, c0w, k0, k1, bar_acc, bar_act;
-  uint32_t remote_act = 0;   // pair kernels, peer CTA: cluster address of the leader's "peer activations ready" barrier
-  int t, colhalf, tid_t, we, lane, quarter, slot_w, tl;
-  bool row_valid;
-  float* tab;
-  float* tab_w;
-  float* zp;
-  int* err_flag;
-};
-
-// "this tile's activations are in place": local arrive (the issuer lives in this CTA), or -- peer CTA of a pair -- one
-// remote arrive on the leader's barrier after all 256 threads have fenced their stores.
-template <int EPI_THREADS>
-__device__ __forceinline__ void epi_signal_act(const EpiCtx& c) {
-  if (c.remote_act == 0) {
-    // one arrival per warp (the barrier counts EPI_THREADS / 32): every lane has fenced its own stores, __syncwarp
-    // orders them before lane 0's release-arrive -- 8 mbarrier operations per hand-off instead of 256
-    __syncwarp();
-    if (c.lane == 0) mbar_arrive(c.bar_act);
-  } else {
-    named_bar_sync(1 + c.tl, EPI_THREADS);
-    if (c.tid_t == 0) mbar_arrive_remote(c.remote_act);
-  }
-}
-
-// Keep-flags of this thread's row for layer L (byte-lane layout of keep_insert), all zero for padding rows.
-//  - kDropPhilox: the dropout masks do not depend on the data, so they are generated while the layer's MMAs run and
-//    the epilogue warps would otherwise sleep on the accumulator barrier (10 Philox rounds per 8 channels leave the
-//    critical path of the epilogue);
-//  - kDropBits (mask injection, parity tests): explicit keep-bits from global memory, bit c%32 of word c/32.
-template <int L, int DROP>
-__device__ __forceinline__ void make_keep_flags(const EpiCtx& c, const FusedArgs& a, int g, long long win, uint32_t (&kb)[4]) {
-  constexpr int my = fl_cout(L) / 32;
-  kb[0] = kb[1] = kb[2] = kb[3] = 0u;
-  if (DROP == kDropBits) {
-    const uint32_t* mrow = a.mask_bits + ((((size_t)g * a.n + (c.row_valid ? win : 0)) * kBlocks + L) * kL + (c.row_valid ? c.t : 0)) * 8;
-#pragma unroll
-    for (int j = 0; j < my; ++j) {
-      const int k = c.colhalf + 2 * j;
-      const uint32_t w16 = (__ldg(mrow + (k >> 1)) >> (16 * (k & 1))) & 0xFFFFu;
-#pragma unroll
-      for (int u = 0; u < 4; ++u)      // 4 bits -> bit 7 of 4 bytes (bit k lands on 8k + 7; the partial products never collide)
-        keep_insert(kb, 4 * j + u, (((w16 >> (4 * u)) & 0xFu) * 0x10204080u) & 0x80808080u);
-    }
-  }
-  if (DROP == kDropPhilox) {
-    constexpr uint32_t thr2 = drop_thr15(L) * 0x00010001u;
-    const uint32_t c2 = ((uint32_t)L << 16) | (uint32_t)c.t;
-    const uint32_t pass = (uint32_t)(a.pass_base + g);
-#pragma unroll
-    for (int j = 0; j < my; ++j) {
-      const uint32_t ch8 = (uint32_t)(2 * (c.colhalf + 2 * j));
-#pragma unroll
-      for (int u = 0; u < 2; ++u) {
-        uint32_t g0, g1;
-        philox_keep8(c.c0w, pass, c2, ch8 + (uint32_t)u, c.k0, c.k1, thr2, g0, g1);
-        keep_insert(kb, 4 * j + 2 * u, g0);
-        keep_insert(kb, 4 * j + 2 * u + 1, g1);
-      }
-    }
-  }
-  if (DROP != kDropNone) {
-#pragma unroll
-    for (int i = 0; i < 4; ++i) kb[i] = c.row_valid ? kb[i] : 0u;   // padding rows keep nothing
-  }
-}
-
-template <int L, int DROP, bool DBG, int EPI_THREADS, bool CKPT = false>
-__device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, const float* __restrict__ tab_g, int g,
-                                          long long win, uint32_t& n_acc, float* probs_s, float* dbg_base,
-                                          uint4* ckpt_row = nullptr) {
-  constexpr int cout = fl_cout(L);
-  constexpr int my = cout / 32;            // 16-column chunks owned by this warp (chunks colhalf, colhalf+2, ...)
-  constexpr bool kLastLayer = (L == kBlocks - 1);
-  // stage this layer's scale / shift (double buffered) while the MMAs run
-  float* tab_s = c.tab + (L & 1) * 512;
-  float* tab_h = tab_s + 256;
-  for (int i = c.tid_t; i < cout; i += EPI_THREADS) {
-    tab_s[i] = __ldg(tab_g + kChTotal + ch_off(L) + i);
-    tab_h[i] = __ldg(tab_g + 2 * kChTotal + ch_off(L) + i);
-  }
-  if (kLastLayer && c.tid_t < kDenseIn + 1) c.tab_w[c.tid_t] = __ldg(tab_g + 3 * kChTotal + c.tid_t);
-
-  // keep-flags of this thread's row for this layer (see keep_insert): produced while the layer's MMAs run
-  uint32_t kb[4];
-  make_keep_flags<L, DROP>(c, a, g, win, kb);
-  constexpr uint32_t thr2 = drop_thr15(L) * 0x00010001u;
-  const uint32_t c2 = ((uint32_t)L << 16) | (uint32_t)c.t;
-  const uint32_t row_mask = c.row_valid ? 0xFFFFFFFFu : 0u;   // zero rows = the next layer's `same` padding
-
-  // one warp polls the accumulator barrier; the others sleep in the named barrier (no issue slots burnt)
-  if (c.we == 0) {
-    mbar_wait2(c.bar_acc, n_acc & 1, c.err_flag, 4);
-    tc_fence_after();
-    tc_fence_before();
-  }
-  ++n_acc;
-  named_bar_sync(1 + c.tl, EPI_THREADS);
-  tc_fence_after();
-
-  float* dbg = nullptr;
-  if (DBG) {
-    if (dbg_base) dbg = dbg_base + (size_t)L * 128 * 256;
-  }
-  float zacc = 0.f;
-  // software pipeline: the TMEM load of the next chunk is in flight while the current one is processed
-  uint32_t va[16], vb[16];
-  tmem_ld16(c.taddr + (uint32_t)(16 * c.colhalf), va);
-#pragma unroll
-  for (int j = 0; j < my; j += 2) {
-    tmem_wait16(va);
-    if (j + 1 < my) tmem_ld16(c.taddr + (uint32_t)(16 * (c.colhalf + 2 * (j + 1))), vb);
-    {
-      const uint32_t zq[4] = {keep_extract(kb, 4 * j), keep_extract(kb, 4 * j + 1), keep_extract(kb, 4 * j + 2), keep_extract(kb, 4 * j + 3)};
-      epi_chunk16<DROP, kLastLayer, DBG, CKPT>(va, 16 * (c.colhalf + 2 * j), tab_s, tab_h, c.tab_w, c.act_row, c.row_valid, row_mask,
-                                               thr2, c.c0w, (uint32_t)g, c2, c.k0, c.k1, zq, zacc, dbg, ckpt_row);
-    }
-    if (j + 1 < my) {
-      tmem_wait16(vb);
-      if (j + 2 < my) tmem_ld16(c.taddr + (uint32_t)(16 * (c.colhalf + 2 * (j + 2))), va);
-      const uint32_t zq[4] = {keep_extract(kb, 4 * j + 4), keep_extract(kb, 4 * j + 5), keep_extract(kb, 4 * j + 6), keep_extract(kb, 4 * j + 7)};
-      epi_chunk16<DROP, kLastLayer, DBG, CKPT>(vb, 16 * (c.colhalf + 2 * (j + 1)), tab_s, tab_h, c.tab_w, c.act_row, c.row_valid,
-                                               row_mask, thr2, c.c0w, (uint32_t)g, c2, c.k0, c.k1, zq, zacc, dbg, ckpt_row);
-    }
-  }
-
-  if (!kLastLayer) {
-    // activations of the next layer are in place: publish to the tensor-core proxy, hand TMEM back
-    fence_proxy_async();
-    tc_fence_before();
-    epi_signal_act<EPI_THREADS>(c);
-  } else {
-    // ---- head: GlobalAveragePooling1D + Dense(96->1) + sigmoid; one window = 2 lane quarters x 2 column halves
-    tc_fence_before();
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) zacc += __shfl_xor_sync(0xffffffffu, zacc, o);
-    if (c.lane == 0) c.zp[c.slot_w * 4 + (c.quarter & 1) * 2 + c.colhalf] = zacc;
-    named_bar_sync(1 + c.tl, EPI_THREADS);
-    if (c.colhalf == 0 && c.t == 0 && (c.quarter & 1) == 0) {
-      const float* z4 = c.zp + c.slot_w * 4;
-      const float z = (((z4[0] + z4[1]) + z4[2]) + z4[3]) * (1.0f / (float)kL) + c.tab_w[kDenseIn];   // fixed order
-      const float p = 1.0f / (1.0f + expf(-z));
-      if (a.smem_probs) probs_s[(2 * c.tl + c.slot_w) * a.n_groups + g] = p;
-      if (a.probs && win < a.n) a.probs[(size_t)g * a.n + win] = p;
-    }
-  }
-}
-
-// ---- statistics epilogue (exact batch-statistic mode) -------------------------------------------------------------
-// Sum of 16 per-lane values over the 32 lanes of a warp by recursive halving: after the xor-16/8/4/2 exchanges a lane
-// holds ONE of the 16 columns -- column (lane >> 1) & 15 -- summed over 16 lanes, and the xor-1 step completes it.
-// 16 shuffles instead of 80, and a fixed summation tree (the result does not depend on scheduling).
-__device__ __forceinline__ float warp_halve16(const float (&v)[16], int lane) {
-  float t8[8], t4[4], t2[2];
-  const bool b4 = (lane & 16) != 0, b3 = (lane & 8) != 0, b2 = (lane & 4) != 0, b1 = (lane & 2) != 0;
-#pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const float keep = b4 ? v[8 + i] : v[i], send = b4 ? v[i] : v[8 + i];
-    t8[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
-  }
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const float keep = b3 ? t8[4 + i] : t8[i], send = b3 ? t8[i] : t8[4 + i];
-    t4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
-  }
-#pragma unroll
-  for (int i = 0; i < 2; ++i) {
-    const float keep = b2 ? t4[2 + i] : t4[i], send = b2 ? t4[i] : t4[2 + i];
-    t2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-  }
-  const float keep = b1 ? t2[1] : t2[0], send = b1 ? t2[0] : t2[1];
-  float r = keep + __shfl_xor_sync(0xffffffffu, send, 2);
-  r += __shfl_xor_sync(0xffffffffu, r, 1);
-  return r;
-}
-
-
-// Layer L is the last layer of a statistics sweep: ReLU of the accumulator (bias already added by the MMA), then the
-// per-channel sum / sum of squares over the valid rows.  One warp's partial covers 32 rows of one window; it is
-// converted to fixed point BEFORE it meets any other partial, so the totals are sums of integers that depend only on
-// (window, row half, channel) -- independent of the grid, of scheduling and of how windows are sharded over GPUs.
-template <int L, int DROP, int EPI_THREADS>
-__device__ __forceinline__ void epi_stats(const EpiCtx& c, const FusedArgs& a, int g, long long win, uint32_t& n_acc,
-                                          unsigned long long* s_stats) {
-  constexpr int cout = fl_cout(L);
-  constexpr int my = cout / 32;
-  constexpr bool kHead = (L == kBlocks - 1);
-  const bool head = kHead && a.head_sum != nullptr;
-  uint32_t kb[4] = {0u, 0u, 0u, 0u};
-  if (kHead) {
-    if (head) make_keep_flags<L, DROP>(c, a, g, win, kb);      // layer-6 dropout masks, in the MMA shadow
-  }
-  if (c.we == 0) {
-    mbar_wait2(c.bar_acc, n_acc & 1, c.err_flag, 4);
-    tc_fence_after();
-    tc_fence_before();
-  }
-  ++n_acc;
-  named_bar_sync(1 + c.tl, EPI_THREADS);
-  tc_fence_after();
-  uint32_t va[16];
-  // (pass, window, row half) block of the head partials; this warp covers rows [32*(quarter&1), +32) of its window
-  const size_t head_row = (((size_t)g * a.n + (win < a.n ? win : 0)) * 2 + (size_t)(c.quarter & 1)) * kDenseIn;
-#pragma unroll
-  for (int j = 0; j < my; ++j) {
-    const int col0 = 16 * (c.colhalf + 2 * j);
-    tmem_ld16(c.taddr + (uint32_t)col0, va);
-    tmem_wait16(va);
-    float sv[16], qv[16];
-#pragma unroll
-    for (int e = 0; e < 16; ++e) {
-      const float r = c.row_valid ? fmaxf(__uint_as_float(va[e]), 0.f) : 0.f;
-      sv[e] = r;
-      qv[e] = r * r;
-    }
-    const float rs = warp_halve16(sv, c.lane);
-    const float rq = warp_halve16(qv, c.lane);
-    const int ch = col0 + ((c.lane >> 1) & 15);
-    const float mine = (c.lane & 1) ? rq : rs;      // even lane adds the sum, odd lane the sum of squares
-    atomicAdd(&s_stats[2 * ch + (c.lane & 1)], (unsigned long long)__double2ll_rn((double)mine * kFusedStatScale));
-    if (kHead) {
-      if (head) {
-        // dropout-masked column sums and kept-row counts of this warp's 32 rows (flags are zero on padding rows)
-        float mv[16], fv[16];
-#pragma unroll
-        for (int e = 0; e < 16; ++e) {
-          const uint32_t z = keep_extract(kb, 4 * j + (e >> 2));          // quad's flags in the byte sign bits
-          const bool keep = (z >> (8 * (e & 3) + 7)) & 1u;
-          mv[e] = keep ? sv[e] : 0.f;
-          fv[e] = keep ? 1.f : 0.f;
-        }
-        const float ra = warp_halve16(mv, c.lane);
-        const float rb = warp_halve16(fv, c.lane);
-        if (win < a.n) {
-          if (c.lane & 1) a.head_cnt[head_row + ch] = (unsigned char)__float2int_rn(rb);
-          else a.head_sum[head_row + ch] = ra;
-        }
-      }
-    }
-  }
-  tc_fence_before();   // TMEM reads are complete before this thread lets the next unit's MMAs start
-}
-
-// Epilogue chain of a statistics sweep: normal epilogues for layers < n_layers-1, statistics for layer n_layers-1.
-template <int L, int DROP, int EPI_THREADS>
-__device__ __forceinline__ void epi_sweep(const EpiCtx& c, const FusedArgs& a, const float* __restrict__ tab_g, int g,
-                                          long long win, uint32_t& n_acc, unsigned long long* s_stats) {
-  if (L < a.first_layer) {                    // resumed sweep: the earlier layers came from the checkpoint
-    if constexpr (L + 1 < kBlocks) epi_sweep<L + 1, DROP, EPI_THREADS>(c, a, tab_g, g, win, n_acc, s_stats);
-    return;
-  }
-  if (a.n_layers == L + 1) {
-    epi_stats<L, DROP, EPI_THREADS>(c, a, g, win, n_acc, s_stats);
-    return;
-  }
-  if constexpr (L + 1 < kBlocks) {
-    bool done = false;
-    if constexpr (L == 1 || L == 3) {
-      if (a.ckpt_out_layer == L + 1) {
-        // the output of this layer is a checkpointed activation: copy it to HBM on the way (rows 0..63 of the window)
-        uint4* row = win < a.n ? a.ckpt_out + (((size_t)g * a.n + win) * ckpt_planes(L + 1)) * 64 + c.t : nullptr;
-        epi_layer<L, DROP, false, EPI_THREADS, true>(c, a, tab_g, g, win, n_acc, nullptr, nullptr, row);
-        done = true;
-      }
-    }
-    if (!done) epi_layer<L, DROP, false, EPI_THREADS>(c, a, tab_g, g, win, n_acc, nullptr, nullptr);
-    epi_sweep<L + 1, DROP, EPI_THREADS>(c, a, tab_g, g, win, n_acc, s_stats);
-  }
-}
-
-template <int TILES, int NSLOTS, int DROP, bool DBG>
-__global__ void __launch_bounds__(FusedCfg<TILES, NSLOTS>::kThreads, TILES == 1 ? 2 : 1)
-fused_forward_kernel(const FusedArgs a) {
-  using Cfg = FusedCfg<TILES, NSLOTS>;
-  extern __shared__ __align__(1024) uint8_t smem[];
-  const uint32_t s_base = smem_u32(smem);
-  const int warp = threadIdx.x >> 5;
-  const int lane = threadIdx.x & 31;
-
-  const uint32_t bar_full = s_base + Cfg::oBar;                 // [NSLOTS]
-  const uint32_t bar_empty = bar_full + 8 * NSLOTS;             // [NSLOTS]
-  const uint32_t bar_acc = bar_empty + 8 * NSLOTS;              // [TILES]  accumulator complete (MMA -> epilogue)
-  const uint32_t bar_act = bar_acc + 8 * TILES;                 // [TILES]  activations ready (epilogue -> MMA)
-  volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(smem + Cfg::oMisc);
-  float* zpart = reinterpret_cast<float*>(smem + Cfg::oMisc + 16);  // [TILES][2 windows][4 partial sums]
-  uint32_t* s_alo = reinterpret_cast<uint32_t*>(smem + Cfg::oAlo);  // [kTotalSteps] A-descriptor low words (tile 0)
-  float* probs_s = reinterpret_cast<float*>(smem + Cfg::oProbs);    // [kWpu][n_groups]
-
-  // ---- one-time set-up
-  for (int i = threadIdx.x; i < (TILES * kActBytes) / 16; i += Cfg::kThreads)
-    reinterpret_cast<uint4*>(smem + Cfg::oAct)[i] = make_uint4(0, 0, 0, 0);   // halo rows stay zero for ever
-  for (int i = threadIdx.x; i < kTotalSteps; i += Cfg::kThreads) {
-    int l = 0, sidx = i;
-    while (sidx >= c_layers[l].nsteps) { sidx -= c_layers[l].nsteps; ++l; }
-    const FusedLayer fl = c_layers[l];
-    uint32_t a_off, a_lbo;
-    if (sidx == fl.nconv) { a_off = (uint32_t)kOnesPlane * kPlaneBytes + 4u * 16u; a_lbo = 16u; }          // bias step
-    else if (l == 0) { a_off = (uint32_t)(2 * sidx + 1) * 16u; a_lbo = 16u; }                               // tap pair
-    else {
-      const int slabs = fl.cinp / 16, tap = sidx / slabs, slab = sidx % slabs;
-      a_off = (uint32_t)(2 * slab) * kPlaneBytes + (uint32_t)(tap - fl.halo + 4) * 16u;                     // shifted rows
-      a_lbo = kPlaneBytes;
-    }
-    s_alo[i] = (((s_base + Cfg::oAct + a_off) >> 4) & 0x3FFFu) | ((a_lbo >> 4) << 16);
-  }
-  if (threadIdx.x == 0) {
-    for (int i = 0; i < NSLOTS; ++i) { mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, 1); }
-    for (int i = 0; i < TILES; ++i) { mbar_init(bar_acc + 8 * i, 1); mbar_init(bar_act + 8 * i, Cfg::kEpiThreads / 32); }
-    fence_barrier_init();
-  }
-  if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
-                     smem_u32(const_cast<uint32_t*>(tmem_ptr))),
-                 "r"((uint32_t)Cfg::kTmemCols)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-  }
-  fence_proxy_async();   // zero-filled activations must be visible to the tensor-core (async) proxy
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_ptr;
-
-  // perf-decomposition switches (tools only): results are WRONG when any is set
-  const bool dbg_no_copy = (a.variant & 2) != 0;   // producer does not fetch weights
-  const bool dbg_no_mma = (a.variant & 8) != 0;    // issuer skips the MMAs
-
-  if (warp == 0) {
-    // =========================== weight producer (one thread) ===========================
-    if (lane == 0) {
-      uint32_t it = 0;
-      for (long long unit = blockIdx.x; unit < a.n_units; unit += gridDim.x) {
-        for (int g = 0; g < a.n_groups; ++g) {
-          const uint8_t* wmem = a.packed + (size_t)(a.mode_de ? g : 0) * kPackedBytes;
-#pragma unroll 1
-          for (int l = 0; l < kBlocks; ++l) {
-            const FusedLayer fl = c_layers[l];
-            int step = 0;
-            for (int st = 0; st < fl.nstages; ++st, ++it) {
-              const int slot = it % NSLOTS;
-              const uint32_t ph = (it / NSLOTS) & 1;
-              mbar_wait2(bar_empty + 8 * slot, ph ^ 1, a.err_flag, 1);
-              const int nst = min(fl.sps, fl.nsteps - step);
-              const uint32_t bytes = (uint32_t)nst * fl.step_bytes;
-              if (dbg_no_copy) { mbar_arrive(bar_full + 8 * slot); }
-              else {
-                mbar_arrive_expect_tx(bar_full + 8 * slot, bytes);
-                bulk_g2s(s_base + Cfg::oRing + slot * kSlotBytes, wmem + fl.w_off + (size_t)step * fl.step_bytes, bytes,
-                         bar_full + 8 * slot);
-              }
-              step += nst;
-            }
-          }
-        }
-      }
-    }
-  } else if (warp == 1) {
-    // =========================== MMA issuer ===========================
-    uint32_t it = 0, n_act = 0;
-    for (long long unit = blockIdx.x; unit < a.n_units; unit += gridDim.x) {
-      for (int g = 0; g < a.n_groups; ++g) {
-        issue_layer<0, TILES, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_acc, bar_act, it, n_act, a.err_flag, dbg_no_mma);
-        issue_layer<1, TILES, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_acc, bar_act, it, n_act, a.err_flag, dbg_no_mma);
-        issue_layer<2, TILES, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_acc, bar_act, it, n_act, a.err_flag, dbg_no_mma);
-        issue_layer<3, TILES, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_acc, bar_act, it, n_act, a.err_flag, dbg_no_mma);
-        issue_layer<4, TILES, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_acc, bar_act, it, n_act, a.err_flag, dbg_no_mma);
-        issue_layer<5, TILES, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_acc, bar_act, it, n_act, a.err_flag, dbg_no_mma);
-      }
-    }
-  } else {
-    // =========================== epilogue warps: 8 per tile ===========================
-    const int ew = warp - 2;
-    EpiCtx c;
-    c.tl = ew >> 3;
-    c.we = ew & 7;
-    c.lane = lane;
-    c.quarter = warp & 3;                         // TMEM lanes [32*quarter, +32) are accessible to this warp
-    c.colhalf = c.we >> 2;                        // which half of the 16-column chunks this warp owns
-    const int row = c.quarter * 32 + lane;        // accumulator row = TMEM lane
-    c.slot_w = row >> 6;                          // which of the tile's two windows
-    c.t = row & 63;                               // time step (60..63 = zero rows)
-    c.tid_t = c.we * 32 + lane;                   // 0..255 within the tile's epilogue group
-    c.tab = reinterpret_cast<float*>(smem + Cfg::oTab) + c.tl * Cfg::kTabFloats;
-    c.tab_w = c.tab + 1024;
-    c.act_row = s_base + Cfg::oAct + c.tl * kActBytes + (uint32_t)(row + 4) * 16u;
-    c.taddr = tmem_base + ((uint32_t)(c.quarter * 32) << 16) + (uint32_t)(c.tl * 256);
-    c.zp = zpart + c.tl * 8;
-    c.bar_acc = bar_acc + 8 * c.tl;
-    c.bar_act = bar_act + 8 * c.tl;
-    c.k0 = a.k0; c.k1 = a.k1;
-    c.err_flag = a.err_flag;
-    uint32_t n_acc = 0;
-
-    for (long long unit = blockIdx.x; unit < a.n_units; unit += gridDim.x) {
-      const long long win = unit * Cfg::kWpu + 2 * c.tl + c.slot_w;
-      c.row_valid = (c.t < kL) && (win < a.n);
-      // this row's 4 input features as bf16 (kept in registers for all groups of the unit)
-      uint32_t xin0 = 0, xin1 = 0;
-      if (c.colhalf == 0) {
-        if (c.row_valid) {
-          float f0, f1, f2, f3;
-          if (a.x_f64) {
-            const double2* p = reinterpret_cast<const double2*>(static_cast<const double*>(a.x) + ((size_t)win * kL + c.t) * kF);
-            const double2 u = __ldg(p), v = __ldg(p + 1);
-            f0 = (float)u.x; f1 = (float)u.y; f2 = (float)v.x; f3 = (float)v.y;
-          } else {
-            const float4 u = __ldg(reinterpret_cast<const float4*>(static_cast<const float*>(a.x) + ((size_t)win * kL + c.t) * kF));
-            f0 = u.x; f1 = u.y; f2 = u.z; f3 = u.w;
-          }
-          xin0 = pack_bf16x2(f0, f1);
-          xin1 = pack_bf16x2(f2, f3);
-        }
-      } else {
-        // constant plane [1, 1, 0, ...] on valid rows: the bias step of every layer reads it as its A operand
-        st_shared_v4(c.act_row + (uint32_t)kOnesPlane * kPlaneBytes, c.row_valid ? 0x3F803F80u : 0u, 0u, 0u, 0u);
-      }
-      c.c0w = (uint32_t)(a.window_base + win);
-      float* dbg_base = nullptr;
-      if (DBG) {
-        if (a.dbg_act && blockIdx.x == 0 && unit == blockIdx.x && c.tl == 0) dbg_base = a.dbg_act + (size_t)row * 256;
-      }
-
-      for (int g = 0; g < a.n_groups; ++g) {
-        // ---- layer-1 input: channels 0..3 real, 4..7 zero, in plane 0
-        if (c.colhalf == 0) st_shared_v4(c.act_row, xin0, xin1, 0u, 0u);
-        fence_proxy_async();
-        epi_signal_act<Cfg::kEpiThreads>(c);
-        const float* tab_g = a.tables + (size_t)((a.mode_de || a.tab_per_group) ? g : 0) * kTableFloats;
-        float* dbg_g = (DBG && g == 0) ? dbg_base : nullptr;
-        epi_layer<0, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
-        epi_layer<1, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
-        epi_layer<2, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
-        epi_layer<3, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
-        epi_layer<4, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
-        epi_layer<5, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
-      }
-      // ---- K3: per-window reductions over the T (or M) probabilities, in the reference's evaluation order
-      if (a.smem_probs && c.colhalf == 0 && c.t == 0 && (c.quarter & 1) == 0 && win < a.n) {
-        const float* pw = probs_s + (2 * c.tl + c.slot_w) * a.n_groups;
-        window_metrics([&](int tt) { return pw[tt]; }, a.n_groups, win, a.out);
-      }
-    }
-  }
-
-  // ---- teardown
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 1) {
-    tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)Cfg::kTmemCols)
-                 : "memory");
-  }
-}
-
-// =====================================================================================================================
-// CTA-pair variant (cta_group::2): a cluster of two CTAs on the two SMs of a TPC owns a unit of 4 windows; each CTA
-// holds ONE tile (its 2 windows) and HALF of every weight stage; the leader CTA issues M=256 MMAs that span both SMs.
-// Two pairs are co-resident per SM pair (2 CTAs / SM), so one pair's epilogue overlaps the other pair's MMAs, while
-// the weight traffic per SM stays that of the two-tile kernel (R = 4 window-passes per stream).
-// Peer -> leader signalling ("my half of stage s has landed", "my activations are ready") is relayed by the peer's
-// otherwise idle warp 1 with remote mbarrier arrives; leader -> both signalling uses tcgen05.commit multicast.
-// =====================================================================================================================
-template <int NSLOTS>
-struct PairCfg {
-  static constexpr int kEpiThreads = 256;
-  static constexpr int kWarps = 10;
-  static constexpr int kThreads = 32 * kWarps;
-  static constexpr int kWpu = 4;                   // windows per pair unit
-  static constexpr int kTmemCols = 256;
-  static constexpr int kSlot = kSlotBytes / 2;     // each CTA keeps half of a stage
-  static constexpr int oAct = 0;
-  static constexpr int oRing = oAct + kActBytes;
-  static constexpr int kTabFloats = 2 * 512 + 128;
-  static constexpr int oTab = oRing + NSLOTS * kSlot;
-  static constexpr int oBar = oTab + kTabFloats * 4;
-  static constexpr int kNumBars = 3 * NSLOTS + 3;  // full, empty, peer_full [NSLOTS]; acc, act, peer_act
-  static constexpr int oMisc = oBar + 8 * kNumBars;
-  static constexpr int oAlo = oMisc + 16 + 32;
-  static constexpr int oProbs = oAlo + 4 * 392;    // probs[2][n_groups]
-};
-
-__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity, int* err_flag, int code) {
-  long long t0 = 0;
-  for (;;) {
-    uint32_t ok;
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t.reg .b32 n;\n\t"
-        "mov.u32 n, 2048;\n"
-        "UQK_TRY:\n\t"
-        "mbarrier.try_wait.parity.relaxed.cluster.shared::cta.b64 p, [%1], %2, %3;\n\t"
-        "@p bra UQK_DONE;\n\t"
-        "sub.u32 n, n, 1;\n\t"
-        "setp.ne.u32 p, n, 0;\n\t"
-        "@p bra UQK_TRY;\n\t"
-        "mov.u32 %0, 0;\n\t"
-        "bra UQK_END;\n"
-        "UQK_DONE:\n\t"
-        "mov.u32 %0, 1;\n"
-        "UQK_END:\n\t}"
-        : "=r"(ok)
-        : "r"(bar), "r"(parity), "r"(20000u)
-        : "memory");
-    if (ok) return;
-    const long long now = clock64();
-    if (t0 == 0) t0 = now;
-    else if (now - t0 > 4000000000ll) mbar_timeout(err_flag, code);
-  }
-}
-
-template <int L, int NSLOTS, typename Cfg>
-__device__ __forceinline__ void issue_layer_pair(uint32_t s_base, uint32_t tmem_base, const uint32_t* s_alo,
-                                                 uint32_t bar_full, uint32_t bar_empty, uint32_t bar_peer_full,
-                                                 uint32_t bar_acc, uint32_t bar_act, uint32_t bar_peer_act, uint32_t& it,
-                                                 uint32_t& n_act, int* err_flag, bool no_mma, uint32_t a_tile = 0u) {
-  constexpr FusedLayer fl = fused_layer(L);
-  constexpr uint32_t kHi = (128u >> 4) | (1u << 14);
-  constexpr uint32_t kBLbo = ((uint32_t)((fl.cout / 2) * 16) >> 4) << 16;
-  constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(fl.cout >> 3) << 17) | ((256u >> 4) << 24);
-  constexpr int kLast = fl.nsteps - (fl.nstages - 1) * fl.sps;
-  mbar_wait_cluster(bar_act, n_act & 1, err_flag, 2);      // 8 local warp arrivals + 1 relayed from the peer
-  ++n_act;
-  tc_fence_after();
-#pragma unroll 1
-  for (int st = 0; st < fl.nstages; ++st, ++it) {
-    const int slot = it % NSLOTS;
-    const uint32_t ph = (it / NSLOTS) & 1;
-    mbar_wait_cluster(bar_full + 8 * slot, ph, err_flag, 3);   // own half landed (tx) + peer's half (relayed arrive)
-    tc_fence_after();
-    const int nst = (st == fl.nstages - 1) ? kLast : fl.sps;
-    const uint32_t b_lo0 = (((s_base + Cfg::oRing + slot * Cfg::kSlot) >> 4) & 0x3FFFu) | kBLbo;
-    if (elect_one()) {
-      const uint32_t* alo = s_alo + fl_step_base(L) + st * fl.sps;
-      if (!no_mma) {
-#pragma unroll
-        for (int sl = 0; sl < fl.sps; ++sl) {
-          if (sl < nst) {
-            const uint64_t bdesc = mk64(b_lo0 + (uint32_t)sl * (uint32_t)(fl.step_bytes >> 5), kHi);
-            umma_bf16_2cta(tmem_base, mk64(alo[sl] + a_tile, kHi), bdesc, kIdesc, (st > 0 || sl > 0) ? 1u : 0u);
-          }
-        }
-      }
-      umma_commit_2cta(bar_empty + 8 * slot);   // both CTAs' ring slots are free once these MMAs have read them
-    }
-    __syncwarp();
-  }
-  if (elect_one()) umma_commit_2cta(bar_acc);   // both CTAs' accumulators complete
-  __syncwarp();
-}
-
-template <int L, int NSLOTS>
-__device__ __forceinline__ void relay_layer(uint32_t bar_full, uint32_t bar_act, uint32_t r_peer_full, uint32_t r_peer_act,
-                                            uint32_t& it, uint32_t& n_act, int* err_flag) {
-  constexpr FusedLayer fl = fused_layer(L);
-  mbar_wait2(bar_act, n_act & 1, err_flag, 22);
-  ++n_act;
-  mbar_arrive_remote(r_peer_act);
-#pragma unroll 1
-  for (int st = 0; st < fl.nstages; ++st, ++it) {
-    const int slot = it % NSLOTS;
-    mbar_wait2(bar_full + 8 * slot, (it / NSLOTS) & 1, err_flag, 23);
-    mbar_arrive_remote(r_peer_full + 8 * slot);
-  }
-}
-
-// STAT = true: statistics sweep of the exact batch-statistic mode (see FusedArgs::n_layers); the epilogue warps then
-// walk passes in the OUTER loop so that one pass's statistics are accumulated in shared memory and flushed once.
-template <int NSLOTS, int DROP, bool DBG, bool STAT = false>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(PairCfg<NSLOTS>::kThreads, 2)
-fused_pair_kernel(const FusedArgs a) {
-  using Cfg = PairCfg<NSLOTS>;
-  extern __shared__ __align__(1024) uint8_t smem[];
-  const uint32_t s_base = smem_u32(smem);
-  const int warp = threadIdx.x >> 5;
-  const int lane = threadIdx.x & 31;
-  const uint32_t rank = cluster_ctarank();
-  const long long pair_id = blockIdx.x >> 1;
-  const long long n_pairs = gridDim.x >> 1;
-
-  const uint32_t bar_full = s_base + Cfg::oBar;
-  const uint32_t bar_empty = bar_full + 8 * NSLOTS;
-  const uint32_t bar_peer_full = bar_empty + 8 * NSLOTS;        // used in the leader only
-  const uint32_t bar_acc = bar_peer_full + 8 * NSLOTS;
-  const uint32_t bar_act = bar_acc + 8;
-  const uint32_t bar_peer_act = bar_act + 8;                    // used in the leader only
-  volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(smem + Cfg::oMisc);
-  float* zpart = reinterpret_cast<float*>(smem + Cfg::oMisc + 16);
-  uint32_t* s_alo = reinterpret_cast<uint32_t*>(smem + Cfg::oAlo);
-  float* probs_s = reinterpret_cast<float*>(smem + Cfg::oProbs);
-
-  for (int i = threadIdx.x; i < kActBytes / 16; i += Cfg::kThreads)
-    reinterpret_cast<uint4*>(smem + Cfg::oAct)[i] = make_uint4(0, 0, 0, 0);
-  for (int i = threadIdx.x; i < kTotalSteps; i += Cfg::kThreads) {
-    int l = 0, sidx = i;
-    while (sidx >= c_layers[l].nsteps) { sidx -= c_layers[l].nsteps; ++l; }
-    const FusedLayer fl = c_layers[l];
-    uint32_t a_off, a_lbo;
-    if (sidx == fl.nconv) { a_off = (uint32_t)kOnesPlane * kPlaneBytes + 4u * 16u; a_lbo = 16u; }
-    else if (l == 0) { a_off = (uint32_t)(2 * sidx + 1) * 16u; a_lbo = 16u; }
-    else {
-      const int slabs = fl.cinp / 16, tap = sidx / slabs, slab = sidx % slabs;
-      a_off = (uint32_t)(2 * slab) * kPlaneBytes + (uint32_t)(tap - fl.halo + 4) * 16u;
-      a_lbo = kPlaneBytes;
-    }
-    s_alo[i] = (((s_base + Cfg::oAct + a_off) >> 4) & 0x3FFFu) | ((a_lbo >> 4) << 16);
-  }
-  if (threadIdx.x == 0) {
-    // leader: every "full" / "act" barrier also counts one arrival relayed from the peer CTA
-    const uint32_t extra = rank == 0 ? 1u : 0u;
-    for (int i = 0; i < NSLOTS; ++i) {
-      mbar_init(bar_full + 8 * i, 1 + extra); mbar_init(bar_empty + 8 * i, 1); mbar_init(bar_peer_full + 8 * i, 1);
-    }
-    mbar_init(bar_acc, 1); mbar_init(bar_act, Cfg::kEpiThreads / 32 + extra); mbar_init(bar_peer_act, 1);
-    fence_barrier_init();
-  }
-  if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
-                     smem_u32(const_cast<uint32_t*>(tmem_ptr))),
-                 "r"((uint32_t)Cfg::kTmemCols)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
-  }
-  fence_proxy_async();
-  tc_fence_before();
-  cluster_sync_all();          // barriers of BOTH CTAs are initialised before anyone signals across the pair
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_ptr;
-  const bool dbg_no_copy = (a.variant & 2) != 0;
-  const bool dbg_no_mma = (a.variant & 8) != 0;
-
-  if (warp == 0) {
-    // ---- weight producer: this CTA's half of every stage
-    if (lane == 0) {
-      uint32_t it = 0;
-      for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
-        for (int g = 0; g < a.n_groups; ++g) {
-          const uint8_t* wmem = a.packed + (size_t)(a.mode_de ? g : 0) * kPackedBytes + (size_t)rank * (kPackedBytes / 2);
-          const int n_layers = STAT ? a.n_layers : kBlocks;
-#pragma unroll 1
-          for (int l = STAT ? a.first_layer : 0; l < n_layers; ++l) {
-            const FusedLayer fl = c_layers[l];
-            const uint32_t sb = (uint32_t)fl.step_bytes / 2;
-            int step = 0;
-            for (int st = 0; st < fl.nstages; ++st, ++it) {
-              const int slot = it % NSLOTS;
-              const uint32_t ph = (it / NSLOTS) & 1;
-              mbar_wait2(bar_empty + 8 * slot, ph ^ 1, a.err_flag, 1);
-              const int nst = min(fl.sps, fl.nsteps - step);
-              const uint32_t bytes = (uint32_t)nst * sb;
-              if (dbg_no_copy) { mbar_arrive(bar_full + 8 * slot); }
-              else {
-                mbar_arrive_expect_tx(bar_full + 8 * slot, bytes);
-                bulk_g2s(s_base + Cfg::oRing + slot * Cfg::kSlot, wmem + fl.w_off / 2 + (size_t)step * sb, bytes,
-                         bar_full + 8 * slot);
-              }
-              step += nst;
-            }
-          }
-        }
-      }
-    }
-  } else if (warp == 1) {
-    uint32_t it = 0, n_act = 0;
-    if (rank == 0) {
-      // ---- leader: MMA issuer for the pair
-      for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
-        for (int g = 0; g < a.n_groups; ++g) {
-          if (!STAT || a.first_layer <= 0) issue_layer_pair<0, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
-          if (!STAT || (a.n_layers > 1 && a.first_layer <= 1)) issue_layer_pair<1, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
-          if (!STAT || (a.n_layers > 2 && a.first_layer <= 2)) issue_layer_pair<2, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
-          if (!STAT || (a.n_layers > 3 && a.first_layer <= 3)) issue_layer_pair<3, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
-          if (!STAT || (a.n_layers > 4 && a.first_layer <= 4)) issue_layer_pair<4, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
-          if (!STAT || (a.n_layers > 5 && a.first_layer <= 5)) issue_layer_pair<5, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
-        }
-      }
-    } else if (lane == 0) {
-      // ---- peer: relay "stage landed" / "activations ready" to the leader's barriers
-      const uint32_t r_peer_full = mapa_shared(bar_full, 0);
-      const uint32_t r_peer_act = mapa_shared(bar_act, 0);
-      for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
-        for (int g = 0; g < a.n_groups; ++g) {
-          if (!STAT || a.first_layer <= 0) relay_layer<0, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
-          if (!STAT || (a.n_layers > 1 && a.first_layer <= 1)) relay_layer<1, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
-          if (!STAT || (a.n_layers > 2 && a.first_layer <= 2)) relay_layer<2, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
-          if (!STAT || (a.n_layers > 3 && a.first_layer <= 3)) relay_layer<3, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
-          if (!STAT || (a.n_layers > 4 && a.first_layer <= 4)) relay_layer<4, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
-          if (!STAT || (a.n_layers > 5 && a.first_layer <= 5)) relay_layer<5, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
-        }
-      }
-    }
-  } else {
-    // ---- epilogue: 8 warps, this CTA's tile
-    EpiCtx c;
-    c.tl = 0;
-    c.we = warp - 2;
-    c.lane = lane;
-    c.quarter = warp & 3;
-    c.colhalf = c.we >> 2;
-    const int row = c.quarter * 32 + lane;
-    c.slot_w = row >> 6;
-    c.t = row & 63;
-    c.tid_t = c.we * 32 + lane;
-    c.tab = reinterpret_cast<float*>(smem + Cfg::oTab);
-    c.tab_w = c.tab + 1024;
-    c.act_row = s_base + Cfg::oAct + (uint32_t)(row + 4) * 16u;
-    c.taddr = tmem_base + ((uint32_t)(c.quarter * 32) << 16);
-    c.zp = zpart;
-    c.bar_acc = bar_acc;
-    c.bar_act = bar_act;
-    c.k0 = a.k0; c.k1 = a.k1;
-    c.err_flag = a.err_flag;
-    uint32_t n_acc = 0;
-    // per-unit prologue: which window this thread's row belongs to, its input row (bf16), the ones-plane row
-    auto unit_prologue = [&](long long unit, long long& win, uint32_t& xin0, uint32_t& xin1) {
-      win = unit * Cfg::kWpu + 2 * (long long)rank + c.slot_w;
-      c.row_valid = (c.t < kL) && (win < a.n);
-      xin0 = 0; xin1 = 0;
-      if (c.colhalf == 0) {
-        if (c.row_valid) {
-          float f0, f1, f2, f3;
-          if (a.x_f64) {
-            const double2* p = reinterpret_cast<const double2*>(static_cast<const double*>(a.x) + ((size_t)win * kL + c.t) * kF);
-            const double2 u = __ldg(p), v = __ldg(p + 1);
-            f0 = (float)u.x; f1 = (float)u.y; f2 = (float)v.x; f3 = (float)v.y;
-          } else {
-            const float4 u = __ldg(reinterpret_cast<const float4*>(static_cast<const float*>(a.x) + ((size_t)win * kL + c.t) * kF));
-            f0 = u.x; f1 = u.y; f2 = u.z; f3 = u.w;
-          }
-          xin0 = pack_bf16x2(f0, f1);
-          xin1 = pack_bf16x2(f2, f3);
-        }
-      } else {
-        st_shared_v4(c.act_row + (uint32_t)kOnesPlane * kPlaneBytes, c.row_valid ? 0x3F803F80u : 0u, 0u, 0u, 0u);
-      }
-      c.c0w = (uint32_t)(a.window_base + win);
-    };
-    if (STAT) {
-      unsigned long long* s_stats = reinterpret_cast<unsigned long long*>(smem + Cfg::oProbs);   // [2 * 256], no probs here
-      for (int i = c.tid_t; i < 2 * kMaxCh; i += Cfg::kEpiThreads) s_stats[i] = 0ull;
-      named_bar_sync(1, Cfg::kEpiThreads);
-      for (int g = 0; g < a.n_groups; ++g) {
-        const float* tab_g = a.tables + (size_t)g * kTableFloats;
-        for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
-          long long win; uint32_t xin0, xin1;
-          unit_prologue(unit, win, xin0, xin1);
-          if (a.first_layer == 0) {
-            if (c.colhalf == 0) st_shared_v4(c.act_row, xin0, xin1, 0u, 0u);
-          } else {
-            // resume from a checkpoint: this row's planes of the first layer's input, half of them per column-half thread
-            const int planes = ckpt_planes(a.first_layer);
-            const uint4* src = a.ckpt_in + (((size_t)g * a.n + (win < a.n ? win : 0)) * planes) * 64 + c.t;
-#pragma unroll 4
-            for (int q = 0; q < planes / 2; ++q) {
-              const int pl = c.colhalf * (planes / 2) + q;
-              const uint4 v = win < a.n ? __ldcs(src + (size_t)pl * 64) : make_uint4(0u, 0u, 0u, 0u);
-              st_shared_v4(c.act_row + (uint32_t)pl * kPlaneBytes, v.x, v.y, v.z, v.w);
-            }
-          }
-          fence_proxy_async();
-          epi_signal_act<Cfg::kEpiThreads>(c);
-          epi_sweep<0, DROP, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, s_stats);
-        }
-        // this pass is complete in this CTA: add its fixed-point sums to the global accumulators of pass g
-        named_bar_sync(1, Cfg::kEpiThreads);
-        for (int i = c.tid_t; i < 2 * kMaxCh; i += Cfg::kEpiThreads) {
-          const unsigned long long v = s_stats[i];
-          if (v != 0ull) { atomicAdd(a.stats + (size_t)g * 2 * kMaxCh + i, v); s_stats[i] = 0ull; }
-        }
-        named_bar_sync(1, Cfg::kEpiThreads);
-      }
-    } else {
-    for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
-      long long win; uint32_t xin0, xin1;
-      unit_prologue(unit, win, xin0, xin1);
-      float* dbg_base = nullptr;
-      if (DBG) {
-        if (a.dbg_act && blockIdx.x == 0 && unit == pair_id) dbg_base = a.dbg_act + (size_t)row * 256;
-      }
-      for (int g = 0; g < a.n_groups; ++g) {
-        if (c.colhalf == 0) st_shared_v4(c.act_row, xin0, xin1, 0u, 0u);
-        fence_proxy_async();
-        epi_signal_act<Cfg::kEpiThreads>(c);
-        const float* tab_g = a.tables + (size_t)((a.mode_de || a.tab_per_group) ? g : 0) * kTableFloats;
-        float* dbg_g = (DBG && g == 0) ? dbg_base : nullptr;
-        // probs_s rows are indexed by (2*tl + slot_w) = slot_w here
-        epi_layer<0, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
-        epi_layer<1, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
-        epi_layer<2, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
-        epi_layer<3, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
-        epi_layer<4, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
-        epi_layer<5, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
-      }
-      if (a.smem_probs && c.colhalf == 0 && c.t == 0 && (c.quarter & 1) == 0 && win < a.n) {
-        const float* pw = probs_s + c.slot_w * a.n_groups;
-        window_metrics([&](int tt) { return pw[tt]; }, a.n_groups, win, a.out);
-      }
-    }
-    }
-  }
-
-  // ---- teardown: nobody may leave while the pair can still touch its shared memory / TMEM
-  tc_fence_before();
-  cluster_sync_all();
-  if (warp == 1) {
-    tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)Cfg::kTmemCols)
-                 : "memory");
-  }
-}
-
-template <int NSLOTS, int DROP, bool DBG, bool STAT = false>
-static int launch_pair_variant(const FusedParams& p, cudaStream_t s) {
-  using Cfg = PairCfg<NSLOTS>;
-  FusedArgs a{};
-  a.x = p.x; a.x_f64 = p.x_dtype == UQK_F64; a.n = p.n; a.n_groups = p.n_groups; a.mode_de = p.mode_de; a.tab_per_group = p.tab_per_group; a.pass_base = p.pass_base;
-  a.k0 = (uint32_t)(p.seed & 0xFFFFFFFFull); a.k1 = (uint32_t)(p.seed >> 32);
-  a.window_base = p.window_base; a.mask_bits = p.mask_bits; a.packed = reinterpret_cast<const uint8_t*>(p.packed_pair);
-  a.tables = p.tables; a.probs = p.probs; a.out = p.out; a.dbg_act = p.dbg_act; a.err_flag = p.err_flag;
-  a.variant = p.variant;
-  a.n_units = (p.n + Cfg::kWpu - 1) / Cfg::kWpu;
-  a.smem_probs = (p.no_smem_probs || STAT) ? 0 : 1;
-  a.n_layers = STAT ? p.n_layers : kBlocks; a.stats = p.stats;
-  a.pass_base = p.pass_base; a.head_sum = STAT ? p.head_sum : nullptr; a.head_cnt = STAT ? p.head_cnt : nullptr;
-  a.ckpt_out = STAT ? reinterpret_cast<uint4*>(p.ckpt_out) : nullptr; a.ckpt_out_layer = (STAT && p.ckpt_out) ? p.ckpt_out_layer : 0;
-  a.ckpt_in = STAT ? reinterpret_cast<const uint4*>(p.ckpt_in) : nullptr; a.first_layer = (STAT && p.ckpt_in) ? p.first_layer : 0;
-  if (STAT && (p.n_layers < 1 || p.n_layers > kBlocks || p.stats == nullptr)) {
-    set_error("statistics sweep needs 1 <= n_layers <= 6 and a statistics buffer"); return UQK_E_BADARG;
-  }
-  // the probability buffer of the fused reductions doubles as the statistics accumulator [2 x 256] u64 of a sweep
-  const size_t smem = (size_t)Cfg::oProbs + (STAT ? (size_t)2 * kMaxCh * sizeof(unsigned long long)
-                                                  : (p.no_smem_probs ? 0 : (size_t)2 * p.n_groups * sizeof(float)));
-  if (smem > 113 * 1024) return UQK_E_SHAPE;   // must leave room for two CTAs per SM
-  int dev = 0, sms = 148;
-  UQK_CUDA(cudaGetDevice(&dev));
-  UQK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  auto kern = fused_pair_kernel<NSLOTS, DROP, DBG, STAT>;
-  UQK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  UQK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-  int per_sm = 1;
-  UQK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, Cfg::kThreads, smem));
-  if (per_sm < 1) { set_error("pair kernel does not fit on an SM (smem %zu)", smem); return UQK_E_CUDA; }
-  // The occupancy API reports 1 block/SM for tcgen05 kernels on this driver although the hardware limits
-  // (registers, shared memory, 2 x 256 TMEM columns) admit two -- ncu's launch__occupancy_limit_* agree with two.
-  per_sm = (2 * (smem + 1024) <= 233472) ? 2 : 1;
-  const long long pairs = std::min<long long>(a.n_units, (long long)(sms / 2) * per_sm);
-  kern<<<(unsigned)(2 * pairs), Cfg::kThreads, smem, s>>>(a);
-  UQK_LAUNCH_CHECK();
-  return UQK_OK;
-}
-
-template <int NSLOTS>
-static int launch_pair(const FusedParams& p, cudaStream_t s) {
-  const int drop = !p.dropout ? kDropNone : (p.mask_bits ? kDropBits : kDropPhilox);
-  if (p.stats) {   // statistics sweep of the exact batch-statistic mode (training=True: dropout is always on)
-    if (drop == kDropNone) { set_error("statistics sweeps exist for the dropout (training=True) passes only"); return UQK_E_BADARG; }
-    return drop == kDropPhilox ? launch_pair_variant<NSLOTS, kDropPhilox, false, true>(p, s)
-                               : launch_pair_variant<NSLOTS, kDropBits, false, true>(p, s);
-  }
-  if (p.dbg_act) {
-    switch (drop) {
-      case kDropNone: return launch_pair_variant<NSLOTS, kDropNone, true>(p, s);
-      case kDropPhilox: return launch_pair_variant<NSLOTS, kDropPhilox, true>(p, s);
-      default: return launch_pair_variant<NSLOTS, kDropBits, true>(p, s);
-    }
-  }
-  switch (drop) {
-    case kDropNone: return launch_pair_variant<NSLOTS, kDropNone, false>(p, s);
-    case kDropPhilox: return launch_pair_variant<NSLOTS, kDropPhilox, false>(p, s);
-    default: return launch_pair_variant<NSLOTS, kDropBits, false>(p, s);
-  }
-}
-
-// =====================================================================================================================
-// CTA-pair variant with TWO tiles per CTA ("P2"): 1 CTA per SM, the pair owns a unit of 8 windows = tile-pairs A and B
-// (each an M=256 accumulator spanning both SMs).  Both tile-pairs consume the SAME weight stream (R = 8 window-passes
-// per stream, half the L2->SM traffic of the default pair kernel) through a 9-slot ring of half-stages.  The leader CTA
-// runs ONE MMA-ISSUER WARP PER TILE-PAIR: each walks the schedule on its own, blocks only on its own activations,
-// and the two drift apart at layer boundaries so one tile-pair's MMAs cover the other's epilogue.  A ring slot is
-// free when BOTH tile-pairs have consumed it (mbarrier count 2, tcgen05.commit multicast to both CTAs).
-// =====================================================================================================================
-template <int NSLOTS>
-struct Pair2Cfg {
-  static constexpr int kEpiThreads = 256;
-  static constexpr int kCtrlWarps = 3;             // producer, issuer of tile-pair 0 (peer: relay), issuer of tile-pair 1
-  static constexpr int kWarps = kCtrlWarps + 16;
-  static constexpr int kThreads = 32 * kWarps;
-  static constexpr int kWpu = 8;                   // windows per pair unit
-  static constexpr int kTmemCols = 512;
-  static constexpr int kSlot = kSlotBytes / 2;
-  static constexpr int oAct = 0;
-  static constexpr int oRing = oAct + 2 * kActBytes;
-  static constexpr int kTabFloats = 2 * 512 + 128;
-  static constexpr int oTab = oRing + NSLOTS * kSlot;
-  static constexpr int oBar = oTab + 2 * kTabFloats * 4;
-  static constexpr int kNumBars = 3 * NSLOTS + 6;  // full, empty, peer_full [NSLOTS]; acc[2], act[2], peer_act[2]
-  static constexpr int oMisc = oBar + 8 * kNumBars;
-  static constexpr int oAlo = oMisc + 16 + 64;
-  static constexpr int oProbs = (oAlo + 4 * 392 + 15) & ~15;   // probs[4][n_groups]
-};
-
-template <int NSLOTS, int DROP, bool DBG>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Pair2Cfg<NSLOTS>::kThreads, 1)
-fused_pair2_kernel(const FusedArgs a) {
-  using Cfg = Pair2Cfg<NSLOTS>;
-  extern __shared__ __align__(1024) uint8_t smem[];
-  const uint32_t s_base = smem_u32(smem);
-  const int warp = threadIdx.x >> 5;
-  const int lane = threadIdx.x & 31;
-  const uint32_t rank = cluster_ctarank();
-  const long long pair_id = blockIdx.x >> 1;
-  const long long n_pairs = gridDim.x >> 1;
-
-  const uint32_t bar_full = s_base + Cfg::oBar;
-  const uint32_t bar_empty = bar_full + 8 * NSLOTS;
-  const uint32_t bar_peer_full = bar_empty + 8 * NSLOTS;        // leader only
-  const uint32_t bar_acc = bar_peer_full + 8 * NSLOTS;          // [2]
-  const uint32_t bar_act = bar_acc + 16;                        // [2] leader only: its own epilogue threads
-  const uint32_t bar_peer_act = bar_act + 16;                   // [2] leader only: one remote arrive per layer
-  volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(smem + Cfg::oMisc);
-  float* zpart = reinterpret_cast<float*>(smem + Cfg::oMisc + 16);
-  uint32_t* s_alo = reinterpret_cast<uint32_t*>(smem + Cfg::oAlo);
-  float* probs_s = reinterpret_cast<float*>(smem + Cfg::oProbs);
-
-  for (int i = threadIdx.x; i < (2 * kActBytes) / 16; i += Cfg::kThreads)
-    reinterpret_cast<uint4*>(smem + Cfg::oAct)[i] = make_uint4(0, 0, 0, 0);
-  for (int i = threadIdx.x; i < kTotalSteps; i += Cfg::kThreads) {
-    int l = 0, sidx = i;
-    while (sidx >= c_layers[l].nsteps) { sidx -= c_layers[l].nsteps; ++l; }
-    const FusedLayer fl = c_layers[l];
-    uint32_t a_off, a_lbo;
-    if (sidx == fl.nconv) { a_off = (uint32_t)kOnesPlane * kPlaneBytes + 4u * 16u; a_lbo = 16u; }
-    else if (l == 0) { a_off = (uint32_t)(2 * sidx + 1) * 16u; a_lbo = 16u; }
-    else {
-      const int slabs = fl.cinp / 16, tap = sidx / slabs, slab = sidx % slabs;
-      a_off = (uint32_t)(2 * slab) * kPlaneBytes + (uint32_t)(tap - fl.halo + 4) * 16u;
-      a_lbo = kPlaneBytes;
-    }
-    s_alo[i] = (((s_base + Cfg::oAct + a_off) >> 4) & 0x3FFFu) | ((a_lbo >> 4) << 16);
-  }
-  if (threadIdx.x == 0) {
-    // leader: every "full" / "act" barrier also counts one arrival relayed from the peer CTA; a ring slot is free when
-    // BOTH tile-pairs have consumed it (two commits)
-    const uint32_t extra = rank == 0 ? 1u : 0u;
-    for (int i = 0; i < NSLOTS; ++i) {
-      mbar_init(bar_full + 8 * i, 1 + extra); mbar_init(bar_empty + 8 * i, 2); mbar_init(bar_peer_full + 8 * i, 1);
-    }
-    for (int i = 0; i < 2; ++i) {
-      mbar_init(bar_acc + 8 * i, 1); mbar_init(bar_act + 8 * i, Cfg::kEpiThreads / 32 + extra); mbar_init(bar_peer_act + 8 * i, 1);
-    }
-    fence_barrier_init();
-  }
-  if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
-                     smem_u32(const_cast<uint32_t*>(tmem_ptr))),
-                 "r"((uint32_t)Cfg::kTmemCols)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
-  }
-  fence_proxy_async();
-  tc_fence_before();
-  cluster_sync_all();
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_ptr;
-  const bool dbg_no_copy = (a.variant & 2) != 0;
-  const bool dbg_no_mma = (a.variant & 8) != 0;
-
-  if (warp == 0) {
-    // ---- weight producer: this CTA's half of every stage
-    if (lane == 0) {
-      uint32_t it = 0;
-      for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
-        for (int g = 0; g < a.n_groups; ++g) {
-          const uint8_t* wmem = a.packed + (size_t)(a.mode_de ? g : 0) * kPackedBytes + (size_t)rank * (kPackedBytes / 2);
-#pragma unroll 1
-          for (int l = 0; l < kBlocks; ++l) {
-            const FusedLayer fl = c_layers[l];
-            const uint32_t sb = (uint32_t)fl.step_bytes / 2;
-            int step = 0;
-            for (int st = 0; st < fl.nstages; ++st, ++it) {
-              const int slot = it % NSLOTS;
-              const uint32_t ph = (it / NSLOTS) & 1;
-              mbar_wait2(bar_empty + 8 * slot, ph ^ 1, a.err_flag, 1);
-              const int nst = min(fl.sps, fl.nsteps - step);
-              const uint32_t bytes = (uint32_t)nst * sb;
-              if (dbg_no_copy) { mbar_arrive(bar_full + 8 * slot); }
-              else {
-                mbar_arrive_expect_tx(bar_full + 8 * slot, bytes);
-                bulk_g2s(s_base + Cfg::oRing + slot * Cfg::kSlot, wmem + fl.w_off / 2 + (size_t)step * sb, bytes,
-                         bar_full + 8 * slot);
-              }
-              step += nst;
-            }
-          }
-        }
-      }
-    }
-  } else if (warp == 1 || warp == 2) {
-    const int tl = warp - 1;
-    if (rank == 0) {
-      // ---- leader: one MMA-issuer warp per tile-pair.  Both walk the same weight stream; they drift apart at layer
-      //      boundaries (one waits for its epilogue while the other keeps the tensor pipe busy), bounded by the ring.
-      uint32_t it = 0, n_act = 0;
-      const uint32_t tm = tmem_base + (uint32_t)tl * 256u;
-      const uint32_t a_tile = (uint32_t)tl * (uint32_t)(kActBytes >> 4);
-      const uint32_t b_acc = bar_acc + 8 * tl, b_act = bar_act + 8 * tl;
-      for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
-        for (int g = 0; g < a.n_groups; ++g) {
-          issue_layer_pair<0, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
-          issue_layer_pair<1, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
-          issue_layer_pair<2, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
-          issue_layer_pair<3, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
-          issue_layer_pair<4, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
-          issue_layer_pair<5, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
-        }
-      }
-    } else if (warp == 1 && lane == 0) {
-      // ---- peer: relay "my half of stage q has landed" to the leader's full barriers, in stream order
-      const uint32_t r_full = mapa_shared(bar_full, 0);
-      uint32_t it = 0;
-      for (long long unit = pair_id; unit < a.n_units; unit += n_pairs)
-        for (int g = 0; g < a.n_groups; ++g)
-#pragma unroll 1
-          for (int l = 0; l < kBlocks; ++l) {
-            const int ns = c_layers[l].nstages;
-            for (int st = 0; st < ns; ++st, ++it) {
-              const int slot = it % NSLOTS;
-              mbar_wait2(bar_full + 8 * slot, (it / NSLOTS) & 1, a.err_flag, 23);
-              mbar_arrive_remote(r_full + 8 * slot);
-            }
-          }
-    }
-  } else {
-    // ---- epilogue: 8 warps per tile
-    const int ew = warp - Cfg::kCtrlWarps;
-    EpiCtx c;
-    c.tl = ew >> 3;
-    c.we = ew & 7;
-    c.lane = lane;
-    c.quarter = warp & 3;
-    c.colhalf = c.we >> 2;
-    const int row = c.quarter * 32 + lane;
-    c.slot_w = row >> 6;
-    c.t = row & 63;
-    c.tid_t = c.we * 32 + lane;
-    c.tab = reinterpret_cast<float*>(smem + Cfg::oTab) + c.tl * Cfg::kTabFloats;
-    c.tab_w = c.tab + 1024;
-    c.act_row = s_base + Cfg::oAct + c.tl * kActBytes + (uint32_t)(row + 4) * 16u;
-    c.taddr = tmem_base + ((uint32_t)(c.quarter * 32) << 16) + (uint32_t)(c.tl * 256);
-    c.zp = zpart + c.tl * 8;
-    c.bar_acc = bar_acc + 8 * c.tl;
-    c.bar_act = bar_act + 8 * c.tl;
-    c.remote_act = rank == 0 ? 0u : mapa_shared(bar_act + 8 * c.tl, 0);
-    c.k0 = a.k0; c.k1 = a.k1;
-    c.err_flag = a.err_flag;
-    uint32_t n_acc = 0;
-    for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
-      // unit = 8 windows: tile-pair tl covers windows 4*tl .. 4*tl+3; this CTA (rank) takes 2 of them
-      const long long win = unit * Cfg::kWpu + 4 * c.tl + 2 * (long long)rank + c.slot_w;
-      c.row_valid = (c.t < kL) && (win < a.n);
-      uint32_t xin0 = 0, xin1 = 0;
-      if (c.colhalf == 0) {
-        if (c.row_valid) {
-          float f0, f1, f2, f3;
-          if (a.x_f64) {
-            const double2* p = reinterpret_cast<const double2*>(static_cast<const double*>(a.x) + ((size_t)win * kL + c.t) * kF);
-            const double2 u = __ldg(p), v = __ldg(p + 1);
-            f0 = (float)u.x; f1 = (float)u.y; f2 = (float)v.x; f3 = (float)v.y;
-          } else {
-            const float4 u = __ldg(reinterpret_cast<const float4*>(static_cast<const float*>(a.x) + ((size_t)win * kL + c.t) * kF));
-            f0 = u.x; f1 = u.y; f2 = u.z; f3 = u.w;
-          }
-          xin0 = pack_bf16x2(f0, f1);
-          xin1 = pack_bf16x2(f2, f3);
-        }
-      } else {
-        st_shared_v4(c.act_row + (uint32_t)kOnesPlane * kPlaneBytes, c.row_valid ? 0x3F803F80u : 0u, 0u, 0u, 0u);
-      }
-      c.c0w = (uint32_t)(a.window_base + win);
-      float* dbg_base = nullptr;
-      if (DBG) {
-        if (a.dbg_act && blockIdx.x == 0 && unit == pair_id && c.tl == 0) dbg_base = a.dbg_act + (size_t)row * 256;
-      }
-      for (int g = 0; g < a.n_groups; ++g) {
-        if (c.colhalf == 0) st_shared_v4(c.act_row, xin0, xin1, 0u, 0u);
-        fence_proxy_async();
-        epi_signal_act<Cfg::kEpiThreads>(c);
-        const float* tab_g = a.tables + (size_t)((a.mode_de || a.tab_per_group) ? g : 0) * kTableFloats;
-        float* dbg_g = (DBG && g == 0) ? dbg_base : nullptr;
-        epi_layer<0, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
-        epi_layer<1, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
-        epi_layer<2, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
-        epi_layer<3, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
-        epi_layer<4, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
-        epi_layer<5, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
-      }
-      if (a.smem_probs && c.colhalf == 0 && c.t == 0 && (c.quarter & 1) == 0 && win < a.n) {
-        const float* pw = probs_s + (2 * c.tl + c.slot_w) * a.n_groups;
-        window_metrics([&](int tt) { return pw[tt]; }, a.n_groups, win, a.out);
-      }
-    }
-  }
-
-  tc_fence_before();
-  cluster_sync_all();
-  if (warp == 1) {
-    tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)Cfg::kTmemCols)
-                 : "memory");
-  }
-}
-
-template <int NSLOTS, int DROP, bool DBG>
-static int launch_pair2_variant(const FusedParams& p, cudaStream_t s) {
-  using Cfg = Pair2Cfg<NSLOTS>;
-  FusedArgs a{};
-  a.x = p.x; a.x_f64 = p.x_dtype == UQK_F64; a.n = p.n; a.n_groups = p.n_groups; a.mode_de = p.mode_de; a.tab_per_group = p.tab_per_group; a.pass_base = p.pass_base;
-  a.k0 = (uint32_t)(p.seed & 0xFFFFFFFFull); a.k1 = (uint32_t)(p.seed >> 32);
-  a.window_base = p.window_base; a.mask_bits = p.mask_bits; a.packed = reinterpret_cast<const uint8_t*>(p.packed_pair);
-  a.tables = p.tables; a.probs = p.probs; a.out = p.out; a.dbg_act = p.dbg_act; a.err_flag = p.err_flag;
-  a.variant = p.variant;
-  a.n_units = (p.n + Cfg::kWpu - 1) / Cfg::kWpu;
-  a.smem_probs = p.no_smem_probs ? 0 : 1;
-  const size_t smem = (size_t)Cfg::oProbs + (p.no_smem_probs ? 0 : (size_t)4 * p.n_groups * sizeof(float));
-  if (smem > 227 * 1024) return UQK_E_SHAPE;
-  int dev = 0, sms = 148;
-  UQK_CUDA(cudaGetDevice(&dev));
-  UQK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  auto kern = fused_pair2_kernel<NSLOTS, DROP, DBG>;
-  UQK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  UQK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-  const long long pairs = std::min<long long>(a.n_units, (long long)(sms / 2));
-  kern<<<(unsigned)(2 * pairs), Cfg::kThreads, smem, s>>>(a);
-  UQK_LAUNCH_CHECK();
-  return UQK_OK;
-}
-
-template <int NSLOTS>
-static int launch_pair2(const FusedParams& p, cudaStream_t s) {
-  const int drop = !p.dropout ? kDropNone : (p.mask_bits ? kDropBits : kDropPhilox);
-  if (p.dbg_act) {
-    switch (drop) {
-      case kDropNone: return launch_pair2_variant<NSLOTS, kDropNone, true>(p, s);
-      case kDropPhilox: return launch_pair2_variant<NSLOTS, kDropPhilox, true>(p, s);
-      default: return launch_pair2_variant<NSLOTS, kDropBits, true>(p, s);
-    }
-  }
-  switch (drop) {
-    case kDropNone: return launch_pair2_variant<NSLOTS, kDropNone, false>(p, s);
-    case kDropPhilox: return launch_pair2_variant<NSLOTS, kDropPhilox, false>(p, s);
-    default: return launch_pair2_variant<NSLOTS, kDropBits, false>(p, s);
-  }
-}
-
-// ---- host launcher ----------------------------------------------------------------------------------------------
-template <int TILES, int NSLOTS, int DROP, bool DBG>
-static int launch_variant(const FusedParams& p, cudaStream_t s) {
-  using Cfg = FusedCfg<TILES, NSLOTS>;
-  FusedArgs a{};
-  a.x = p.x; a.x_f64 = p.x_dtype == UQK_F64; a.n = p.n; a.n_groups = p.n_groups; a.mode_de = p.mode_de; a.tab_per_group = p.tab_per_group; a.pass_base = p.pass_base;
-  a.k0 = (uint32_t)(p.seed & 0xFFFFFFFFull); a.k1 = (uint32_t)(p.seed >> 32);
-  a.window_base = p.window_base; a.mask_bits = p.mask_bits; a.packed = reinterpret_cast<const uint8_t*>(p.packed);
-  a.tables = p.tables; a.probs = p.probs; a.out = p.out; a.dbg_act = p.dbg_act; a.err_flag = p.err_flag;
-  a.variant = p.variant;
-  a.n_units = (p.n + Cfg::kWpu - 1) / Cfg::kWpu;
-  a.smem_probs = p.no_smem_probs ? 0 : 1;
-  const size_t smem = (size_t)Cfg::oProbs + (p.no_smem_probs ? 0 : (size_t)Cfg::kWpu * p.n_groups * sizeof(float));
-  if (smem > 227 * 1024) return UQK_E_SHAPE;   // caller falls back to the smaller configuration
-  int dev = 0, sms = 148;
-  UQK_CUDA(cudaGetDevice(&dev));
-  UQK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  auto kern = fused_forward_kernel<TILES, NSLOTS, DROP, DBG>;
-  UQK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  UQK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-  int per_sm = 1;
-  UQK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, Cfg::kThreads, smem));
-  if (per_sm < 1) { set_error("fused kernel does not fit on an SM (smem %zu)", smem); return UQK_E_CUDA; }
-  if (per_sm * Cfg::kTmemCols > 512) per_sm = 512 / Cfg::kTmemCols;   // TMEM: 512 columns per SM
-  const long long grid = std::min<long long>(a.n_units, (long long)sms * per_sm);
-  kern<<<(unsigned)grid, Cfg::kThreads, smem, s>>>(a);
-  UQK_LAUNCH_CHECK();
-  return UQK_OK;
-}
-
-template <int TILES, int NSLOTS>
-static int launch_drop(const FusedParams& p, cudaStream_t s) {
-  const int drop = !p.dropout ? kDropNone : (p.mask_bits ? kDropBits : kDropPhilox);
-  if (p.dbg_act) {
-    switch (drop) {
-      case kDropNone: return launch_variant<TILES, NSLOTS, kDropNone, true>(p, s);
-      case kDropPhilox: return launch_variant<TILES, NSLOTS, kDropPhilox, true>(p, s);
-      default: return launch_variant<TILES, NSLOTS, kDropBits, true>(p, s);
-    }
-  }
-  switch (drop) {
-    case kDropNone: return launch_variant<TILES, NSLOTS, kDropNone, false>(p, s);
-    case kDropPhilox: return launch_variant<TILES, NSLOTS, kDropPhilox, false>(p, s);
-    default: return launch_variant<TILES, NSLOTS, kDropBits, false>(p, s);
-  }
-}
-
 int fused_launch(const FusedParams& p, cudaStream_t s) {
   if (p.n == 0) return UQK_OK;
   // variant >> 4: 0 / 3 = CTA pairs with two tiles per CTA (default), 2 = CTA pairs with one tile per CTA and two CTAs
   // per SM, 4 = two tiles per CTA, 1 = one tile per CTA.  Every configuration falls through to a smaller one when T
   // (or M) probabilities per window do not fit its shared memory.
   const int v = p.variant >> 4;
-  if (p.stats) return launch_pair<4>(p, s);   // statistics sweeps exist in the CTA-pair kernel only
+  if (p.stats) return fused_launch_pair_stat(p, s);   // statistics sweeps exist in the CTA-pair kernel only
   int rc = UQK_E_SHAPE;
-  if (v == 0 || v == 3) rc = launch_pair2<9>(p, s);
-  if (rc == UQK_E_SHAPE && (v == 0 || v == 2 || v == 3)) rc = launch_pair<4>(p, s);
-  if (rc == UQK_E_SHAPE && v != 1) rc = launch_drop<2, 4>(p, s);
-  if (rc == UQK_E_SHAPE) rc = launch_drop<1, 2>(p, s);
+  if (v == 0 || v == 3) rc = fused_launch_pair2(p, s);
+  if (rc == UQK_E_SHAPE && (v == 0 || v == 2 || v == 3)) rc = fused_launch_pair(p, s);
+  if (rc == UQK_E_SHAPE && v != 1) rc = fused_launch_single2(p, s);
+  if (rc == UQK_E_SHAPE) rc = fused_launch_single1(p, s);
   if (rc == UQK_E_SHAPE) set_error("fused kernel: %d passes/members do not fit in shared memory", p.n_groups);
   return rc;
 }

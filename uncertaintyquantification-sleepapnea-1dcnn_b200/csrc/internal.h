@@ -76,6 +76,12 @@ struct FusedParams {
 constexpr size_t kCkpt4BytesPerWindowPass = 12 * 64 * 16;   // input of layer index 4 (96 channels)
 constexpr size_t kCkpt2BytesPerWindowPass = 24 * 64 * 16;   // input of layer index 2 (192 channels)
 int fused_launch(const FusedParams& p, cudaStream_t s);
+// one kernel family per translation unit (fused_pair2.cu, fused_pair.cu, fused_pair_stat.cu, fused_single2.cu, fused_single1.cu)
+int fused_launch_pair2(const FusedParams& p, cudaStream_t s);
+int fused_launch_pair(const FusedParams& p, cudaStream_t s);
+int fused_launch_pair_stat(const FusedParams& p, cudaStream_t s);
+int fused_launch_single2(const FusedParams& p, cudaStream_t s);
+int fused_launch_single1(const FusedParams& p, cudaStream_t s);
 
 // tables builder: bias/scale/shift/dense for one set.  mean/var: 6x256 floats (frozen) or null -> moving stats.
 int build_tables(const float* blob_dev, const float* mean, const float* var, int fold_dropout, float* table_dev,
