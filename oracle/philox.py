@@ -7,14 +7,16 @@ outside TensorFlow; the build's kernels use Philox4x32-10 keyed by (seed) and co
 so that the oracle network can be driven by the masks the kernels use ("masks exported from the
 reference" in BASELINE.json is realised as masks exported from this twin).
 
-Counter mapping (must match csrc/philox.cuh):
-    c0 = global window index (low 32 bits)
-    c1 = pass index t
-    c2 = (layer << 16) | row          layer in 0..5, row in 0..59
-    c3 = channel chunk q              (8 consecutive channels share one Philox call)
-    key = (seed & 0xffffffff, seed >> 32)
-    element e in 0..7 of the chunk uses the 15-bit field  (out[e >> 1] >> (16 * (e & 1))) & 0x7fff
-    keep  <=>  field >= round(rate * 32768)      (TF: keep iff u >= rate; kept values scaled by 1/(1-rate))
+Keep-flag definition (must match csrc/common.cuh, "dropout keep-flags"); key = (seed & 0xffffffff, seed >> 32):
+    The flags of (window, pass t, layer, row) are generated bit-sliced, 32 elements per 32-bit word.  Channel c belongs
+    to column half h = (c >> 4) & 1, flag word i = c >> 6, bit 8*(c & 3) + 4*((c >> 5) & 1) + ((c >> 2) & 3).
+    * rate 0.5 (layer 6): flag word i = output word i of ONE Philox call with counter
+      (window, t, layer << 16 | row, h): one random bit per element, keep iff the bit is 1.
+    * other rates: U = (hi8 << 8) | lo8 is the element's 16-bit uniform, keep <=> U >= round(rate * 65536)
+      (TF: keep iff u >= rate; kept values scaled by 1/(1-rate)).  Bit k of hi8 is the element's bit of plane word P_k;
+      P_0..P_7 are the 2 x 4 output words of the calls with counter (window, t, layer << 16 | row, h | i << 1 | q << 3),
+      q = 0, 1.  lo8 is a tie-break byte shared by the elements of (row, h, layer): byte `layer` of output words (x, y)
+      of the call with counter (window, t, 6 << 16 | row, h).
 """
 from __future__ import annotations
 
@@ -49,23 +51,44 @@ def philox4x32(c0, c1, c2, c3, k0: int, k1: int, rounds: int = 10):
     return (c0.astype(np.uint32), c1.astype(np.uint32), c2.astype(np.uint32), c3.astype(np.uint32))
 
 
+def drop_bitpos(c):
+    c = np.asarray(c)
+    return 8 * (c & 3) + 4 * ((c >> 5) & 1) + ((c >> 2) & 3)
+
+
 def dropout_keep_mask(seed: int, window_idx, t: int, layer: int, cout: int, rate: float,
                       rows: int = 60) -> np.ndarray:
     """Boolean keep-mask of shape (len(window_idx), rows, cout) for pass ``t`` and ``layer``."""
     window_idx = np.asarray(window_idx, dtype=np.uint64)
     n = window_idx.shape[0]
-    nq = cout // 8
-    thr = int(round(rate * 32768.0))
+    k0, k1 = seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF
+    thr16 = int(round(rate * 65536.0))
+    nw = (cout + 63) // 64
     c0 = (window_idx & MASK32).reshape(n, 1, 1)
     c1 = np.uint64(t)
-    c2 = (np.uint64(layer << 16) | np.arange(rows, dtype=np.uint64)).reshape(1, rows, 1)
-    c3 = np.arange(nq, dtype=np.uint64).reshape(1, 1, nq)
-    out = philox4x32(c0, c1, c2, c3, seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)
-    words = np.stack(out, axis=-1)                                  # (n, rows, nq, 4)
-    lo = words & np.uint32(0x7FFF)
-    hi = (words >> np.uint32(16)) & np.uint32(0x7FFF)
-    fields = np.stack([lo, hi], axis=-1).reshape(n, rows, nq * 8)  # e = 2*word + half
-    return fields >= thr
+    rws = np.arange(rows, dtype=np.uint64).reshape(1, rows, 1)
+    c2 = np.uint64(layer << 16) | rws
+    hh = np.arange(2, dtype=np.uint64).reshape(1, 1, 2)
+    words = np.zeros((n, rows, 2, nw), dtype=np.uint32)              # [window, row, h, i]
+    if thr16 == 32768:
+        out = philox4x32(c0, c1, c2, hh, k0, k1)
+        for i in range(nw):
+            words[..., i] = out[i]
+    else:
+        tie = philox4x32(c0, c1, np.uint64(6 << 16) | rws, hh, k0, k1)
+        tb = ((tie[0] >> np.uint32(8 * layer)) if layer < 4 else tie[1]) & np.uint32(0xFF)
+        g0 = np.where(tb >= (thr16 & 0xFF), np.uint32(0xFFFFFFFF), np.uint32(0))
+        thi = thr16 >> 8
+        for i in range(nw):
+            pa = philox4x32(c0, c1, c2, hh | np.uint64(i << 1), k0, k1)
+            pb = philox4x32(c0, c1, c2, hh | np.uint64((i << 1) | 8), k0, k1)
+            g = g0.copy()
+            for k, pl in enumerate(list(pa) + list(pb)):
+                g = (pl & g) if (thi >> k) & 1 else (pl | g)
+            words[..., i] = g
+    c = np.arange(cout)
+    sel = words[:, :, (c >> 4) & 1, c >> 6]                          # (n, rows, cout)
+    return ((sel >> drop_bitpos(c).astype(np.uint32)) & np.uint32(1)).astype(bool)
 
 
 def pack_mask_bits(keep: np.ndarray) -> np.ndarray:

@@ -65,7 +65,28 @@ def f32_cases():
     return p, y
 
 
+def forward_golden():
+    """Section 4 alone (`python make_golden.py forward`): it is the only part that depends on the build's own RNG
+    definition (oracle/philox.py), not on the reference."""
+    out = {}
+    X = uqk.synthetic.make_windows(24, seed=11)
+    for m_ in range(2):
+        ws = uqk.synthetic.make_member_weights(m_)
+        out[f"det_member{m_}"] = network.forward_f64(ws, X)
+    ws = uqk.synthetic.make_member_weights(0)
+    seed, T = 2025, 3
+    for t in range(T):
+        masks = [philox.dropout_keep_mask(seed, np.arange(24), t, i, b.cout, b.rate)
+                 for i, b in enumerate(uqk.arch.BLOCKS)]
+        out[f"mcd_batch_t{t}"] = network.forward_f64(ws, X, training=True, masks=masks)
+        out[f"mcd_frozen_t{t}"] = network.forward_f64(ws, X, training=True, masks=masks, bn_mode="inference")
+    np.savez_compressed(os.path.join(HERE, "forward_oracle_golden.npz"), **out)
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "forward":
+        forward_golden()
+        return
     ref = reference_loader.load_reference_uq_techniques()
     sink = io.StringIO()
 
@@ -147,19 +168,7 @@ def main():
         shutil.rmtree(work, ignore_errors=True)
 
     # ---- 4. forward: oracle float64 on seeded synthetic inputs (self-generated, unpinned)
-    out = {}
-    X = uqk.synthetic.make_windows(24, seed=11)
-    for m_ in range(2):
-        ws = uqk.synthetic.make_member_weights(m_)
-        out[f"det_member{m_}"] = network.forward_f64(ws, X)
-    ws = uqk.synthetic.make_member_weights(0)
-    seed, T = 2025, 3
-    for t in range(T):
-        masks = [philox.dropout_keep_mask(seed, np.arange(24), t, i, b.cout, b.rate)
-                 for i, b in enumerate(uqk.arch.BLOCKS)]
-        out[f"mcd_batch_t{t}"] = network.forward_f64(ws, X, training=True, masks=masks)
-        out[f"mcd_frozen_t{t}"] = network.forward_f64(ws, X, training=True, masks=masks, bn_mode="inference")
-    np.savez_compressed(os.path.join(HERE, "forward_oracle_golden.npz"), **out)
+    forward_golden()
 
     # ---- 5. window standardisation: the reference's own standardize_per_window
     #         (data_prepocessing/prepare_numpy_datasets.py:83-95; imblearn is absent and only used elsewhere -> stubbed)

@@ -44,8 +44,8 @@ struct Handle {
   float* d_stats_pass = nullptr; size_t stats_pass_cap = 0;     // ... and n_passes x 2 x 256 int64 statistics (as floats x2)
   float* d_head_sum = nullptr; size_t head_sum_cap = 0;         // exact mode: head partials of one chunk of passes
   float* d_head_cnt = nullptr; size_t head_cnt_cap = 0;         // ... kept-row counts (bytes, allocated in floats)
-  float* d_ckpt = nullptr; size_t ckpt_cap = 0;                 // ... the layer-4/5 activation checkpoint
-  float* d_ckpt2 = nullptr; size_t ckpt2_cap = 0;               // ... and the layer-2/3 activation checkpoint
+  float* d_ckpt = nullptr; size_t ckpt_cap = 0;                 // ... per-layer hand-off buffer A (outputs of layers 2 and 4)
+  float* d_ckpt2 = nullptr; size_t ckpt2_cap = 0;               // ... and B (outputs of layers 3 and 5)
   float* d_dbg = nullptr;         // 6 x 128 x 256 debug dump of the fused kernel (tests)
   int variant = 0;
   int dbg_dump = 0;
@@ -151,9 +151,18 @@ static int run_fused(Handle* h, int member0, const void* x, int x_dtype, int64_t
 // The six statistics sweeps over passes [pass0, pass0 + n_passes): leaves every pass's BatchNorm affine in
 // h->d_tables_pass and, when `frozen` is given, the pass-averaged (mean, variance) of every layer there (tensor-core
 // calibration).  When head buffers are given the sixth sweep also emits the head partials (see exact_head_kernel).
+// Every layer is computed ONCE: sweep k (k >= 3) reads layer k-1's post-ReLU output from HBM (bf16), normalises it with
+// the statistics the previous sweep produced, runs layer k and stores ITS post-ReLU output; sweep 2 recomputes the
+// cheap, pass-invariant layer 1 from the windows (0.4 % of the flops) instead of storing it.  bufA / bufB: ping-pong
+// buffers of exact_buf_bytes(0 / 1) bytes per window-pass.
+constexpr size_t exact_buf_bytes(int which) {
+  return which == 0 ? std::max(exact_layer_bytes(1), exact_layer_bytes(3)) : std::max(exact_layer_bytes(2), exact_layer_bytes(4));
+}
+constexpr size_t kExactBytesPerWindowPass = exact_buf_bytes(0) + exact_buf_bytes(1) + 2 * kDenseIn * 5;
+
 static int run_exact_sweeps(Handle* h, const void* x, int x_dtype, int64_t n, int pass0, int n_passes, uint64_t seed,
                             int64_t window_base, const uint32_t* mask_bits, float* frozen, float* head_sum,
-                            unsigned char* head_cnt, void* ckpt2, void* ckpt4, cudaStream_t s) {
+                            unsigned char* head_cnt, void* bufA, void* bufB, cudaStream_t s) {
   int rc;
   if ((rc = ensure(&h->d_tables_pass, &h->tables_pass_cap, (size_t)n_passes * kTableFloats))) return rc;
   if ((rc = ensure(&h->d_stats_pass, &h->stats_pass_cap, (size_t)n_passes * 2 * kMaxCh * 2))) return rc;
@@ -172,21 +181,17 @@ static int run_exact_sweeps(Handle* h, const void* x, int x_dtype, int64_t n, in
   if (stat_windows < 1) return UQK_OK;
   for (int k = 0; k < kBlocks; ++k) {
     UQK_CUDA(cudaMemsetAsync(stats, 0, sizeof(unsigned long long) * (size_t)n_passes * 2 * kMaxCh, s));
-    p.stats = stats; p.n_layers = k + 1;
+    p.stats = stats;
     // nothing is random before the first BatchNorm: layer 1's statistics are the same for every pass, so its sweep runs
     // one pass and the sums are copied to the other passes' rows
     p.n_groups = k == 0 ? 1 : n_passes;
     p.head_sum = k == kBlocks - 1 ? head_sum : nullptr;
     p.head_cnt = k == kBlocks - 1 ? head_cnt : nullptr;
-    // checkpoints (both or none): sweep 3 leaves layer 3's input in ckpt2, sweeps 4 and 5 resume from it; sweep 5 leaves
-    // layer 5's input in ckpt4, sweep 6 resumes from it -- no layer is computed more than three times
-    p.ckpt_out = nullptr; p.ckpt_out_layer = 0; p.ckpt_in = nullptr; p.first_layer = 0;
-    if (ckpt2 && ckpt4) {
-      if (k == 2) { p.ckpt_out = ckpt2; p.ckpt_out_layer = 2; }
-      if (k == 3) { p.ckpt_in = ckpt2; p.first_layer = 2; }
-      if (k == 4) { p.ckpt_in = ckpt2; p.first_layer = 2; p.ckpt_out = ckpt4; p.ckpt_out_layer = 4; }
-      if (k == 5) { p.ckpt_in = ckpt4; p.first_layer = 4; }
-    }
+    void* const buf_of[kBlocks] = {nullptr, bufA, bufB, bufA, bufB, nullptr};    // where layer k's output lives
+    p.first_layer = k <= 1 ? 0 : k;
+    p.n_layers = k + 1;
+    p.ckpt_in = k >= 2 ? buf_of[k - 1] : nullptr;
+    p.ckpt_out = buf_of[k];
     if ((rc = fused_launch(p, s))) return rc;           // n == 0 (empty shard): no launch, statistics stay zero
     if (k == 0 && n_passes > 1 && (rc = exact_replicate_stats(stats, n_passes, s))) return rc;
     if (exchanging &&
@@ -202,16 +207,21 @@ static int run_exact_sweeps(Handle* h, const void* x, int x_dtype, int64_t n, in
 
 // Exact Keras `training=True` semantics on the tensor-core kernel (uq_techniques.py:22: BatchNormalization uses the
 // statistics of the whole call).  The statistics of layer k depend on the normalised output of layers < k over ALL
-// windows, so the passes are swept k = 1..6 times through layers [0, k): sweep k accumulates layer k's per-pass
-// (sum, sum of squares) with the earlier layers already normalised exactly.  The sixth sweep also leaves, per
-// (pass, window), the dropout-masked column sums of the layer-6 output; BatchNorm-6, GlobalAveragePooling and Dense are
-// linear in them, so a small kernel turns them into the probabilities once layer 6's statistics are known -- no seventh
-// pass over the network.  Layers are recomputed instead of spilling all N x T x 60 x Cout activations to HBM (2.67x the
-// flops of one run without checkpoints); the passes are processed in chunks so that the head partials
-// (960 B per window-pass) and the two activation checkpoints (inputs of layers 3 and 5, 24 + 12 KB per window-pass:
-// later sweeps resume from them instead of recomputing the layers in front, 1.89x the flops of one run in total)
-// stay within kExactScratchBudget.
-constexpr size_t kExactScratchBudget = (size_t)80 << 30;
+// windows, so the network is swept layer by layer (run_exact_sweeps): sweep k accumulates layer k's per-pass
+// (sum, sum of squares) and hands its un-normalised output to sweep k+1 through HBM (96 KB written + 96 KB read per
+// window-pass in total, bf16).  The sixth sweep leaves, per (pass, window), the dropout-masked column sums of the
+// layer-6 output; BatchNorm-6, GlobalAveragePooling and Dense are linear in them, so a small kernel turns them into
+// the probabilities once layer 6's statistics are known.  The passes are processed in chunks so that the two
+// hand-off buffers and the head partials stay within kExactScratchBudget.
+constexpr size_t kExactScratchBudget = (size_t)120 << 30;
+
+static int exact_scratch(Handle* h, int64_t n, int chunk, bool with_head) {
+  int rc = ensure(&h->d_ckpt, &h->ckpt_cap, ((size_t)chunk * n * exact_buf_bytes(0) + 3) / 4);
+  if (!rc) rc = ensure(&h->d_ckpt2, &h->ckpt2_cap, ((size_t)chunk * n * exact_buf_bytes(1) + 3) / 4);
+  if (!rc && with_head) rc = ensure(&h->d_head_sum, &h->head_sum_cap, (size_t)chunk * n * 2 * kDenseIn);
+  if (!rc && with_head) rc = ensure(&h->d_head_cnt, &h->head_cnt_cap, ((size_t)chunk * n * 2 * kDenseIn + 3) / 4);
+  return rc;
+}
 
 static int run_fused_exact(Handle* h, const void* x, int x_dtype, int64_t n, int n_passes, uint64_t seed, int64_t window_base,
                            const uint32_t* mask_bits, float* probs, const MetricsOut& out, bool want_metrics, cudaStream_t s) {
@@ -219,17 +229,14 @@ static int run_fused_exact(Handle* h, const void* x, int x_dtype, int64_t n, int
   const bool exchanging = h->xchg != nullptr;
   // every rank of a sharded call must cut the passes identically: size the chunks by the windows of the whole call
   const int64_t n_for_chunks = std::max<int64_t>(1, exchanging ? h->xchg_global_n : n);
-  const size_t per_pass = (size_t)n_for_chunks * (2 * kDenseIn * 5 + kCkpt2BytesPerWindowPass + kCkpt4BytesPerWindowPass);   // head partials + checkpoints
+  const size_t per_pass = (size_t)n_for_chunks * kExactBytesPerWindowPass;
   int chunk = (int)std::max<size_t>(1, std::min<size_t>((size_t)n_passes, std::min<size_t>(kExactScratchBudget / per_pass, kMaxFusedGroups)));
   if (h->exact_chunk_max > 0) chunk = std::min(chunk, h->exact_chunk_max);
   if (n > 0) {
     for (;;) {
       // the result does not depend on the chunk size, so a GPU short of memory gets smaller chunks instead of an error
       // (not when the passes are cut jointly with other ranks)
-      rc = ensure(&h->d_head_sum, &h->head_sum_cap, (size_t)chunk * n * 2 * kDenseIn);
-      if (!rc) rc = ensure(&h->d_head_cnt, &h->head_cnt_cap, ((size_t)chunk * n * 2 * kDenseIn + 3) / 4);
-      if (!rc) rc = ensure(&h->d_ckpt, &h->ckpt_cap, (size_t)chunk * n * (kCkpt4BytesPerWindowPass / 4));
-      if (!rc) rc = ensure(&h->d_ckpt2, &h->ckpt2_cap, (size_t)chunk * n * (kCkpt2BytesPerWindowPass / 4));
+      rc = exact_scratch(h, n, chunk, true);
       if (rc != UQK_E_NOMEM || chunk == 1 || exchanging) break;
       chunk = (chunk + 1) / 2;
     }
@@ -242,7 +249,7 @@ static int run_fused_exact(Handle* h, const void* x, int x_dtype, int64_t n, int
   unsigned char* head_cnt = reinterpret_cast<unsigned char*>(h->d_head_cnt);
   for (int g0 = 0; g0 < n_passes; g0 += chunk) {
     const int gc = std::min(chunk, n_passes - g0);
-    if ((rc = run_exact_sweeps(h, x, x_dtype, n, g0, gc, seed, window_base, mask_bits, nullptr, h->d_head_sum, head_cnt, h->d_ckpt2, h->d_ckpt, s))) return rc;
+    if ((rc = run_exact_sweeps(h, x, x_dtype, n, g0, gc, seed, window_base, mask_bits, nullptr, h->d_head_sum, head_cnt, h->d_ckpt, h->d_ckpt2, s))) return rc;
     if (n > 0 && (rc = exact_head(h->d_head_sum, head_cnt, h->d_tables_pass, gc, n, probs + (size_t)g0 * n, s))) return rc;
   }
   if (n == 0) return UQK_OK;
@@ -383,7 +390,8 @@ int uqk_calibrate(uqk_handle* hh, const void* x_dev, int x_dtype, int64_t n, int
     // batch statistics of the exact training=True forward, averaged over the passes)
     if (n_passes > kMaxFusedGroups) { set_error("calibration on more than %lld windows takes at most %d passes",
                                                 (long long)h->calib_fp32_max, kMaxFusedGroups); return UQK_E_BADARG; }
-    if ((rc = run_exact_sweeps(h, x_dev, x_dtype, n, 0, n_passes, seed, 0, nullptr, h->d_frozen, nullptr, nullptr, nullptr, nullptr, s))) return rc;
+    if ((rc = exact_scratch(h, n, n_passes, false))) return rc;
+    if ((rc = run_exact_sweeps(h, x_dev, x_dtype, n, 0, n_passes, seed, 0, nullptr, h->d_frozen, nullptr, nullptr, h->d_ckpt, h->d_ckpt2, s))) return rc;
     h->have_frozen = true;
     return UQK_OK;
   }

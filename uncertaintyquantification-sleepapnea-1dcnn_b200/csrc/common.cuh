@@ -26,11 +26,13 @@ __host__ __device__ constexpr BlockDef block_def(int l) {
        : l == 4 ? BlockDef{96, 256, 9, 4, 0.3f}
                 : BlockDef{256, 96, 9, 4, 0.5f};
 }
-// 15-bit dropout threshold round(rate * 32768): an element is kept iff its 15-bit uniform draw >= thr
+// 16-bit dropout threshold round(rate * 65536): an element is kept iff its 16-bit uniform draw >= thr
 // (TF: keep iff u >= rate).  Rates 0.3, 0.3, 0.4, 0.2, 0.3, 0.5 (cnn_baseline_train.py:61,65,70,75,80,86).
-__host__ __device__ constexpr uint32_t drop_thr15(int l) {
-  return l == 0 ? 9830u : l == 1 ? 9830u : l == 2 ? 13107u : l == 3 ? 6554u : l == 4 ? 9830u : 16384u;
+__host__ __device__ constexpr uint32_t drop_thr16(int l) {
+  return l == 0 ? 19661u : l == 1 ? 19661u : l == 2 ? 26214u : l == 3 ? 13107u : l == 4 ? 19661u : 32768u;
 }
+// rate exactly 0.5: one random bit per element is an exact Bernoulli(1/2) draw
+__host__ __device__ constexpr bool drop_is_half(int l) { return drop_thr16(l) == 32768u; }
 
 // Offsets (in floats) into one member's Keras-order blob.
 struct BlobOffsets {
@@ -105,10 +107,49 @@ __device__ __forceinline__ Philox4 philox4x32_10(uint32_t c0, uint32_t c1, uint3
   }
   return Philox4{c0, c1, c2, c3};
 }
-// 15-bit field e (0..7) of one Philox call: word e>>1, half e&1, low 15 bits of that half
-__device__ __forceinline__ uint32_t philox_field15(const Philox4& r, int e) {
-  const uint32_t w = (e >> 1) == 0 ? r.x : (e >> 1) == 1 ? r.y : (e >> 1) == 2 ? r.z : r.w;
-  return ((e & 1) ? (w >> 16) : w) & 0x7FFFu;
+// ---- dropout keep-flags (must match oracle/philox.py) ---------------------------------------------------------------
+// The flags are generated BIT-SLICED, 32 elements per 32-bit word, so that a keep-mask costs a handful of logic
+// instructions per 32 elements instead of a compare per element:
+//   * the flags of (window, pass, layer, row) are grouped by column half h = (c >> 4) & 1 (the 16-column chunks a
+//     fused-kernel epilogue thread owns alternate between two warps) and flag word i = c >> 6; inside the word channel
+//     c sits at bit 8*(c & 3) + 4*((c >> 5) & 1) + ((c >> 2) & 3)   (the byte-lane layout of the fused epilogue);
+//   * rate 0.5 (layer 6): flag word i = output word i of ONE Philox4x32-10 call, counter
+//     (window, pass, layer << 16 | row, h) -- one random bit per element, exact;
+//   * other rates: the element's 16-bit uniform U = (hi8 << 8) | lo8 is compared with thr16 = round(rate * 65536);
+//     bit k of hi8 is the element's bit of plane word P_k, the planes P_0..P_7 being the 2 x 4 output words of the calls
+//     with counter (window, pass, layer << 16 | row, h | i << 1 | q << 3), q = 0, 1 (8 fresh bits per element);
+//     lo8 is a tie-break byte SHARED by the elements of (row, h, layer): byte `layer` of the call with counter
+//     (window, pass, 6 << 16 | row, h) (words x, y).  Every element's keep probability is exactly 1 - thr16 / 65536;
+//     two elements of one thread are correlated only when both tie on the 8 fresh bits (probability 2^-16).
+//   keep <=> U >= thr16 is evaluated for 32 elements at once, from the least significant bit up:
+//     g = (lo8 >= thr_lo) ? ~0 : 0;   g = thr_hi bit k ? (P_k & g) : (P_k | g),  k = 0..7.
+__host__ __device__ constexpr int drop_flag_words(int cout) { return (cout + 63) / 64; }
+__host__ __device__ constexpr uint32_t drop_bitpos(int c) { return 8u * (c & 3) + 4u * ((c >> 5) & 1) + ((c >> 2) & 3); }
+
+struct DropTie { uint32_t x, y; };     // tie-break bytes of one (window, pass, row, h): layers 0..3 in x, layer 4 in y
+__device__ __forceinline__ DropTie drop_tie(uint32_t c0w, uint32_t pass, uint32_t row, uint32_t h, uint32_t k0, uint32_t k1) {
+  const Philox4 r = philox4x32_10(c0w, pass, (6u << 16) | row, h, k0, k1);
+  return DropTie{r.x, r.y};
+}
+__device__ __forceinline__ uint32_t drop_tie_byte(const DropTie& t, int layer) {
+  return ((layer < 4 ? (t.x >> (8 * layer)) : t.y)) & 0xFFu;
+}
+// flag word i of (window, pass, layer, row, h); thr16 < 32768 + 32768 (any rate); for rate 0.5 use drop_half_words
+__device__ __forceinline__ uint32_t drop_keep_word(uint32_t c0w, uint32_t pass, uint32_t layer, uint32_t row, uint32_t h,
+                                                   uint32_t i, uint32_t thr16, uint32_t tie_byte, uint32_t k0, uint32_t k1) {
+  const uint32_t c2 = (layer << 16) | row;
+  const Philox4 a = philox4x32_10(c0w, pass, c2, h | (i << 1), k0, k1);
+  const Philox4 b = philox4x32_10(c0w, pass, c2, h | (i << 1) | 8u, k0, k1);
+  const uint32_t P[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+  const uint32_t thi = thr16 >> 8;
+  uint32_t g = tie_byte >= (thr16 & 0xFFu) ? 0xFFFFFFFFu : 0u;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) g = ((thi >> k) & 1u) ? (P[k] & g) : (P[k] | g);
+  return g;
+}
+__device__ __forceinline__ Philox4 drop_half_words(uint32_t c0w, uint32_t pass, uint32_t layer, uint32_t row, uint32_t h,
+                                                   uint32_t k0, uint32_t k1) {
+  return philox4x32_10(c0w, pass, (layer << 16) | row, h, k0, k1);
 }
 
 // ---- per-window reductions, exact evaluation order of the reference's NumPy code ----------------------------

@@ -213,19 +213,17 @@ struct FusedArgs {
   // linear in them, so the probabilities follow without another pass over the network (exact_head_kernel)
   float* head_sum;                // (n_groups, n, 2, 96) float32, or null
   unsigned char* head_cnt;        // (n_groups, n, 2, 96) uint8
-  // activation checkpoints of the exact mode: the bf16 planes of a layer's input, (n_groups, n, Cin/8 planes, 64 rows)
-  // x 16 B, written by the sweep that first has them in final form and read by the later sweeps instead of recomputing
-  // the layers in front (layer index 2: 192 channels = 24 planes; layer index 4: 96 channels = 12 planes)
-  uint4* ckpt_out;                // checkpoint written by this sweep, or null
-  int ckpt_out_layer;             // ... it holds the input of this layer index (2 or 4)
-  const uint4* ckpt_in;           // checkpoint this sweep resumes from, or null
-  int first_layer;                // ... it holds the input of this layer index (2 or 4); 0 = start from the windows
+  // per-layer activation hand-off of the exact mode: a sweep computes ONE layer (two for the sweep that starts at the
+  // windows) and leaves its post-ReLU output, rounded to bf16 and NOT yet normalised, in HBM as planes
+  // (n_groups, n, Cout/8 planes, 60 rows) x 16 B; the next sweep applies this layer's BatchNorm affine (now known for
+  // all windows) + dropout while it stages the planes into shared memory
+  uint4* ckpt_out;                // post-ReLU output of layer n_layers-1, or null
+  const uint4* ckpt_in;           // post-ReLU output of layer first_layer-1 (first_layer >= 2), or null
+  int first_layer;                // first layer this sweep computes; 0 = start from the windows
 };
 
 // dropout source of the epilogue
 constexpr int kDropNone = 0, kDropPhilox = 1, kDropBits = 2;
-// exact-mode checkpoints: planes (8-channel chunks) of the input of layer index l
-__host__ __device__ constexpr int ckpt_planes(int l) { return l == 2 ? 24 : 12; }
 
 template <int TILES, int NSLOTS>
 struct FusedCfg {
@@ -322,19 +320,6 @@ __device__ __forceinline__ uint32_t prmt_sign_bytes(uint32_t z) {
   return r;
 }
 
-// Keep-flags of 8 consecutive channels (one Philox4x32-10 call): element e is kept iff its 15-bit field >= thr15.
-// The compare runs on both 16-bit halves of a word at once -- ((w & 0x7FFF7FFF) | 0x80008000) - thr15*0x00010001 leaves
-// the flag in bits 15 / 31 -- and a PRMT gathers the four flag bytes of two words: g0 carries elements 0..3 and g1
-// elements 4..7 in the SIGN BITS of their four bytes.
-__device__ __forceinline__ void philox_keep8(uint32_t c0w, uint32_t pass, uint32_t c2, uint32_t chunk8, uint32_t k0,
-                                             uint32_t k1, uint32_t thr2, uint32_t& g0, uint32_t& g1) {
-  const Philox4 r = philox4x32_10(c0w, pass, c2, chunk8, k0, k1);
-  const uint32_t d0 = ((r.x & 0x7FFF7FFFu) | 0x80008000u) - thr2, d1 = ((r.y & 0x7FFF7FFFu) | 0x80008000u) - thr2;
-  const uint32_t d2 = ((r.z & 0x7FFF7FFFu) | 0x80008000u) - thr2, d3 = ((r.w & 0x7FFF7FFFu) | 0x80008000u) - thr2;
-  asm("prmt.b32 %0, %1, %2, 0x7531;" : "=r"(g0) : "r"(d0), "r"(d1));   // bytes: d0[15:8], d0[31:24], d1[15:8], d1[31:24]
-  asm("prmt.b32 %0, %1, %2, 0x7531;" : "=r"(g1) : "r"(d2), "r"(d3));
-}
-
 // Keep-flag store of one thread and layer: the flags of 4 consecutive channels ("quad" t = channel_in_thread / 4) sit
 // in bit (t & 7) of the four bytes of word t >> 3 -- 32 flags per register, Cout/2 flags = at most 4 registers.
 // Insert = shift the byte-sign form into place (SHF + LOP3); extract = shift back to the byte signs (SHF), which is
@@ -356,12 +341,12 @@ __device__ __forceinline__ uint32_t keep_extract(const uint32_t (&kb)[4], int t)
 // done on both halves of a word at once -- ((w & 0x7FFF7FFF) | 0x80008000) - thr15*0x00010001 leaves the keep flag in
 // bits 15 / 31, PRMT with sign replication turns it into a 0xFFFF / 0 mask per bf16 half, and one LOP3 applies the
 // mask (and the zero-row mask) to the packed pair: 4 ALU instructions per 2 elements, no predicates.
-template <int DROP, bool LAST, bool DBG, bool CKPT = false>
+template <int DROP, bool LAST, bool DBG>
 __device__ __forceinline__ void epi_chunk16(const uint32_t (&v)[16], int c0, const float* __restrict__ tab_s,
                                             const float* __restrict__ tab_h, const float* __restrict__ tab_w,
                                             uint32_t act_row, bool row_valid, uint32_t row_mask, uint32_t thr2,
                                             uint32_t c0w, uint32_t pass, uint32_t c2, uint32_t k0, uint32_t k1,
-                                            const uint32_t (&zq)[4], float& zacc, float* dbg, uint4* ckpt = nullptr) {
+                                            const uint32_t (&zq)[4], float& zacc, float* dbg) {
 #pragma unroll
   for (int q = 0; q < 2; ++q) {
     const int cb = c0 + 8 * q;
@@ -397,10 +382,6 @@ __device__ __forceinline__ void epi_chunk16(const uint32_t (&v)[16], int c0, con
       const uint32_t p0 = pack_bf16x2(y[0], y[1]) & m[0], p1 = pack_bf16x2(y[2], y[3]) & m[1];
       const uint32_t p2 = pack_bf16x2(y[4], y[5]) & m[2], p3 = pack_bf16x2(y[6], y[7]) & m[3];
       st_shared_v4(act_row + (uint32_t)(cb >> 3) * kPlaneBytes, p0, p1, p2, p3);
-      if (CKPT) {
-        // exact-mode checkpoint: the same 8 channels of this row also go to HBM ([plane][row] x 16 B per window-pass)
-        if (ckpt) ckpt[(cb >> 3) * 64] = make_uint4(p0, p1, p2, p3);
-      }
     } else {
       const float4 w0 = *reinterpret_cast<const float4*>(tab_w + cb), w1 = *reinterpret_cast<const float4*>(tab_w + cb + 4);
       zacc = fmaf(y[0], w0.x, zacc); zacc = fmaf(y[1], w0.y, zacc); zacc = fmaf(y[2], w0.z, zacc); zacc = fmaf(y[3], w0.w, zacc);
@@ -413,6 +394,7 @@ __host__ __device__ constexpr int fl_step_base(int l) { return l == 0 ? 0 : fl_s
 constexpr int kTotalSteps = fl_step_base(kBlocks);   // 382 convolution steps + 6 bias steps
 constexpr int kStagesPerGroup = fused_layer(0).nstages + fused_layer(1).nstages + fused_layer(2).nstages +
                                 fused_layer(3).nstages + fused_layer(4).nstages + fused_layer(5).nstages;
+static __constant__ int c_ch_off[kBlocks] = {ch_off(0), ch_off(1), ch_off(2), ch_off(3), ch_off(4), ch_off(5)};
 static __constant__ int c_step_base[kBlocks + 1] = {fl_step_base(0), fl_step_base(1), fl_step_base(2), fl_step_base(3),
                                              fl_step_base(4), fl_step_base(5), fl_step_base(6)};
 
@@ -468,6 +450,7 @@ __device__ __forceinline__ void issue_layer(uint32_t s_base, uint32_t tmem_base,
 // ---- epilogue of one layer (8 warps per tile) -----------------------------------------------------------------------
 struct EpiCtx {
   uint32_t act_row, taddr, c0w, k0, k1, bar_acc, bar_act;
+  DropTie tie = {0u, 0u};    // dropout tie-break bytes of this thread's (window, pass, row, column half), see common.cuh
   uint32_t remote_act = 0;   // pair kernels, peer CTA: cluster address of the leader's "peer activations ready" barrier
   int t, colhalf, tid_t, we, lane, quarter, slot_w, tl;
   bool row_valid;
@@ -492,6 +475,12 @@ __device__ __forceinline__ void epi_signal_act(const EpiCtx& c) {
   }
 }
 
+// Start of pass g for this thread's (window, row, column half): the dropout tie-break bytes of the pass (one Philox call).
+template <int DROP>
+__device__ __forceinline__ void epi_pass_setup(EpiCtx& c, const FusedArgs& a, int g) {
+  if (DROP == kDropPhilox) c.tie = drop_tie(c.c0w, (uint32_t)(a.pass_base + g), (uint32_t)c.t, (uint32_t)c.colhalf, c.k0, c.k1);
+}
+
 // Keep-flags of this thread's row for layer L (byte-lane layout of keep_insert), all zero for padding rows.
 //  - kDropPhilox: the dropout masks do not depend on the data, so they are generated while the layer's MMAs run and
 //    the epilogue warps would otherwise sleep on the accumulator barrier (10 Philox rounds per 8 channels leave the
@@ -513,19 +502,19 @@ __device__ __forceinline__ void make_keep_flags(const EpiCtx& c, const FusedArgs
     }
   }
   if (DROP == kDropPhilox) {
-    constexpr uint32_t thr2 = drop_thr15(L) * 0x00010001u;
-    const uint32_t c2 = ((uint32_t)L << 16) | (uint32_t)c.t;
+    // bit-sliced flags (common.cuh): the byte-lane layout of keep_insert IS the layout the generator produces, so a
+    // flag word is used as generated -- two Philox calls and four LOP3 per 32 elements, one call per 128 at rate 0.5
+    constexpr int nw = drop_flag_words(fl_cout(L));
     const uint32_t pass = (uint32_t)(a.pass_base + g);
+    if constexpr (drop_is_half(L)) {
+      const Philox4 r = drop_half_words(c.c0w, pass, (uint32_t)L, (uint32_t)c.t, (uint32_t)c.colhalf, c.k0, c.k1);
+      kb[0] = r.x; kb[1] = r.y;
+      if (nw > 2) { kb[2] = r.z; kb[3] = r.w; }
+    } else {
+      const uint32_t tb = drop_tie_byte(c.tie, L);
 #pragma unroll
-    for (int j = 0; j < my; ++j) {
-      const uint32_t ch8 = (uint32_t)(2 * (c.colhalf + 2 * j));
-#pragma unroll
-      for (int u = 0; u < 2; ++u) {
-        uint32_t g0, g1;
-        philox_keep8(c.c0w, pass, c2, ch8 + (uint32_t)u, c.k0, c.k1, thr2, g0, g1);
-        keep_insert(kb, 4 * j + 2 * u, g0);
-        keep_insert(kb, 4 * j + 2 * u + 1, g1);
-      }
+      for (int i = 0; i < nw; ++i)
+        kb[i] = drop_keep_word(c.c0w, pass, (uint32_t)L, (uint32_t)c.t, (uint32_t)c.colhalf, (uint32_t)i, drop_thr16(L), tb, c.k0, c.k1);
     }
   }
   if (DROP != kDropNone) {
@@ -534,10 +523,9 @@ __device__ __forceinline__ void make_keep_flags(const EpiCtx& c, const FusedArgs
   }
 }
 
-template <int L, int DROP, bool DBG, int EPI_THREADS, bool CKPT = false>
+template <int L, int DROP, bool DBG, int EPI_THREADS>
 __device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, const float* __restrict__ tab_g, int g,
-                                          long long win, uint32_t& n_acc, float* probs_s, float* dbg_base,
-                                          uint4* ckpt_row = nullptr) {
+                                          long long win, uint32_t& n_acc, float* probs_s, float* dbg_base) {
   constexpr int cout = fl_cout(L);
   constexpr int my = cout / 32;            // 16-column chunks owned by this warp (chunks colhalf, colhalf+2, ...)
   constexpr bool kLastLayer = (L == kBlocks - 1);
@@ -553,7 +541,7 @@ __device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, c
   // keep-flags of this thread's row for this layer (see keep_insert): produced while the layer's MMAs run
   uint32_t kb[4];
   make_keep_flags<L, DROP>(c, a, g, win, kb);
-  constexpr uint32_t thr2 = drop_thr15(L) * 0x00010001u;
+  constexpr uint32_t thr2 = 0u;
   const uint32_t c2 = ((uint32_t)L << 16) | (uint32_t)c.t;
   const uint32_t row_mask = c.row_valid ? 0xFFFFFFFFu : 0u;   // zero rows = the next layer's `same` padding
 
@@ -581,15 +569,15 @@ __device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, c
     if (j + 1 < my) tmem_ld16(c.taddr + (uint32_t)(16 * (c.colhalf + 2 * (j + 1))), vb);
     {
       const uint32_t zq[4] = {keep_extract(kb, 4 * j), keep_extract(kb, 4 * j + 1), keep_extract(kb, 4 * j + 2), keep_extract(kb, 4 * j + 3)};
-      epi_chunk16<DROP, kLastLayer, DBG, CKPT>(va, 16 * (c.colhalf + 2 * j), tab_s, tab_h, c.tab_w, c.act_row, c.row_valid, row_mask,
-                                               thr2, c.c0w, (uint32_t)g, c2, c.k0, c.k1, zq, zacc, dbg, ckpt_row);
+      epi_chunk16<DROP, kLastLayer, DBG>(va, 16 * (c.colhalf + 2 * j), tab_s, tab_h, c.tab_w, c.act_row, c.row_valid, row_mask,
+                                               thr2, c.c0w, (uint32_t)g, c2, c.k0, c.k1, zq, zacc, dbg);
     }
     if (j + 1 < my) {
       tmem_wait16(vb);
       if (j + 2 < my) tmem_ld16(c.taddr + (uint32_t)(16 * (c.colhalf + 2 * (j + 2))), va);
       const uint32_t zq[4] = {keep_extract(kb, 4 * j + 4), keep_extract(kb, 4 * j + 5), keep_extract(kb, 4 * j + 6), keep_extract(kb, 4 * j + 7)};
-      epi_chunk16<DROP, kLastLayer, DBG, CKPT>(vb, 16 * (c.colhalf + 2 * (j + 1)), tab_s, tab_h, c.tab_w, c.act_row, c.row_valid,
-                                               row_mask, thr2, c.c0w, (uint32_t)g, c2, c.k0, c.k1, zq, zacc, dbg, ckpt_row);
+      epi_chunk16<DROP, kLastLayer, DBG>(vb, 16 * (c.colhalf + 2 * (j + 1)), tab_s, tab_h, c.tab_w, c.act_row, c.row_valid,
+                                               row_mask, thr2, c.c0w, (uint32_t)g, c2, c.k0, c.k1, zq, zacc, dbg);
     }
   }
 
@@ -644,16 +632,21 @@ __device__ __forceinline__ float warp_halve16(const float (&v)[16], int lane) {
 }
 
 
-// Layer L is the last layer of a statistics sweep: ReLU of the accumulator (bias already added by the MMA), then the
+// Layer L is the (last) layer of a statistics sweep: ReLU of the accumulator (bias already added by the MMA), then the
 // per-channel sum / sum of squares over the valid rows.  One warp's partial covers 32 rows of one window; it is
 // converted to fixed point BEFORE it meets any other partial, so the totals are sums of integers that depend only on
 // (window, row half, channel) -- independent of the grid, of scheduling and of how windows are sharded over GPUs.
-template <int L, int DROP, int EPI_THREADS>
+// Layers 2..5 (L = 1..4) also leave their post-ReLU output in HBM, rounded to bf16 (a.ckpt_out, see FusedArgs); their
+// statistics are those of the ROUNDED values, i.e. of exactly the numbers the next sweep normalises.
+// `after_acc()` runs once every MMA of the layer has retired: the activation planes are free again, the next unit's
+// input can be fetched into them while this epilogue works out of TMEM.
+template <int L, int DROP, int EPI_THREADS, typename AfterAcc>
 __device__ __forceinline__ void epi_stats(const EpiCtx& c, const FusedArgs& a, int g, long long win, uint32_t& n_acc,
-                                          unsigned long long* s_stats) {
+                                          unsigned long long* s_stats, AfterAcc&& after_acc) {
   constexpr int cout = fl_cout(L);
   constexpr int my = cout / 32;
   constexpr bool kHead = (L == kBlocks - 1);
+  constexpr bool kStore = (L >= 1 && L <= kBlocks - 2);
   const bool head = kHead && a.head_sum != nullptr;
   uint32_t kb[4] = {0u, 0u, 0u, 0u};
   if (kHead) {
@@ -667,9 +660,14 @@ __device__ __forceinline__ void epi_stats(const EpiCtx& c, const FusedArgs& a, i
   ++n_acc;
   named_bar_sync(1 + c.tl, EPI_THREADS);
   tc_fence_after();
+  after_acc();
   uint32_t va[16];
   // (pass, window, row half) block of the head partials; this warp covers rows [32*(quarter&1), +32) of its window
   const size_t head_row = (((size_t)g * a.n + (win < a.n ? win : 0)) * 2 + (size_t)(c.quarter & 1)) * kDenseIn;
+  uint4* out_row = nullptr;
+  if (kStore) {
+    if (a.ckpt_out && c.row_valid) out_row = a.ckpt_out + (((size_t)g * a.n + win) * (cout / 8)) * kL + c.t;
+  }
 #pragma unroll
   for (int j = 0; j < my; ++j) {
     const int col0 = 16 * (c.colhalf + 2 * j);
@@ -677,11 +675,22 @@ __device__ __forceinline__ void epi_stats(const EpiCtx& c, const FusedArgs& a, i
     tmem_wait16(va);
     float sv[16], qv[16];
 #pragma unroll
-    for (int e = 0; e < 16; ++e) {
-      const float r = c.row_valid ? fmaxf(__uint_as_float(va[e]), 0.f) : 0.f;
-      sv[e] = r;
-      qv[e] = r * r;
+    for (int e = 0; e < 16; ++e) sv[e] = c.row_valid ? fmaxf(__uint_as_float(va[e]), 0.f) : 0.f;
+    if (kStore) {
+      uint32_t pk[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        pk[i] = pack_bf16x2(sv[2 * i], sv[2 * i + 1]);
+        sv[2 * i] = __uint_as_float(pk[i] << 16);
+        sv[2 * i + 1] = __uint_as_float(pk[i] & 0xFFFF0000u);
+      }
+      if (out_row) {
+        __stcs(out_row + (size_t)(col0 >> 3) * kL, make_uint4(pk[0], pk[1], pk[2], pk[3]));
+        __stcs(out_row + (size_t)((col0 >> 3) + 1) * kL, make_uint4(pk[4], pk[5], pk[6], pk[7]));
+      }
     }
+#pragma unroll
+    for (int e = 0; e < 16; ++e) qv[e] = sv[e] * sv[e];
     const float rs = warp_halve16(sv, c.lane);
     const float rq = warp_halve16(qv, c.lane);
     const int ch = col0 + ((c.lane >> 1) & 15);
@@ -710,30 +719,33 @@ __device__ __forceinline__ void epi_stats(const EpiCtx& c, const FusedArgs& a, i
   tc_fence_before();   // TMEM reads are complete before this thread lets the next unit's MMAs start
 }
 
-// Epilogue chain of a statistics sweep: normal epilogues for layers < n_layers-1, statistics for layer n_layers-1.
-template <int L, int DROP, int EPI_THREADS>
-__device__ __forceinline__ void epi_sweep(const EpiCtx& c, const FusedArgs& a, const float* __restrict__ tab_g, int g,
-                                          long long win, uint32_t& n_acc, unsigned long long* s_stats) {
-  if (L < a.first_layer) {                    // resumed sweep: the earlier layers came from the checkpoint
-    if constexpr (L + 1 < kBlocks) epi_sweep<L + 1, DROP, EPI_THREADS>(c, a, tab_g, g, win, n_acc, s_stats);
-    return;
-  }
-  if (a.n_layers == L + 1) {
-    epi_stats<L, DROP, EPI_THREADS>(c, a, g, win, n_acc, s_stats);
-    return;
-  }
-  if constexpr (L + 1 < kBlocks) {
-    bool done = false;
-    if constexpr (L == 1 || L == 3) {
-      if (a.ckpt_out_layer == L + 1) {
-        // the output of this layer is a checkpointed activation: copy it to HBM on the way (rows 0..63 of the window)
-        uint4* row = win < a.n ? a.ckpt_out + (((size_t)g * a.n + win) * ckpt_planes(L + 1)) * 64 + c.t : nullptr;
-        epi_layer<L, DROP, false, EPI_THREADS, true>(c, a, tab_g, g, win, n_acc, nullptr, nullptr, row);
-        done = true;
-      }
-    }
-    if (!done) epi_layer<L, DROP, false, EPI_THREADS>(c, a, tab_g, g, win, n_acc, nullptr, nullptr);
-    epi_sweep<L + 1, DROP, EPI_THREADS>(c, a, tab_g, g, win, n_acc, s_stats);
+__device__ __forceinline__ void ld_shared_v4(uint32_t addr, uint32_t& a, uint32_t& b, uint32_t& c, uint32_t& d) {
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "r"(addr) : "memory");
+}
+
+// Load stage of a resumed statistics sweep: the raw (post-ReLU, bf16) output of layer L0 has landed in this tile's
+// activation planes (bulk copies); every thread turns ITS row of ITS 16-column chunks into layer L0+1's input in place:
+// BatchNorm affine of pass g (dropout scale folded) -> dropout -> bf16, exactly the arithmetic of the fused epilogue.
+template <int L0, int DROP>
+__device__ __forceinline__ void load_stage(const EpiCtx& c, const FusedArgs& a, int g, long long win, const float* tab_s,
+                                           const float* tab_h) {
+  constexpr int my = fl_cout(L0) / 32;
+  uint32_t kb[4];
+  make_keep_flags<L0, DROP>(c, a, g, win, kb);
+  const uint32_t row_mask = c.row_valid ? 0xFFFFFFFFu : 0u;
+  float zdummy = 0.f;
+#pragma unroll
+  for (int j = 0; j < my; ++j) {
+    const int c0 = 16 * (c.colhalf + 2 * j);
+    uint32_t u[8];
+    ld_shared_v4(c.act_row + (uint32_t)(c0 >> 3) * kPlaneBytes, u[0], u[1], u[2], u[3]);
+    ld_shared_v4(c.act_row + (uint32_t)((c0 >> 3) + 1) * kPlaneBytes, u[4], u[5], u[6], u[7]);
+    uint32_t v[16];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { v[2 * i] = u[i] << 16; v[2 * i + 1] = u[i] & 0xFFFF0000u; }
+    const uint32_t zq[4] = {keep_extract(kb, 4 * j), keep_extract(kb, 4 * j + 1), keep_extract(kb, 4 * j + 2), keep_extract(kb, 4 * j + 3)};
+    epi_chunk16<DROP, false, false>(v, c0, tab_s, tab_h, nullptr, c.act_row, c.row_valid, row_mask, 0u, c.c0w, (uint32_t)g, 0u,
+                                    c.k0, c.k1, zq, zdummy, nullptr);
   }
 }
 
@@ -890,6 +902,7 @@ fused_forward_kernel(const FusedArgs a) {
       }
 
       for (int g = 0; g < a.n_groups; ++g) {
+        epi_pass_setup<DROP>(c, a, g);
         // ---- layer-1 input: channels 0..3 real, 4..7 zero, in plane 0
         if (c.colhalf == 0) st_shared_v4(c.act_row, xin0, xin1, 0u, 0u);
         fence_proxy_async();
@@ -942,7 +955,7 @@ struct PairCfg {
   static constexpr int kTabFloats = 2 * 512 + 128;
   static constexpr int oTab = oRing + NSLOTS * kSlot;
   static constexpr int oBar = oTab + kTabFloats * 4;
-  static constexpr int kNumBars = 3 * NSLOTS + 3;  // full, empty, peer_full [NSLOTS]; acc, act, peer_act
+  static constexpr int kNumBars = 3 * NSLOTS + 4;  // full, empty, peer_full [NSLOTS]; acc, act, peer_act, in (exact-mode input planes)
   static constexpr int oMisc = oBar + 8 * kNumBars;
   static constexpr int oAlo = oMisc + 16 + 32;
   static constexpr int oProbs = oAlo + 4 * 392;    // probs[2][n_groups]
@@ -1051,6 +1064,7 @@ fused_pair_kernel(const FusedArgs a) {
   const uint32_t bar_acc = bar_peer_full + 8 * NSLOTS;
   const uint32_t bar_act = bar_acc + 8;
   const uint32_t bar_peer_act = bar_act + 8;                    // used in the leader only
+  const uint32_t bar_in = bar_peer_act + 8;                     // statistics sweeps: this tile's input planes have landed
   volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(smem + Cfg::oMisc);
   float* zpart = reinterpret_cast<float*>(smem + Cfg::oMisc + 16);
   uint32_t* s_alo = reinterpret_cast<uint32_t*>(smem + Cfg::oAlo);
@@ -1078,7 +1092,7 @@ fused_pair_kernel(const FusedArgs a) {
     for (int i = 0; i < NSLOTS; ++i) {
       mbar_init(bar_full + 8 * i, 1 + extra); mbar_init(bar_empty + 8 * i, 1); mbar_init(bar_peer_full + 8 * i, 1);
     }
-    mbar_init(bar_acc, 1); mbar_init(bar_act, Cfg::kEpiThreads / 32 + extra); mbar_init(bar_peer_act, 1);
+    mbar_init(bar_acc, 1); mbar_init(bar_act, Cfg::kEpiThreads / 32 + extra); mbar_init(bar_peer_act, 1); mbar_init(bar_in, 1);
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -1206,27 +1220,76 @@ fused_pair_kernel(const FusedArgs a) {
       unsigned long long* s_stats = reinterpret_cast<unsigned long long*>(smem + Cfg::oProbs);   // [2 * 256], no probs here
       for (int i = c.tid_t; i < 2 * kMaxCh; i += Cfg::kEpiThreads) s_stats[i] = 0ull;
       named_bar_sync(1, Cfg::kEpiThreads);
+      // Resumed sweep (first_layer >= 2): the input of a unit is the raw post-ReLU output of layer L0 = first_layer - 1,
+      // fetched by bulk copies straight into the activation planes ([plane][60 rows] x 16 B per window in HBM, the same
+      // order as a plane in shared memory) and normalised in place by load_stage.  The copies of iteration q + 1 are
+      // issued as soon as the MMAs of iteration q have retired, so they overlap this tile's epilogue.
+      const int L0 = a.first_layer - 1;
+      const int planes_in = L0 >= 1 ? c_layers[L0].cout / 8 : 0;
+      const long long my_units = pair_id < a.n_units ? (a.n_units - pair_id + n_pairs - 1) / n_pairs : 0;
+      const long long total_it = my_units * a.n_groups;
+      auto issue_in = [&](long long q) {            // whole warp we == 0
+        if (planes_in == 0 || q >= total_it) return;
+        const long long gq = q / my_units, uq = pair_id + (q % my_units) * n_pairs;
+        const long long w0 = uq * Cfg::kWpu + 2 * (long long)rank;
+        const int valid = (w0 < a.n ? 1 : 0) + (w0 + 1 < a.n ? 1 : 0);
+        if (lane == 0) mbar_arrive_expect_tx(bar_in, (uint32_t)(valid * planes_in * kL * 16));
+        __syncwarp();
+        for (int idx = lane; idx < 2 * planes_in; idx += 32) {
+          const int slot = idx >= planes_in ? 1 : 0, pl = idx - slot * planes_in;
+          if (w0 + slot < a.n)
+            bulk_g2s(s_base + Cfg::oAct + (uint32_t)pl * kPlaneBytes + (uint32_t)(4 + 64 * slot) * 16u,
+                     a.ckpt_in + (((size_t)gq * a.n + (size_t)(w0 + slot)) * planes_in + pl) * kL, (uint32_t)(kL * 16), bar_in);
+        }
+      };
+      if (c.we == 0) issue_in(0);
+      uint32_t n_in = 0;
+      long long q = 0;
+      float* tab_s = c.tab + (L0 & 1) * 512;
+      float* tab_h = tab_s + 256;
       for (int g = 0; g < a.n_groups; ++g) {
         const float* tab_g = a.tables + (size_t)g * kTableFloats;
-        for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
+        if (planes_in > 0) {
+          // BatchNorm affine of layer L0 for pass g (dropout scale folded), used by the load stage of every unit
+          for (int i = c.tid_t; i < 8 * planes_in; i += Cfg::kEpiThreads) {
+            tab_s[i] = __ldg(tab_g + kChTotal + c_ch_off[L0] + i);
+            tab_h[i] = __ldg(tab_g + 2 * kChTotal + c_ch_off[L0] + i);
+          }
+          named_bar_sync(1, Cfg::kEpiThreads);
+        }
+        for (long long unit = pair_id; unit < a.n_units; unit += n_pairs, ++q) {
           long long win; uint32_t xin0, xin1;
           unit_prologue(unit, win, xin0, xin1);
+          epi_pass_setup<DROP>(c, a, g);
           if (a.first_layer == 0) {
             if (c.colhalf == 0) st_shared_v4(c.act_row, xin0, xin1, 0u, 0u);
           } else {
-            // resume from a checkpoint: this row's planes of the first layer's input, half of them per column-half thread
-            const int planes = ckpt_planes(a.first_layer);
-            const uint4* src = a.ckpt_in + (((size_t)g * a.n + (win < a.n ? win : 0)) * planes) * 64 + c.t;
-#pragma unroll 4
-            for (int q = 0; q < planes / 2; ++q) {
-              const int pl = c.colhalf * (planes / 2) + q;
-              const uint4 v = win < a.n ? __ldcs(src + (size_t)pl * 64) : make_uint4(0u, 0u, 0u, 0u);
-              st_shared_v4(c.act_row + (uint32_t)pl * kPlaneBytes, v.x, v.y, v.z, v.w);
+            mbar_wait2(bar_in, n_in & 1, a.err_flag, 5);
+            ++n_in;
+            switch (L0) {
+              case 1: load_stage<1, DROP>(c, a, g, win, tab_s, tab_h); break;
+              case 2: load_stage<2, DROP>(c, a, g, win, tab_s, tab_h); break;
+              case 3: load_stage<3, DROP>(c, a, g, win, tab_s, tab_h); break;
+              default: load_stage<4, DROP>(c, a, g, win, tab_s, tab_h); break;
             }
           }
           fence_proxy_async();
           epi_signal_act<Cfg::kEpiThreads>(c);
-          epi_sweep<0, DROP, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, s_stats);
+          auto after_acc = [&]() { if (c.we == 0) issue_in(q + 1); };
+          switch (a.first_layer) {
+            case 0:
+              if (a.n_layers == 1) {
+                epi_stats<0, DROP, Cfg::kEpiThreads>(c, a, g, win, n_acc, s_stats, after_acc);
+              } else {
+                epi_layer<0, DROP, false, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, nullptr, nullptr);
+                epi_stats<1, DROP, Cfg::kEpiThreads>(c, a, g, win, n_acc, s_stats, after_acc);
+              }
+              break;
+            case 2: epi_stats<2, DROP, Cfg::kEpiThreads>(c, a, g, win, n_acc, s_stats, after_acc); break;
+            case 3: epi_stats<3, DROP, Cfg::kEpiThreads>(c, a, g, win, n_acc, s_stats, after_acc); break;
+            case 4: epi_stats<4, DROP, Cfg::kEpiThreads>(c, a, g, win, n_acc, s_stats, after_acc); break;
+            default: epi_stats<5, DROP, Cfg::kEpiThreads>(c, a, g, win, n_acc, s_stats, after_acc); break;
+          }
         }
         // this pass is complete in this CTA: add its fixed-point sums to the global accumulators of pass g
         named_bar_sync(1, Cfg::kEpiThreads);
@@ -1245,6 +1308,7 @@ fused_pair_kernel(const FusedArgs a) {
         if (a.dbg_act && blockIdx.x == 0 && unit == pair_id) dbg_base = a.dbg_act + (size_t)row * 256;
       }
       for (int g = 0; g < a.n_groups; ++g) {
+        epi_pass_setup<DROP>(c, a, g);
         if (c.colhalf == 0) st_shared_v4(c.act_row, xin0, xin1, 0u, 0u);
         fence_proxy_async();
         epi_signal_act<Cfg::kEpiThreads>(c);
@@ -1289,10 +1353,15 @@ static int launch_pair_variant(const FusedParams& p, cudaStream_t s) {
   a.smem_probs = (p.no_smem_probs || STAT) ? 0 : 1;
   a.n_layers = STAT ? p.n_layers : kBlocks; a.stats = p.stats;
   a.pass_base = p.pass_base; a.head_sum = STAT ? p.head_sum : nullptr; a.head_cnt = STAT ? p.head_cnt : nullptr;
-  a.ckpt_out = STAT ? reinterpret_cast<uint4*>(p.ckpt_out) : nullptr; a.ckpt_out_layer = (STAT && p.ckpt_out) ? p.ckpt_out_layer : 0;
-  a.ckpt_in = STAT ? reinterpret_cast<const uint4*>(p.ckpt_in) : nullptr; a.first_layer = (STAT && p.ckpt_in) ? p.first_layer : 0;
-  if (STAT && (p.n_layers < 1 || p.n_layers > kBlocks || p.stats == nullptr)) {
-    set_error("statistics sweep needs 1 <= n_layers <= 6 and a statistics buffer"); return UQK_E_BADARG;
+  a.ckpt_out = STAT ? reinterpret_cast<uint4*>(p.ckpt_out) : nullptr;
+  a.ckpt_in = STAT ? reinterpret_cast<const uint4*>(p.ckpt_in) : nullptr; a.first_layer = STAT ? p.first_layer : 0;
+  if (STAT) {
+    // a sweep computes one layer: [0,1) or [0,2) from the windows, [k,k+1) for k >= 2 from layer k-1's stored output
+    const bool from_x = p.first_layer == 0 && (p.n_layers == 1 || p.n_layers == 2) && p.ckpt_in == nullptr;
+    const bool resumed = p.first_layer >= 2 && p.first_layer < kBlocks && p.n_layers == p.first_layer + 1 && p.ckpt_in != nullptr;
+    if (!(from_x || resumed) || p.stats == nullptr) {
+      set_error("statistics sweep: unsupported layer range [%d, %d)", p.first_layer, p.n_layers); return UQK_E_BADARG;
+    }
   }
   // the probability buffer of the fused reductions doubles as the statistics accumulator [2 x 256] u64 of a sweep
   const size_t smem = (size_t)Cfg::oProbs + (STAT ? (size_t)2 * kMaxCh * sizeof(unsigned long long)
@@ -1547,6 +1616,7 @@ fused_pair2_kernel(const FusedArgs a) {
         if (a.dbg_act && blockIdx.x == 0 && unit == pair_id && c.tl == 0) dbg_base = a.dbg_act + (size_t)row * 256;
       }
       for (int g = 0; g < a.n_groups; ++g) {
+        epi_pass_setup<DROP>(c, a, g);
         if (c.colhalf == 0) st_shared_v4(c.act_row, xin0, xin1, 0u, 0u);
         fence_proxy_async();
         epi_signal_act<Cfg::kEpiThreads>(c);

@@ -67,14 +67,13 @@ struct FusedParams {
   int pass_base;              // Philox pass counter of group 0
   float* head_sum;            // sixth sweep: (n_groups, n, 2, 96) masked column sums of the layer-6 output, or null
   unsigned char* head_cnt;    // ... and kept-row counts
-  // exact-mode activation checkpoints (bf16 planes of a layer's input, (n_groups, n, Cin/8, 64) x 16 B)
-  void* ckpt_out;             // written by this sweep, or null
-  int ckpt_out_layer;         // ... input of this layer index (2 or 4)
-  const void* ckpt_in;        // this sweep resumes from it, or null
-  int first_layer;            // ... input of this layer index (2 or 4)
+  // exact mode, per-layer hand-off through HBM: post-ReLU output of a layer, bf16, (n_groups, n, Cout/8, 60) x 16 B
+  void* ckpt_out;             // written by this sweep (output of layer n_layers-1), or null
+  const void* ckpt_in;        // output of layer first_layer-1, read by a sweep that starts at first_layer >= 2, or null
+  int first_layer;            // first layer the sweep computes (0 = from the windows)
 };
-constexpr size_t kCkpt4BytesPerWindowPass = 12 * 64 * 16;   // input of layer index 4 (96 channels)
-constexpr size_t kCkpt2BytesPerWindowPass = 24 * 64 * 16;   // input of layer index 2 (192 channels)
+// bytes of a layer's stored output per window-pass
+constexpr size_t exact_layer_bytes(int l) { return (size_t)(block_def(l).cout / 8) * kL * 16; }
 int fused_launch(const FusedParams& p, cudaStream_t s);
 // one kernel family per translation unit (fused_pair2.cu, fused_pair.cu, fused_pair_stat.cu, fused_single2.cu, fused_single1.cu)
 int fused_launch_pair2(const FusedParams& p, cudaStream_t s);

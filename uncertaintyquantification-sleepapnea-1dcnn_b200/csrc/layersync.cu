@@ -130,14 +130,15 @@ __global__ void bn_affine_kernel(const float* __restrict__ mean, const float* __
 }
 
 // ---- BN affine + dropout, in place ----------------------------------------------------------------------------
-// One thread per (window, row, 8-channel chunk) = one Philox4x32-10 call.
+// One thread per (window, row, 8-channel chunk); the keep-flags come from the bit-sliced generator of common.cuh
+// (the thread regenerates the flag word its 8 channels live in).
 __global__ void bn_dropout_kernel(float* __restrict__ act, const float* __restrict__ scale,
                                   const float* __restrict__ shift, int cout, int64_t n, int layer, int dropout,
                                   uint32_t k0, uint32_t k1, uint32_t pass, int64_t window_base,
                                   const uint32_t* __restrict__ mask_bits /* (N,6,60,8) for this pass or null */) {
   const int nq = cout / 8;
   const int64_t total = n * kL * nq;
-  const uint32_t thr = drop_thr15(layer);
+  const uint32_t thr16 = drop_thr16(layer);
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int q = (int)(i % nq);
     const int64_t wr = i / nq;
@@ -152,11 +153,18 @@ __global__ void bn_dropout_kernel(float* __restrict__ act, const float* __restri
         const uint32_t word = __ldg(mask_bits + (((size_t)win * kBlocks + layer) * kL + row) * 8 + (q >> 2));
         keep = (word >> ((q & 3) * 8)) & 0xFFu;
       } else {
-        const Philox4 r = philox4x32_10((uint32_t)(window_base + win), pass, ((uint32_t)layer << 16) | (uint32_t)row,
-                                        (uint32_t)q, k0, k1);
+        const uint32_t c0w = (uint32_t)(window_base + win), h = (uint32_t)(q >> 1) & 1u, wi = (uint32_t)(q >> 3);
+        uint32_t word;
+        if (thr16 == 32768u) {
+          const Philox4 r = drop_half_words(c0w, pass, (uint32_t)layer, (uint32_t)row, h, k0, k1);
+          word = wi == 0 ? r.x : wi == 1 ? r.y : wi == 2 ? r.z : r.w;
+        } else {
+          const DropTie tie = drop_tie(c0w, pass, (uint32_t)row, h, k0, k1);
+          word = drop_keep_word(c0w, pass, (uint32_t)layer, (uint32_t)row, h, wi, thr16, drop_tie_byte(tie, layer), k0, k1);
+        }
         keep = 0;
 #pragma unroll
-        for (int e = 0; e < 8; ++e) keep |= (philox_field15(r, e) >= thr ? 1u : 0u) << e;
+        for (int e = 0; e < 8; ++e) keep |= ((word >> drop_bitpos(q * 8 + e)) & 1u) << e;
       }
     }
 #pragma unroll
