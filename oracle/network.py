@@ -7,8 +7,10 @@ call semantics of uncertainty_quantification/uq_techniques.py:22 (``model(x, tra
 one batch, BatchNormalization uses batch statistics, Dropout is active) and :29 (``model.predict``:
 inference mode).
 
-Two implementations of the same function:
+Implementations of the same function:
   * ``forward_f64``  -- NumPy float64, ground truth for tolerances and the label guard band.
+  * ``forward_f64_torch`` -- the same arithmetic in torch float64 (multi-threaded), for the parity tests at the sizes
+    the bench times (N >= 1024 windows x T = 50 passes); pinned to ``forward_f64`` by tests/test_oracle_network.py.
   * ``forward_f32_torch`` -- torch-CPU float32, the timed CPU baseline (bench.py cpu_baseline leg).
 
 Weights are the 38 arrays of Keras ``get_weights()`` order:
@@ -34,10 +36,10 @@ def _conv1d_same(x: np.ndarray, w: np.ndarray, b: np.ndarray) -> np.ndarray:
     h = (k - 1) // 2
     xp = np.zeros((n, L + k - 1, cin), dtype=x.dtype)
     xp[:, h:h + L, :] = x
-    y = np.zeros((n, L, cout), dtype=x.dtype)
-    for j in range(k):
-        y += xp[:, j:j + L, :] @ w[j]
-    return y + b
+    # one GEMM over the unfolded taps: cols[n, t, j*cin + c] = xp[n, t + j, c]
+    cols = np.lib.stride_tricks.sliding_window_view(xp, k, axis=1)           # (n, L, cin, k)
+    cols = np.ascontiguousarray(cols.transpose(0, 1, 3, 2)).reshape(n * L, k * cin)
+    return (cols @ w.reshape(k * cin, cout)).reshape(n, L, cout) + b
 
 
 def forward_f64(weights: Sequence[np.ndarray], x: np.ndarray, training: bool = False,
@@ -90,6 +92,36 @@ def forward_f64(weights: Sequence[np.ndarray], x: np.ndarray, training: bool = F
     if return_stats:
         return p, stats_out
     return p
+
+
+def forward_f64_torch(weights: Sequence[np.ndarray], x: np.ndarray, training: bool = False,
+                      masks: Optional[List[np.ndarray]] = None, bn_mode: Optional[str] = None,
+                      bn_stats: Optional[List] = None) -> np.ndarray:
+    """``forward_f64`` with torch float64 tensors (same semantics and argument meaning, no exchange model)."""
+    import torch
+    import torch.nn.functional as F
+
+    if bn_mode is None:
+        bn_mode = "batch" if training else "inference"
+    with torch.no_grad():
+        a = torch.from_numpy(np.ascontiguousarray(x, dtype=np.float64)).permute(0, 2, 1)      # (N, C, L)
+        tw = [torch.from_numpy(np.ascontiguousarray(w, dtype=np.float64)) for w in weights]
+        for i, (cin, cout, k, rate) in enumerate(BLOCKS):
+            w, b, g, be, mm, mv = tw[6 * i:6 * i + 6]
+            a = F.relu(F.conv1d(a, w.permute(2, 1, 0).contiguous(), b, padding=(k - 1) // 2))
+            if bn_stats is not None:
+                mu, var = [torch.as_tensor(np.asarray(t, dtype=np.float64)) for t in bn_stats[i]]
+            elif bn_mode == "batch":
+                mu = a.mean(dim=(0, 2))
+                var = a.var(dim=(0, 2), unbiased=False)
+            else:
+                mu, var = mm, mv
+            a = (g / torch.sqrt(var + BN_EPS))[None, :, None] * (a - mu[None, :, None]) + be[None, :, None]
+            if training and masks is not None:
+                m = torch.from_numpy(np.ascontiguousarray(masks[i])).permute(0, 2, 1)
+                a = a * m / (1.0 - rate)
+        z = a.mean(dim=2) @ tw[36] + tw[37]
+        return torch.sigmoid(z).numpy()
 
 
 def forward_f32_torch(weights: Sequence[np.ndarray], x: np.ndarray, training: bool = False,

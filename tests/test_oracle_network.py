@@ -47,6 +47,33 @@ def test_forward_regression_and_f32(uqk, golden_dir):
     assert np.abs(pt32 - pt).max() < 1e-4
 
 
+def test_torch_f64_restatement_equals_numpy_f64(uqk):
+    """forward_f64_torch (used by the T=50 parity tests) is the same function as forward_f64."""
+    X = uqk.synthetic.make_windows(40, seed=13)
+    ws = uqk.synthetic.make_member_weights(1)
+    masks = [philox.dropout_keep_mask(5, np.arange(40), 2, i, b.cout, b.rate) for i, b in enumerate(uqk.arch.BLOCKS)]
+    _, st = network.forward_f64(ws, X, training=True, masks=masks, return_stats=True)
+    for kw in (dict(), dict(training=True, masks=masks), dict(training=True, masks=masks, bn_mode="inference"),
+               dict(training=True, masks=masks, bn_stats=st)):
+        np.testing.assert_allclose(network.forward_f64_torch(ws, X, **kw), network.forward_f64(ws, X, **kw), rtol=0, atol=1e-12)
+
+
+def test_trained_fixture_is_pinned_to_its_golden(uqk, golden_dir):
+    """tests/golden/trained_member0.keras (made by make_trained_fixture.py) loads through the package's reader and the
+    oracle reproduces the committed outputs; its probabilities spread over (0, 1)."""
+    import importlib
+    from conftest import PKG_NAME
+    model = importlib.import_module(PKG_NAME + ".model")
+    ws = model.load_model(os.path.join(golden_dir, "trained_member0.keras")).get_weights()
+    g = np.load(os.path.join(golden_dir, "trained_member0_golden.npz"))
+    X = uqk.synthetic.make_windows(256, seed=4242)
+    det = network.forward_f64(ws, X)[:, 0]
+    np.testing.assert_allclose(det, g["det"], rtol=0, atol=1e-12)
+    masks = [philox.dropout_keep_mask(2025, np.arange(256), 0, i, b.cout, b.rate) for i, b in enumerate(uqk.arch.BLOCKS)]
+    np.testing.assert_allclose(network.forward_f64(ws, X, training=True, masks=masks)[:, 0], g["mcd_pass0_seed2025"], rtol=0, atol=1e-12)
+    assert np.quantile(det, 0.1) < 0.1 and np.quantile(det, 0.9) > 0.8
+
+
 def test_flop_counts(uqk):
     # SURVEY.md section 8(d)
     assert uqk.arch.flops_per_window_pass(False) == 101_806_272

@@ -202,7 +202,7 @@ struct FusedArgs {
   int variant;
   int smem_probs;   // 1: per-window probabilities are kept in shared memory for the fused K3 reductions
   long long n_units;
-  // statistics sweep of the exact batch-statistic mode (pair kernel, STAT instantiation): run layers [0, n_layers) and
+  // statistics sweep of the exact batch-statistic mode (two-tile pair kernel, STAT instantiation): run layers [first_layer, n_layers) and
   // accumulate the per-channel (sum, sum of squares) of layer n_layers-1's post-ReLU output into stats[g][2*256]
   int n_layers;
   int tab_per_group;              // 1: epilogue tables of group g are tables[g] although the weights are member 0's
@@ -341,7 +341,7 @@ __device__ __forceinline__ uint32_t keep_extract(const uint32_t (&kb)[4], int t)
 // done on both halves of a word at once -- ((w & 0x7FFF7FFF) | 0x80008000) - thr15*0x00010001 leaves the keep flag in
 // bits 15 / 31, PRMT with sign replication turns it into a 0xFFFF / 0 mask per bf16 half, and one LOP3 applies the
 // mask (and the zero-row mask) to the packed pair: 4 ALU instructions per 2 elements, no predicates.
-template <int DROP, bool LAST, bool DBG>
+template <int DROP, bool LAST, bool DBG, bool RELU = true>
 __device__ __forceinline__ void epi_chunk16(const uint32_t (&v)[16], int c0, const float* __restrict__ tab_s,
                                             const float* __restrict__ tab_h, const float* __restrict__ tab_w,
                                             uint32_t act_row, bool row_valid, uint32_t row_mask, uint32_t thr2,
@@ -356,7 +356,7 @@ __device__ __forceinline__ void epi_chunk16(const uint32_t (&v)[16], int c0, con
     const float hh[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
     float y[8];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) y[e] = fmaf(fmaxf(__uint_as_float(v[8 * q + e]), 0.f), ss[e], hh[e]);
+    for (int e = 0; e < 8; ++e) y[e] = fmaf(RELU ? fmaxf(__uint_as_float(v[8 * q + e]), 0.f) : __uint_as_float(v[8 * q + e]), ss[e], hh[e]);
     uint32_t m[4] = {row_mask, row_mask, row_mask, row_mask};     // per bf16 pair: 0xFFFF per kept half
     if (DROP != kDropNone) {
       // zq[2q], zq[2q+1]: keep-flags of channels 0..3 / 4..7 of this half in the byte sign bits (zero for padding
@@ -604,33 +604,59 @@ __device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, c
 }
 
 // ---- statistics epilogue (exact batch-statistic mode) -------------------------------------------------------------
-// Sum of 16 per-lane values over the 32 lanes of a warp by recursive halving: after the xor-16/8/4/2 exchanges a lane
-// holds ONE of the 16 columns -- column (lane >> 1) & 15 -- summed over 16 lanes, and the xor-1 step completes it.
-// 16 shuffles instead of 80, and a fixed summation tree (the result does not depend on scheduling).
-__device__ __forceinline__ float warp_halve16(const float (&v)[16], int lane) {
-  float t8[8], t4[4], t2[2];
-  const bool b4 = (lane & 16) != 0, b3 = (lane & 8) != 0, b2 = (lane & 4) != 0, b1 = (lane & 2) != 0;
+// The accumulator is read with the 16x256b TMEM load shape (the MMA C-fragment layout): lane (r = lane >> 2, q = lane & 3)
+// receives rows {r, r+8} of a 16-row block and columns {2q, 2q+1, 8+2q, 9+2q} of a 16-column chunk; two loads (rows
+// 0..15 and 16..31 of the warp's lane quarter) give every thread 4 rows x 4 columns.  A column sum over the warp's 32
+// rows is then 3 in-thread additions and a reduction over the 8 lanes that share q -- 7 shuffles per chunk for the sums
+// AND the sums of squares together (recursive halving), against 32 with one row per lane.
+__device__ __forceinline__ void tmem_ld_16x256b_x2(uint32_t taddr, uint32_t (&v)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.16x256b.x2.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+               : "r"(taddr)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_wait8x2(uint32_t (&a)[8], uint32_t (&b)[8]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(a[0]), "+r"(a[1]), "+r"(a[2]), "+r"(a[3]), "+r"(a[4]), "+r"(a[5]), "+r"(a[6]), "+r"(a[7]),
+                 "+r"(b[0]), "+r"(b[1]), "+r"(b[2]), "+r"(b[3]), "+r"(b[4]), "+r"(b[5]), "+r"(b[6]), "+r"(b[7])
+               :
+               : "memory");
+}
+// Recursive halving over the lane bits 4, 3, 2 (the 8 lanes that share lane & 3): NV values per lane in, NV / 8 out.
+// Lane bit 4 selects the upper / lower half of the values, bit 3 the quarter, bit 2 the eighth; fixed summation tree.
+template <int NV>
+__device__ __forceinline__ void quad_halve(float (&v)[NV], int lane) {
+  static_assert(NV % 8 == 0, "NV must be a multiple of 8");
+  const bool b4 = (lane & 16) != 0, b3 = (lane & 8) != 0, b2 = (lane & 4) != 0;
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const float keep = b4 ? v[8 + i] : v[i], send = b4 ? v[i] : v[8 + i];
-    t8[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+  for (int i = 0; i < NV / 2; ++i) {
+    const float keep = b4 ? v[NV / 2 + i] : v[i], send = b4 ? v[i] : v[NV / 2 + i];
+    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
   }
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const float keep = b3 ? t8[4 + i] : t8[i], send = b3 ? t8[i] : t8[4 + i];
-    t4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+  for (int i = 0; i < NV / 4; ++i) {
+    const float keep = b3 ? v[NV / 4 + i] : v[i], send = b3 ? v[i] : v[NV / 4 + i];
+    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
   }
 #pragma unroll
-  for (int i = 0; i < 2; ++i) {
-    const float keep = b2 ? t4[2 + i] : t4[i], send = b2 ? t4[i] : t4[2 + i];
-    t2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+  for (int i = 0; i < NV / 8; ++i) {
+    const float keep = b2 ? v[NV / 8 + i] : v[i], send = b2 ? v[i] : v[NV / 8 + i];
+    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
   }
-  const float keep = b1 ? t2[1] : t2[0], send = b1 ? t2[0] : t2[1];
-  float r = keep + __shfl_xor_sync(0xffffffffu, send, 2);
-  r += __shfl_xor_sync(0xffffffffu, r, 1);
-  return r;
 }
 
+// Adds a non-negative partial sum to a 2^-24 fixed-point 64-bit accumulator in shared memory with two native 32-bit
+// atomics (the 64-bit shared-memory atomic is a compare-and-swap loop, slow under the 8-way contention of the epilogue
+// warps): the low word's add reports the wrap-around that carries into the high word.  v * 2^24 is exact in float, so
+// the integer is the same one the double-precision conversion of the fp32 kernels produces.
+__device__ __forceinline__ void stat_add(unsigned long long* s_stats, int idx, float v) {
+  const unsigned long long f = __float2ull_rn(v * 16777216.0f);
+  uint32_t* w = reinterpret_cast<uint32_t*>(s_stats + idx);
+  const uint32_t lo = (uint32_t)f, hi = (uint32_t)(f >> 32);
+  const uint32_t old = atomicAdd(w, lo);
+  const uint32_t up = hi + ((uint32_t)(old + lo) < old ? 1u : 0u);
+  if (up) atomicAdd(w + 1, up);
+}
 
 // Layer L is the (last) layer of a statistics sweep: ReLU of the accumulator (bias already added by the MMA), then the
 // per-channel sum / sum of squares over the valid rows.  One warp's partial covers 32 rows of one window; it is
@@ -640,18 +666,21 @@ __device__ __forceinline__ float warp_halve16(const float (&v)[16], int lane) {
 // statistics are those of the ROUNDED values, i.e. of exactly the numbers the next sweep normalises.
 // `after_acc()` runs once every MMA of the layer has retired: the activation planes are free again, the next unit's
 // input can be fetched into them while this epilogue works out of TMEM.
-template <int L, int DROP, int EPI_THREADS, typename AfterAcc>
+// `in_shadow()` runs before the wait for the accumulator, i.e. while the layer's MMAs are in flight.
+template <int L, int DROP, int EPI_THREADS, typename InShadow, typename AfterAcc>
 __device__ __forceinline__ void epi_stats(const EpiCtx& c, const FusedArgs& a, int g, long long win, uint32_t& n_acc,
-                                          unsigned long long* s_stats, AfterAcc&& after_acc) {
+                                          unsigned long long* s_stats, InShadow&& in_shadow, AfterAcc&& after_acc) {
   constexpr int cout = fl_cout(L);
   constexpr int my = cout / 32;
   constexpr bool kHead = (L == kBlocks - 1);
   constexpr bool kStore = (L >= 1 && L <= kBlocks - 2);
+  constexpr int NV = kHead ? 16 : 8;        // values reduced per chunk and thread: 4 columns x {sum, sum of squares [, masked sum, kept count]}
   const bool head = kHead && a.head_sum != nullptr;
   uint32_t kb[4] = {0u, 0u, 0u, 0u};
   if (kHead) {
-    if (head) make_keep_flags<L, DROP>(c, a, g, win, kb);      // layer-6 dropout masks, in the MMA shadow
+    if (head) make_keep_flags<L, DROP>(c, a, g, win, kb);      // layer-6 dropout flags of row c.t (one row per lane), in the MMA shadow
   }
+  in_shadow();
   if (c.we == 0) {
     mbar_wait2(c.bar_acc, n_acc & 1, c.err_flag, 4);
     tc_fence_after();
@@ -661,91 +690,296 @@ __device__ __forceinline__ void epi_stats(const EpiCtx& c, const FusedArgs& a, i
   named_bar_sync(1 + c.tl, EPI_THREADS);
   tc_fence_after();
   after_acc();
-  uint32_t va[16];
-  // (pass, window, row half) block of the head partials; this warp covers rows [32*(quarter&1), +32) of its window
-  const size_t head_row = (((size_t)g * a.n + (win < a.n ? win : 0)) * 2 + (size_t)(c.quarter & 1)) * kDenseIn;
-  uint4* out_row = nullptr;
-  if (kStore) {
-    if (a.ckpt_out && c.row_valid) out_row = a.ckpt_out + (((size_t)g * a.n + win) * (cout / 8)) * kL + c.t;
+  const int q = c.lane & 3, r = c.lane >> 2;
+  const int t0 = (c.quarter & 1) * 32 + r;                       // time steps of this thread's four rows: t0 + 8k
+  const bool win_ok = win < a.n;
+  bool ok[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) ok[k] = win_ok && (t0 + 8 * k < kL);
+  // layer-6 flags of this thread's four rows: row t0 + 8k is lane r + 8k of this warp in the one-row-per-lane mapping
+  uint32_t fw[4][2];
+  if (kHead) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      fw[k][0] = __shfl_sync(0xffffffffu, kb[0], r + 8 * k);
+      fw[k][1] = __shfl_sync(0xffffffffu, kb[1], r + 8 * k);
+    }
   }
+  // (pass, window, row half) block of the head partials; this warp covers rows [32*(quarter&1), +32) of its window
+  const size_t head_row = (((size_t)g * a.n + (win_ok ? win : 0)) * 2 + (size_t)(c.quarter & 1)) * kDenseIn;
+  uint32_t* out32 = nullptr;
+  if (kStore) {
+    if (a.ckpt_out && win_ok)
+      out32 = reinterpret_cast<uint32_t*>(a.ckpt_out + (((size_t)g * a.n + win) * (cout / 8)) * kL + t0) + q;
+  }
+  // software pipeline: the TMEM loads of chunk j + 1 are in flight while chunk j is processed
+  uint32_t lo[8], hi[8], lo2[8], hi2[8];
+  tmem_ld_16x256b_x2(c.taddr + (uint32_t)(16 * c.colhalf), lo);
+  tmem_ld_16x256b_x2(c.taddr + (16u << 16) + (uint32_t)(16 * c.colhalf), hi);
 #pragma unroll
   for (int j = 0; j < my; ++j) {
     const int col0 = 16 * (c.colhalf + 2 * j);
-    tmem_ld16(c.taddr + (uint32_t)col0, va);
-    tmem_wait16(va);
-    float sv[16], qv[16];
+    tmem_wait8x2(lo, hi);
+    if (j + 1 < my) {
+      tmem_ld_16x256b_x2(c.taddr + (uint32_t)(col0 + 32), lo2);
+      tmem_ld_16x256b_x2(c.taddr + (16u << 16) + (uint32_t)(col0 + 32), hi2);
+    }
+    // x[k][cc]: row t0 + 8k, column col0 + {2q, 2q+1, 8+2q, 9+2q}[cc]
+    float x[4][4];
 #pragma unroll
-    for (int e = 0; e < 16; ++e) sv[e] = c.row_valid ? fmaxf(__uint_as_float(va[e]), 0.f) : 0.f;
-    if (kStore) {
-      uint32_t pk[8];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        pk[i] = pack_bf16x2(sv[2 * i], sv[2 * i + 1]);
-        sv[2 * i] = __uint_as_float(pk[i] << 16);
-        sv[2 * i + 1] = __uint_as_float(pk[i] & 0xFFFF0000u);
-      }
-      if (out_row) {
-        __stcs(out_row + (size_t)(col0 >> 3) * kL, make_uint4(pk[0], pk[1], pk[2], pk[3]));
-        __stcs(out_row + (size_t)((col0 >> 3) + 1) * kL, make_uint4(pk[4], pk[5], pk[6], pk[7]));
-      }
+    for (int cc = 0; cc < 4; ++cc) {
+      const int o = (cc & 1) + 4 * (cc >> 1);
+      x[0][cc] = __uint_as_float(lo[o]); x[1][cc] = __uint_as_float(lo[o + 2]);
+      x[2][cc] = __uint_as_float(hi[o]); x[3][cc] = __uint_as_float(hi[o + 2]);
     }
 #pragma unroll
-    for (int e = 0; e < 16; ++e) qv[e] = sv[e] * sv[e];
-    const float rs = warp_halve16(sv, c.lane);
-    const float rq = warp_halve16(qv, c.lane);
-    const int ch = col0 + ((c.lane >> 1) & 15);
-    const float mine = (c.lane & 1) ? rq : rs;      // even lane adds the sum, odd lane the sum of squares
-    atomicAdd(&s_stats[2 * ch + (c.lane & 1)], (unsigned long long)__double2ll_rn((double)mine * kFusedStatScale));
-    if (kHead) {
-      if (head) {
-        // dropout-masked column sums and kept-row counts of this warp's 32 rows (flags are zero on padding rows)
-        float mv[16], fv[16];
+    for (int k = 0; k < 4; ++k)
 #pragma unroll
-        for (int e = 0; e < 16; ++e) {
-          const uint32_t z = keep_extract(kb, 4 * j + (e >> 2));          // quad's flags in the byte sign bits
-          const bool keep = (z >> (8 * (e & 3) + 7)) & 1u;
-          mv[e] = keep ? sv[e] : 0.f;
-          fv[e] = keep ? 1.f : 0.f;
-        }
-        const float ra = warp_halve16(mv, c.lane);
-        const float rb = warp_halve16(fv, c.lane);
-        if (win < a.n) {
-          if (c.lane & 1) a.head_cnt[head_row + ch] = (unsigned char)__float2int_rn(rb);
-          else a.head_sum[head_row + ch] = ra;
+      for (int cc = 0; cc < 4; ++cc) x[k][cc] = ok[k] ? fmaxf(x[k][cc], 0.f) : 0.f;
+    if (kStore) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const uint32_t p0 = pack_bf16x2(x[k][0], x[k][1]), p1 = pack_bf16x2(x[k][2], x[k][3]);
+        x[k][0] = __uint_as_float(p0 << 16); x[k][1] = __uint_as_float(p0 & 0xFFFF0000u);
+        x[k][2] = __uint_as_float(p1 << 16); x[k][3] = __uint_as_float(p1 & 0xFFFF0000u);
+        if (out32 && ok[k]) {
+          // a quad of lanes writes the 16 bytes (8 channels) of one row; 8 rows per store instruction = 128 contiguous bytes
+          __stcs(out32 + ((size_t)(col0 >> 3) * kL + 8 * k) * 4, p0);
+          __stcs(out32 + ((size_t)((col0 >> 3) + 1) * kL + 8 * k) * 4, p1);
         }
       }
+    }
+    float v[NV];
+#pragma unroll
+    for (int cc = 0; cc < 4; ++cc) {
+      v[cc] = (x[0][cc] + x[1][cc]) + (x[2][cc] + x[3][cc]);
+      v[4 + cc] = fmaf(x[0][cc], x[0][cc], x[1][cc] * x[1][cc]) + fmaf(x[2][cc], x[2][cc], x[3][cc] * x[3][cc]);
+    }
+    if (kHead) {
+      // dropout-masked column sums and kept-row counts (flags are zero on padding rows)
+#pragma unroll
+      for (int cc = 0; cc < 4; ++cc) {
+        const int cl = (cc & 1) + 8 * (cc >> 1);                   // column offset inside the chunk, before + 2q
+        float ms = 0.f, cnt = 0.f;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int ch = col0 + cl + 2 * q;
+          const uint32_t w = ((col0 + cl) >> 6) ? fw[k][1] : fw[k][0];
+          const bool keep = ((w >> drop_bitpos(ch)) & 1u) != 0u && ok[k];
+          ms += keep ? x[k][cc] : 0.f;
+          cnt += keep ? 1.f : 0.f;
+        }
+        v[8 + cc] = ms;
+        v[12 + cc] = cnt;
+      }
+    }
+    quad_halve<NV>(v, c.lane);
+    const int b4 = (c.lane >> 4) & 1, b3 = (c.lane >> 3) & 1, b2 = (c.lane >> 2) & 1;
+    if (!kHead) {
+      // NV = 8: lane bit 4 chose sums / sums of squares, bits 3 and 2 the column cc = 2 * b3 + b2
+      const int ch = col0 + b2 + 8 * b3 + 2 * q;
+      stat_add(s_stats, 2 * ch + b4, v[0]);
+    } else {
+      // NV = 16: bit 4 chose plain / dropout-masked, bit 3 chose (sum | sum of squares) resp. (masked sum | kept count),
+      // bit 2 the column pair; v[0], v[1] are the two columns of the pair
+      const int ch = col0 + 8 * b2 + 2 * q;
+      if (!b4) {
+        stat_add(s_stats, 2 * ch + b3, v[0]);
+        stat_add(s_stats, 2 * (ch + 1) + b3, v[1]);
+      } else if (head && win_ok) {
+        if (!b3) {
+          a.head_sum[head_row + ch] = v[0];
+          a.head_sum[head_row + ch + 1] = v[1];
+        } else {
+          a.head_cnt[head_row + ch] = (unsigned char)__float2int_rn(v[0]);
+          a.head_cnt[head_row + ch + 1] = (unsigned char)__float2int_rn(v[1]);
+        }
+      }
+    }
+    if (j + 1 < my) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { lo[i] = lo2[i]; hi[i] = hi2[i]; }
     }
   }
   tc_fence_before();   // TMEM reads are complete before this thread lets the next unit's MMAs start
 }
 
-__device__ __forceinline__ void ld_shared_v4(uint32_t addr, uint32_t& a, uint32_t& b, uint32_t& c, uint32_t& d) {
-  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "r"(addr) : "memory");
-}
-
 // Load stage of a resumed statistics sweep: the raw (post-ReLU, bf16) output of layer L0 has landed in this tile's
 // activation planes (bulk copies); every thread turns ITS row of ITS 16-column chunks into layer L0+1's input in place:
 // BatchNorm affine of pass g (dropout scale folded) -> dropout -> bf16, exactly the arithmetic of the fused epilogue.
+// kb: the row's keep-flags of layer L0 (make_keep_flags), produced earlier in the shadow of the previous unit's MMAs.
+__device__ __forceinline__ void ld_shared_v4_nc(uint32_t addr, uint32_t& a, uint32_t& b, uint32_t& c, uint32_t& d) {
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "r"(addr));
+}
 template <int L0, int DROP>
-__device__ __forceinline__ void load_stage(const EpiCtx& c, const FusedArgs& a, int g, long long win, const float* tab_s,
-                                           const float* tab_h) {
+__device__ __forceinline__ void load_stage(const EpiCtx& c, const uint32_t (&kb)[4], const float* tab_s, const float* tab_h) {
   constexpr int my = fl_cout(L0) / 32;
-  uint32_t kb[4];
-  make_keep_flags<L0, DROP>(c, a, g, win, kb);
   const uint32_t row_mask = c.row_valid ? 0xFFFFFFFFu : 0u;
   float zdummy = 0.f;
+  // a thread reads and rewrites only its own 16 bytes of every plane, so the next chunk's loads may pass this chunk's
+  // stores: they are issued one chunk ahead
+  uint32_t u[8], un[8];
+  ld_shared_v4_nc(c.act_row + (uint32_t)(2 * c.colhalf) * kPlaneBytes, u[0], u[1], u[2], u[3]);
+  ld_shared_v4_nc(c.act_row + (uint32_t)(2 * c.colhalf + 1) * kPlaneBytes, u[4], u[5], u[6], u[7]);
 #pragma unroll
   for (int j = 0; j < my; ++j) {
     const int c0 = 16 * (c.colhalf + 2 * j);
-    uint32_t u[8];
-    ld_shared_v4(c.act_row + (uint32_t)(c0 >> 3) * kPlaneBytes, u[0], u[1], u[2], u[3]);
-    ld_shared_v4(c.act_row + (uint32_t)((c0 >> 3) + 1) * kPlaneBytes, u[4], u[5], u[6], u[7]);
+    if (j + 1 < my) {
+      ld_shared_v4_nc(c.act_row + (uint32_t)((c0 >> 3) + 4) * kPlaneBytes, un[0], un[1], un[2], un[3]);
+      ld_shared_v4_nc(c.act_row + (uint32_t)((c0 >> 3) + 5) * kPlaneBytes, un[4], un[5], un[6], un[7]);
+    }
     uint32_t v[16];
 #pragma unroll
     for (int i = 0; i < 8; ++i) { v[2 * i] = u[i] << 16; v[2 * i + 1] = u[i] & 0xFFFF0000u; }
     const uint32_t zq[4] = {keep_extract(kb, 4 * j), keep_extract(kb, 4 * j + 1), keep_extract(kb, 4 * j + 2), keep_extract(kb, 4 * j + 3)};
-    epi_chunk16<DROP, false, false>(v, c0, tab_s, tab_h, nullptr, c.act_row, c.row_valid, row_mask, 0u, c.c0w, (uint32_t)g, 0u,
-                                    c.k0, c.k1, zq, zdummy, nullptr);
+    epi_chunk16<DROP, false, false, false>(v, c0, tab_s, tab_h, nullptr, c.act_row, c.row_valid, row_mask, 0u, c.c0w, 0u, 0u,
+                                           c.k0, c.k1, zq, zdummy, nullptr);
+    if (j + 1 < my) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) u[i] = un[i];
+    }
+  }
+}
+
+// ---- epilogue loop of a statistics sweep (exact batch-statistic mode), one tile of the two-tile CTA-pair kernel ------
+// The epilogue warps walk the passes in the OUTER loop so that one pass's statistics are accumulated in shared memory
+// and flushed once.  Resumed sweep (first_layer >= 2): the input of a unit is the raw post-ReLU output of layer
+// L0 = first_layer - 1, fetched by bulk copies straight into the tile's activation planes ([plane][60 rows] x 16 B per
+// window in HBM, the same order as a plane in shared memory) and normalised in place by load_stage.  The copies of
+// iteration q + 1 are issued as soon as the MMAs of iteration q have retired, so they overlap the tile's epilogue.
+struct StatGeo {
+  uint32_t act_base;     // shared-memory address of this tile's activation planes
+  uint32_t bar_in;       // mbarrier: this tile's input planes have landed
+  uint32_t rank;         // CTA rank in the pair
+  long long pair_id, n_pairs;
+  int all_threads;       // epilogue threads of BOTH tiles (named barrier 3)
+};
+
+template <int DROP, int EPI_THREADS, int WPU>
+__device__ __forceinline__ void stat_epilogue_loop(EpiCtx& c, const FusedArgs& a, const StatGeo& geo,
+                                                   unsigned long long* s_stats, uint32_t& n_acc) {
+  for (int i = c.tl * EPI_THREADS + c.tid_t; i < 2 * kMaxCh; i += geo.all_threads) s_stats[i] = 0ull;
+  named_bar_sync(3, geo.all_threads);
+  const int L0 = a.first_layer - 1;
+  const int planes_in = L0 >= 1 ? c_layers[L0].cout / 8 : 0;
+  const long long my_units = geo.pair_id < a.n_units ? (a.n_units - geo.pair_id + geo.n_pairs - 1) / geo.n_pairs : 0;
+  const long long total_it = my_units * a.n_groups;
+  const long long tile_win0 = 4 * c.tl + 2 * (long long)geo.rank;     // first window of this tile inside a unit
+  auto issue_in = [&](long long q) {            // whole warp we == 0 of the tile
+    if (planes_in == 0 || q >= total_it) return;
+    const long long gq = q / my_units, uq = geo.pair_id + (q % my_units) * geo.n_pairs;
+    const long long w0 = uq * WPU + tile_win0;
+    const bool dbg_no_in = (a.variant & 4) != 0;      // perf-decomposition switch (tools only): no input copies, results WRONG
+    const int valid = dbg_no_in ? 0 : (w0 < a.n ? 1 : 0) + (w0 + 1 < a.n ? 1 : 0);
+    if (c.lane == 0) mbar_arrive_expect_tx(geo.bar_in, (uint32_t)(valid * planes_in * kL * 16));
+    __syncwarp();
+    for (int idx = c.lane; idx < 2 * planes_in; idx += 32) {
+      const int slot = idx >= planes_in ? 1 : 0, pl = idx - slot * planes_in;
+      if (w0 + slot < a.n && !dbg_no_in)
+        bulk_g2s(geo.act_base + (uint32_t)pl * kPlaneBytes + (uint32_t)(4 + 64 * slot) * 16u,
+                 a.ckpt_in + (((size_t)gq * a.n + (size_t)(w0 + slot)) * planes_in + pl) * kL, (uint32_t)(kL * 16), geo.bar_in);
+    }
+  };
+  if (c.we == 0) issue_in(0);
+  // keep-flags of layer L0 for the load stage of (pass g2, unit u2): data-independent, so they are produced one
+  // iteration ahead, while the MMAs of the current unit run
+  auto flags_for = [&](int g2, long long u2, uint32_t (&kb)[4]) {
+    EpiCtx cn = c;
+    const long long win2 = u2 * WPU + tile_win0 + c.slot_w;
+    cn.row_valid = (c.t < kL) && (win2 < a.n);
+    cn.c0w = (uint32_t)(a.window_base + win2);
+    epi_pass_setup<DROP>(cn, a, g2);
+    switch (L0) {
+      case 1: make_keep_flags<1, DROP>(cn, a, g2, win2, kb); break;
+      case 2: make_keep_flags<2, DROP>(cn, a, g2, win2, kb); break;
+      case 3: make_keep_flags<3, DROP>(cn, a, g2, win2, kb); break;
+      default: make_keep_flags<4, DROP>(cn, a, g2, win2, kb); break;
+    }
+  };
+  uint32_t kb_cur[4] = {0u, 0u, 0u, 0u}, kb_next[4] = {0u, 0u, 0u, 0u};
+  if (planes_in > 0 && total_it > 0) flags_for(0, geo.pair_id, kb_cur);
+  uint32_t n_in = 0;
+  long long q = 0;
+  float* tab_s = c.tab + (L0 & 1) * 512;
+  float* tab_h = tab_s + 256;
+  for (int g = 0; g < a.n_groups; ++g) {
+    const float* tab_g = a.tables + (size_t)g * kTableFloats;
+    if (planes_in > 0) {
+      // BatchNorm affine of layer L0 for pass g (dropout scale folded), used by the load stage of every unit
+      for (int i = c.tid_t; i < 8 * planes_in; i += EPI_THREADS) {
+        tab_s[i] = __ldg(tab_g + kChTotal + c_ch_off[L0] + i);
+        tab_h[i] = __ldg(tab_g + 2 * kChTotal + c_ch_off[L0] + i);
+      }
+      named_bar_sync(1 + c.tl, EPI_THREADS);
+    }
+    for (long long unit = geo.pair_id; unit < a.n_units; unit += geo.n_pairs, ++q) {
+      const long long win = unit * WPU + tile_win0 + c.slot_w;
+      c.row_valid = (c.t < kL) && (win < a.n);
+      c.c0w = (uint32_t)(a.window_base + win);
+      if (c.colhalf == 1) st_shared_v4(c.act_row + (uint32_t)kOnesPlane * kPlaneBytes, c.row_valid ? 0x3F803F80u : 0u, 0u, 0u, 0u);
+      if (a.first_layer == 0) {
+        epi_pass_setup<DROP>(c, a, g);
+        if (c.colhalf == 0) {
+          // this row's 4 input features as bf16: channels 0..3 real, 4..7 zero, in plane 0
+          uint32_t xin0 = 0, xin1 = 0;
+          if (c.row_valid) {
+            float f0, f1, f2, f3;
+            if (a.x_f64) {
+              const double2* px = reinterpret_cast<const double2*>(static_cast<const double*>(a.x) + ((size_t)win * kL + c.t) * kF);
+              const double2 u = __ldg(px), v = __ldg(px + 1);
+              f0 = (float)u.x; f1 = (float)u.y; f2 = (float)v.x; f3 = (float)v.y;
+            } else {
+              const float4 u = __ldg(reinterpret_cast<const float4*>(static_cast<const float*>(a.x) + ((size_t)win * kL + c.t) * kF));
+              f0 = u.x; f1 = u.y; f2 = u.z; f3 = u.w;
+            }
+            xin0 = pack_bf16x2(f0, f1);
+            xin1 = pack_bf16x2(f2, f3);
+          }
+          st_shared_v4(c.act_row, xin0, xin1, 0u, 0u);
+        }
+      } else {
+        mbar_wait2(geo.bar_in, n_in & 1, a.err_flag, 5);
+        ++n_in;
+        switch (L0) {
+          case 1: load_stage<1, DROP>(c, kb_cur, tab_s, tab_h); break;
+          case 2: load_stage<2, DROP>(c, kb_cur, tab_s, tab_h); break;
+          case 3: load_stage<3, DROP>(c, kb_cur, tab_s, tab_h); break;
+          default: load_stage<4, DROP>(c, kb_cur, tab_s, tab_h); break;
+        }
+      }
+      fence_proxy_async();
+      epi_signal_act<EPI_THREADS>(c);
+      auto after_acc = [&]() { if (c.we == 0) issue_in(q + 1); };
+      auto in_shadow = [&]() {
+        if (planes_in > 0 && q + 1 < total_it) {
+          const bool same_pass = unit + geo.n_pairs < a.n_units;
+          flags_for(same_pass ? g : g + 1, same_pass ? unit + geo.n_pairs : geo.pair_id, kb_next);
+        }
+      };
+      switch (a.first_layer) {
+        case 0:
+          if (a.n_layers == 1) {
+            epi_stats<0, DROP, EPI_THREADS>(c, a, g, win, n_acc, s_stats, in_shadow, after_acc);
+          } else {
+            epi_layer<0, DROP, false, EPI_THREADS>(c, a, tab_g, g, win, n_acc, nullptr, nullptr);
+            epi_stats<1, DROP, EPI_THREADS>(c, a, g, win, n_acc, s_stats, in_shadow, after_acc);
+          }
+          break;
+        case 2: epi_stats<2, DROP, EPI_THREADS>(c, a, g, win, n_acc, s_stats, in_shadow, after_acc); break;
+        case 3: epi_stats<3, DROP, EPI_THREADS>(c, a, g, win, n_acc, s_stats, in_shadow, after_acc); break;
+        case 4: epi_stats<4, DROP, EPI_THREADS>(c, a, g, win, n_acc, s_stats, in_shadow, after_acc); break;
+        default: epi_stats<5, DROP, EPI_THREADS>(c, a, g, win, n_acc, s_stats, in_shadow, after_acc); break;
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) kb_cur[i] = kb_next[i];
+    }
+    // this pass is complete in both tiles of this CTA: add its fixed-point sums to the global accumulators of pass g
+    named_bar_sync(3, geo.all_threads);
+    for (int i = c.tl * EPI_THREADS + c.tid_t; i < 2 * kMaxCh; i += geo.all_threads) {
+      const unsigned long long v = s_stats[i];
+      if (v != 0ull) { atomicAdd(a.stats + (size_t)g * 2 * kMaxCh + i, v); s_stats[i] = 0ull; }
+    }
+    named_bar_sync(3, geo.all_threads);
   }
 }
 
@@ -955,7 +1189,7 @@ struct PairCfg {
   static constexpr int kTabFloats = 2 * 512 + 128;
   static constexpr int oTab = oRing + NSLOTS * kSlot;
   static constexpr int oBar = oTab + kTabFloats * 4;
-  static constexpr int kNumBars = 3 * NSLOTS + 4;  // full, empty, peer_full [NSLOTS]; acc, act, peer_act, in (exact-mode input planes)
+  static constexpr int kNumBars = 3 * NSLOTS + 3;  // full, empty, peer_full [NSLOTS]; acc, act, peer_act
   static constexpr int oMisc = oBar + 8 * kNumBars;
   static constexpr int oAlo = oMisc + 16 + 32;
   static constexpr int oProbs = oAlo + 4 * 392;    // probs[2][n_groups]
@@ -1044,9 +1278,7 @@ __device__ __forceinline__ void relay_layer(uint32_t bar_full, uint32_t bar_act,
   }
 }
 
-// STAT = true: statistics sweep of the exact batch-statistic mode (see FusedArgs::n_layers); the epilogue warps then
-// walk passes in the OUTER loop so that one pass's statistics are accumulated in shared memory and flushed once.
-template <int NSLOTS, int DROP, bool DBG, bool STAT = false>
+template <int NSLOTS, int DROP, bool DBG>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(PairCfg<NSLOTS>::kThreads, 2)
 fused_pair_kernel(const FusedArgs a) {
   using Cfg = PairCfg<NSLOTS>;
@@ -1064,7 +1296,6 @@ fused_pair_kernel(const FusedArgs a) {
   const uint32_t bar_acc = bar_peer_full + 8 * NSLOTS;
   const uint32_t bar_act = bar_acc + 8;
   const uint32_t bar_peer_act = bar_act + 8;                    // used in the leader only
-  const uint32_t bar_in = bar_peer_act + 8;                     // statistics sweeps: this tile's input planes have landed
   volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(smem + Cfg::oMisc);
   float* zpart = reinterpret_cast<float*>(smem + Cfg::oMisc + 16);
   uint32_t* s_alo = reinterpret_cast<uint32_t*>(smem + Cfg::oAlo);
@@ -1092,7 +1323,7 @@ fused_pair_kernel(const FusedArgs a) {
     for (int i = 0; i < NSLOTS; ++i) {
       mbar_init(bar_full + 8 * i, 1 + extra); mbar_init(bar_empty + 8 * i, 1); mbar_init(bar_peer_full + 8 * i, 1);
     }
-    mbar_init(bar_acc, 1); mbar_init(bar_act, Cfg::kEpiThreads / 32 + extra); mbar_init(bar_peer_act, 1); mbar_init(bar_in, 1);
+    mbar_init(bar_acc, 1); mbar_init(bar_act, Cfg::kEpiThreads / 32 + extra); mbar_init(bar_peer_act, 1);
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -1117,9 +1348,8 @@ fused_pair_kernel(const FusedArgs a) {
       for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
         for (int g = 0; g < a.n_groups; ++g) {
           const uint8_t* wmem = a.packed + (size_t)(a.mode_de ? g : 0) * kPackedBytes + (size_t)rank * (kPackedBytes / 2);
-          const int n_layers = STAT ? a.n_layers : kBlocks;
 #pragma unroll 1
-          for (int l = STAT ? a.first_layer : 0; l < n_layers; ++l) {
+          for (int l = 0; l < kBlocks; ++l) {
             const FusedLayer fl = c_layers[l];
             const uint32_t sb = (uint32_t)fl.step_bytes / 2;
             int step = 0;
@@ -1147,12 +1377,12 @@ fused_pair_kernel(const FusedArgs a) {
       // ---- leader: MMA issuer for the pair
       for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
         for (int g = 0; g < a.n_groups; ++g) {
-          if (!STAT || a.first_layer <= 0) issue_layer_pair<0, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
-          if (!STAT || (a.n_layers > 1 && a.first_layer <= 1)) issue_layer_pair<1, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
-          if (!STAT || (a.n_layers > 2 && a.first_layer <= 2)) issue_layer_pair<2, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
-          if (!STAT || (a.n_layers > 3 && a.first_layer <= 3)) issue_layer_pair<3, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
-          if (!STAT || (a.n_layers > 4 && a.first_layer <= 4)) issue_layer_pair<4, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
-          if (!STAT || (a.n_layers > 5 && a.first_layer <= 5)) issue_layer_pair<5, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
+          issue_layer_pair<0, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
+          issue_layer_pair<1, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
+          issue_layer_pair<2, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
+          issue_layer_pair<3, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
+          issue_layer_pair<4, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
+          issue_layer_pair<5, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
         }
       }
     } else if (lane == 0) {
@@ -1161,12 +1391,12 @@ fused_pair_kernel(const FusedArgs a) {
       const uint32_t r_peer_act = mapa_shared(bar_act, 0);
       for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
         for (int g = 0; g < a.n_groups; ++g) {
-          if (!STAT || a.first_layer <= 0) relay_layer<0, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
-          if (!STAT || (a.n_layers > 1 && a.first_layer <= 1)) relay_layer<1, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
-          if (!STAT || (a.n_layers > 2 && a.first_layer <= 2)) relay_layer<2, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
-          if (!STAT || (a.n_layers > 3 && a.first_layer <= 3)) relay_layer<3, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
-          if (!STAT || (a.n_layers > 4 && a.first_layer <= 4)) relay_layer<4, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
-          if (!STAT || (a.n_layers > 5 && a.first_layer <= 5)) relay_layer<5, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
+          relay_layer<0, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
+          relay_layer<1, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
+          relay_layer<2, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
+          relay_layer<3, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
+          relay_layer<4, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
+          relay_layer<5, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
         }
       }
     }
@@ -1216,90 +1446,6 @@ fused_pair_kernel(const FusedArgs a) {
       }
       c.c0w = (uint32_t)(a.window_base + win);
     };
-    if (STAT) {
-      unsigned long long* s_stats = reinterpret_cast<unsigned long long*>(smem + Cfg::oProbs);   // [2 * 256], no probs here
-      for (int i = c.tid_t; i < 2 * kMaxCh; i += Cfg::kEpiThreads) s_stats[i] = 0ull;
-      named_bar_sync(1, Cfg::kEpiThreads);
-      // Resumed sweep (first_layer >= 2): the input of a unit is the raw post-ReLU output of layer L0 = first_layer - 1,
-      // fetched by bulk copies straight into the activation planes ([plane][60 rows] x 16 B per window in HBM, the same
-      // order as a plane in shared memory) and normalised in place by load_stage.  The copies of iteration q + 1 are
-      // issued as soon as the MMAs of iteration q have retired, so they overlap this tile's epilogue.
-      const int L0 = a.first_layer - 1;
-      const int planes_in = L0 >= 1 ? c_layers[L0].cout / 8 : 0;
-      const long long my_units = pair_id < a.n_units ? (a.n_units - pair_id + n_pairs - 1) / n_pairs : 0;
-      const long long total_it = my_units * a.n_groups;
-      auto issue_in = [&](long long q) {            // whole warp we == 0
-        if (planes_in == 0 || q >= total_it) return;
-        const long long gq = q / my_units, uq = pair_id + (q % my_units) * n_pairs;
-        const long long w0 = uq * Cfg::kWpu + 2 * (long long)rank;
-        const int valid = (w0 < a.n ? 1 : 0) + (w0 + 1 < a.n ? 1 : 0);
-        if (lane == 0) mbar_arrive_expect_tx(bar_in, (uint32_t)(valid * planes_in * kL * 16));
-        __syncwarp();
-        for (int idx = lane; idx < 2 * planes_in; idx += 32) {
-          const int slot = idx >= planes_in ? 1 : 0, pl = idx - slot * planes_in;
-          if (w0 + slot < a.n)
-            bulk_g2s(s_base + Cfg::oAct + (uint32_t)pl * kPlaneBytes + (uint32_t)(4 + 64 * slot) * 16u,
-                     a.ckpt_in + (((size_t)gq * a.n + (size_t)(w0 + slot)) * planes_in + pl) * kL, (uint32_t)(kL * 16), bar_in);
-        }
-      };
-      if (c.we == 0) issue_in(0);
-      uint32_t n_in = 0;
-      long long q = 0;
-      float* tab_s = c.tab + (L0 & 1) * 512;
-      float* tab_h = tab_s + 256;
-      for (int g = 0; g < a.n_groups; ++g) {
-        const float* tab_g = a.tables + (size_t)g * kTableFloats;
-        if (planes_in > 0) {
-          // BatchNorm affine of layer L0 for pass g (dropout scale folded), used by the load stage of every unit
-          for (int i = c.tid_t; i < 8 * planes_in; i += Cfg::kEpiThreads) {
-            tab_s[i] = __ldg(tab_g + kChTotal + c_ch_off[L0] + i);
-            tab_h[i] = __ldg(tab_g + 2 * kChTotal + c_ch_off[L0] + i);
-          }
-          named_bar_sync(1, Cfg::kEpiThreads);
-        }
-        for (long long unit = pair_id; unit < a.n_units; unit += n_pairs, ++q) {
-          long long win; uint32_t xin0, xin1;
-          unit_prologue(unit, win, xin0, xin1);
-          epi_pass_setup<DROP>(c, a, g);
-          if (a.first_layer == 0) {
-            if (c.colhalf == 0) st_shared_v4(c.act_row, xin0, xin1, 0u, 0u);
-          } else {
-            mbar_wait2(bar_in, n_in & 1, a.err_flag, 5);
-            ++n_in;
-            switch (L0) {
-              case 1: load_stage<1, DROP>(c, a, g, win, tab_s, tab_h); break;
-              case 2: load_stage<2, DROP>(c, a, g, win, tab_s, tab_h); break;
-              case 3: load_stage<3, DROP>(c, a, g, win, tab_s, tab_h); break;
-              default: load_stage<4, DROP>(c, a, g, win, tab_s, tab_h); break;
-            }
-          }
-          fence_proxy_async();
-          epi_signal_act<Cfg::kEpiThreads>(c);
-          auto after_acc = [&]() { if (c.we == 0) issue_in(q + 1); };
-          switch (a.first_layer) {
-            case 0:
-              if (a.n_layers == 1) {
-                epi_stats<0, DROP, Cfg::kEpiThreads>(c, a, g, win, n_acc, s_stats, after_acc);
-              } else {
-                epi_layer<0, DROP, false, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, nullptr, nullptr);
-                epi_stats<1, DROP, Cfg::kEpiThreads>(c, a, g, win, n_acc, s_stats, after_acc);
-              }
-              break;
-            case 2: epi_stats<2, DROP, Cfg::kEpiThreads>(c, a, g, win, n_acc, s_stats, after_acc); break;
-            case 3: epi_stats<3, DROP, Cfg::kEpiThreads>(c, a, g, win, n_acc, s_stats, after_acc); break;
-            case 4: epi_stats<4, DROP, Cfg::kEpiThreads>(c, a, g, win, n_acc, s_stats, after_acc); break;
-            default: epi_stats<5, DROP, Cfg::kEpiThreads>(c, a, g, win, n_acc, s_stats, after_acc); break;
-          }
-        }
-        // this pass is complete in this CTA: add its fixed-point sums to the global accumulators of pass g
-        named_bar_sync(1, Cfg::kEpiThreads);
-        for (int i = c.tid_t; i < 2 * kMaxCh; i += Cfg::kEpiThreads) {
-          const unsigned long long v = s_stats[i];
-          if (v != 0ull) { atomicAdd(a.stats + (size_t)g * 2 * kMaxCh + i, v); s_stats[i] = 0ull; }
-        }
-        named_bar_sync(1, Cfg::kEpiThreads);
-      }
-    } else {
     for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
       long long win; uint32_t xin0, xin1;
       unit_prologue(unit, win, xin0, xin1);
@@ -1327,7 +1473,6 @@ fused_pair_kernel(const FusedArgs a) {
         window_metrics([&](int tt) { return pw[tt]; }, a.n_groups, win, a.out);
       }
     }
-    }
   }
 
   // ---- teardown: nobody may leave while the pair can still touch its shared memory / TMEM
@@ -1340,7 +1485,7 @@ fused_pair_kernel(const FusedArgs a) {
   }
 }
 
-template <int NSLOTS, int DROP, bool DBG, bool STAT = false>
+template <int NSLOTS, int DROP, bool DBG>
 static int launch_pair_variant(const FusedParams& p, cudaStream_t s) {
   using Cfg = PairCfg<NSLOTS>;
   FusedArgs a{};
@@ -1350,27 +1495,14 @@ static int launch_pair_variant(const FusedParams& p, cudaStream_t s) {
   a.tables = p.tables; a.probs = p.probs; a.out = p.out; a.dbg_act = p.dbg_act; a.err_flag = p.err_flag;
   a.variant = p.variant;
   a.n_units = (p.n + Cfg::kWpu - 1) / Cfg::kWpu;
-  a.smem_probs = (p.no_smem_probs || STAT) ? 0 : 1;
-  a.n_layers = STAT ? p.n_layers : kBlocks; a.stats = p.stats;
-  a.pass_base = p.pass_base; a.head_sum = STAT ? p.head_sum : nullptr; a.head_cnt = STAT ? p.head_cnt : nullptr;
-  a.ckpt_out = STAT ? reinterpret_cast<uint4*>(p.ckpt_out) : nullptr;
-  a.ckpt_in = STAT ? reinterpret_cast<const uint4*>(p.ckpt_in) : nullptr; a.first_layer = STAT ? p.first_layer : 0;
-  if (STAT) {
-    // a sweep computes one layer: [0,1) or [0,2) from the windows, [k,k+1) for k >= 2 from layer k-1's stored output
-    const bool from_x = p.first_layer == 0 && (p.n_layers == 1 || p.n_layers == 2) && p.ckpt_in == nullptr;
-    const bool resumed = p.first_layer >= 2 && p.first_layer < kBlocks && p.n_layers == p.first_layer + 1 && p.ckpt_in != nullptr;
-    if (!(from_x || resumed) || p.stats == nullptr) {
-      set_error("statistics sweep: unsupported layer range [%d, %d)", p.first_layer, p.n_layers); return UQK_E_BADARG;
-    }
-  }
-  // the probability buffer of the fused reductions doubles as the statistics accumulator [2 x 256] u64 of a sweep
-  const size_t smem = (size_t)Cfg::oProbs + (STAT ? (size_t)2 * kMaxCh * sizeof(unsigned long long)
-                                                  : (p.no_smem_probs ? 0 : (size_t)2 * p.n_groups * sizeof(float)));
+  a.smem_probs = p.no_smem_probs ? 0 : 1;
+  a.n_layers = kBlocks;
+  const size_t smem = (size_t)Cfg::oProbs + (p.no_smem_probs ? 0 : (size_t)2 * p.n_groups * sizeof(float));
   if (smem > 113 * 1024) return UQK_E_SHAPE;   // must leave room for two CTAs per SM
   int dev = 0, sms = 148;
   UQK_CUDA(cudaGetDevice(&dev));
   UQK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  auto kern = fused_pair_kernel<NSLOTS, DROP, DBG, STAT>;
+  auto kern = fused_pair_kernel<NSLOTS, DROP, DBG>;
   UQK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   UQK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
   int per_sm = 1;
@@ -1396,15 +1528,6 @@ static int launch_pair(const FusedParams& p, cudaStream_t s) {
   }
 }
 
-// statistics sweep of the exact batch-statistic mode (training=True: dropout is always on)
-template <int NSLOTS>
-static int launch_pair_stat(const FusedParams& p, cudaStream_t s) {
-  const int drop = !p.dropout ? kDropNone : (p.mask_bits ? kDropBits : kDropPhilox);
-  if (drop == kDropNone) { set_error("statistics sweeps exist for the dropout (training=True) passes only"); return UQK_E_BADARG; }
-  return drop == kDropPhilox ? launch_pair_variant<NSLOTS, kDropPhilox, false, true>(p, s)
-                             : launch_pair_variant<NSLOTS, kDropBits, false, true>(p, s);
-}
-
 // =====================================================================================================================
 // CTA-pair variant with TWO tiles per CTA ("P2"): 1 CTA per SM, the pair owns a unit of 8 windows = tile-pairs A and B
 // (each an M=256 accumulator spanning both SMs).  Both tile-pairs consume the SAME weight stream (R = 8 window-passes
@@ -1427,13 +1550,15 @@ struct Pair2Cfg {
   static constexpr int kTabFloats = 2 * 512 + 128;
   static constexpr int oTab = oRing + NSLOTS * kSlot;
   static constexpr int oBar = oTab + 2 * kTabFloats * 4;
-  static constexpr int kNumBars = 3 * NSLOTS + 6;  // full, empty, peer_full [NSLOTS]; acc[2], act[2], peer_act[2]
+  static constexpr int kNumBars = 3 * NSLOTS + 8;  // full, empty, peer_full [NSLOTS]; acc[2], act[2], peer_act[2], in[2] (sweeps)
   static constexpr int oMisc = oBar + 8 * kNumBars;
   static constexpr int oAlo = oMisc + 16 + 64;
   static constexpr int oProbs = (oAlo + 4 * 392 + 15) & ~15;   // probs[4][n_groups]
 };
 
-template <int NSLOTS, int DROP, bool DBG>
+// STAT = true: statistics sweep of the exact batch-statistic mode (see FusedArgs::n_layers, stat_epilogue_loop): the
+// kernel computes layers [first_layer, n_layers) only; both tiles of a CTA still share every weight stage.
+template <int NSLOTS, int DROP, bool DBG, bool STAT = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Pair2Cfg<NSLOTS>::kThreads, 1)
 fused_pair2_kernel(const FusedArgs a) {
   using Cfg = Pair2Cfg<NSLOTS>;
@@ -1451,6 +1576,7 @@ fused_pair2_kernel(const FusedArgs a) {
   const uint32_t bar_acc = bar_peer_full + 8 * NSLOTS;          // [2]
   const uint32_t bar_act = bar_acc + 16;                        // [2] leader only: its own epilogue threads
   const uint32_t bar_peer_act = bar_act + 16;                   // [2] leader only: one remote arrive per layer
+  const uint32_t bar_in = bar_peer_act + 16;                    // [2] statistics sweeps: the tile's input planes have landed
   volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(smem + Cfg::oMisc);
   float* zpart = reinterpret_cast<float*>(smem + Cfg::oMisc + 16);
   uint32_t* s_alo = reinterpret_cast<uint32_t*>(smem + Cfg::oAlo);
@@ -1481,6 +1607,7 @@ fused_pair2_kernel(const FusedArgs a) {
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar_acc + 8 * i, 1); mbar_init(bar_act + 8 * i, Cfg::kEpiThreads / 32 + extra); mbar_init(bar_peer_act + 8 * i, 1);
+      mbar_init(bar_in + 8 * i, 1);
     }
     fence_barrier_init();
   }
@@ -1506,8 +1633,9 @@ fused_pair2_kernel(const FusedArgs a) {
       for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
         for (int g = 0; g < a.n_groups; ++g) {
           const uint8_t* wmem = a.packed + (size_t)(a.mode_de ? g : 0) * kPackedBytes + (size_t)rank * (kPackedBytes / 2);
+          const int l_end = STAT ? a.n_layers : kBlocks;
 #pragma unroll 1
-          for (int l = 0; l < kBlocks; ++l) {
+          for (int l = STAT ? a.first_layer : 0; l < l_end; ++l) {
             const FusedLayer fl = c_layers[l];
             const uint32_t sb = (uint32_t)fl.step_bytes / 2;
             int step = 0;
@@ -1540,12 +1668,12 @@ fused_pair2_kernel(const FusedArgs a) {
       const uint32_t b_acc = bar_acc + 8 * tl, b_act = bar_act + 8 * tl;
       for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
         for (int g = 0; g < a.n_groups; ++g) {
-          issue_layer_pair<0, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
-          issue_layer_pair<1, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
-          issue_layer_pair<2, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
-          issue_layer_pair<3, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
-          issue_layer_pair<4, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
-          issue_layer_pair<5, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
+          if (!STAT || a.first_layer <= 0) issue_layer_pair<0, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
+          if (!STAT || (a.n_layers > 1 && a.first_layer <= 1)) issue_layer_pair<1, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
+          if (!STAT || (a.n_layers > 2 && a.first_layer <= 2)) issue_layer_pair<2, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
+          if (!STAT || (a.n_layers > 3 && a.first_layer <= 3)) issue_layer_pair<3, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
+          if (!STAT || (a.n_layers > 4 && a.first_layer <= 4)) issue_layer_pair<4, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
+          if (!STAT || (a.n_layers > 5 && a.first_layer <= 5)) issue_layer_pair<5, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
         }
       }
     } else if (warp == 1 && lane == 0) {
@@ -1555,7 +1683,7 @@ fused_pair2_kernel(const FusedArgs a) {
       for (long long unit = pair_id; unit < a.n_units; unit += n_pairs)
         for (int g = 0; g < a.n_groups; ++g)
 #pragma unroll 1
-          for (int l = 0; l < kBlocks; ++l) {
+          for (int l = STAT ? a.first_layer : 0; l < (STAT ? a.n_layers : kBlocks); ++l) {
             const int ns = c_layers[l].nstages;
             for (int st = 0; st < ns; ++st, ++it) {
               const int slot = it % NSLOTS;
@@ -1588,6 +1716,13 @@ fused_pair2_kernel(const FusedArgs a) {
     c.k0 = a.k0; c.k1 = a.k1;
     c.err_flag = a.err_flag;
     uint32_t n_acc = 0;
+    if constexpr (STAT) {
+      StatGeo geo;
+      geo.act_base = s_base + Cfg::oAct + c.tl * kActBytes;
+      geo.bar_in = bar_in + 8 * c.tl;
+      geo.rank = rank; geo.pair_id = pair_id; geo.n_pairs = n_pairs; geo.all_threads = 2 * Cfg::kEpiThreads;
+      stat_epilogue_loop<DROP, Cfg::kEpiThreads, Cfg::kWpu>(c, a, geo, reinterpret_cast<unsigned long long*>(smem + Cfg::oProbs), n_acc);
+    } else
     for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
       // unit = 8 windows: tile-pair tl covers windows 4*tl .. 4*tl+3; this CTA (rank) takes 2 of them
       const long long win = unit * Cfg::kWpu + 4 * c.tl + 2 * (long long)rank + c.slot_w;
@@ -1645,7 +1780,7 @@ fused_pair2_kernel(const FusedArgs a) {
   }
 }
 
-template <int NSLOTS, int DROP, bool DBG>
+template <int NSLOTS, int DROP, bool DBG, bool STAT = false>
 static int launch_pair2_variant(const FusedParams& p, cudaStream_t s) {
   using Cfg = Pair2Cfg<NSLOTS>;
   FusedArgs a{};
@@ -1655,19 +1790,42 @@ static int launch_pair2_variant(const FusedParams& p, cudaStream_t s) {
   a.tables = p.tables; a.probs = p.probs; a.out = p.out; a.dbg_act = p.dbg_act; a.err_flag = p.err_flag;
   a.variant = p.variant;
   a.n_units = (p.n + Cfg::kWpu - 1) / Cfg::kWpu;
-  a.smem_probs = p.no_smem_probs ? 0 : 1;
-  const size_t smem = (size_t)Cfg::oProbs + (p.no_smem_probs ? 0 : (size_t)4 * p.n_groups * sizeof(float));
+  a.smem_probs = (p.no_smem_probs || STAT) ? 0 : 1;
+  a.n_layers = STAT ? p.n_layers : kBlocks; a.stats = STAT ? p.stats : nullptr; a.first_layer = STAT ? p.first_layer : 0;
+  a.head_sum = STAT ? p.head_sum : nullptr; a.head_cnt = STAT ? p.head_cnt : nullptr;
+  a.ckpt_out = STAT ? reinterpret_cast<uint4*>(p.ckpt_out) : nullptr;
+  a.ckpt_in = STAT ? reinterpret_cast<const uint4*>(p.ckpt_in) : nullptr;
+  if (STAT) {
+    // a sweep computes one layer: [0,1) or [0,2) from the windows, [k,k+1) for k >= 2 from layer k-1's stored output
+    const bool from_x = p.first_layer == 0 && (p.n_layers == 1 || p.n_layers == 2) && p.ckpt_in == nullptr;
+    const bool resumed = p.first_layer >= 2 && p.first_layer < kBlocks && p.n_layers == p.first_layer + 1 && p.ckpt_in != nullptr;
+    if (!(from_x || resumed) || p.stats == nullptr) {
+      set_error("statistics sweep: unsupported layer range [%d, %d)", p.first_layer, p.n_layers); return UQK_E_BADARG;
+    }
+  }
+  // the probability buffer of the fused reductions doubles as the statistics accumulator [2 x 256] u64 of a sweep
+  const size_t smem = (size_t)Cfg::oProbs + (STAT ? (size_t)2 * kMaxCh * sizeof(unsigned long long)
+                                                  : (p.no_smem_probs ? 0 : (size_t)4 * p.n_groups * sizeof(float)));
   if (smem > 227 * 1024) return UQK_E_SHAPE;
   int dev = 0, sms = 148;
   UQK_CUDA(cudaGetDevice(&dev));
   UQK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  auto kern = fused_pair2_kernel<NSLOTS, DROP, DBG>;
+  auto kern = fused_pair2_kernel<NSLOTS, DROP, DBG, STAT>;
   UQK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   UQK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
   const long long pairs = std::min<long long>(a.n_units, (long long)(sms / 2));
   kern<<<(unsigned)(2 * pairs), Cfg::kThreads, smem, s>>>(a);
   UQK_LAUNCH_CHECK();
   return UQK_OK;
+}
+
+// statistics sweep of the exact batch-statistic mode (training=True: dropout is always on)
+template <int NSLOTS>
+static int launch_pair2_stat(const FusedParams& p, cudaStream_t s) {
+  const int drop = !p.dropout ? kDropNone : (p.mask_bits ? kDropBits : kDropPhilox);
+  if (drop == kDropNone) { set_error("statistics sweeps exist for the dropout (training=True) passes only"); return UQK_E_BADARG; }
+  return drop == kDropPhilox ? launch_pair2_variant<NSLOTS, kDropPhilox, false, true>(p, s)
+                             : launch_pair2_variant<NSLOTS, kDropBits, false, true>(p, s);
 }
 
 template <int NSLOTS>
