@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define UQK_VERSION 100
+#define UQK_VERSION 101
 
 #define UQK_OK 0
 #define UQK_E_BADARG (-1)
@@ -90,9 +90,13 @@ int uqk_forward_det(uqk_handle* h, int member, const void* x_dev, int x_dtype, i
 /* Estimate the per-layer batch statistics that Keras training=True would use, on n_windows windows and
  * n_passes stochastic passes, average them over the passes and freeze them for UQK_BN_CALIBRATED.  Up to 8192
  * windows (option "calib_fp32_max") the exact fp32 layer-synchronous kernels compute them; larger sets go through
- * the statistics sweeps of the tensor-core kernel (same definition, bf16 operands).  Enqueued on stream. */
+ * the statistics sweeps of the tensor-core kernel (same definition, bf16 operands).  window_index_base = position of the
+ * first window in the call (dropout masks are keyed by it, as in uqk_mcd).  With a statistics exchange installed
+ * (uqk_set_stats_exchange) every rank passes ITS shard and the frozen statistics are those of the windows of all ranks
+ * (the fp32 / tensor-core choice then follows the global window count, so all ranks take the same path).
+ * Enqueued on stream. */
 int uqk_calibrate(uqk_handle* h, const void* x_dev, int x_dtype, int64_t n_windows, int n_passes, uint64_t seed,
-                  void* stream);
+                  int64_t window_index_base, void* stream);
 /* Read back / install the frozen statistics: mean and var are host arrays of 6 x 256 floats (layer-major,
  * only the first Cout entries of each layer are used).  Synchronous on the handle's device. */
 int uqk_get_bn_stats(uqk_handle* h, float* mean_host, float* var_host);
@@ -132,6 +136,21 @@ int uqk_mcd(uqk_handle* h, const void* x_dev, int x_dtype, int64_t n_windows, in
  * probs_dev: NULL or (n_members, N). */
 int uqk_de(uqk_handle* h, const void* x_dev, int x_dtype, int64_t n_windows, int n_members, int precision,
            float* probs_dev, const uqk_metrics_out* out, void* stream);
+
+/* Guard band of the labels.  The reference's label is `mean_p > 0.5` in fp32 (analyze_mcd_patient_level.py:117,
+ * analyze_de_patient_level.py:132, evaluate_classification.py:49); with bf16 operands a window whose mean probability
+ * lies within the arithmetic error of 0.5 can land on the other side.  After uqk_mcd / uqk_de on the bf16 path, this
+ * call re-evaluates every window with |out->mean_pred - 0.5| < delta on the fp32 layer-synchronous path -- same
+ * windows, same dropout masks (seed, window_index_base + position, or mask_bits_dev), same BatchNorm statistics
+ * (UQK_BN_CALIBRATED / UQK_BN_INFERENCE: the frozen ones; UQK_BN_BATCH: the per-pass batch statistics of the whole call
+ * as the preceding uqk_mcd(UQK_BN_BATCH, UQK_PREC_BF16_TC) measured them -- it must be the handle's last such call) -- and
+ * overwrites ALL of that window's outputs (and its column of probs_dev, when given) with the fp32 results.
+ *   mode_de = 0: the n_groups passes of uqk_mcd;  mode_de = 1: the n_groups members of uqk_de (seed, bn_mode, masks unused).
+ *   n_refined_host: receives the number of re-evaluated windows.
+ * SYNCHRONOUS (the band population is read back to size the launches).  out->mean_pred must be non-NULL. */
+int uqk_refine_band(uqk_handle* h, int mode_de, const void* x_dev, int x_dtype, int64_t n_windows, int n_groups,
+                    uint64_t seed, int bn_mode, int64_t window_index_base, const uint32_t* mask_bits_dev, float delta,
+                    float* probs_dev, const uqk_metrics_out* out, int64_t* n_refined_host, void* stream);
 
 /* Stand-alone reductions over an existing (n_passes, N) float32 probability tensor.
  * Replaces uq_evaluation_dist (uq_techniques.py:40-112) and the inline metrics. */

@@ -2,7 +2,7 @@
 tensor-core kernel: six statistics sweeps + the final run (csrc/api.cu run_fused_exact).
 
 Oracle: float64 restatement with the same dropout masks.  Tolerances are the bf16 ones of tests/test_gpu_fused.py
-(max |dp| <= 4e-2 under dropout; mean |dp| <= 5e-3 for n >= 64); the per-layer statistics themselves are checked much
+(max |dp| <= 3.5e-2 under dropout; mean |dp| <= 5e-3 for n >= 64); the per-layer statistics themselves are checked much
 tighter against the fp32 layer-synchronous path."""
 import numpy as np
 import pytest
@@ -27,7 +27,7 @@ def test_exact_batch_philox_vs_oracle(uqk, n):
     ref = np.stack([network.forward_f64(members()[0], x, training=True, masks=twin_masks(seed, n, t))[:, 0]
                     for t in range(T)])
     err = np.abs(out["probs"] - ref)
-    assert err.max() < 4e-2, err.max()
+    assert err.max() < 3.5e-2, err.max()
     if n >= 64:
         assert err.mean() < 5e-3, err.mean()
     m2 = eng.reduce(out["probs"])                       # fused reductions of the final run = stand-alone kernel
@@ -49,7 +49,7 @@ def test_exact_batch_mask_injection_vs_oracle(uqk):
             bits[t, :, l] = philox.pack_mask_bits(masks[t][l])
     out = eng.mcd(x, n_passes=T, seed=0, bn_mode="batch", precision="bf16", masks=bits, return_probs=True)
     ref = np.stack([network.forward_f64(members()[0], x, training=True, masks=masks[t])[:, 0] for t in range(T)])
-    assert np.abs(out["probs"] - ref).max() < 4e-2
+    assert np.abs(out["probs"] - ref).max() < 3.5e-2
 
 
 def test_exact_batch_matches_the_fp32_exact_path(uqk):

@@ -1,8 +1,10 @@
 """Fused tcgen05 kernel (bf16 operands, fp32 accumulate) vs the float64 oracle, through the C-ABI.
 
 Stated tolerance of the bf16 tensor-core mode (BASELINE.json north_star "within a stated fp32/bf16 tolerance";
-SURVEY.md section 8c): max |dp| <= 2e-2 and mean |dp| <= 5e-3 (n >= 64) for deterministic / ensemble passes,
-max |dp| <= 4e-2 and mean |dp| <= 6e-3 under dropout (kept activations are scaled by up to 2x).
+SURVEY.md section 8c) on the Glorot synthetic members, whose scaled dense head amplifies rounding ~100x: max |dp| <= 2e-2
+and mean |dp| <= 4e-3 (n >= 64) for deterministic / ensemble passes, max |dp| <= 3.5e-2 and mean |dp| <= 5e-3 under
+dropout (kept activations are scaled by up to 2x) -- ~1.5x the measured distribution of
+profiles/r02_parity_distribution.json.  The pseudo-trained model meets 6e-3 / 6e-4 (tests/test_gpu_parity_timed.py).
 Labels (mean_p > 0.5) must be exact outside the guard band |mean_p - 0.5| <= max|dp|; per-window metrics
 computed in the kernel epilogue must equal the stand-alone reduction kernel on the same probabilities bit for bit."""
 import numpy as np
@@ -36,7 +38,7 @@ def test_deterministic_ragged_sizes(uqk, eng, n):
     p = eng.forward_det(x, member=1)
     ref = network.forward_f64(members()[1], x)[:, 0]
     err = np.abs(p - ref)
-    assert err.max() < 2e-2 and (n < 64 or err.mean() < 5e-3)
+    assert err.max() < 2e-2 and (n < 64 or err.mean() < 4e-3)
     assert eng.forward_det(x[:0], member=0).shape == (0,)
 
 
@@ -46,7 +48,7 @@ def test_ensemble_probs_metrics_labels(uqk, eng):
     out = eng.de(x, n_members=3, return_probs=True)
     ref = np.stack([network.forward_f64(w, x)[:, 0] for w in members()])
     err = np.abs(out["probs"] - ref)
-    assert err.max() < 2e-2 and err.mean() < 5e-3
+    assert err.max() < 2e-2 and err.mean() < 4e-3
     m2 = eng.reduce(out["probs"])
     for k in ("mean_pred", "pred_variance", "total_pred_entropy", "expected_aleatoric_entropy", "mutual_info",
               "entropy_bits", "label"):
@@ -72,7 +74,7 @@ def test_mcd_philox_vs_oracle_twin_masks(uqk, eng, n, T):
     ref = np.stack([network.forward_f64(members()[0], x, training=True, masks=twin_masks(seed, n, t),
                                         bn_mode="inference")[:, 0] for t in range(T)])
     err = np.abs(out["probs"] - ref)
-    assert err.max() < 4e-2 and err.mean() < 6e-3
+    assert err.max() < 3.5e-2 and err.mean() < 5e-3
     m2 = eng.reduce(out["probs"])
     for k in ("mean_pred", "pred_variance", "mutual_info", "label"):
         np.testing.assert_array_equal(out[k], m2[k], err_msg=k)
@@ -103,7 +105,7 @@ def test_mcd_mask_injection_and_calibrated_stats(uqk, eng):
                                         bn_stats=[(mean[l, :b.cout].astype(np.float64), var[l, :b.cout].astype(np.float64))
                                                   for l, b in enumerate(uqk.arch.BLOCKS)])[:, 0] for t in range(T)])
     err = np.abs(out["probs"] - ref)
-    assert err.max() < 4e-2 and err.mean() < 6e-3
+    assert err.max() < 3.5e-2 and err.mean() < 5e-3
 
 
 def test_shard_invariance_and_fp32_agreement(uqk, eng):

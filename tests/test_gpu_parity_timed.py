@@ -5,9 +5,9 @@ in calibrated mode -- the same frozen statistics, on a pseudo-trained model whos
 
 Bounds (SURVEY.md section 8c states max |dp| <= 2e-2 and mean |dp| <= 3e-3 for the bf16 mode, "to be tightened by
 measurement"): the measured distributions are written to gpurun_out/r02_parity_distribution.json (a copy is committed
-under profiles/); the asserted bounds sit ~1.5x above the measured values of the trained model and are never looser
-than the survey's.  The Glorot stress model amplifies rounding through its scaled dense head (logit gain ~100) and keeps
-the looser round-1 bounds.
+under profiles/); the asserted bounds sit ~2x above the measured values.  For the trained model that is 3-5x TIGHTER
+than the survey's numbers (max 6e-3, mean 6e-4 per pass under dropout).  The Glorot stress model amplifies rounding
+through its scaled dense head (logit gain ~100): its dropout bounds (max 3.5e-2, mean 5e-3) stay above the survey's.
 """
 import json
 import os
@@ -24,8 +24,10 @@ N, T, SEED = 1024, 50, 20252
 OUT = os.path.join(ROOT, "gpurun_out", "r02_parity_distribution.json")
 
 # (max |dp| per pass, mean |dp| per pass, max |d mean_pred|): trained model / Glorot stress model
-BOUNDS = {"trained": {"det": (2e-2, 3e-3, 2e-2), "calibrated": (2e-2, 3e-3, 1e-2), "batch": (2e-2, 3e-3, 1e-2)},
-          "glorot": {"det": (2e-2, 5e-3, 2e-2), "calibrated": (4e-2, 6e-3, 2e-2), "batch": (4e-2, 6e-3, 2e-2)}}
+# measured (profiles/r02_parity_distribution.json): trained det 1.9e-3 / 2.4e-4, dropout T=50 2.8e-3 / 2.9e-4 / 1.5e-3;
+# Glorot det 1.2e-2 / 2.6e-3, dropout T=50 2.3e-2 / 3.1e-3 / 2.3e-3
+BOUNDS = {"trained": {"det": (4e-3, 5e-4, 4e-3), "calibrated": (6e-3, 6e-4, 3e-3), "batch": (6e-3, 6e-4, 3e-3)},
+          "glorot": {"det": (2e-2, 4e-3, 2e-2), "calibrated": (3.5e-2, 5e-3, 5e-3), "batch": (3.5e-2, 5e-3, 5e-3)}}
 
 
 def _record(key, value):

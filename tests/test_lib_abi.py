@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
     for s in syms:
         assert hasattr(cdll, s), f"{s} declared in include/uqk.h but not exported by libuqk.so"
     assert set(lib.EXPORTS) == set(syms)
-    assert cdll.uqk_version() == 100
+    assert cdll.uqk_version() == 101
 
 
 @pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU error path")

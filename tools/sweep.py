@@ -25,7 +25,7 @@ def main():
     x = xu.repeat((n >> 16) + 1, 1, 1)[:n].contiguous().cuda()
     res = []
     eng.set_members(blobs[:1])
-    eng.calibrate(x, n_windows=32768, n_passes=2)
+    eng.calibrate(x, n_passes=1)
     for T in (10, 25, 50, 100):
         ms = timed(lambda: eng.mcd(x, n_passes=T, bn_mode="calibrated", device_out=True))
         res.append({"mode": "mcd", "T": T, "windows": n, "ms": ms, "windows_per_s": n / ms * 1e3, "tflops_valid": n * T * FLOP / ms / 1e9})

@@ -20,7 +20,7 @@ EXPORTS = [
     "uqk_version", "uqk_last_error", "uqk_create", "uqk_destroy", "uqk_set_model", "uqk_forward_det",
     "uqk_calibrate", "uqk_get_bn_stats", "uqk_set_bn_stats", "uqk_mcd", "uqk_de", "uqk_reduce",
     "uqk_patient_reduce", "uqk_standardize", "uqk_bootstrap", "uqk_bootstrap_noalloc", "uqk_launch_count", "uqk_set_option",
-    "uqk_set_stats_exchange", "uqk_write_detail_csv", "uqk_window_summary",
+    "uqk_set_stats_exchange", "uqk_write_detail_csv", "uqk_window_summary", "uqk_refine_band",
 ]
 
 # int fn(void* user, long long* stats_dev, int count, void* stream)  -- include/uqk.h uqk_stats_exchange_fn
@@ -58,12 +58,13 @@ def load() -> C.CDLL:
     lib.uqk_destroy.argtypes = [vp]
     lib.uqk_set_model.argtypes = [vp, i32, vp, C.c_size_t]
     lib.uqk_forward_det.argtypes = [vp, i32, vp, i32, i64, i32, vp, vp]
-    lib.uqk_calibrate.argtypes = [vp, vp, i32, i64, i32, u64, vp]
+    lib.uqk_calibrate.argtypes = [vp, vp, i32, i64, i32, u64, i64, vp]
     lib.uqk_get_bn_stats.argtypes = [vp, vp, vp]
     lib.uqk_set_bn_stats.argtypes = [vp, vp, vp]
     lib.uqk_mcd.argtypes = [vp, vp, i32, i64, i32, u64, i32, i32, i64, vp, vp, C.POINTER(MetricsOut), vp]
     lib.uqk_de.argtypes = [vp, vp, i32, i64, i32, i32, vp, C.POINTER(MetricsOut), vp]
     lib.uqk_reduce.argtypes = [vp, i32, i64, C.POINTER(MetricsOut), vp]
+    lib.uqk_refine_band.argtypes = [vp, i32, vp, i32, i64, i32, u64, i32, i64, vp, C.c_float, vp, C.POINTER(MetricsOut), C.POINTER(i64), vp]
     lib.uqk_patient_reduce.argtypes = [vp, vp, vp, vp, vp, i64, vp, vp]
     lib.uqk_standardize.argtypes = [vp, i32, i64, vp, vp]
     lib.uqk_bootstrap.argtypes = [vp, vp, vp, vp, vp, vp, i32, i64, vp, vp]

@@ -46,6 +46,10 @@ struct Handle {
   float* d_head_cnt = nullptr; size_t head_cnt_cap = 0;         // ... kept-row counts (bytes, allocated in floats)
   float* d_ckpt = nullptr; size_t ckpt_cap = 0;                 // ... per-layer hand-off buffer A (outputs of layers 2 and 4)
   float* d_ckpt2 = nullptr; size_t ckpt2_cap = 0;               // ... and B (outputs of layers 3 and 5)
+  float* d_tables_all = nullptr; size_t tables_all_cap = 0;     // exact mode: the per-pass epilogue tables of ALL passes of the last call
+  int exact_passes = 0; uint64_t exact_seed = 0; int64_t exact_n = -1;   // ... which call they belong to (guard-band re-evaluation)
+  float* d_band_idx = nullptr; size_t band_idx_cap = 0;         // guard band: int64 positions of the windows to re-evaluate (as floats x2)
+  unsigned long long* d_band_count = nullptr;
   float* d_dbg = nullptr;         // 6 x 128 x 256 debug dump of the fused kernel (tests)
   int variant = 0;
   int dbg_dump = 0;
@@ -85,9 +89,12 @@ static int check_x(const void* x, int dtype, int64_t n) {
 }
 
 // Layer-synchronous T passes (or M members) over all windows into probs (n_groups, n).
+// win_ids (optional, device): the n rows are rows win_ids[i] of a call of n_call windows (guard-band re-evaluation):
+// x is gathered through them, masks are keyed / indexed by them; frozen-statistics modes only.
 static int run_layersync(Handle* h, int member0, const void* x, int x_dtype, int64_t n, int n_groups, bool de, bool dropout,
                          int bn_mode, uint64_t seed, int64_t window_base, const uint32_t* mask_bits, float* probs,
-                         double* accum_mean, double* accum_var, cudaStream_t s) {
+                         double* accum_mean, double* accum_var, cudaStream_t s, const int64_t* win_ids = nullptr,
+                         int64_t n_call = 0, const float* affine_tabs = nullptr) {
   const bool exchanging = bn_mode == UQK_BN_BATCH && h->xchg != nullptr;
   if (n == 0 && !exchanging) return UQK_OK;   // an empty shard still takes part in every exchange of the call
   const int64_t chunk = bn_mode == UQK_BN_BATCH ? std::max<int64_t>(n, 1) : std::min<int64_t>(n, 16384);
@@ -97,7 +104,9 @@ static int run_layersync(Handle* h, int member0, const void* x, int x_dtype, int
   if ((rc = ensure(&h->d_act[0], &cap0, (size_t)chunk * kL * kMaxCh))) return rc;
   if ((rc = ensure(&h->d_act[1], &cap1, (size_t)chunk * kL * kMaxCh))) { h->act_cap = 0; return rc; }
   h->act_cap = std::min(cap0, cap1);
-  if ((rc = ls_cast_input(x, x_dtype, h->d_x32, n, s))) return rc;
+  if (win_ids) rc = ls_gather_input(x, x_dtype, win_ids, h->d_x32, n, s);
+  else rc = ls_cast_input(x, x_dtype, h->d_x32, n, s);
+  if (rc) return rc;
   for (int g = 0; g < n_groups; ++g) {
     for (int64_t c0 = 0; c0 < std::max<int64_t>(n, 1); c0 += chunk) {
       const int64_t cn = std::min(chunk, n - c0);
@@ -107,7 +116,10 @@ static int run_layersync(Handle* h, int member0, const void* x, int x_dtype, int
       p.act0 = h->d_act[0]; p.act1 = h->d_act[1];
       p.n = cn; p.bn_mode = bn_mode; p.dropout = dropout ? 1 : 0; p.seed = seed; p.pass = g;
       p.window_base = window_base + c0;
-      p.mask_bits = mask_bits ? mask_bits + ((size_t)g * n + c0) * kBlocks * kL * 8 : nullptr;
+      p.mask_bits = mask_bits ? mask_bits + ((size_t)g * (win_ids ? n_call : n) + (win_ids ? 0 : c0)) * kBlocks * kL * 8 : nullptr;
+      p.win_ids = win_ids ? win_ids + c0 : nullptr;
+      if (win_ids) p.window_base = window_base;
+      p.affine_tab = affine_tabs ? affine_tabs + (size_t)g * kTableFloats : nullptr;
       p.frozen_mean = h->d_frozen; p.frozen_var = h->d_frozen + kBlocks * kMaxCh;
       p.stats_scratch = h->d_stats; p.affine_scratch = h->d_affine;
       p.accum_mean = accum_mean; p.accum_var = accum_var;
@@ -247,11 +259,17 @@ static int run_fused_exact(Handle* h, const void* x, int x_dtype, int64_t n, int
     }
   }
   unsigned char* head_cnt = reinterpret_cast<unsigned char*>(h->d_head_cnt);
+  h->exact_passes = 0;
+  if ((rc = ensure(&h->d_tables_all, &h->tables_all_cap, (size_t)n_passes * kTableFloats))) return rc;
   for (int g0 = 0; g0 < n_passes; g0 += chunk) {
     const int gc = std::min(chunk, n_passes - g0);
     if ((rc = run_exact_sweeps(h, x, x_dtype, n, g0, gc, seed, window_base, mask_bits, nullptr, h->d_head_sum, head_cnt, h->d_ckpt, h->d_ckpt2, s))) return rc;
+    // keep every pass's BatchNorm affine: uqk_refine_band re-evaluates guard-band windows with exactly these statistics
+    UQK_CUDA(cudaMemcpyAsync(h->d_tables_all + (size_t)g0 * kTableFloats, h->d_tables_pass, sizeof(float) * (size_t)gc * kTableFloats,
+                             cudaMemcpyDeviceToDevice, s));
     if (n > 0 && (rc = exact_head(h->d_head_sum, head_cnt, h->d_tables_pass, gc, n, probs + (size_t)g0 * n, s))) return rc;
   }
+  h->exact_passes = n_passes; h->exact_seed = seed; h->exact_n = n;
   if (n == 0) return UQK_OK;
   return want_metrics ? launch_reduce(probs, n_passes, n, out, s) : UQK_OK;
 }
@@ -305,7 +323,7 @@ int uqk_destroy(uqk_handle* hh) {
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
   void* ptrs[] = {h->d_blobs, h->d_packed, h->d_packed_pair, h->d_tables_inf, h->d_table_mcd, h->d_frozen, h->d_stats, h->d_affine,
-                  h->d_accum, h->d_err, h->d_x32, h->d_act[0], h->d_act[1], h->d_probs_tmp, h->d_dbg, h->d_tables_pass, h->d_stats_pass, h->d_head_sum, h->d_head_cnt, h->d_ckpt, h->d_ckpt2};
+                  h->d_accum, h->d_err, h->d_tables_all, h->d_band_idx, h->d_band_count, h->d_x32, h->d_act[0], h->d_act[1], h->d_probs_tmp, h->d_dbg, h->d_tables_pass, h->d_stats_pass, h->d_head_sum, h->d_head_cnt, h->d_ckpt, h->d_ckpt2};
   for (void* p : ptrs) if (p) cudaFree(p);
   cudaGetLastError();
   delete h;
@@ -376,28 +394,31 @@ int uqk_forward_det(uqk_handle* hh, int member, const void* x_dev, int x_dtype, 
                    probs_dev, MetricsOut{}, false, s);
 }
 
-int uqk_calibrate(uqk_handle* hh, const void* x_dev, int x_dtype, int64_t n, int n_passes, uint64_t seed, void* stream) {
+int uqk_calibrate(uqk_handle* hh, const void* x_dev, int x_dtype, int64_t n, int n_passes, uint64_t seed, int64_t window_base,
+                  void* stream) {
   if (!hh) { set_error("handle is NULL"); return UQK_E_BADARG; }
   Handle* h = reinterpret_cast<Handle*>(hh);
   if (h->n_members == 0) { set_error("uqk_set_model has not been called"); return UQK_E_STATE; }
-  if (n < 1 || n_passes < 1) { set_error("calibration needs n_windows >= 1 and n_passes >= 1"); return UQK_E_BADARG; }
+  const bool exchanging = h->xchg != nullptr;
+  const int64_t n_all = exchanging ? h->xchg_global_n : n;      // windows the statistics are taken over (all ranks)
+  if (n < (exchanging ? 0 : 1) || n_all < 1 || n_passes < 1) { set_error("calibration needs n_windows >= 1 and n_passes >= 1"); return UQK_E_BADARG; }
   int rc = check_x(x_dev, x_dtype, n);
   if (rc) return rc;
   UQK_CUDA(cudaSetDevice(h->device));
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  if (n > h->calib_fp32_max) {
+  if (n_all > h->calib_fp32_max) {
     // larger calibration sets go through the statistics sweeps of the tensor-core kernel (same definition: per-pass
     // batch statistics of the exact training=True forward, averaged over the passes)
     if (n_passes > kMaxFusedGroups) { set_error("calibration on more than %lld windows takes at most %d passes",
                                                 (long long)h->calib_fp32_max, kMaxFusedGroups); return UQK_E_BADARG; }
-    if ((rc = exact_scratch(h, n, n_passes, false))) return rc;
-    if ((rc = run_exact_sweeps(h, x_dev, x_dtype, n, 0, n_passes, seed, 0, nullptr, h->d_frozen, nullptr, nullptr, h->d_ckpt, h->d_ckpt2, s))) return rc;
+    if (n > 0 && (rc = exact_scratch(h, n, n_passes, false))) return rc;
+    if ((rc = run_exact_sweeps(h, x_dev, x_dtype, n, 0, n_passes, seed, window_base, nullptr, h->d_frozen, nullptr, nullptr, h->d_ckpt, h->d_ckpt2, s))) return rc;
     h->have_frozen = true;
     return UQK_OK;
   }
   if ((rc = ensure(&h->d_probs_tmp, &h->probs_cap, (size_t)n * n_passes))) return rc;
   UQK_CUDA(cudaMemsetAsync(h->d_accum, 0, sizeof(double) * 2 * kBlocks * kMaxCh, s));
-  rc = run_layersync(h, 0, x_dev, x_dtype, n, n_passes, false, true, UQK_BN_BATCH, seed, 0, nullptr, h->d_probs_tmp,
+  rc = run_layersync(h, 0, x_dev, x_dtype, n, n_passes, false, true, UQK_BN_BATCH, seed, window_base, nullptr, h->d_probs_tmp,
                      h->d_accum, h->d_accum + kBlocks * kMaxCh, s);
   if (rc) return rc;
   average_stats_kernel<<<(2 * kBlocks * kMaxCh + 255) / 256, 256, 0, s>>>(h->d_accum, n_passes, h->d_frozen);
@@ -506,6 +527,54 @@ int uqk_de(uqk_handle* hh, const void* x_dev, int x_dtype, int64_t n, int n_memb
                      nullptr, s);
   if (rc) return rc;
   if (out) return launch_reduce(probs, n_members, n, mo, s);
+  return UQK_OK;
+}
+
+int uqk_refine_band(uqk_handle* hh, int mode_de, const void* x_dev, int x_dtype, int64_t n, int n_groups, uint64_t seed,
+                    int bn_mode, int64_t window_base, const uint32_t* mask_bits_dev, float delta, float* probs_dev,
+                    const uqk_metrics_out* out, int64_t* n_refined_host, void* stream) {
+  if (!hh) { set_error("handle is NULL"); return UQK_E_BADARG; }
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  if (n_refined_host) *n_refined_host = 0;
+  if (h->n_members == 0) { set_error("uqk_set_model has not been called"); return UQK_E_STATE; }
+  if (!out || !out->mean_pred) { set_error("uqk_refine_band needs out->mean_pred (the result of the bf16 call)"); return UQK_E_BADARG; }
+  if (!(delta >= 0.f)) { set_error("delta must be >= 0"); return UQK_E_BADARG; }
+  if (mode_de) {
+    if (n_groups < 1 || n_groups > h->n_members) { set_error("n_groups=%d but the handle holds %d members", n_groups, h->n_members); return UQK_E_BADARG; }
+    bn_mode = UQK_BN_INFERENCE;
+  } else {
+    if (n_groups < 1 || n_groups > 8192) { set_error("n_groups must be in 1..8192"); return UQK_E_BADARG; }
+    if (bn_mode == UQK_BN_BATCH && (h->exact_passes != n_groups || h->exact_seed != seed || h->exact_n != n)) {
+      set_error("uqk_refine_band(UQK_BN_BATCH) must follow the uqk_mcd(UQK_BN_BATCH, UQK_PREC_BF16_TC) call it refines "
+                "(same windows, passes and seed): it reuses that call's per-pass batch statistics");
+      return UQK_E_STATE;
+    }
+    if (bn_mode != UQK_BN_INFERENCE && bn_mode != UQK_BN_CALIBRATED && bn_mode != UQK_BN_BATCH) { set_error("unknown bn_mode %d", bn_mode); return UQK_E_BADARG; }
+    if (bn_mode == UQK_BN_CALIBRATED && !h->have_frozen) { set_error("UQK_BN_CALIBRATED needs uqk_calibrate() or uqk_set_bn_stats() first"); return UQK_E_STATE; }
+  }
+  int rc = check_x(x_dev, x_dtype, n);
+  if (rc) return rc;
+  if (n == 0) return UQK_OK;
+  UQK_CUDA(cudaSetDevice(h->device));
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if ((rc = ensure(&h->d_band_idx, &h->band_idx_cap, (size_t)n * 2))) return rc;
+  if (!h->d_band_count) UQK_CUDA(cudaMalloc(&h->d_band_count, sizeof(unsigned long long)));
+  int64_t* idx = reinterpret_cast<int64_t*>(h->d_band_idx);
+  if ((rc = launch_select_band(out->mean_pred, n, delta, idx, h->d_band_count, s))) return rc;
+  unsigned long long cnt = 0;
+  UQK_CUDA(cudaMemcpyAsync(&cnt, h->d_band_count, sizeof(cnt), cudaMemcpyDeviceToHost, s));
+  UQK_CUDA(cudaStreamSynchronize(s));
+  const int64_t m = (int64_t)cnt;
+  if (n_refined_host) *n_refined_host = m;
+  if (m == 0) return UQK_OK;
+  if ((rc = ensure(&h->d_probs_tmp, &h->probs_cap, (size_t)m * n_groups))) return rc;
+  // UQK_BN_BATCH: the statistics are those of the whole call, measured by the swept run (its per-pass tables)
+  const float* tabs = (!mode_de && bn_mode == UQK_BN_BATCH) ? h->d_tables_all : nullptr;
+  rc = run_layersync(h, 0, x_dev, x_dtype, m, n_groups, mode_de != 0, mode_de == 0, tabs ? UQK_BN_INFERENCE : bn_mode, seed, window_base,
+                     mask_bits_dev, h->d_probs_tmp, nullptr, nullptr, s, idx, n, tabs);
+  if (rc) return rc;
+  if ((rc = launch_reduce(h->d_probs_tmp, n_groups, m, to_metrics(out), s, idx))) return rc;
+  if (probs_dev && (rc = launch_scatter_probs(h->d_probs_tmp, idx, n_groups, m, n, probs_dev, s))) return rc;
   return UQK_OK;
 }
 

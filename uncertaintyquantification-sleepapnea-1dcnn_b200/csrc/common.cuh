@@ -216,6 +216,8 @@ __device__ __forceinline__ void window_metrics(Load load, int n_pass, int64_t n,
 // ---- launchers implemented in the other translation units ---------------------------------------------------
 struct Handle;  // api.cu
 
-int launch_reduce(const float* probs, int n_pass, int64_t n, const MetricsOut& o, cudaStream_t s);
+int launch_reduce(const float* probs, int n_pass, int64_t n, const MetricsOut& o, cudaStream_t s, const int64_t* out_idx = nullptr);
+int launch_select_band(const float* mean_pred, int64_t n, float delta, int64_t* idx, unsigned long long* count, cudaStream_t s);
+int launch_scatter_probs(const float* sub, const int64_t* idx, int n_pass, int64_t n_sub, int64_t n, float* probs, cudaStream_t s);
 
 }  // namespace uqk

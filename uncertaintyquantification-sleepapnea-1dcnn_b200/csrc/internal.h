@@ -28,8 +28,11 @@ struct LsPassParams {
   int (*exchange)(void* user, long long* stats_dev, int count, void* stream);
   void* exchange_user;
   int64_t global_n;           // windows of the whole call over all ranks (divisor of the statistics) when exchanging
+  const int64_t* win_ids;     // optional (n,): position of row i in the call (masks are keyed by it); null = i
+  const float* affine_tab;    // optional epilogue table (kTableFloats) whose scale / shift rows replace the BatchNorm affine
 };
 int ls_cast_input(const void* x, int x_dtype, float* out, int64_t n_windows, cudaStream_t s);
+int ls_gather_input(const void* x, int x_dtype, const int64_t* idx, float* out, int64_t n_idx, cudaStream_t s);
 int ls_forward_pass(const LsPassParams& p, cudaStream_t s);
 
 // ---- fused tcgen05 path (fused.cu) ----------------------------------------------------------------------------

@@ -19,6 +19,26 @@ __global__ void cast_input_kernel(const T* __restrict__ x, float* __restrict__ o
     out[i] = (float)x[i];
 }
 
+// rows idx[i] of (N,60,4) float64/float32 -> float32 (n_idx,60,4): the windows a guard-band re-evaluation visits
+template <typename T>
+__global__ void gather_input_kernel(const T* __restrict__ x, const int64_t* __restrict__ idx, float* __restrict__ out, int64_t n_idx) {
+  const int64_t total = n_idx * kL * kF;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t w = i / (kL * kF);
+    out[i] = (float)x[(size_t)__ldg(idx + w) * (kL * kF) + (i - w * (kL * kF))];
+  }
+}
+
+int ls_gather_input(const void* x, int x_dtype, const int64_t* idx, float* out, int64_t n_idx, cudaStream_t s) {
+  const int64_t ne = n_idx * kL * kF;
+  if (ne == 0) return UQK_OK;
+  const int grid = (int)std::min<int64_t>((ne + 255) / 256, 148 * 16);
+  if (x_dtype == UQK_F64) gather_input_kernel<double><<<grid, 256, 0, s>>>((const double*)x, idx, out, n_idx);
+  else gather_input_kernel<float><<<grid, 256, 0, s>>>((const float*)x, idx, out, n_idx);
+  UQK_LAUNCH_CHECK();
+  return UQK_OK;
+}
+
 // ---- Conv1D(same) + bias + ReLU, optional per-channel sum / sum-of-squares for batch-statistic BN -----------
 // One block per window. 128 threads = 8 channel-quads x 16 row-quads; output tile 60 rows x 32 channels per
 // iteration; the whole input window (+ zero halo) is staged in shared memory once.
@@ -135,7 +155,8 @@ __global__ void bn_affine_kernel(const float* __restrict__ mean, const float* __
 __global__ void bn_dropout_kernel(float* __restrict__ act, const float* __restrict__ scale,
                                   const float* __restrict__ shift, int cout, int64_t n, int layer, int dropout,
                                   uint32_t k0, uint32_t k1, uint32_t pass, int64_t window_base,
-                                  const uint32_t* __restrict__ mask_bits /* (N,6,60,8) for this pass or null */) {
+                                  const uint32_t* __restrict__ mask_bits /* (N,6,60,8) for this pass or null */,
+                                  const int64_t* __restrict__ win_ids /* position of row i in the call, or null = i */) {
   const int nq = cout / 8;
   const int64_t total = n * kL * nq;
   const uint32_t thr16 = drop_thr16(layer);
@@ -143,7 +164,7 @@ __global__ void bn_dropout_kernel(float* __restrict__ act, const float* __restri
     const int q = (int)(i % nq);
     const int64_t wr = i / nq;
     const int row = (int)(wr % kL);
-    const int64_t win = wr / kL;
+    const int64_t win = win_ids ? __ldg(win_ids + wr / kL) : wr / kL;    // the masks are keyed by the window's position in the call
     float4* p = reinterpret_cast<float4*>(act + (size_t)wr * cout + q * 8);
     float4 a = p[0], b = p[1];
     float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
@@ -266,27 +287,31 @@ int ls_forward_pass(const LsPassParams& p, cudaStream_t s) {
       stat_windows = p.global_n;
     }
     const float inv_keep = p.dropout ? 1.0f / (1.0f - b.rate) : 1.0f;
-    float* scale = p.affine_scratch + (size_t)l * kMaxCh * 2;
-    float* shift = scale + kMaxCh;
+    const float* scale = p.affine_scratch + (size_t)l * kMaxCh * 2;
+    const float* shift = scale + kMaxCh;
     const int tb = 128, gb = (b.cout + tb - 1) / tb;
-    if (p.bn_mode == UQK_BN_BATCH) {
+    if (p.affine_tab) {
+      // the affine of this pass was fixed elsewhere (per-pass batch statistics of the swept tensor-core run)
+      scale = p.affine_tab + kChTotal + ch_off(l);
+      shift = p.affine_tab + 2 * kChTotal + ch_off(l);
+    } else if (p.bn_mode == UQK_BN_BATCH) {
       bn_finalize_kernel<<<gb, tb, 0, s>>>(stats, (double)stat_windows * kL, blob + off.gamma[l], blob + off.beta[l], inv_keep,
-                                           b.cout, scale, shift,
+                                           b.cout, const_cast<float*>(scale), const_cast<float*>(shift),
                                            p.accum_mean ? p.accum_mean + (size_t)l * kMaxCh : nullptr,
                                            p.accum_var ? p.accum_var + (size_t)l * kMaxCh : nullptr);
     } else {
       const float* mean = p.bn_mode == UQK_BN_CALIBRATED ? p.frozen_mean + (size_t)l * kMaxCh : blob + off.mmean[l];
       const float* var = p.bn_mode == UQK_BN_CALIBRATED ? p.frozen_var + (size_t)l * kMaxCh : blob + off.mvar[l];
-      bn_affine_kernel<<<gb, tb, 0, s>>>(mean, var, blob + off.gamma[l], blob + off.beta[l], inv_keep, b.cout, scale,
-                                         shift);
+      bn_affine_kernel<<<gb, tb, 0, s>>>(mean, var, blob + off.gamma[l], blob + off.beta[l], inv_keep, b.cout,
+                                         const_cast<float*>(scale), const_cast<float*>(shift));
     }
-    UQK_LAUNCH_CHECK();
+    if (!p.affine_tab) UQK_LAUNCH_CHECK();
     if (p.n > 0) {
       const int64_t total = p.n * kL * (b.cout / 8);
       const int grid = (int)std::min<int64_t>((total + 255) / 256, 148 * 32);
       bn_dropout_kernel<<<grid, 256, 0, s>>>(out, scale, shift, b.cout, p.n, l, p.dropout ? 1 : 0,
                                              (uint32_t)(p.seed & 0xFFFFFFFFull), (uint32_t)(p.seed >> 32),
-                                             (uint32_t)p.pass, p.window_base, p.mask_bits);
+                                             (uint32_t)p.pass, p.window_base, p.mask_bits, p.win_ids);
       UQK_LAUNCH_CHECK();
     }
     in = out;

@@ -14,7 +14,7 @@ namespace uqk {
 constexpr int kReduceThreads = 128;
 
 __global__ void __launch_bounds__(kReduceThreads)
-reduce_kernel_smem(const float* __restrict__ probs, int n_pass, int64_t n, MetricsOut o) {
+reduce_kernel_smem(const float* __restrict__ probs, int n_pass, int64_t n, MetricsOut o, const int64_t* __restrict__ out_idx) {
   extern __shared__ float tile[];  // [n_pass][kReduceThreads]
   const int64_t n_tiles = (n + kReduceThreads - 1) / kReduceThreads;
   for (int64_t tix = blockIdx.x; tix < n_tiles; tix += gridDim.x) {
@@ -37,7 +37,8 @@ reduce_kernel_smem(const float* __restrict__ probs, int n_pass, int64_t n, Metri
     __syncthreads();
     if ((int)threadIdx.x < w) {
       const float* col = tile + threadIdx.x;
-      window_metrics([&](int t) { return col[t * kReduceThreads]; }, n_pass, n0 + threadIdx.x, o);
+      const int64_t w_in = n0 + threadIdx.x;
+      window_metrics([&](int t) { return col[t * kReduceThreads]; }, n_pass, out_idx ? __ldg(out_idx + w_in) : w_in, o);
     }
     __syncthreads();
   }
@@ -45,14 +46,15 @@ reduce_kernel_smem(const float* __restrict__ probs, int n_pass, int64_t n, Metri
 
 // Fallback for very large T (tile would not fit in shared memory): re-reads the column (second read hits L2).
 __global__ void __launch_bounds__(kReduceThreads)
-reduce_kernel_direct(const float* __restrict__ probs, int n_pass, int64_t n, MetricsOut o) {
+reduce_kernel_direct(const float* __restrict__ probs, int n_pass, int64_t n, MetricsOut o, const int64_t* __restrict__ out_idx) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const float* col = probs + i;
-    window_metrics([&](int t) { return __ldg(col + (size_t)t * n); }, n_pass, i, o);
+    window_metrics([&](int t) { return __ldg(col + (size_t)t * n); }, n_pass, out_idx ? __ldg(out_idx + i) : i, o);
   }
 }
 
-int launch_reduce(const float* probs, int n_pass, int64_t n, const MetricsOut& o, cudaStream_t s) {
+// out_idx (optional): window i of `probs` is written to row out_idx[i] of the outputs (guard-band re-evaluation).
+int launch_reduce(const float* probs, int n_pass, int64_t n, const MetricsOut& o, cudaStream_t s, const int64_t* out_idx) {
   if (n == 0) return UQK_OK;
   int dev = 0, sms = 148;
   UQK_CUDA(cudaGetDevice(&dev));
@@ -64,11 +66,44 @@ int launch_reduce(const float* probs, int n_pass, int64_t n, const MetricsOut& o
       UQK_CUDA(cudaFuncSetAttribute(reduce_kernel_smem, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int per_sm = (int)max((size_t)1, min((size_t)8, (size_t)(220 * 1024) / max(smem, (size_t)1)));
     const int grid = (int)min(n_tiles, (int64_t)sms * per_sm);
-    reduce_kernel_smem<<<grid, kReduceThreads, smem, s>>>(probs, n_pass, n, o);
+    reduce_kernel_smem<<<grid, kReduceThreads, smem, s>>>(probs, n_pass, n, o, out_idx);
   } else {
     const int grid = (int)min(n_tiles, (int64_t)sms * 8);
-    reduce_kernel_direct<<<grid, kReduceThreads, 0, s>>>(probs, n_pass, n, o);
+    reduce_kernel_direct<<<grid, kReduceThreads, 0, s>>>(probs, n_pass, n, o, out_idx);
   }
+  UQK_LAUNCH_CHECK();
+  return UQK_OK;
+}
+
+// ---- guard band of the labels (analyze_mcd_patient_level.py:117: label = mean_p > 0.5) --------------------------------
+// Windows whose mean probability from the bf16 tensor-core path lies within `delta` of 0.5 are listed (any order) for
+// re-evaluation on the fp32 path; count[0] receives their number.
+__global__ void select_band_kernel(const float* __restrict__ mean_pred, int64_t n, float delta, int64_t* __restrict__ idx,
+                                   unsigned long long* __restrict__ count) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    if (fabsf(mean_pred[i] - 0.5f) < delta) idx[atomicAdd(count, 1ull)] = i;
+  }
+}
+int launch_select_band(const float* mean_pred, int64_t n, float delta, int64_t* idx, unsigned long long* count, cudaStream_t s) {
+  UQK_CUDA(cudaMemsetAsync(count, 0, sizeof(unsigned long long), s));
+  if (n == 0) return UQK_OK;
+  select_band_kernel<<<(int)std::min<int64_t>((n + 255) / 256, 148 * 8), 256, 0, s>>>(mean_pred, n, delta, idx, count);
+  UQK_LAUNCH_CHECK();
+  return UQK_OK;
+}
+// probs_sub (T, n_sub) -> columns idx[i] of probs (T, n)
+__global__ void scatter_probs_kernel(const float* __restrict__ sub, const int64_t* __restrict__ idx, int n_pass, int64_t n_sub,
+                                     int64_t n, float* __restrict__ probs) {
+  const int64_t total = (int64_t)n_pass * n_sub;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t t = i / n_sub, w = i - t * n_sub;
+    probs[t * n + __ldg(idx + w)] = sub[i];
+  }
+}
+int launch_scatter_probs(const float* sub, const int64_t* idx, int n_pass, int64_t n_sub, int64_t n, float* probs, cudaStream_t s) {
+  const int64_t total = (int64_t)n_pass * n_sub;
+  if (total == 0) return UQK_OK;
+  scatter_probs_kernel<<<(int)std::min<int64_t>((total + 255) / 256, 148 * 8), 256, 0, s>>>(sub, idx, n_pass, n_sub, n, probs);
   UQK_LAUNCH_CHECK();
   return UQK_OK;
 }

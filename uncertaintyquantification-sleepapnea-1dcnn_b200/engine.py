@@ -16,6 +16,10 @@ from . import _lib, arch
 METRIC_KEYS = ("mean_pred", "pred_variance", "total_pred_entropy", "expected_aleatoric_entropy", "mutual_info",
                "entropy_bits", "label")
 _PREC = {"bf16": _lib.PREC_BF16_TC, "bf16_tc": _lib.PREC_BF16_TC, "fp32": _lib.PREC_FP32}
+# Guard band of the labels: half-width around 0.5 inside which a bf16 mean probability is re-evaluated in fp32.  The
+# measured |d mean_pred| of the bf16 path against the float64 oracle is <= 2.4e-3 over both test models
+# (profiles/r02_parity_distribution.json), so 5e-3 leaves a factor 2.
+GUARD_DELTA = 5e-3
 _BN = {"inference": _lib.BN_INFERENCE, "frozen": _lib.BN_INFERENCE, "batch": _lib.BN_BATCH,
        "calibrated": _lib.BN_CALIBRATED}
 
@@ -52,6 +56,7 @@ class Engine:
         self.calibrated = False
         self._xchg_cb = None
         self._xchg_error = None
+        self.last_guard_band = (0, 0)
 
     def close(self):
         if getattr(self, "_h", None):
@@ -146,18 +151,34 @@ class Engine:
                                                 probs.data_ptr(), self._stream()), "uqk_forward_det")
             return probs if device_out else probs.cpu().numpy()
 
-    def calibrate(self, x, n_windows: int = 32768, n_passes: int = 2, seed: int = 2025):
-        """Freezes the batch statistics Keras ``training=True`` would use, estimated on the first
-        ``n_windows`` windows (fp32 layer-synchronous kernels up to 8192 windows, the statistics sweeps of the
-        tensor-core kernel above; see DESIGN.md, BN modes)."""
+    def calibrate(self, x, n_windows: Optional[int] = None, n_passes: int = 1, seed: int = 2025, sampling: str = "strided",
+                  window_base: int = 0):
+        """Freezes the batch statistics Keras ``training=True`` would use (uq_techniques.py:22), measured on ``x``:
+        per-pass batch mean / biased variance of the exact forward, averaged over ``n_passes`` passes (fp32
+        layer-synchronous kernels up to 8192 windows, the statistics sweeps of the tensor-core kernel above).
+        Default: ALL windows of the call, one pass -- the statistics the reference normalises pass 0 with, at the cost of
+        one exact pass (~3 % of a T=50 run).  ``n_windows`` < len(x) calibrates on a subset instead (measured: mean
+        |d mean_pred| vs the exact mode 1.2e-3 for 8192..32768 of 65536 windows, 6e-5 for all of them --
+        profiles/r02_calibration_compare.json): ``sampling='strided'`` takes every (N // n_windows)-th window of the WHOLE
+        call -- rows of a real data set are patient-contiguous (preprocess_shhs_raw.py:323-325), so a prefix would be
+        the first few dozen patients, a biased sample; ``'prefix'`` takes ``x[:n_windows]`` (tests).
+        With a statistics exchange installed, ``x`` is this rank's shard (``window_base`` = its first global index)
+        and the statistics are those of the windows of all ranks."""
         with torch.cuda.device(self.device):
-            if isinstance(x, torch.Tensor):
-                xs = x[:n_windows]
-            else:
-                xs = np.asarray(x)[:n_windows]
+            n = len(x)
+            xs = x
+            if n_windows is not None and 0 < int(n_windows) < n:
+                if sampling == "strided":
+                    xs = x[::max(1, n // int(n_windows))][:int(n_windows)]
+                elif sampling == "prefix":
+                    xs = x[:int(n_windows)]
+                else:
+                    raise ValueError(f"unknown calibration sampling '{sampling}'")
+            if not isinstance(xs, torch.Tensor):
+                xs = np.asarray(xs)
             xt, dt = self.to_device(xs)
             _lib.check(self.lib.uqk_calibrate(self._h, xt.data_ptr(), dt, xt.shape[0], int(n_passes),
-                                              C.c_uint64(seed & (2 ** 64 - 1)), self._stream()), "uqk_calibrate")
+                                              C.c_uint64(seed & (2 ** 64 - 1)), int(window_base), self._stream()), "uqk_calibrate")
             self.calibrated = True
 
     def set_stats_exchange(self, reduce_fn, global_windows: int = 0):
@@ -203,9 +224,12 @@ class Engine:
 
     def mcd(self, x, n_passes: int = 50, seed: int = 2025, bn_mode: str = "calibrated", precision: str = "bf16",
             masks=None, return_probs: bool = False, metrics: Sequence[str] = METRIC_KEYS, window_base: int = 0,
-            device_out: bool = False) -> Dict:
+            device_out: bool = False, exact_labels: bool = False, guard_delta: float = GUARD_DELTA) -> Dict:
         """T stochastic passes of member 0 + per-window reductions (uq_techniques.py:12-24 fused with :40-112).
-        ``masks``: optional (T,N,6,60,8) uint32 keep-bits (mask injection)."""
+        ``masks``: optional (T,N,6,60,8) uint32 keep-bits (mask injection).
+        ``exact_labels``: windows whose bf16 mean probability lies within ``guard_delta`` of 0.5 are re-evaluated on
+        the fp32 path with the same masks and statistics (``uqk_refine_band``); ``self.last_guard_band`` then holds
+        (re-evaluated windows, all windows)."""
         with torch.cuda.device(self.device):
             xt, dt = self.to_device(x)
             n = xt.shape[0]
@@ -226,11 +250,15 @@ class Engine:
                 err, self._xchg_error = self._xchg_error, None
                 raise RuntimeError("batch-statistics exchange failed") from err
             _lib.check(rc, "uqk_mcd")
+            if exact_labels and precision in ("bf16", "bf16_tc") and "mean_pred" in bufs and n > 0:
+                self._refine(0, xt, dt, n, int(n_passes), seed, _BN[bn_mode], int(window_base), mt, guard_delta, probs, mo)
             return self._finish(bufs, probs, device_out)
 
     def de(self, x, n_members: Optional[int] = None, precision: str = "bf16", return_probs: bool = False,
-           metrics: Sequence[str] = METRIC_KEYS, device_out: bool = False) -> Dict:
-        """M ensemble members in inference mode + per-window reductions (uq_techniques.py:26-32 fused with :40-112)."""
+           metrics: Sequence[str] = METRIC_KEYS, device_out: bool = False, exact_labels: bool = False,
+           guard_delta: float = GUARD_DELTA) -> Dict:
+        """M ensemble members in inference mode + per-window reductions (uq_techniques.py:26-32 fused with :40-112).
+        ``exact_labels``: see ``mcd``."""
         with torch.cuda.device(self.device):
             m = self.n_members if n_members is None else int(n_members)
             xt, dt = self.to_device(x)
@@ -240,7 +268,18 @@ class Engine:
             _lib.check(self.lib.uqk_de(self._h, xt.data_ptr(), dt, n, m, _PREC[precision],
                                        probs.data_ptr() if probs is not None else None,
                                        C.byref(mo) if bufs else None, self._stream()), "uqk_de")
+            if exact_labels and precision in ("bf16", "bf16_tc") and "mean_pred" in bufs and n > 0:
+                self._refine(1, xt, dt, n, m, 0, _lib.BN_INFERENCE, 0, None, guard_delta, probs, mo)
             return self._finish(bufs, probs, device_out)
+
+    def _refine(self, mode_de, xt, dt, n, n_groups, seed, bn_code, window_base, mt, delta, probs, mo):
+        cnt = C.c_int64(0)
+        _lib.check(self.lib.uqk_refine_band(self._h, int(mode_de), xt.data_ptr(), dt, n, int(n_groups),
+                                            C.c_uint64(seed & (2 ** 64 - 1)), int(bn_code), int(window_base),
+                                            mt.data_ptr() if mt is not None else None, C.c_float(delta),
+                                            probs.data_ptr() if probs is not None else None, C.byref(mo),
+                                            C.byref(cnt), self._stream()), "uqk_refine_band")
+        self.last_guard_band = (int(cnt.value), int(n))
 
     def reduce(self, probs, metrics: Sequence[str] = METRIC_KEYS, device_out: bool = False) -> Dict:
         """(T,N) float32 probabilities -> per-window metrics (uq_techniques.py:40-112)."""

@@ -86,8 +86,11 @@ class UQModel:
 
 
 def _default_precision() -> str:
+    """Single deterministic passes (``model(x, training=False)``, ``model.predict``) run in fp32 like the reference
+    unless UQK_PRECISION says otherwise: one pass is cheap, and labels / accuracy checks derived from it
+    (analyze_mcd_patient_level.py:204-207, evaluate_classification.py:49) then need no guard band."""
     import os
-    return os.environ.get("UQK_PRECISION", "bf16")
+    return os.environ.get("UQK_PRECISION", "fp32")
 
 
 def fingerprint(blob: np.ndarray) -> int:

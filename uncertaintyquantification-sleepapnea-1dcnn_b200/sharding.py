@@ -100,17 +100,20 @@ class StatsExchange:
 
 
 def sharded_mc_dropout_uq(uq_module, model, x, n_pred: int = 50, patient_ids=None, seed: Optional[int] = None,
-                          bn_mode: str = "calibrated", calib_windows: int = 32768, group=None, **kw) -> Dict[str, np.ndarray]:
+                          bn_mode: str = "calibrated", calib_windows: Optional[int] = None, group=None, **kw) -> Dict[str, np.ndarray]:
     """Each rank runs the MC-Dropout path on its shard of ``x`` (host array, identical on all ranks) and the
     per-window metrics are gathered on every rank.  The dropout masks are keyed by the global window index.
-    ``bn_mode='calibrated'``: every rank estimates the frozen statistics on the SAME global windows
-    ``x[:calib_windows]`` (no data-path collective).  ``bn_mode='batch'``: exact Keras semantics -- the per-layer
+    ``bn_mode='calibrated'``: one exact pass over the whole call measures the statistics -- every rank sweeps its own
+    shard and the per-layer sums are all-reduced (``StatsExchange``, 6 messages of 4 KB); with ``calib_windows`` every
+    rank instead uses the SAME strided subset of the global windows (no collective at all).  ``bn_mode='batch'``: exact Keras semantics -- the per-layer
     statistics are all-reduced over the ranks (``StatsExchange``).  Either way the gathered result is bit-identical
     to a single-GPU run over all of ``x``."""
     rank, world = _world(group)
     n = len(x)
     shards = patient_aligned_shards(patient_ids, world) if patient_ids is not None else window_shards(n, world)
     s, e = shards[rank]
+    if seed is None:
+        seed = uq_module._call_seed()      # one key for the whole sharded call (the ranks' call counters advance in step)
     if bn_mode == "batch":
         uq_module.mc_dropout_uq(model, x[:0], n_pred=1, seed=seed, bn_mode="inference")   # uploads the model
         eng = uq_module._engine.get_engine()
@@ -123,9 +126,16 @@ def sharded_mc_dropout_uq(uq_module, model, x, n_pred: int = 50, patient_ids=Non
         local = {k: v for k, v in out.items() if isinstance(v, torch.Tensor)}
         return {k: v.cpu().numpy() for k, v in gather_metrics(local, shards, group).items()}
     if bn_mode == "calibrated":
-        uq_module.mc_dropout_uq(model, x[:min(n, calib_windows)][:0], n_pred=1, seed=seed, bn_mode="inference")  # uploads the model
-        uq_module._engine.get_engine().calibrate(x, n_windows=calib_windows, n_passes=2,
-                                                 seed=uq_module._seed() if seed is None else int(seed))
+        uq_module.mc_dropout_uq(model, x[:0], n_pred=1, seed=seed, bn_mode="inference")  # uploads the model
+        eng = uq_module._engine.get_engine()
+        if calib_windows is not None and calib_windows < n:
+            eng.calibrate(x, n_windows=calib_windows, n_passes=1, seed=int(seed))
+        else:
+            eng.set_stats_exchange(StatsExchange(group), global_windows=n)
+            try:
+                eng.calibrate(x[s:e], n_passes=1, seed=int(seed), window_base=s)
+            finally:
+                eng.set_stats_exchange(None)
     out = uq_module.mc_dropout_uq(model, x[s:e], n_pred=n_pred, seed=seed, bn_mode=bn_mode, recalibrate=False,
                                   device_out=True, window_base=s, **kw)
     local = {k: v for k, v in out.items() if isinstance(v, torch.Tensor)}

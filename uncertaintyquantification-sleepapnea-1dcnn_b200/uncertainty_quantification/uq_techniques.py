@@ -12,9 +12,15 @@ Build-side knobs (the callers' positional signatures are frozen, so these are en
                  auto = batch = exact Keras ``training=True`` semantics (statistics of the whole call): fp32
                  layer-synchronous kernels up to UQK_EXACT_MAX_WINDOWS windows, above that the bf16 tensor-core
                  kernel swept once per layer (same semantics, 1.9x the flops of one run).
-                 calibrated = statistics estimated once on UQK_CALIB_WINDOWS windows and frozen (fastest)
-  UQK_PRECISION  bf16 | fp32   (fp32 forces the layer-synchronous kernels at any size)
-  UQK_SEED       Philox key of the dropout masks (default: the seed given to tf.random.set_seed, else 2025)
+                 calibrated = statistics of one exact pass over the call (or over a strided subset of
+                 UQK_CALIB_WINDOWS windows), frozen for all passes (fastest)
+  UQK_PRECISION  bf16 | fp32   arithmetic of the compat entry points.  Unset: MC-Dropout as described under UQK_BN_MODE;
+                 deep_ensembles_predict, model(x, training=False) and model.predict run in fp32 like the reference
+                 (one to M passes are cheap).  bf16 = tensor-core kernel + fp32 re-evaluation of the windows whose mean
+                 probability lies within 5e-3 of 0.5, so that `mean > 0.5` labels are those of the fp32 path.
+  UQK_SEED       fixed Philox key of the dropout masks.  Unset: the key is derived from the seed given to
+                 tf.random.set_seed (else 2025) AND a per-process call counter, so that -- as with TensorFlow's
+                 stateful generator (uq_techniques.py:22) -- every call draws fresh masks.
 """
 from __future__ import annotations
 
@@ -47,6 +53,23 @@ def _seed() -> int:
     return int(s) if s is not None else int(_model.UQModel._global_seed)
 
 
+_calls = {"base": None, "n": 0}
+
+
+def _call_seed() -> int:
+    """Philox key of ONE stochastic call: UQK_SEED when set (reproducible runs), else the global seed folded with a
+    call counter that restarts whenever the global seed changes (tf.random.set_seed)."""
+    s = os.environ.get("UQK_SEED")
+    if s is not None:
+        return int(s)
+    base = int(_model.UQModel._global_seed)
+    if _calls["base"] != base:
+        _calls["base"], _calls["n"] = base, 0
+    k = (base * 0x9E3779B97F4A7C15 + 0xD1B54A32D192ED03 * _calls["n"]) & (2 ** 64 - 1)
+    _calls["n"] += 1
+    return k
+
+
 def _members_key(blobs):
     return tuple(_model.fingerprint(b) for b in blobs)
 
@@ -70,9 +93,13 @@ def mc_dropout_predict(model, x_test_data: np.ndarray, n_pred: int = 50) -> np.n
         # activations fit comfortably, the swept tensor-core kernel above
         if n <= int(_env("UQK_EXACT_MAX_WINDOWS", "16384")) and "UQK_PRECISION" not in os.environ:
             prec = "fp32"
-    elif mode == "calibrated" and not eng.calibrated:
-        eng.calibrate(x, n_windows=int(_env("UQK_CALIB_WINDOWS", "32768")), n_passes=2, seed=_seed())
-    out = eng.mcd(x, n_passes=int(n_pred), seed=_seed(), bn_mode=mode, precision=prec, return_probs=True, metrics=())
+    seed = _call_seed()
+    if mode == "calibrated" and not eng.calibrated:
+        eng.calibrate(x, n_windows=int(_env("UQK_CALIB_WINDOWS", "0")) or None, n_passes=1, seed=seed)
+    # bf16 passes: the windows whose mean probability is within the guard band of 0.5 are re-evaluated in fp32, so the
+    # labels the drivers derive from the returned tensor (analyze_mcd_patient_level.py:109-117) are the fp32 path's
+    out = eng.mcd(x, n_passes=int(n_pred), seed=seed, bn_mode=mode, precision=prec, return_probs=True,
+                  metrics=("mean_pred",), exact_labels=True)
     mc_predictions = out["probs"].reshape(int(n_pred), n, 1)
     print(f"MC Dropout completed in {time.time()-t0:.1f}s ({n_pred} passes)")
     return mc_predictions
@@ -86,7 +113,8 @@ def deep_ensembles_predict(ensemble_models: List, x_test_data: np.ndarray) -> np
     blobs = [_model.weights_of(m) for m in models]
     eng.ensure_members(lambda: np.stack(blobs), key=("de",) + _members_key(blobs))
     x = np.asarray(x_test_data)
-    out = eng.de(x, n_members=len(models), precision=_env("UQK_PRECISION", "bf16"), return_probs=True, metrics=())
+    out = eng.de(x, n_members=len(models), precision=_env("UQK_PRECISION", "fp32"), return_probs=True,
+                 metrics=("mean_pred",), exact_labels=True)
     de_predictions = out["probs"].reshape(len(models), x.shape[0], 1)
     print(f"Deep Ensemble completed in {time.time()-t0:.1f}s ({len(models)} models)")
     return de_predictions
@@ -112,37 +140,53 @@ def _finish_uq(out: Dict, y_true) -> Dict:
 
 def mc_dropout_uq(model, x_test_data, n_pred: int = 50, *, y_true=None, return_probs: bool = False,
                   bn_mode: str = "calibrated", precision: str = "bf16", seed: Optional[int] = None, masks=None,
-                  calib_windows: int = 32768, calib_passes: int = 2, recalibrate: bool = True,
-                  device_out: bool = False, window_base: int = 0) -> Dict:
+                  calib_windows: Optional[int] = None, calib_passes: int = 1, recalibrate: bool = True,
+                  device_out: bool = False, window_base: int = 0, exact_labels: bool = False,
+                  guard_delta: Optional[float] = None) -> Dict:
     """mc_dropout_predict + uq_evaluation_dist + the drivers' inline CSV metrics in ONE fused call: the
     (T,N) probability tensor is never written to HBM unless ``return_probs``.  Returns the per-window arrays of
     uq_techniques.py:103-108 plus ``predictive_entropy_bits`` / ``predicted_label``
-    (analyze_mcd_patient_level.py:113-117).  ``bn_mode='calibrated'`` first estimates the batch statistics on
-    ``calib_windows`` windows with the exact path (inside this call when ``recalibrate``);
+    (analyze_mcd_patient_level.py:113-117).  ``bn_mode='calibrated'`` first measures the batch statistics with
+    ``calib_passes`` exact pass(es) over all windows of the call (or a strided subset of ``calib_windows``), inside this
+    call when ``recalibrate``, and freezes them for the T passes;
     ``bn_mode='batch'`` is the exact Keras ``training=True`` behaviour (statistics of all windows of this call):
     ``precision='bf16'`` sweeps the tensor-core kernel once per layer, ``'fp32'`` uses the layer-synchronous kernels.
-    ``window_base`` = global index of the first window (multi-GPU shards: masks are keyed by the global index)."""
+    ``window_base`` = global index of the first window (multi-GPU shards: masks are keyed by the global index).
+    ``exact_labels``: re-evaluate in fp32 (same masks, same statistics) every window whose bf16 mean probability lies
+    within ``guard_delta`` (default 5e-3) of 0.5 and replace all of its outputs -- `predicted_label` is then the fp32
+    path's label; the result carries ``guard_band = (re-evaluated windows, all windows)``.
+    ``seed=None`` draws a fresh key per call (see UQK_SEED in the module docstring)."""
     eng = _engine.get_engine()
     blob = _model.weights_of(model)
     eng.ensure_members(lambda: blob[None], key=("mcd",) + _members_key([blob]))
-    seed = _seed() if seed is None else int(seed)
+    seed = _call_seed() if seed is None else int(seed)
     if bn_mode == "calibrated" and (recalibrate or not eng.calibrated):
         eng.calibrate(x_test_data, n_windows=calib_windows, n_passes=calib_passes, seed=seed)
+    kw = {} if guard_delta is None else {"guard_delta": float(guard_delta)}
     out = eng.mcd(x_test_data, n_passes=int(n_pred), seed=seed, bn_mode=bn_mode, precision=precision, masks=masks,
-                  return_probs=return_probs, device_out=device_out, window_base=int(window_base))
-    return _finish_uq(out, y_true)
+                  return_probs=return_probs, device_out=device_out, window_base=int(window_base),
+                  exact_labels=exact_labels, **kw)
+    res = _finish_uq(out, y_true)
+    if exact_labels:
+        res["guard_band"] = eng.last_guard_band
+    return res
 
 
 def deep_ensemble_uq(ensemble_models: List, x_test_data, *, y_true=None, return_probs: bool = False,
-                     precision: str = "bf16", device_out: bool = False) -> Dict:
+                     precision: str = "bf16", device_out: bool = False, exact_labels: bool = False,
+                     guard_delta: Optional[float] = None) -> Dict:
     """deep_ensembles_predict + uq_evaluation_dist + inline CSV metrics in one fused call (see mc_dropout_uq)."""
     eng = _engine.get_engine()
     models = list(ensemble_models)
     blobs = [_model.weights_of(m) for m in models]
     eng.ensure_members(lambda: np.stack(blobs), key=("de",) + _members_key(blobs))
+    kw = {} if guard_delta is None else {"guard_delta": float(guard_delta)}
     out = eng.de(x_test_data, n_members=len(models), precision=precision, return_probs=return_probs,
-                 device_out=device_out)
-    return _finish_uq(out, y_true)
+                 device_out=device_out, exact_labels=exact_labels, **kw)
+    res = _finish_uq(out, y_true)
+    if exact_labels:
+        res["guard_band"] = eng.last_guard_band
+    return res
 
 
 # ===================== uncertainty metrics =====================
