@@ -159,7 +159,9 @@ int uqk_reduce(const float* probs_dev, int n_passes, int64_t n_windows, const uq
 /* Per-patient aggregation of per-window rows.  Replaces the pandas groupby of
  * aggregate_patient_uq_metrics.py:34-46.  Rows of patient p are seg_offsets_dev[p] .. seg_offsets_dev[p+1]-1
  * of the (already patient-sorted) columns.  out_dev: (n_patients, 8) float64 rows =
- * [mean_var, median_var, std_var(ddof=1; 0 if n<=1), mean_ent, median_ent, std_ent, accuracy, num_windows]. */
+ * [mean_var, median_var, std_var(ddof=1; 0 if n<=1), mean_ent, median_ent, std_ent, accuracy, num_windows].
+ * SYNCHRONOUS: a patient with more than 8192 windows does not fit the in-kernel sort; the kernel's flag is read back
+ * and the call returns UQK_E_SHAPE (the rows of such patients are NaN) instead of failing later. */
 int uqk_patient_reduce(const float* variance_dev, const float* entropy_dev, const int32_t* true_label_dev,
                        const int32_t* pred_label_dev, const int64_t* seg_offsets_dev, int64_t n_patients,
                        double* out_dev, void* stream);

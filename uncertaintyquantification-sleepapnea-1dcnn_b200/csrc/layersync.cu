@@ -40,80 +40,98 @@ int ls_gather_input(const void* x, int x_dtype, const int64_t* idx, float* out, 
 }
 
 // ---- Conv1D(same) + bias + ReLU, optional per-channel sum / sum-of-squares for batch-statistic BN -----------
-// One block per window. 128 threads = 8 channel-quads x 16 row-quads; output tile 60 rows x 32 channels per
-// iteration; the whole input window (+ zero halo) is staged in shared memory once.
+// One block per window, 128 threads = 8 channel quads x 8 row octets x 2 channel tiles: a thread owns 8 rows x 4 channels
+// of a 32-channel tile, two tiles (64 channels) are in flight per iteration.  The window (+ zero halo) is staged in
+// shared memory TRANSPOSED ([channel][row], odd row pitch), so that for one input channel a thread loads its K + 7
+// consecutive rows once and reuses them for all K taps from registers: K x 32 FMAs per (K + 7) shared loads + K
+// weight loads.
 constexpr int kConvThreads = 128;
 constexpr double kStatScale = 16777216.0;   // 2^24 fixed point of the batch-statistic accumulators
+
+template <int K>
+__host__ __device__ constexpr int conv_row_pitch() { return ((64 + K - 1) | 1) + 2; }   // odd: conflict-free transposed staging
 
 template <int CIN, int COUT, int K>
 __global__ void __launch_bounds__(kConvThreads)
 conv_relu_kernel(const float* __restrict__ in, const float* __restrict__ w, const float* __restrict__ bias,
                  float* __restrict__ out, double* __restrict__ stats, int64_t n) {
   constexpr int H = (K - 1) / 2;
-  constexpr int ROWS = kL + 2 * H + 4;  // +4: row-quad 15 reads rows 60..63 (+j) -- keep them in bounds
-  constexpr int XS = CIN + 1;
+  constexpr int RP = conv_row_pitch<K>();
+  constexpr int NT = COUT / 32;              // 32-channel tiles
   extern __shared__ float smem[];
-  float* xs = smem;               // [ROWS][XS]
+  float* xs = smem;                          // [CIN][RP]: xs[c][r] = x[r - H][c], zero outside the window
   // per-channel (sum, sum of squares) of the block, 2^-24 fixed point: integer accumulation is associative, so the
   // batch statistics -- and everything computed from them -- are bit-reproducible run to run and across GPUs
-  unsigned long long* ssum = reinterpret_cast<unsigned long long*>(xs + ((ROWS * XS + 1) & ~1));   // [32][2]
-  const int tx = threadIdx.x & 7;   // channel quad within the 32-channel tile
-  const int ty = threadIdx.x >> 3;  // row quad: rows 4*ty .. 4*ty+3
+  unsigned long long* ssum = reinterpret_cast<unsigned long long*>(xs + ((CIN * RP + 1) & ~1));   // [64][2]
+  const int tx = threadIdx.x & 7;            // channel quad within the 32-channel tile
+  const int ro = (threadIdx.x >> 3) & 7;     // row octet: rows 8*ro .. 8*ro+7
+  const int th = threadIdx.x >> 6;           // which of the two tiles in flight
 
   for (int64_t win = blockIdx.x; win < n; win += gridDim.x) {
     __syncthreads();
-    for (int i = threadIdx.x; i < ROWS * CIN; i += kConvThreads) {
-      const int r = i / CIN, c = i % CIN;
+    for (int i = threadIdx.x; i < RP * CIN; i += kConvThreads) {
+      const int r = i / CIN, c = i - r * CIN;
       const int src = r - H;
-      xs[r * XS + c] = (src >= 0 && src < kL) ? __ldg(in + ((size_t)win * kL + src) * CIN + c) : 0.f;
+      xs[c * RP + r] = (src >= 0 && src < kL) ? __ldg(in + ((size_t)win * kL + src) * CIN + c) : 0.f;
     }
     __syncthreads();
-    for (int ct = 0; ct < COUT / 32; ++ct) {
-      const int ch0 = ct * 32 + tx * 4;
-      float acc[4][4];
+    for (int ct0 = 0; ct0 < NT; ct0 += 2) {
+      const int ct = ct0 + th;
+      const bool active = ct < NT;
+      const int ch0 = (active ? ct : 0) * 32 + tx * 4;
+      float acc[8][4];
       const float4 b4 = __ldg(reinterpret_cast<const float4*>(bias + ch0));
 #pragma unroll
-      for (int i = 0; i < 4; ++i) { acc[i][0] = b4.x; acc[i][1] = b4.y; acc[i][2] = b4.z; acc[i][3] = b4.w; }
-      for (int j = 0; j < K; ++j) {
-        const float* xr = xs + (4 * ty + j) * XS;
-        const float* wr = w + (size_t)j * CIN * COUT + ch0;
-#pragma unroll 4
+      for (int i = 0; i < 8; ++i) { acc[i][0] = b4.x; acc[i][1] = b4.y; acc[i][2] = b4.z; acc[i][3] = b4.w; }
+      if (active) {
+#pragma unroll 2
         for (int c = 0; c < CIN; ++c) {
-          const float4 wv = __ldg(reinterpret_cast<const float4*>(wr + (size_t)c * COUT));
+          float xw[K + 7];
+          const float* xr = xs + c * RP + 8 * ro;
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const float xv = xr[i * XS + c];
-            acc[i][0] = fmaf(xv, wv.x, acc[i][0]);
-            acc[i][1] = fmaf(xv, wv.y, acc[i][1]);
-            acc[i][2] = fmaf(xv, wv.z, acc[i][2]);
-            acc[i][3] = fmaf(xv, wv.w, acc[i][3]);
+          for (int i = 0; i < K + 7; ++i) xw[i] = xr[i];
+          const float* wr = w + (size_t)c * COUT + ch0;
+#pragma unroll
+          for (int j = 0; j < K; ++j) {
+            const float4 wv = __ldg(reinterpret_cast<const float4*>(wr + (size_t)j * CIN * COUT));
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              acc[i][0] = fmaf(xw[i + j], wv.x, acc[i][0]);
+              acc[i][1] = fmaf(xw[i + j], wv.y, acc[i][1]);
+              acc[i][2] = fmaf(xw[i + j], wv.z, acc[i][2]);
+              acc[i][3] = fmaf(xw[i + j], wv.w, acc[i][3]);
+            }
           }
         }
       }
       float s[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
+      if (active) {
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int row = 4 * ty + i;
-        if (row < kL) {
-          float4 v;
-          v.x = fmaxf(acc[i][0], 0.f); v.y = fmaxf(acc[i][1], 0.f);
-          v.z = fmaxf(acc[i][2], 0.f); v.w = fmaxf(acc[i][3], 0.f);
-          *reinterpret_cast<float4*>(out + ((size_t)win * kL + row) * COUT + ch0) = v;
-          s[0] += v.x; s[1] += v.y; s[2] += v.z; s[3] += v.w;
-          s2[0] += v.x * v.x; s2[1] += v.y * v.y; s2[2] += v.z * v.z; s2[3] += v.w * v.w;
+        for (int i = 0; i < 8; ++i) {
+          const int row = 8 * ro + i;
+          if (row < kL) {
+            float4 v;
+            v.x = fmaxf(acc[i][0], 0.f); v.y = fmaxf(acc[i][1], 0.f);
+            v.z = fmaxf(acc[i][2], 0.f); v.w = fmaxf(acc[i][3], 0.f);
+            *reinterpret_cast<float4*>(out + ((size_t)win * kL + row) * COUT + ch0) = v;
+            s[0] += v.x; s[1] += v.y; s[2] += v.z; s[3] += v.w;
+            s2[0] += v.x * v.x; s2[1] += v.y * v.y; s2[2] += v.z * v.z; s2[3] += v.w * v.w;
+          }
         }
       }
       if (stats != nullptr) {
-        if (threadIdx.x < 64) ssum[threadIdx.x] = 0ull;
+        ssum[threadIdx.x] = 0ull;
         __syncthreads();
+        if (active) {
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          atomicAdd(&ssum[(tx * 4 + q) * 2 + 0], (unsigned long long)__double2ll_rn((double)s[q] * kStatScale));
-          atomicAdd(&ssum[(tx * 4 + q) * 2 + 1], (unsigned long long)__double2ll_rn((double)s2[q] * kStatScale));
+          for (int q = 0; q < 4; ++q) {
+            atomicAdd(&ssum[((th * 32) + tx * 4 + q) * 2 + 0], (unsigned long long)__double2ll_rn((double)s[q] * kStatScale));
+            atomicAdd(&ssum[((th * 32) + tx * 4 + q) * 2 + 1], (unsigned long long)__double2ll_rn((double)s2[q] * kStatScale));
+          }
         }
         __syncthreads();
-        if (threadIdx.x < 64)
-          atomicAdd(reinterpret_cast<unsigned long long*>(stats) + (size_t)(ct * 32) * 2 + threadIdx.x, ssum[threadIdx.x]);
+        if (ct0 * 32 + (int)(threadIdx.x >> 1) < COUT)
+          atomicAdd(reinterpret_cast<unsigned long long*>(stats) + (size_t)(ct0 * 32) * 2 + threadIdx.x, ssum[threadIdx.x]);
         __syncthreads();
       }
     }
@@ -225,8 +243,7 @@ __global__ void head_kernel(const float* __restrict__ act, const float* __restri
 template <int CIN, int COUT, int K>
 static int launch_conv(const float* in, const float* w, const float* b, float* out, double* stats, int64_t n,
                        cudaStream_t s) {
-  constexpr int H = (K - 1) / 2;
-  const size_t smem = ((size_t)(kL + 2 * H + 4) * (CIN + 1) + 2 + 128) * sizeof(float);
+  const size_t smem = ((size_t)CIN * conv_row_pitch<K>() + 2 + 256) * sizeof(float);
   if (smem > 48 * 1024)
     UQK_CUDA(cudaFuncSetAttribute(conv_relu_kernel<CIN, COUT, K>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)smem));

@@ -209,15 +209,20 @@ int uqk_patient_reduce(const float* variance_dev, const float* entropy_dev, cons
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   int* d_err = nullptr;
   UQK_CUDA(cudaMallocAsync(&d_err, sizeof(int), s));
-  UQK_CUDA(cudaMemsetAsync(d_err, 0, sizeof(int), s));
-  const int grid = (int)std::min<int64_t>(n_patients, 148 * 8);
-  patient_reduce_kernel<<<grid, kPatThreads, 0, s>>>(variance_dev, entropy_dev, true_label_dev, pred_label_dev,
-                                                     seg_offsets_dev, n_patients, out_dev, d_err);
-  UQK_LAUNCH_CHECK();
   int herr = 0;
-  UQK_CUDA(cudaMemcpyAsync(&herr, d_err, sizeof(int), cudaMemcpyDeviceToHost, s));
-  UQK_CUDA(cudaStreamSynchronize(s));
-  UQK_CUDA(cudaFreeAsync(d_err, s));
+  cudaError_t e = cudaMemsetAsync(d_err, 0, sizeof(int), s);
+  if (e == cudaSuccess) {
+    const int grid = (int)std::min<int64_t>(n_patients, 148 * 8);
+    patient_reduce_kernel<<<grid, kPatThreads, 0, s>>>(variance_dev, entropy_dev, true_label_dev, pred_label_dev,
+                                                       seg_offsets_dev, n_patients, out_dev, d_err);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    e = cudaGetLastError();
+  }
+  // SYNCHRONOUS by contract (include/uqk.h): the oversize-segment flag is read back before the call returns
+  if (e == cudaSuccess) e = cudaMemcpyAsync(&herr, d_err, sizeof(int), cudaMemcpyDeviceToHost, s);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+  cudaFreeAsync(d_err, s);                      // on every path
+  if (e != cudaSuccess) { set_error("uqk_patient_reduce: %s", cudaGetErrorString(e)); return UQK_E_CUDA; }
   if (herr) { set_error("a patient has more than %d windows; segment does not fit the in-kernel sort", kPatMaxSeg); return UQK_E_SHAPE; }
   return UQK_OK;
 }
@@ -229,22 +234,25 @@ int uqk_bootstrap(const float* variance_dev, const float* total_entropy_dev, con
   if (!variance_dev || !total_entropy_dev || !expected_entropy_dev || !mutual_info_dev || !y_dev || !idx_dev || !out_dev) {
     set_error("NULL argument"); return UQK_E_BADARG;
   }
+  if (n_boot > 65535) { set_error("n_boot=%d exceeds 65535 iterations per call (grid dimension); split the call", n_boot); return UQK_E_SHAPE; }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   double* sums = nullptr;
   BootRow* rows = nullptr;
   UQK_CUDA(cudaMallocAsync(&sums, sizeof(double) * 8 * n_boot, s));
-  UQK_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&rows), sizeof(BootRow) * (size_t)n_windows, s));
-  UQK_CUDA(cudaMemsetAsync(sums, 0, sizeof(double) * 8 * n_boot, s));
-  bootstrap_pack_kernel<<<(int)std::min<int64_t>((n_windows + 255) / 256, 148 * 8), 256, 0, s>>>(
-      variance_dev, total_entropy_dev, expected_entropy_dev, mutual_info_dev, y_dev, n_windows, rows);
-  UQK_LAUNCH_CHECK();
-  const int gx = (int)std::max<int64_t>(1, std::min<int64_t>((n_windows + kBootThreads * 8 - 1) / (kBootThreads * 8), 148));
-  bootstrap_rows_kernel<<<dim3(gx, n_boot), kBootThreads, 0, s>>>(rows, idx_dev, n_windows, sums);
-  UQK_LAUNCH_CHECK();
-  bootstrap_finalize_kernel<<<(n_boot + 127) / 128, 128, 0, s>>>(sums, n_boot, n_windows, out_dev);
-  UQK_LAUNCH_CHECK();
-  UQK_CUDA(cudaFreeAsync(rows, s));
-  UQK_CUDA(cudaFreeAsync(sums, s));
+  cudaError_t e = cudaMallocAsync(reinterpret_cast<void**>(&rows), sizeof(BootRow) * (size_t)n_windows, s);
+  if (e == cudaSuccess) e = cudaMemsetAsync(sums, 0, sizeof(double) * 8 * n_boot, s);
+  if (e == cudaSuccess) {
+    bootstrap_pack_kernel<<<(int)std::min<int64_t>((n_windows + 255) / 256, 148 * 8), 256, 0, s>>>(
+        variance_dev, total_entropy_dev, expected_entropy_dev, mutual_info_dev, y_dev, n_windows, rows);
+    const int gx = (int)std::max<int64_t>(1, std::min<int64_t>((n_windows + kBootThreads * 8 - 1) / (kBootThreads * 8), 148));
+    bootstrap_rows_kernel<<<dim3(gx, n_boot), kBootThreads, 0, s>>>(rows, idx_dev, n_windows, sums);
+    bootstrap_finalize_kernel<<<(n_boot + 127) / 128, 128, 0, s>>>(sums, n_boot, n_windows, out_dev);
+    g_launches.fetch_add(3, std::memory_order_relaxed);
+    e = cudaGetLastError();
+  }
+  if (rows) cudaFreeAsync(rows, s);             // the stream-ordered scratch is released on every path
+  cudaFreeAsync(sums, s);
+  if (e != cudaSuccess) { set_error("uqk_bootstrap: %s", cudaGetErrorString(e)); return UQK_E_CUDA; }
   return UQK_OK;
 }
 

@@ -308,21 +308,25 @@ class Engine:
                                               it.data_ptr(), int(b), int(n), out.data_ptr(), self._stream()), "uqk_bootstrap")
             return out.cpu().numpy()
 
-    def patient_reduce(self, variance, entropy, y_true, y_pred, seg_offsets) -> np.ndarray:
-        """Per-patient rows (P,8) float64 from patient-sorted columns (aggregate_patient_uq_metrics.py:34-46)."""
+    def patient_reduce(self, variance, entropy, y_true, y_pred, seg_offsets, device_out: bool = False):
+        """Per-patient rows (P,8) float64 from patient-sorted columns (aggregate_patient_uq_metrics.py:34-46).
+        Columns may be host arrays or CUDA tensors of this device (float32 / int32 / int64 offsets)."""
         with torch.cuda.device(self.device):
             dev = self._dev()
-            v = torch.as_tensor(np.ascontiguousarray(variance, dtype=np.float32)).to(dev)
-            e = torch.as_tensor(np.ascontiguousarray(entropy, dtype=np.float32)).to(dev)
-            yt = torch.as_tensor(np.ascontiguousarray(y_true).astype(np.int32)).to(dev)
-            yp = torch.as_tensor(np.ascontiguousarray(y_pred).astype(np.int32)).to(dev)
-            seg = torch.as_tensor(np.ascontiguousarray(seg_offsets, dtype=np.int64)).to(dev)
+
+            def col(a, np_dtype, t_dtype):
+                if isinstance(a, torch.Tensor):
+                    return a.to(dev, dtype=t_dtype).contiguous()
+                return torch.as_tensor(np.ascontiguousarray(np.asarray(a).astype(np_dtype))).to(dev)
+            v, e = col(variance, np.float32, torch.float32), col(entropy, np.float32, torch.float32)
+            yt, yp = col(y_true, np.int32, torch.int32), col(y_pred, np.int32, torch.int32)
+            seg = col(seg_offsets, np.int64, torch.int64)
             p = seg.shape[0] - 1
             out = torch.empty((p, 8), dtype=torch.float64, device=dev)
             _lib.check(self.lib.uqk_patient_reduce(v.data_ptr(), e.data_ptr(), yt.data_ptr(), yp.data_ptr(),
                                                    seg.data_ptr(), int(p), out.data_ptr(), self._stream()),
                        "uqk_patient_reduce")
-            return out.cpu().numpy()
+            return out if device_out else out.cpu().numpy()
 
     def standardize(self, x_raw, device_out: bool = False):
         """Per-window z-score of raw (N,60,4) windows (prepare_numpy_datasets.py:83-95), same dtype out."""

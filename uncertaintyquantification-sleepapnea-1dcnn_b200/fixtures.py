@@ -10,7 +10,8 @@ import numpy as np
 from . import model, synthetic
 
 
-def build_fixture_dir(root: str, n_unbalanced: int = 2000, n_rus: int = 500, n_members: int = 5, seed: int = 2025):
+def build_fixture_dir(root: str, n_unbalanced: int = 2000, n_rus: int = 500, n_members: int = 5, seed: int = 2025,
+                      n_global_members: int = 0):
     ds = os.path.join(root, "processed_datasets")
     os.makedirs(ds, exist_ok=True)
     xu = synthetic.make_windows(n_unbalanced, seed=seed)
@@ -25,6 +26,12 @@ def build_fixture_dir(root: str, n_unbalanced: int = 2000, n_rus: int = 500, n_m
     model.synthetic_model(0).save(os.path.join(root, "AlCNN1D_no_pool.keras"))   # analyze_mcd_patient_level.py:19
     ens = os.path.join(root, "models", "ensemble_cnn_no_pool")
     os.makedirs(ens, exist_ok=True)
-    for i in range(n_members):                                                # analyze_de_patient_level.py:45 (i+5)
-        model.synthetic_model(i).save(os.path.join(ens, f"AlCNN_smote_seed{i + 5}.keras"))
+    members = [model.synthetic_model(i) for i in range(n_members)]
+    for i, m in enumerate(members):                                           # analyze_de_patient_level.py:45 (i+5)
+        m.save(os.path.join(ens, f"AlCNN_smote_seed{i + 5}.keras"))
+    if n_global_members:                                                      # evaluate_de_global.py:11,18,29 (seed0..19)
+        glob = os.path.join(root, "models", "ensemble_cnn")
+        os.makedirs(glob, exist_ok=True)
+        for i in range(n_global_members):
+            members[i % len(members)].save(os.path.join(glob, f"AlCNN_smote_seed{i}.keras"))
     return root
