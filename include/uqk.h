@@ -33,7 +33,7 @@ extern "C" {
 #define UQK_E_CUDA (-4)
 #define UQK_E_STATE (-5)  /* e.g. model not set, statistics not calibrated */
 #define UQK_E_NOMEM (-6)
-#define UQK_E_KERNEL (-7) /* device-side watchdog / self-check failed */
+#define UQK_E_KERNEL (-7) /* device-side watchdog / self-check failed, see uqk_poll_error */
 
 /* dtype of the window tensor x (N,60,4): prepare_numpy_datasets.py:93,233 saves float64 */
 #define UQK_F32 0
@@ -151,6 +151,20 @@ int uqk_de(uqk_handle* h, const void* x_dev, int x_dtype, int64_t n_windows, int
 int uqk_refine_band(uqk_handle* h, int mode_de, const void* x_dev, int x_dtype, int64_t n_windows, int n_groups,
                     uint64_t seed, int bn_mode, int64_t window_index_base, const uint32_t* mask_bits_dev, float delta,
                     float* probs_dev, const uqk_metrics_out* out, int64_t* n_refined_host, void* stream);
+
+/* Device-side self-checks.  The kernels report through a flag in mapped pinned host memory, so the reason survives even
+ * a device trap.  Every compute entry point of the handle checks the flag first and returns UQK_E_KERNEL when it is
+ * set; call uqk_poll_error after synchronising a stream to learn about a failure of work that was still in flight.
+ *   codes 1..23: barrier watchdog -- a warp of a fused kernel waited ~2 s (4e9 clock ticks) at one mbarrier, which
+ *     only a protocol fault can cause; the kernel then TRAPS, the CUDA context of the process is lost (every later
+ *     CUDA call fails) and the process must be restarted.  The budget is fixed: under cuda-gdb, a sanitizer or heavy
+ *     time-slicing a healthy kernel could exceed it.
+ *   code 50: a batch-statistics accumulator (2^-24 fixed point in 64 bits) overflowed -- sum of squares of one
+ *     channel above 5.5e11; no trap, the flag is cleared when reported, the results of that call are invalid.
+ * uqk_debug_trip_watchdog (tests): runs a kernel that waits on a barrier nobody signals; returns UQK_E_KERNEL and
+ * leaves the context unusable -- call it only in a process that exits afterwards. */
+int uqk_poll_error(uqk_handle* h);
+int uqk_debug_trip_watchdog(uqk_handle* h);
 
 /* Stand-alone reductions over an existing (n_passes, N) float32 probability tensor.
  * Replaces uq_evaluation_dist (uq_techniques.py:40-112) and the inline metrics. */

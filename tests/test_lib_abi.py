@@ -92,3 +92,26 @@ def test_model_container_and_shim(tmp_path, uqk):
     bad.write_bytes(b"not a zip")
     with pytest.raises(ValueError):
         model.load_model(str(bad))
+
+
+def test_product_never_imports_the_oracle():
+    """oracle/ is test infrastructure: nothing under the package (nor the ctypes layer) may import it; bench.py may do
+    so only inside its CPU-baseline legs."""
+    import re
+    pat = re.compile(r"^\s*(from\s+oracle\b|import\s+oracle\b|from\s+tests\b|import\s+fake_engine\b)", re.M)
+    pkg_dir = os.path.join(ROOT, PKG_NAME)
+    for dirpath, _, files in os.walk(pkg_dir):
+        for f in files:
+            if f.endswith(".py"):
+                text = open(os.path.join(dirpath, f)).read()
+                assert not pat.search(text), f"{os.path.join(dirpath, f)} imports test infrastructure"
+    bench = open(os.path.join(ROOT, "bench.py")).read()
+    for m in pat.finditer(bench):
+        before = bench[:m.start()]
+        fn = re.findall(r"^def (\w+)\(", before, re.M)[-1]
+        assert fn in ("cpu_mcd_sample", "cpu_config0_sample"), f"bench.py imports the oracle inside {fn}()"
+    import subprocess, sys
+    code = (f"import sys, importlib; sys.path.insert(0, {ROOT!r}); importlib.import_module({PKG_NAME!r} + '.engine'); "
+            f"importlib.import_module({PKG_NAME!r} + '.model'); importlib.import_module({PKG_NAME!r} + '.sharding'); "
+            "assert not [m for m in sys.modules if m == 'oracle' or m.startswith('oracle.')], 'oracle got imported'")
+    subprocess.run([sys.executable, "-c", code], check=True)

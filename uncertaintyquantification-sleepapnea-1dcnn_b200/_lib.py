@@ -21,6 +21,7 @@ EXPORTS = [
     "uqk_calibrate", "uqk_get_bn_stats", "uqk_set_bn_stats", "uqk_mcd", "uqk_de", "uqk_reduce",
     "uqk_patient_reduce", "uqk_standardize", "uqk_bootstrap", "uqk_bootstrap_noalloc", "uqk_launch_count", "uqk_set_option",
     "uqk_set_stats_exchange", "uqk_write_detail_csv", "uqk_window_summary", "uqk_refine_band",
+    "uqk_poll_error", "uqk_debug_trip_watchdog",
 ]
 
 # int fn(void* user, long long* stats_dev, int count, void* stream)  -- include/uqk.h uqk_stats_exchange_fn
@@ -65,6 +66,8 @@ def load() -> C.CDLL:
     lib.uqk_de.argtypes = [vp, vp, i32, i64, i32, i32, vp, C.POINTER(MetricsOut), vp]
     lib.uqk_reduce.argtypes = [vp, i32, i64, C.POINTER(MetricsOut), vp]
     lib.uqk_refine_band.argtypes = [vp, i32, vp, i32, i64, i32, u64, i32, i64, vp, C.c_float, vp, C.POINTER(MetricsOut), C.POINTER(i64), vp]
+    lib.uqk_poll_error.argtypes = [vp]
+    lib.uqk_debug_trip_watchdog.argtypes = [vp]
     lib.uqk_patient_reduce.argtypes = [vp, vp, vp, vp, vp, i64, vp, vp]
     lib.uqk_standardize.argtypes = [vp, i32, i64, vp, vp]
     lib.uqk_bootstrap.argtypes = [vp, vp, vp, vp, vp, vp, i32, i64, vp, vp]

@@ -35,7 +35,8 @@ struct Handle {
   double* d_stats = nullptr;      // 6 x 256 x 2
   float* d_affine = nullptr;      // 6 x 2 x 256
   double* d_accum = nullptr;      // 2 x 6 x 256
-  int* d_err = nullptr;
+  int* d_err = nullptr;           // device alias of h_err
+  int* h_err = nullptr;           // watchdog / self-check flag in MAPPED PINNED HOST memory: readable after a device trap
   // grow-on-demand workspace of the layer-synchronous path
   float* d_x32 = nullptr; size_t x32_cap = 0;
   float* d_act[2] = {nullptr, nullptr}; size_t act_cap = 0;
@@ -73,6 +74,39 @@ static int ensure(float** p, size_t* cap, size_t need_floats) {
   }
   *cap = need_floats;
   return UQK_OK;
+}
+
+// Device-side self-checks report through h->h_err (mapped host memory): barrier watchdog codes 1..23 (the kernel then
+// traps: the CUDA context is lost), 50 = a batch-statistics accumulator overflowed its 2^-24 fixed point.
+static int poll_kernel_flag(Handle* h) {
+  const int code = h->h_err ? *reinterpret_cast<volatile int*>(h->h_err) : 0;
+  if (code == 0) return UQK_OK;
+  if (code == 50) {
+    *reinterpret_cast<volatile int*>(h->h_err) = 0;        // reported once; the handle stays usable (no trap happened)
+    set_error("device self-check %d: a batch-statistics sum overflowed its fixed-point accumulator (activations too large); "
+              "results of that call are invalid", code);
+  } else
+    set_error("device watchdog %d: a kernel waited ~2 s on barrier class %d and trapped (protocol fault); the CUDA context of this "
+              "process is lost -- restart the process", code, code);
+  return UQK_E_KERNEL;
+}
+
+// waits ~2 s on a barrier nobody signals: exercises the watchdog path (tests only; the context is lost afterwards)
+__global__ void trip_watchdog_kernel(int* err_flag) {
+  __shared__ unsigned long long bar;
+  const uint32_t b = (uint32_t)__cvta_generic_to_shared(&bar);
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(b));
+  long long t0 = clock64();
+  for (;;) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\tselp.b32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(b) : "memory");
+    if (ok) return;
+    if (clock64() - t0 > 4000000000ll) {
+      *reinterpret_cast<volatile int*>(err_flag) = 99;
+      __threadfence_system();
+      __trap();
+    }
+  }
 }
 
 __global__ void average_stats_kernel(const double* __restrict__ accum, int n_passes, float* __restrict__ frozen) {
@@ -119,6 +153,7 @@ static int run_layersync(Handle* h, int member0, const void* x, int x_dtype, int
       p.mask_bits = mask_bits ? mask_bits + ((size_t)g * (win_ids ? n_call : n) + (win_ids ? 0 : c0)) * kBlocks * kL * 8 : nullptr;
       p.win_ids = win_ids ? win_ids + c0 : nullptr;
       if (win_ids) p.window_base = window_base;
+      p.err_flag = h->d_err;
       p.affine_tab = affine_tabs ? affine_tabs + (size_t)g * kTableFloats : nullptr;
       p.frozen_mean = h->d_frozen; p.frozen_var = h->d_frozen + kBlocks * kMaxCh;
       p.stats_scratch = h->d_stats; p.affine_scratch = h->d_affine;
@@ -211,7 +246,7 @@ static int run_exact_sweeps(Handle* h, const void* x, int x_dtype, int64_t n, in
       set_error("batch-statistics exchange callback failed at layer %d", k);
       return UQK_E_STATE;
     }
-    if ((rc = exact_layer_tables(h->d_blobs, stats, (double)stat_windows * kL, k, n_passes, h->d_tables_pass, s))) return rc;
+    if ((rc = exact_layer_tables(h->d_blobs, stats, (double)stat_windows * kL, k, n_passes, h->d_tables_pass, h->d_err, s))) return rc;
     if (frozen && (rc = exact_layer_average(stats, (double)stat_windows * kL, k, n_passes, frozen, s))) return rc;
   }
   return UQK_OK;
@@ -309,9 +344,10 @@ int uqk_create(int device, uqk_handle** out) {
   UQK_CUDA(cudaMalloc(&h->d_stats, sizeof(double) * kBlocks * kMaxCh * 2));
   UQK_CUDA(cudaMalloc(&h->d_affine, sizeof(float) * kBlocks * 2 * kMaxCh));
   UQK_CUDA(cudaMalloc(&h->d_accum, sizeof(double) * 2 * kBlocks * kMaxCh));
-  UQK_CUDA(cudaMalloc(&h->d_err, sizeof(int)));
+  UQK_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&h->h_err), sizeof(int), cudaHostAllocMapped));
+  *h->h_err = 0;
+  UQK_CUDA(cudaHostGetDevicePointer(reinterpret_cast<void**>(&h->d_err), h->h_err, 0));
   UQK_CUDA(cudaMalloc(&h->d_dbg, sizeof(float) * kBlocks * 128 * 256));
-  UQK_CUDA(cudaMemset(h->d_err, 0, sizeof(int)));
   UQK_CUDA(cudaMemset(h->d_dbg, 0, sizeof(float) * kBlocks * 128 * 256));
   *out = reinterpret_cast<uqk_handle*>(h);
   return UQK_OK;
@@ -323,8 +359,9 @@ int uqk_destroy(uqk_handle* hh) {
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
   void* ptrs[] = {h->d_blobs, h->d_packed, h->d_packed_pair, h->d_tables_inf, h->d_table_mcd, h->d_frozen, h->d_stats, h->d_affine,
-                  h->d_accum, h->d_err, h->d_tables_all, h->d_band_idx, h->d_band_count, h->d_x32, h->d_act[0], h->d_act[1], h->d_probs_tmp, h->d_dbg, h->d_tables_pass, h->d_stats_pass, h->d_head_sum, h->d_head_cnt, h->d_ckpt, h->d_ckpt2};
+                  h->d_accum, h->d_tables_all, h->d_band_idx, h->d_band_count, h->d_x32, h->d_act[0], h->d_act[1], h->d_probs_tmp, h->d_dbg, h->d_tables_pass, h->d_stats_pass, h->d_head_sum, h->d_head_cnt, h->d_ckpt, h->d_ckpt2};
   for (void* p : ptrs) if (p) cudaFree(p);
+  if (h->h_err) cudaFreeHost(h->h_err);
   cudaGetLastError();
   delete h;
   return UQK_OK;
@@ -379,6 +416,7 @@ int uqk_forward_det(uqk_handle* hh, int member, const void* x_dev, int x_dtype, 
                     float* probs_dev, void* stream) {
   if (!hh) { set_error("handle is NULL"); return UQK_E_BADARG; }
   Handle* h = reinterpret_cast<Handle*>(hh);
+  if (int rc_flag = poll_kernel_flag(h)) return rc_flag;
   if (h->n_members == 0) { set_error("uqk_set_model has not been called"); return UQK_E_STATE; }
   if (member < 0 || member >= h->n_members) { set_error("member %d out of range", member); return UQK_E_BADARG; }
   int rc = check_x(x_dev, x_dtype, n);
@@ -398,6 +436,7 @@ int uqk_calibrate(uqk_handle* hh, const void* x_dev, int x_dtype, int64_t n, int
                   void* stream) {
   if (!hh) { set_error("handle is NULL"); return UQK_E_BADARG; }
   Handle* h = reinterpret_cast<Handle*>(hh);
+  if (int rc_flag = poll_kernel_flag(h)) return rc_flag;
   if (h->n_members == 0) { set_error("uqk_set_model has not been called"); return UQK_E_STATE; }
   const bool exchanging = h->xchg != nullptr;
   const int64_t n_all = exchanging ? h->xchg_global_n : n;      // windows the statistics are taken over (all ranks)
@@ -466,6 +505,7 @@ int uqk_mcd(uqk_handle* hh, const void* x_dev, int x_dtype, int64_t n, int n_pas
             const uqk_metrics_out* out, void* stream) {
   if (!hh) { set_error("handle is NULL"); return UQK_E_BADARG; }
   Handle* h = reinterpret_cast<Handle*>(hh);
+  if (int rc_flag = poll_kernel_flag(h)) return rc_flag;
   if (h->n_members == 0) { set_error("uqk_set_model has not been called"); return UQK_E_STATE; }
   if (n_passes < 1 || n_passes > 8192) { set_error("n_passes must be in 1..8192"); return UQK_E_BADARG; }
   if (bn_mode != UQK_BN_INFERENCE && bn_mode != UQK_BN_BATCH && bn_mode != UQK_BN_CALIBRATED) {
@@ -506,6 +546,7 @@ int uqk_de(uqk_handle* hh, const void* x_dev, int x_dtype, int64_t n, int n_memb
            const uqk_metrics_out* out, void* stream) {
   if (!hh) { set_error("handle is NULL"); return UQK_E_BADARG; }
   Handle* h = reinterpret_cast<Handle*>(hh);
+  if (int rc_flag = poll_kernel_flag(h)) return rc_flag;
   if (h->n_members == 0) { set_error("uqk_set_model has not been called"); return UQK_E_STATE; }
   if (n_members < 1 || n_members > h->n_members) {
     set_error("n_members=%d but the handle holds %d members", n_members, h->n_members); return UQK_E_BADARG;
@@ -535,6 +576,7 @@ int uqk_refine_band(uqk_handle* hh, int mode_de, const void* x_dev, int x_dtype,
                     const uqk_metrics_out* out, int64_t* n_refined_host, void* stream) {
   if (!hh) { set_error("handle is NULL"); return UQK_E_BADARG; }
   Handle* h = reinterpret_cast<Handle*>(hh);
+  if (int rc_flag = poll_kernel_flag(h)) return rc_flag;
   if (n_refined_host) *n_refined_host = 0;
   if (h->n_members == 0) { set_error("uqk_set_model has not been called"); return UQK_E_STATE; }
   if (!out || !out->mean_pred) { set_error("uqk_refine_band needs out->mean_pred (the result of the bf16 call)"); return UQK_E_BADARG; }
@@ -576,6 +618,21 @@ int uqk_refine_band(uqk_handle* hh, int mode_de, const void* x_dev, int x_dtype,
   if ((rc = launch_reduce(h->d_probs_tmp, n_groups, m, to_metrics(out), s, idx))) return rc;
   if (probs_dev && (rc = launch_scatter_probs(h->d_probs_tmp, idx, n_groups, m, n, probs_dev, s))) return rc;
   return UQK_OK;
+}
+
+int uqk_poll_error(uqk_handle* hh) {
+  if (!hh) { set_error("handle is NULL"); return UQK_E_BADARG; }
+  return poll_kernel_flag(reinterpret_cast<Handle*>(hh));
+}
+
+int uqk_debug_trip_watchdog(uqk_handle* hh) {
+  if (!hh) { set_error("handle is NULL"); return UQK_E_BADARG; }
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  UQK_CUDA(cudaSetDevice(h->device));
+  trip_watchdog_kernel<<<1, 1>>>(h->d_err);
+  cudaDeviceSynchronize();      // returns an error after the trap; the flag in host memory tells why
+  cudaGetLastError();
+  return poll_kernel_flag(h);
 }
 
 int uqk_reduce(const float* probs_dev, int n_passes, int64_t n, const uqk_metrics_out* out, void* stream) {

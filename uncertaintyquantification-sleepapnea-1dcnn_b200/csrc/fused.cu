@@ -134,11 +134,13 @@ int build_tables(const float* blob_dev, const float* mean, const float* var, int
 // bn_finalize_kernel of the layer-synchronous path.  grid = n_groups, block >= cout.
 __global__ void exact_layer_tables_kernel(const float* __restrict__ blob, BlobOffsets off,
                                           const unsigned long long* __restrict__ stats, double count, int layer,
-                                          float* __restrict__ tables) {
+                                          float* __restrict__ tables, int* __restrict__ err_flag) {
   const int g = blockIdx.x, c = threadIdx.x;
   const BlockDef b = block_def(layer);
   if (c >= b.cout) return;
   const long long* q = reinterpret_cast<const long long*>(stats) + (size_t)g * 2 * kMaxCh;
+  // sums of post-ReLU values are non-negative: a set sign bit means the 2^-24 fixed point wrapped (sum of squares > 5.5e11)
+  if ((q[2 * c] < 0 || q[2 * c + 1] < 0) && err_flag) *reinterpret_cast<volatile int*>(err_flag) = 50;
   const double mu = (double)q[2 * c] / kFusedStatScale / count;
   double var = (double)q[2 * c + 1] / kFusedStatScale / count - mu * mu;   // biased variance (Keras training mode)
   if (var < 0) var = 0;
@@ -238,8 +240,8 @@ int exact_replicate_tables(const float* base_table, int n_groups, float* tables,
 }
 
 int exact_layer_tables(const float* blob_dev, const unsigned long long* stats, double count, int layer, int n_groups,
-                       float* tables, cudaStream_t s) {
-  exact_layer_tables_kernel<<<n_groups, kMaxCh, 0, s>>>(blob_dev, blob_offsets(), stats, count, layer, tables);
+                       float* tables, int* err_flag, cudaStream_t s) {
+  exact_layer_tables_kernel<<<n_groups, kMaxCh, 0, s>>>(blob_dev, blob_offsets(), stats, count, layer, tables, err_flag);
   UQK_LAUNCH_CHECK();
   return UQK_OK;
 }

@@ -76,8 +76,9 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
   return ok != 0;
 }
 // Bounded wait: a protocol bug must end the kernel with an error, never hang the GPU.
+// err_flag points into MAPPED PINNED HOST memory (api.cu): the code survives the trap, which poisons the CUDA context.
 static __device__ __noinline__ void mbar_timeout(int* err_flag, int code) {
-  if (err_flag) atomicExch(err_flag, code);
+  if (err_flag) *reinterpret_cast<volatile int*>(err_flag) = code;
   __threadfence_system();
   __trap();
 }
@@ -162,10 +163,14 @@ __device__ __forceinline__ uint32_t mapa_shared(uint32_t addr, uint32_t rank) {
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
   return r;
 }
-__device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_addr) {
-  // relaxed: a release at cluster scope costs a MEMBAR.ALL.GPU per arrive; the data this signal publishes lives in
-  // shared memory and was already fenced to the async proxy (fence.proxy.async) / written by TMA before the arrive
-  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+// Peer -> leader signal of a CTA pair.  strong = false (default): relaxed at cluster scope -- the data this signal
+// publishes lives in the peer's shared memory, was fenced to the async proxy (fence.proxy.async) or written by TMA
+// before the arrive, and is read by the PEER SM's own tensor core; a release at cluster scope costs a MEMBAR.ALL.GPU
+// per arrive.  strong = true (variant bit 0): release here / acquire in the leader's wait, the pairing the PTX memory
+// model spells out; tests/test_gpu_cluster_sync.py compares the two bit for bit and DESIGN.md records the cost.
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_addr, bool strong = false) {
+  if (strong) asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+  else asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 __device__ __forceinline__ void umma_bf16_2cta(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
                                                uint32_t accumulate) {
@@ -451,6 +456,7 @@ __device__ __forceinline__ void issue_layer(uint32_t s_base, uint32_t tmem_base,
 struct EpiCtx {
   uint32_t act_row, taddr, c0w, k0, k1, bar_acc, bar_act;
   DropTie tie = {0u, 0u};    // dropout tie-break bytes of this thread's (window, pass, row, column half), see common.cuh
+  bool strong_sync = false;  // pair kernels: release / acquire cluster signalling (variant bit 0)
   uint32_t remote_act = 0;   // pair kernels, peer CTA: cluster address of the leader's "peer activations ready" barrier
   int t, colhalf, tid_t, we, lane, quarter, slot_w, tl;
   bool row_valid;
@@ -471,7 +477,7 @@ __device__ __forceinline__ void epi_signal_act(const EpiCtx& c) {
     if (c.lane == 0) mbar_arrive(c.bar_act);
   } else {
     named_bar_sync(1 + c.tl, EPI_THREADS);
-    if (c.tid_t == 0) mbar_arrive_remote(c.remote_act);
+    if (c.tid_t == 0) mbar_arrive_remote(c.remote_act, c.strong_sync);
   }
 }
 
@@ -1104,6 +1110,7 @@ fused_forward_kernel(const FusedArgs a) {
     c.bar_act = bar_act + 8 * c.tl;
     c.k0 = a.k0; c.k1 = a.k1;
     c.err_flag = a.err_flag;
+    c.strong_sync = (a.variant & 1) != 0;
     uint32_t n_acc = 0;
 
     for (long long unit = blockIdx.x; unit < a.n_units; unit += gridDim.x) {
@@ -1195,27 +1202,47 @@ struct PairCfg {
   static constexpr int oProbs = oAlo + 4 * 392;    // probs[2][n_groups]
 };
 
-__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity, int* err_flag, int code) {
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity, int* err_flag, int code, bool strong = false) {
   long long t0 = 0;
   for (;;) {
     uint32_t ok;
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t.reg .b32 n;\n\t"
-        "mov.u32 n, 2048;\n"
-        "UQK_TRY:\n\t"
-        "mbarrier.try_wait.parity.relaxed.cluster.shared::cta.b64 p, [%1], %2, %3;\n\t"
-        "@p bra UQK_DONE;\n\t"
-        "sub.u32 n, n, 1;\n\t"
-        "setp.ne.u32 p, n, 0;\n\t"
-        "@p bra UQK_TRY;\n\t"
-        "mov.u32 %0, 0;\n\t"
-        "bra UQK_END;\n"
-        "UQK_DONE:\n\t"
-        "mov.u32 %0, 1;\n"
-        "UQK_END:\n\t}"
-        : "=r"(ok)
-        : "r"(bar), "r"(parity), "r"(20000u)
-        : "memory");
+    if (strong) {
+      asm volatile(
+          "{\n\t.reg .pred p;\n\t.reg .b32 n;\n\t"
+          "mov.u32 n, 2048;\n"
+          "UQK_TRYA:\n\t"
+          "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2, %3;\n\t"
+          "@p bra UQK_DONEA;\n\t"
+          "sub.u32 n, n, 1;\n\t"
+          "setp.ne.u32 p, n, 0;\n\t"
+          "@p bra UQK_TRYA;\n\t"
+          "mov.u32 %0, 0;\n\t"
+          "bra UQK_ENDA;\n"
+          "UQK_DONEA:\n\t"
+          "mov.u32 %0, 1;\n"
+          "UQK_ENDA:\n\t}"
+          : "=r"(ok)
+          : "r"(bar), "r"(parity), "r"(20000u)
+          : "memory");
+    } else {
+      asm volatile(
+          "{\n\t.reg .pred p;\n\t.reg .b32 n;\n\t"
+          "mov.u32 n, 2048;\n"
+          "UQK_TRY:\n\t"
+          "mbarrier.try_wait.parity.relaxed.cluster.shared::cta.b64 p, [%1], %2, %3;\n\t"
+          "@p bra UQK_DONE;\n\t"
+          "sub.u32 n, n, 1;\n\t"
+          "setp.ne.u32 p, n, 0;\n\t"
+          "@p bra UQK_TRY;\n\t"
+          "mov.u32 %0, 0;\n\t"
+          "bra UQK_END;\n"
+          "UQK_DONE:\n\t"
+          "mov.u32 %0, 1;\n"
+          "UQK_END:\n\t}"
+          : "=r"(ok)
+          : "r"(bar), "r"(parity), "r"(20000u)
+          : "memory");
+    }
     if (ok) return;
     const long long now = clock64();
     if (t0 == 0) t0 = now;
@@ -1227,20 +1254,21 @@ template <int L, int NSLOTS, typename Cfg>
 __device__ __forceinline__ void issue_layer_pair(uint32_t s_base, uint32_t tmem_base, const uint32_t* s_alo,
                                                  uint32_t bar_full, uint32_t bar_empty, uint32_t bar_peer_full,
                                                  uint32_t bar_acc, uint32_t bar_act, uint32_t bar_peer_act, uint32_t& it,
-                                                 uint32_t& n_act, int* err_flag, bool no_mma, uint32_t a_tile = 0u) {
+                                                 uint32_t& n_act, int* err_flag, int flags, uint32_t a_tile = 0u) {
+  const bool no_mma = (flags & 8) != 0, strong = (flags & 1) != 0;   // debug switch / release-acquire cluster signalling
   constexpr FusedLayer fl = fused_layer(L);
   constexpr uint32_t kHi = (128u >> 4) | (1u << 14);
   constexpr uint32_t kBLbo = ((uint32_t)((fl.cout / 2) * 16) >> 4) << 16;
   constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(fl.cout >> 3) << 17) | ((256u >> 4) << 24);
   constexpr int kLast = fl.nsteps - (fl.nstages - 1) * fl.sps;
-  mbar_wait_cluster(bar_act, n_act & 1, err_flag, 2);      // 8 local warp arrivals + 1 relayed from the peer
+  mbar_wait_cluster(bar_act, n_act & 1, err_flag, 2, strong);      // 8 local warp arrivals + 1 relayed from the peer
   ++n_act;
   tc_fence_after();
 #pragma unroll 1
   for (int st = 0; st < fl.nstages; ++st, ++it) {
     const int slot = it % NSLOTS;
     const uint32_t ph = (it / NSLOTS) & 1;
-    mbar_wait_cluster(bar_full + 8 * slot, ph, err_flag, 3);   // own half landed (tx) + peer's half (relayed arrive)
+    mbar_wait_cluster(bar_full + 8 * slot, ph, err_flag, 3, strong);   // own half landed (tx) + peer's half (relayed arrive)
     tc_fence_after();
     const int nst = (st == fl.nstages - 1) ? kLast : fl.sps;
     const uint32_t b_lo0 = (((s_base + Cfg::oRing + slot * Cfg::kSlot) >> 4) & 0x3FFFu) | kBLbo;
@@ -1265,16 +1293,16 @@ __device__ __forceinline__ void issue_layer_pair(uint32_t s_base, uint32_t tmem_
 
 template <int L, int NSLOTS>
 __device__ __forceinline__ void relay_layer(uint32_t bar_full, uint32_t bar_act, uint32_t r_peer_full, uint32_t r_peer_act,
-                                            uint32_t& it, uint32_t& n_act, int* err_flag) {
+                                            uint32_t& it, uint32_t& n_act, int* err_flag, bool strong) {
   constexpr FusedLayer fl = fused_layer(L);
   mbar_wait2(bar_act, n_act & 1, err_flag, 22);
   ++n_act;
-  mbar_arrive_remote(r_peer_act);
+  mbar_arrive_remote(r_peer_act, strong);
 #pragma unroll 1
   for (int st = 0; st < fl.nstages; ++st, ++it) {
     const int slot = it % NSLOTS;
     mbar_wait2(bar_full + 8 * slot, (it / NSLOTS) & 1, err_flag, 23);
-    mbar_arrive_remote(r_peer_full + 8 * slot);
+    mbar_arrive_remote(r_peer_full + 8 * slot, strong);
   }
 }
 
@@ -1377,12 +1405,12 @@ fused_pair_kernel(const FusedArgs a) {
       // ---- leader: MMA issuer for the pair
       for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
         for (int g = 0; g < a.n_groups; ++g) {
-          issue_layer_pair<0, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
-          issue_layer_pair<1, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
-          issue_layer_pair<2, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
-          issue_layer_pair<3, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
-          issue_layer_pair<4, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
-          issue_layer_pair<5, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, dbg_no_mma);
+          issue_layer_pair<0, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, a.variant);
+          issue_layer_pair<1, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, a.variant);
+          issue_layer_pair<2, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, a.variant);
+          issue_layer_pair<3, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, a.variant);
+          issue_layer_pair<4, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, a.variant);
+          issue_layer_pair<5, NSLOTS, Cfg>(s_base, tmem_base, s_alo, bar_full, bar_empty, bar_peer_full, bar_acc, bar_act, bar_peer_act, it, n_act, a.err_flag, a.variant);
         }
       }
     } else if (lane == 0) {
@@ -1391,12 +1419,12 @@ fused_pair_kernel(const FusedArgs a) {
       const uint32_t r_peer_act = mapa_shared(bar_act, 0);
       for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
         for (int g = 0; g < a.n_groups; ++g) {
-          relay_layer<0, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
-          relay_layer<1, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
-          relay_layer<2, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
-          relay_layer<3, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
-          relay_layer<4, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
-          relay_layer<5, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag);
+          relay_layer<0, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag, (a.variant & 1) != 0);
+          relay_layer<1, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag, (a.variant & 1) != 0);
+          relay_layer<2, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag, (a.variant & 1) != 0);
+          relay_layer<3, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag, (a.variant & 1) != 0);
+          relay_layer<4, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag, (a.variant & 1) != 0);
+          relay_layer<5, NSLOTS>(bar_full, bar_act, r_peer_full, r_peer_act, it, n_act, a.err_flag, (a.variant & 1) != 0);
         }
       }
     }
@@ -1421,6 +1449,7 @@ fused_pair_kernel(const FusedArgs a) {
     c.bar_act = bar_act;
     c.k0 = a.k0; c.k1 = a.k1;
     c.err_flag = a.err_flag;
+    c.strong_sync = (a.variant & 1) != 0;
     uint32_t n_acc = 0;
     // per-unit prologue: which window this thread's row belongs to, its input row (bf16), the ones-plane row
     auto unit_prologue = [&](long long unit, long long& win, uint32_t& xin0, uint32_t& xin1) {
@@ -1668,12 +1697,12 @@ fused_pair2_kernel(const FusedArgs a) {
       const uint32_t b_acc = bar_acc + 8 * tl, b_act = bar_act + 8 * tl;
       for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
         for (int g = 0; g < a.n_groups; ++g) {
-          if (!STAT || a.first_layer <= 0) issue_layer_pair<0, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
-          if (!STAT || (a.n_layers > 1 && a.first_layer <= 1)) issue_layer_pair<1, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
-          if (!STAT || (a.n_layers > 2 && a.first_layer <= 2)) issue_layer_pair<2, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
-          if (!STAT || (a.n_layers > 3 && a.first_layer <= 3)) issue_layer_pair<3, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
-          if (!STAT || (a.n_layers > 4 && a.first_layer <= 4)) issue_layer_pair<4, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
-          if (!STAT || (a.n_layers > 5 && a.first_layer <= 5)) issue_layer_pair<5, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, dbg_no_mma, a_tile);
+          if (!STAT || a.first_layer <= 0) issue_layer_pair<0, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, a.variant, a_tile);
+          if (!STAT || (a.n_layers > 1 && a.first_layer <= 1)) issue_layer_pair<1, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, a.variant, a_tile);
+          if (!STAT || (a.n_layers > 2 && a.first_layer <= 2)) issue_layer_pair<2, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, a.variant, a_tile);
+          if (!STAT || (a.n_layers > 3 && a.first_layer <= 3)) issue_layer_pair<3, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, a.variant, a_tile);
+          if (!STAT || (a.n_layers > 4 && a.first_layer <= 4)) issue_layer_pair<4, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, a.variant, a_tile);
+          if (!STAT || (a.n_layers > 5 && a.first_layer <= 5)) issue_layer_pair<5, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, a.variant, a_tile);
         }
       }
     } else if (warp == 1 && lane == 0) {
@@ -1688,7 +1717,7 @@ fused_pair2_kernel(const FusedArgs a) {
             for (int st = 0; st < ns; ++st, ++it) {
               const int slot = it % NSLOTS;
               mbar_wait2(bar_full + 8 * slot, (it / NSLOTS) & 1, a.err_flag, 23);
-              mbar_arrive_remote(r_full + 8 * slot);
+              mbar_arrive_remote(r_full + 8 * slot, (a.variant & 1) != 0);
             }
           }
     }
@@ -1715,6 +1744,7 @@ fused_pair2_kernel(const FusedArgs a) {
     c.remote_act = rank == 0 ? 0u : mapa_shared(bar_act + 8 * c.tl, 0);
     c.k0 = a.k0; c.k1 = a.k1;
     c.err_flag = a.err_flag;
+    c.strong_sync = (a.variant & 1) != 0;
     uint32_t n_acc = 0;
     if constexpr (STAT) {
       StatGeo geo;

@@ -29,6 +29,7 @@ struct LsPassParams {
   void* exchange_user;
   int64_t global_n;           // windows of the whole call over all ranks (divisor of the statistics) when exchanging
   const int64_t* win_ids;     // optional (n,): position of row i in the call (masks are keyed by it); null = i
+  int* err_flag;              // self-check flag (mapped host memory): 50 = statistics accumulator overflow
   const float* affine_tab;    // optional epilogue table (kTableFloats) whose scale / shift rows replace the BatchNorm affine
 };
 int ls_cast_input(const void* x, int x_dtype, float* out, int64_t n_windows, cudaStream_t s);
@@ -92,7 +93,7 @@ int build_tables(const float* blob_dev, const float* mean, const float* var, int
 // exact batch-statistic mode helpers (fused.cu)
 int exact_replicate_tables(const float* base_table, int n_groups, float* tables, cudaStream_t s);
 int exact_layer_tables(const float* blob_dev, const unsigned long long* stats, double count, int layer, int n_groups,
-                       float* tables, cudaStream_t s);
+                       float* tables, int* err_flag, cudaStream_t s);
 
 int exact_head(const float* head_sum, const unsigned char* head_cnt, const float* tables, int n_groups, int64_t n, float* probs,
                cudaStream_t s);

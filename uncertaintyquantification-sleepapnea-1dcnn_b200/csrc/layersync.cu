@@ -143,10 +143,12 @@ conv_relu_kernel(const float* __restrict__ in, const float* __restrict__ w, cons
 __global__ void bn_finalize_kernel(const double* __restrict__ stats, double count, const float* __restrict__ gamma,
                                    const float* __restrict__ beta, float inv_keep, int cout,
                                    float* __restrict__ scale, float* __restrict__ shift,
-                                   double* __restrict__ accum_mean, double* __restrict__ accum_var) {
+                                   double* __restrict__ accum_mean, double* __restrict__ accum_var, int* __restrict__ err_flag) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= cout) return;
   const long long* q = reinterpret_cast<const long long*>(stats);
+  // post-ReLU sums are non-negative: a set sign bit means the 2^-24 fixed point wrapped
+  if ((q[2 * c] < 0 || q[2 * c + 1] < 0) && err_flag) *reinterpret_cast<volatile int*>(err_flag) = 50;
   const double mu = (double)q[2 * c] / kStatScale / count;
   double var = (double)q[2 * c + 1] / kStatScale / count - mu * mu;  // biased variance (Keras training mode)
   if (var < 0) var = 0;
@@ -315,7 +317,7 @@ int ls_forward_pass(const LsPassParams& p, cudaStream_t s) {
       bn_finalize_kernel<<<gb, tb, 0, s>>>(stats, (double)stat_windows * kL, blob + off.gamma[l], blob + off.beta[l], inv_keep,
                                            b.cout, const_cast<float*>(scale), const_cast<float*>(shift),
                                            p.accum_mean ? p.accum_mean + (size_t)l * kMaxCh : nullptr,
-                                           p.accum_var ? p.accum_var + (size_t)l * kMaxCh : nullptr);
+                                           p.accum_var ? p.accum_var + (size_t)l * kMaxCh : nullptr, p.err_flag);
     } else {
       const float* mean = p.bn_mode == UQK_BN_CALIBRATED ? p.frozen_mean + (size_t)l * kMaxCh : blob + off.mmean[l];
       const float* var = p.bn_mode == UQK_BN_CALIBRATED ? p.frozen_var + (size_t)l * kMaxCh : blob + off.mvar[l];

@@ -128,8 +128,12 @@ class Engine:
                 setattr(mo, k, t.data_ptr())
         return bufs, mo
 
-    @staticmethod
-    def _finish(bufs, probs, device_out):
+    def poll_error(self):
+        """Raises if a device-side self-check of earlier work fired (include/uqk.h ``uqk_poll_error``): call after
+        synchronising when results were left on the device."""
+        _lib.check(self.lib.uqk_poll_error(self._h), "uqk_poll_error")
+
+    def _finish(self, bufs, probs, device_out):
         if device_out:
             out = dict(bufs)
             if probs is not None:
@@ -138,6 +142,7 @@ class Engine:
         out = {k: v.cpu().numpy() for k, v in bufs.items()}   # D2H (synchronises)
         if probs is not None:
             out["probs"] = probs.cpu().numpy()
+        self.poll_error()                                      # the work is complete: a watchdog / self-check is visible now
         return out
 
     # ---- compute ----------------------------------------------------------------------------------------------------
