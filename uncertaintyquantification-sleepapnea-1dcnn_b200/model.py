@@ -7,9 +7,10 @@ The reference passes whatever ``tensorflow.keras.models.load_model(path)`` retur
 ``UQModel`` supports exactly those on the GPU; ``weights_of`` also accepts a genuine Keras model
 (duck-typed through ``get_weights()``) when TensorFlow exists.
 
-File format: TensorFlow/h5py are absent from this image, so ``save_model``/``load_model`` use an ``.npz``
-payload of the 38 ``get_weights()`` arrays stored under the ``*.keras`` file name the callers expect
-(SURVEY.md section 7.3 H6).
+File formats: ``load_model`` reads genuine Keras v3 archives (zip of config.json + model.weights.h5, parsed by
+``keras_archive.py`` without h5py/TensorFlow) and this build's own container: an ``.npz`` payload of the 38
+``get_weights()`` arrays stored under the ``*.keras`` file name the callers expect, which is
+what ``save_model`` writes.
 """
 from __future__ import annotations
 
@@ -191,10 +192,12 @@ def load_model(path: str, compile: bool = True, **_) -> UQModel:   # noqa: A002 
     except zipfile.BadZipFile:
         raise ValueError(f"{path}: not a model container this build can read")
     if "model.weights.h5" in names or "config.json" in names:
-        raise NotImplementedError(
-            f"{path} is a genuine Keras v3 archive; reading its HDF5 weights needs h5py/TensorFlow, which are not in "
-            "this image. Export the weights with `np.savez(path, **{f'w{i:02d}': w for i, w in "
-            "enumerate(model.get_weights())})`.")
+        # a genuine Keras v3 archive (model.save("*.keras"), cnn_baseline_train.py:230): config.json is validated against
+        # the architecture the kernels implement, the variables come from model.weights.h5 (keras_archive.py)
+        from . import keras_archive
+        layers, ws = keras_archive.weights_from_keras_archive(data)
+        validate_keras_model(type("KerasArchive", (), {"layers": layers})())
+        return UQModel(ws)
     z = np.load(io.BytesIO(data), allow_pickle=False)
     ws = [z[f"w{i:02d}"] for i in range(len(arch.blob_layout()))]
     return UQModel(ws)
