@@ -255,6 +255,7 @@ def main():
         pcounts = [len(np.unique(pid[s_:e])) for s_, e in shards]
         strong["max_patients"] = max(pcounts)
         strong["patient_counts"] = pcounts
+        uq.mc_dropout_uq(model, strong["x"][:0], n_pred=1, seed=seed, bn_mode="inference", device_out=True)   # uploads the model
         torch.cuda.synchronize()
 
     def step_strong(collect=None):
