@@ -56,6 +56,7 @@ struct Handle {
   int dbg_dump = 0;
   int64_t calib_fp32_max = 8192;  // calibration sets up to this size use the fp32 layer-synchronous kernels
   int exact_chunk_max = 0;        // tests: cap on the passes per chunk of the exact mode (0 = memory budget only)
+  int exact_pipelined = 0;        // resumed sweeps of the exact mode as a three-stage pipeline (measured slower; variant kept for tests)
   // cross-rank exchange of batch statistics (uqk_set_stats_exchange)
   uqk_stats_exchange_fn xchg = nullptr;
   void* xchg_user = nullptr;
@@ -225,6 +226,7 @@ static int run_exact_sweeps(Handle* h, const void* x, int x_dtype, int64_t n, in
   p.mask_bits = mask_bits ? mask_bits + (size_t)pass0 * n * kBlocks * kL * 8 : nullptr;
   p.packed = h->d_packed; p.packed_pair = h->d_packed_pair;
   p.tables = h->d_tables_pass; p.tab_per_group = 1; p.err_flag = h->d_err; p.variant = h->variant;
+  p.pipelined = h->exact_pipelined;
   if (stat_windows < 1) return UQK_OK;
   for (int k = 0; k < kBlocks; ++k) {
     UQK_CUDA(cudaMemsetAsync(stats, 0, sizeof(unsigned long long) * (size_t)n_passes * 2 * kMaxCh, s));
@@ -246,7 +248,8 @@ static int run_exact_sweeps(Handle* h, const void* x, int x_dtype, int64_t n, in
       set_error("batch-statistics exchange callback failed at layer %d", k);
       return UQK_E_STATE;
     }
-    if ((rc = exact_layer_tables(h->d_blobs, stats, (double)stat_windows * kL, k, n_passes, h->d_tables_pass, h->d_err, s))) return rc;
+    if ((rc = exact_layer_tables(h->d_blobs, stats, (double)stat_windows * kL, k, n_passes, h->d_tables_pass,
+                                 (h->variant & 14) ? nullptr : h->d_err /* perf-decomposition switches compute garbage */, s))) return rc;
     if (frozen && (rc = exact_layer_average(stats, (double)stat_windows * kL, k, n_passes, frozen, s))) return rc;
   }
   return UQK_OK;
@@ -373,6 +376,7 @@ int uqk_set_option(uqk_handle* hh, const char* key, int64_t value) {
   if (!strcmp(key, "variant")) { h->variant = (int)value; return UQK_OK; }
   if (!strcmp(key, "dbg_dump")) { h->dbg_dump = (int)value; return UQK_OK; }
   if (!strcmp(key, "calib_fp32_max")) { h->calib_fp32_max = value; return UQK_OK; }   // see uqk_calibrate
+  if (!strcmp(key, "exact_pipelined")) { h->exact_pipelined = (int)value; return UQK_OK; }
   if (!strcmp(key, "exact_chunk_max")) { h->exact_chunk_max = (int)value; return UQK_OK; }   // passes per chunk of the exact mode (0 = by memory budget)
   set_error("unknown option '%s'", key);
   return UQK_E_BADARG;

@@ -52,6 +52,11 @@ static __constant__ FusedLayer c_layers[kBlocks] = {fused_layer(0), fused_layer(
 
 constexpr double kFusedStatScale = 16777216.0;   // 2^24 fixed point of batch statistics, as in layersync.cu
 
+#ifndef UQK_WAIT_HINT_NS
+#define UQK_WAIT_HINT_NS 20000u
+#endif
+constexpr uint32_t kWaitHintNs = UQK_WAIT_HINT_NS;   // suspend-time hint of mbarrier.try_wait
+
 // ---- PTX wrappers -----------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -225,6 +230,7 @@ struct FusedArgs {
   uint4* ckpt_out;                // post-ReLU output of layer n_layers-1, or null
   const uint4* ckpt_in;           // post-ReLU output of layer first_layer-1 (first_layer >= 2), or null
   int first_layer;                // first layer this sweep computes; 0 = start from the windows
+  int pipelined;                  // 1: resumed sweeps run the three-stage pipeline over 4-window units (option exact_pipelined)
 };
 
 // dropout source of the epilogue
@@ -275,7 +281,7 @@ __device__ __forceinline__ void mbar_wait2(uint32_t bar, uint32_t parity, int* e
         "mov.u32 %0, 1;\n"
         "UQK_END:\n\t}"
         : "=r"(ok)
-        : "r"(bar), "r"(parity), "r"(20000u)
+        : "r"(bar), "r"(parity), "r"(kWaitHintNs)
         : "memory");
     if (ok) return;
     const long long now = clock64();                  // watchdog: ~2 s of waiting is a protocol bug
@@ -989,6 +995,157 @@ __device__ __forceinline__ void stat_epilogue_loop(EpiCtx& c, const FusedArgs& a
   }
 }
 
+// ---- pipelined statistics sweep (resumed sweeps, first_layer >= 2; option "exact_pipelined", OFF by default) ----------
+// Measured (262 k windows x 4 passes): 133 ms against 129 ms for the default two-tile sweep -- the load stage and the
+// statistics epilogue are latency-bound instruction streams (IPC 0.12 per scheduler at 4 resident warps), so overlapping
+// them with the MMAs through two buffers does not pay for the halved weight reuse (R = 4).  Kept as a tested variant
+// (bit-identical results, tests/test_gpu_exact.py).
+// One stream of 4-window units per CTA pair, software-pipelined over TWO activation buffers and TWO accumulators:
+// while the tensor cores run the MMAs of unit q (buffer q & 1), the 8 LOADER warps normalise the input of unit q + 1 in
+// the other buffer and the 8 EPILOGUE warps reduce / store the accumulator of unit q - 1.  The three stages only meet
+// at mbarriers:
+//   in[b]    bulk copies of a unit's raw input have landed in buffer b        (TMA -> loaders)
+//   act[b]   buffer b holds normalised activations                           (loaders, both CTAs -> issuer)
+//   acc[b]   the MMAs reading buffer b / writing accumulator b have retired   (issuer -> epilogue, both CTAs)
+//   tfree[b] accumulator b has been read out                                  (epilogue, both CTAs -> issuer)
+// The epilogue warp that observes acc[b] of unit q also issues the input copies of unit q + 2 into buffer b.
+struct PipeGeo {
+  uint32_t act_base;     // shared-memory address of activation buffer 0 (buffer 1 = + kActBytes)
+  uint32_t bar_in, bar_acc, bar_act, bar_tfree;   // barrier pairs [2]
+  uint32_t tmem_base;
+  uint32_t rank;
+  long long pair_id, n_pairs;
+};
+
+template <int DROP, int EPI_THREADS>
+__device__ __forceinline__ void stat_pipelined_loop(EpiCtx& c, const FusedArgs& a, const PipeGeo& geo, unsigned long long* s_stats) {
+  constexpr int WPU = 4;
+  const int L0 = a.first_layer - 1;
+  const int planes_in = c_layers[L0].cout / 8;
+  const long long my_units = geo.pair_id < a.n_units ? (a.n_units - geo.pair_id + geo.n_pairs - 1) / geo.n_pairs : 0;
+  const long long total_it = my_units * a.n_groups;
+  const int row = c.quarter * 32 + c.lane;
+  const bool leader = geo.rank == 0;
+  const bool strong = c.strong_sync;
+  auto unit_of = [&](long long q, int& g, long long& unit) { g = (int)(q / my_units); unit = geo.pair_id + (q % my_units) * geo.n_pairs; };
+  if (c.tl == 0) {
+    // =========================== loaders ===========================
+    uint32_t n_in0 = 0u, n_in1 = 0u;       // phase counters of in[0], in[1] (scalars: a runtime-indexed array would live in local memory)
+    float* tab_s = c.tab + (L0 & 1) * 512;
+    float* tab_h = tab_s + 256;
+    const uint32_t r_act = leader ? 0u : mapa_shared(geo.bar_act, 0);
+    int g_tab = -1;
+    for (long long q = 0; q < total_it; ++q) {
+      const int b = (int)(q & 1);
+      int g; long long unit;
+      unit_of(q, g, unit);
+      const long long win = unit * WPU + 2 * (long long)geo.rank + c.slot_w;
+      c.row_valid = (c.t < kL) && (win < a.n);
+      c.c0w = (uint32_t)(a.window_base + win);
+      c.act_row = geo.act_base + (uint32_t)b * kActBytes + (uint32_t)(row + 4) * 16u;
+      if (g != g_tab) {
+        // BatchNorm affine of layer L0 for pass g (dropout scale folded); the previous pass's last load stage is done
+        named_bar_sync(1, EPI_THREADS);
+        const float* tab_g = a.tables + (size_t)g * kTableFloats;
+        for (int i = c.tid_t; i < 8 * planes_in; i += EPI_THREADS) {
+          tab_s[i] = __ldg(tab_g + kChTotal + c_ch_off[L0] + i);
+          tab_h[i] = __ldg(tab_g + 2 * kChTotal + c_ch_off[L0] + i);
+        }
+        named_bar_sync(1, EPI_THREADS);
+        g_tab = g;
+      }
+      // the row's keep-flags of layer L0 (data independent: produced while the copies are in flight)
+      uint32_t kb[4];
+      epi_pass_setup<DROP>(c, a, g);
+      switch (L0) {
+        case 1: make_keep_flags<1, DROP>(c, a, g, win, kb); break;
+        case 2: make_keep_flags<2, DROP>(c, a, g, win, kb); break;
+        case 3: make_keep_flags<3, DROP>(c, a, g, win, kb); break;
+        default: make_keep_flags<4, DROP>(c, a, g, win, kb); break;
+      }
+      mbar_wait2(geo.bar_in + 8 * b, (b ? n_in1 : n_in0) & 1, a.err_flag, 5);      // implies: the MMAs of unit q - 2 have left this buffer
+      if (b) ++n_in1; else ++n_in0;
+      if (c.colhalf == 1) st_shared_v4(c.act_row + (uint32_t)kOnesPlane * kPlaneBytes, c.row_valid ? 0x3F803F80u : 0u, 0u, 0u, 0u);
+      switch (L0) {
+        case 1: load_stage<1, DROP>(c, kb, tab_s, tab_h); break;
+        case 2: load_stage<2, DROP>(c, kb, tab_s, tab_h); break;
+        case 3: load_stage<3, DROP>(c, kb, tab_s, tab_h); break;
+        default: load_stage<4, DROP>(c, kb, tab_s, tab_h); break;
+      }
+      fence_proxy_async();
+      if (leader) {
+        __syncwarp();
+        if (c.lane == 0) mbar_arrive(geo.bar_act + 8 * b);
+      } else {
+        named_bar_sync(1, EPI_THREADS);
+        if (c.tid_t == 0) mbar_arrive_remote(r_act + 8 * b, strong);
+      }
+    }
+  } else {
+    // =========================== epilogue ===========================
+    for (int i = c.tid_t; i < 2 * kMaxCh; i += EPI_THREADS) s_stats[i] = 0ull;
+    named_bar_sync(2, EPI_THREADS);
+    auto issue_in = [&](long long q) {            // whole warp we == 0: input copies of unit q into buffer q & 1
+      if (q >= total_it) return;
+      const int b = (int)(q & 1);
+      int gq; long long uq;
+      unit_of(q, gq, uq);
+      const long long w0 = uq * WPU + 2 * (long long)geo.rank;
+      const bool dbg_no_in = (a.variant & 4) != 0;
+      const int valid = dbg_no_in ? 0 : (w0 < a.n ? 1 : 0) + (w0 + 1 < a.n ? 1 : 0);
+      if (c.lane == 0) mbar_arrive_expect_tx(geo.bar_in + 8 * b, (uint32_t)(valid * planes_in * kL * 16));
+      __syncwarp();
+      for (int idx = c.lane; idx < 2 * planes_in; idx += 32) {
+        const int slot = idx >= planes_in ? 1 : 0, pl = idx - slot * planes_in;
+        if (w0 + slot < a.n && !dbg_no_in)
+          bulk_g2s(geo.act_base + (uint32_t)b * kActBytes + (uint32_t)pl * kPlaneBytes + (uint32_t)(4 + 64 * slot) * 16u,
+                   a.ckpt_in + (((size_t)gq * a.n + (size_t)(w0 + slot)) * planes_in + pl) * kL, (uint32_t)(kL * 16), geo.bar_in + 8 * b);
+      }
+    };
+    if (c.we == 0) { issue_in(0); issue_in(1); }
+    uint32_t n_acc0 = 0u, n_acc1 = 0u;
+    const uint32_t r_tfree = leader ? 0u : mapa_shared(geo.bar_tfree, 0);
+    const uint32_t taddr0 = geo.tmem_base + ((uint32_t)(c.quarter * 32) << 16);
+    auto nothing = []() {};
+    for (long long q = 0; q < total_it; ++q) {
+      const int b = (int)(q & 1);
+      int g; long long unit;
+      unit_of(q, g, unit);
+      const long long win = unit * WPU + 2 * (long long)geo.rank + c.slot_w;
+      c.row_valid = (c.t < kL) && (win < a.n);
+      c.c0w = (uint32_t)(a.window_base + win);
+      c.taddr = taddr0 + (uint32_t)(b * 256);
+      c.bar_acc = geo.bar_acc + 8 * b;
+      auto after_acc = [&]() { if (c.we == 0) issue_in(q + 2); };
+      uint32_t na = b ? n_acc1 : n_acc0;
+      switch (a.first_layer) {
+        case 2: epi_stats<2, DROP, EPI_THREADS>(c, a, g, win, na, s_stats, nothing, after_acc); break;
+        case 3: epi_stats<3, DROP, EPI_THREADS>(c, a, g, win, na, s_stats, nothing, after_acc); break;
+        case 4: epi_stats<4, DROP, EPI_THREADS>(c, a, g, win, na, s_stats, nothing, after_acc); break;
+        default: epi_stats<5, DROP, EPI_THREADS>(c, a, g, win, na, s_stats, nothing, after_acc); break;
+      }
+      if (b) n_acc1 = na; else n_acc0 = na;
+      // accumulator b has been read out (tcgen05.wait::ld + fence in epi_stats): the MMAs of unit q + 2 may overwrite it
+      if (leader) {
+        __syncwarp();
+        if (c.lane == 0) mbar_arrive(geo.bar_tfree + 8 * b);
+      } else {
+        named_bar_sync(2, EPI_THREADS);
+        if (c.tid_t == 0) mbar_arrive_remote(r_tfree + 8 * b, strong);
+      }
+      if (q + 1 == total_it || (q + 1) % my_units == 0) {
+        // pass g is complete in this CTA: add its fixed-point sums to the global accumulators of pass g
+        named_bar_sync(2, EPI_THREADS);
+        for (int i = c.tid_t; i < 2 * kMaxCh; i += EPI_THREADS) {
+          const unsigned long long v = s_stats[i];
+          if (v != 0ull) { atomicAdd(a.stats + (size_t)g * 2 * kMaxCh + i, v); s_stats[i] = 0ull; }
+        }
+        named_bar_sync(2, EPI_THREADS);
+      }
+    }
+  }
+}
+
 template <int TILES, int NSLOTS, int DROP, bool DBG>
 __global__ void __launch_bounds__(FusedCfg<TILES, NSLOTS>::kThreads, TILES == 1 ? 2 : 1)
 fused_forward_kernel(const FusedArgs a) {
@@ -1222,7 +1379,7 @@ __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity,
           "mov.u32 %0, 1;\n"
           "UQK_ENDA:\n\t}"
           : "=r"(ok)
-          : "r"(bar), "r"(parity), "r"(20000u)
+          : "r"(bar), "r"(parity), "r"(kWaitHintNs)
           : "memory");
     } else {
       asm volatile(
@@ -1240,7 +1397,7 @@ __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity,
           "mov.u32 %0, 1;\n"
           "UQK_END:\n\t}"
           : "=r"(ok)
-          : "r"(bar), "r"(parity), "r"(20000u)
+          : "r"(bar), "r"(parity), "r"(kWaitHintNs)
           : "memory");
     }
     if (ok) return;
@@ -1579,7 +1736,7 @@ struct Pair2Cfg {
   static constexpr int kTabFloats = 2 * 512 + 128;
   static constexpr int oTab = oRing + NSLOTS * kSlot;
   static constexpr int oBar = oTab + 2 * kTabFloats * 4;
-  static constexpr int kNumBars = 3 * NSLOTS + 8;  // full, empty, peer_full [NSLOTS]; acc[2], act[2], peer_act[2], in[2] (sweeps)
+  static constexpr int kNumBars = 3 * NSLOTS + 10; // full, empty, peer_full [NSLOTS]; acc[2], act[2], peer_act[2], in[2], tfree[2] (sweeps)
   static constexpr int oMisc = oBar + 8 * kNumBars;
   static constexpr int oAlo = oMisc + 16 + 64;
   static constexpr int oProbs = (oAlo + 4 * 392 + 15) & ~15;   // probs[4][n_groups]
@@ -1606,6 +1763,8 @@ fused_pair2_kernel(const FusedArgs a) {
   const uint32_t bar_act = bar_acc + 16;                        // [2] leader only: its own epilogue threads
   const uint32_t bar_peer_act = bar_act + 16;                   // [2] leader only: one remote arrive per layer
   const uint32_t bar_in = bar_peer_act + 16;                    // [2] statistics sweeps: the tile's input planes have landed
+  const uint32_t bar_tfree = bar_in + 16;                       // [2] pipelined sweeps: accumulator read out (leader: + peer relay)
+  const bool pipe = STAT && a.first_layer >= 2 && a.pipelined;  // pipelined single-stream sweep (stat_pipelined_loop)
   volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(smem + Cfg::oMisc);
   float* zpart = reinterpret_cast<float*>(smem + Cfg::oMisc + 16);
   uint32_t* s_alo = reinterpret_cast<uint32_t*>(smem + Cfg::oAlo);
@@ -1632,11 +1791,12 @@ fused_pair2_kernel(const FusedArgs a) {
     // BOTH tile-pairs have consumed it (two commits)
     const uint32_t extra = rank == 0 ? 1u : 0u;
     for (int i = 0; i < NSLOTS; ++i) {
-      mbar_init(bar_full + 8 * i, 1 + extra); mbar_init(bar_empty + 8 * i, 2); mbar_init(bar_peer_full + 8 * i, 1);
+      mbar_init(bar_full + 8 * i, 1 + extra); mbar_init(bar_empty + 8 * i, pipe ? 1 : 2); mbar_init(bar_peer_full + 8 * i, 1);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar_acc + 8 * i, 1); mbar_init(bar_act + 8 * i, Cfg::kEpiThreads / 32 + extra); mbar_init(bar_peer_act + 8 * i, 1);
       mbar_init(bar_in + 8 * i, 1);
+      mbar_init(bar_tfree + 8 * i, Cfg::kEpiThreads / 32 + extra);
     }
     fence_barrier_init();
   }
@@ -1688,7 +1848,41 @@ fused_pair2_kernel(const FusedArgs a) {
     }
   } else if (warp == 1 || warp == 2) {
     const int tl = warp - 1;
-    if (rank == 0) {
+    if (pipe) {
+      if (rank == 0 && warp == 1) {
+        // ---- leader, pipelined sweep: ONE issuer walks the units, alternating between the two buffers / accumulators
+        const long long my_units = pair_id < a.n_units ? (a.n_units - pair_id + n_pairs - 1) / n_pairs : 0;
+        const long long total_it = my_units * a.n_groups;
+        uint32_t it = 0, n_act0 = 0u, n_act1 = 0u, n_tf0 = 0u, n_tf1 = 0u;
+        for (long long q = 0; q < total_it; ++q) {
+          const int b = (int)(q & 1);
+          if (q >= 2) {
+            mbar_wait_cluster(bar_tfree + 8 * b, (b ? n_tf1 : n_tf0) & 1, a.err_flag, 6, (a.variant & 1) != 0);
+            if (b) ++n_tf1; else ++n_tf0;
+          }
+          const uint32_t tm = tmem_base + (uint32_t)b * 256u, a_tile = (uint32_t)b * (uint32_t)(kActBytes >> 4);
+          uint32_t na = b ? n_act1 : n_act0;
+          switch (a.first_layer) {
+            case 2: issue_layer_pair<2, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, bar_acc + 8 * b, bar_act + 8 * b, 0u, it, na, a.err_flag, a.variant, a_tile); break;
+            case 3: issue_layer_pair<3, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, bar_acc + 8 * b, bar_act + 8 * b, 0u, it, na, a.err_flag, a.variant, a_tile); break;
+            case 4: issue_layer_pair<4, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, bar_acc + 8 * b, bar_act + 8 * b, 0u, it, na, a.err_flag, a.variant, a_tile); break;
+            default: issue_layer_pair<5, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, bar_acc + 8 * b, bar_act + 8 * b, 0u, it, na, a.err_flag, a.variant, a_tile); break;
+          }
+          if (b) n_act1 = na; else n_act0 = na;
+        }
+      } else if (rank != 0 && warp == 1 && lane == 0) {
+        const uint32_t r_full = mapa_shared(bar_full, 0);
+        uint32_t it = 0;
+        const long long my_units = pair_id < a.n_units ? (a.n_units - pair_id + n_pairs - 1) / n_pairs : 0;
+        const int ns = c_layers[a.first_layer].nstages;
+        for (long long q = 0; q < my_units * a.n_groups; ++q)
+          for (int st = 0; st < ns; ++st, ++it) {
+            const int slot = it % NSLOTS;
+            mbar_wait2(bar_full + 8 * slot, (it / NSLOTS) & 1, a.err_flag, 23);
+            mbar_arrive_remote(r_full + 8 * slot, (a.variant & 1) != 0);
+          }
+      }
+    } else if (rank == 0) {
       // ---- leader: one MMA-issuer warp per tile-pair.  Both walk the same weight stream; they drift apart at layer
       //      boundaries (one waits for its epilogue while the other keeps the tensor pipe busy), bounded by the ring.
       uint32_t it = 0, n_act = 0;
@@ -1746,7 +1940,12 @@ fused_pair2_kernel(const FusedArgs a) {
     c.err_flag = a.err_flag;
     c.strong_sync = (a.variant & 1) != 0;
     uint32_t n_acc = 0;
-    if constexpr (STAT) {
+    if (STAT && pipe) {
+      PipeGeo pg;
+      pg.act_base = s_base + Cfg::oAct; pg.bar_in = bar_in; pg.bar_acc = bar_acc; pg.bar_act = bar_act; pg.bar_tfree = bar_tfree;
+      pg.tmem_base = tmem_base; pg.rank = rank; pg.pair_id = pair_id; pg.n_pairs = n_pairs;
+      stat_pipelined_loop<DROP, Cfg::kEpiThreads>(c, a, pg, reinterpret_cast<unsigned long long*>(smem + Cfg::oProbs));
+    } else if constexpr (STAT) {
       StatGeo geo;
       geo.act_base = s_base + Cfg::oAct + c.tl * kActBytes;
       geo.bar_in = bar_in + 8 * c.tl;
@@ -1819,9 +2018,12 @@ static int launch_pair2_variant(const FusedParams& p, cudaStream_t s) {
   a.window_base = p.window_base; a.mask_bits = p.mask_bits; a.packed = reinterpret_cast<const uint8_t*>(p.packed_pair);
   a.tables = p.tables; a.probs = p.probs; a.out = p.out; a.dbg_act = p.dbg_act; a.err_flag = p.err_flag;
   a.variant = p.variant;
-  a.n_units = (p.n + Cfg::kWpu - 1) / Cfg::kWpu;
-  a.smem_probs = (p.no_smem_probs || STAT) ? 0 : 1;
   a.n_layers = STAT ? p.n_layers : kBlocks; a.stats = STAT ? p.stats : nullptr; a.first_layer = STAT ? p.first_layer : 0;
+  // option exact_pipelined: resumed sweeps run pipelined over 4-window units (stat_pipelined_loop); default: 8-window units
+  a.pipelined = (STAT && p.pipelined && a.first_layer >= 2) ? 1 : 0;
+  const int wpu = a.pipelined ? 4 : Cfg::kWpu;
+  a.n_units = (p.n + wpu - 1) / wpu;
+  a.smem_probs = (p.no_smem_probs || STAT) ? 0 : 1;
   a.head_sum = STAT ? p.head_sum : nullptr; a.head_cnt = STAT ? p.head_cnt : nullptr;
   a.ckpt_out = STAT ? reinterpret_cast<uint4*>(p.ckpt_out) : nullptr;
   a.ckpt_in = STAT ? reinterpret_cast<const uint4*>(p.ckpt_in) : nullptr;

@@ -75,6 +75,7 @@ struct FusedParams {
   void* ckpt_out;             // written by this sweep (output of layer n_layers-1), or null
   const void* ckpt_in;        // output of layer first_layer-1, read by a sweep that starts at first_layer >= 2, or null
   int first_layer;            // first layer the sweep computes (0 = from the windows)
+  int pipelined;              // option exact_pipelined: three-stage pipelined variant of the resumed sweeps
 };
 // bytes of a layer's stored output per window-pass
 constexpr size_t exact_layer_bytes(int l) { return (size_t)(block_def(l).cout / 8) * kL * 16; }
