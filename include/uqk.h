@@ -210,7 +210,8 @@ int uqk_bootstrap_noalloc(const float* variance_dev, const float* total_entropy_
                           const float* mutual_info_dev, const int32_t* y_dev, const int64_t* idx_dev, int n_boot,
                           int64_t n_windows, double* out_dev, void* stream);
 
-/* Diagnostics: number of kernel launches the library has issued on this handle since creation. */
+/* Diagnostics: number of kernel launches the library has issued in this PROCESS since it was loaded (one counter for all
+ * handles; the handle argument is accepted for symmetry and may be NULL). */
 int64_t uqk_launch_count(uqk_handle* h);
 /* N2 -- the per-window detail CSV (analyze_mcd_patient_level.py:134-152 builds the DataFrame and calls
  * to_csv(path, index=False); analyze_de_patient_level.py does the same).  HOST function: writes, byte for byte, what

@@ -40,9 +40,15 @@ def test_noalloc_bootstrap_matches_allocating_entry_point_twice():
         lib_mod.check(_call(lib.uqk_bootstrap_noalloc, cols, y, idx, got), "uqk_bootstrap_noalloc")
         torch.cuda.synchronize()
         np.testing.assert_allclose(got.cpu().numpy(), want.cpu().numpy(), rtol=1e-12, atol=0)
-        # and against a direct NumPy gather-mean of the first column
-        ref0 = cols[0].cpu().numpy().astype(np.float64)[idx.cpu().numpy()].mean(axis=1)
-        np.testing.assert_allclose(got.cpu().numpy()[:, 0], ref0, rtol=1e-10)
+        # and against direct NumPy gather-means of every output column, the class-conditional ones included
+        # (row layout of uqk_bootstrap: variance overall / class 0 / class 1, then the means of the other three columns)
+        ih, yh = idx.cpu().numpy(), y.cpu().numpy()
+        c = [t.cpu().numpy().astype(np.float64) for t in cols]
+        v, yy = c[0][ih], yh[ih]
+        ref = np.stack([v.mean(axis=1), (v * (yy == 0)).sum(axis=1) / (yy == 0).sum(axis=1),
+                        (v * (yy == 1)).sum(axis=1) / (yy == 1).sum(axis=1),
+                        c[1][ih].mean(axis=1), c[2][ih].mean(axis=1), c[3][ih].mean(axis=1)], axis=1)
+        np.testing.assert_allclose(got.cpu().numpy(), ref, rtol=1e-6)          # inputs are float32
     # sizes beyond the fixed scratch are rejected with a clear error, nothing is launched
     idx = torch.zeros((1, 8), dtype=torch.int64, device=dev)
     out = torch.empty((2000, 6), dtype=torch.float64, device=dev)
