@@ -164,6 +164,9 @@ def main():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="weak (default): --windows per GPU; strong: the configs[3] cohort split over the GPUs at patient boundaries")
     ap.add_argument("--patients", type=int, default=2651, help="patients of the strong-scaling cohort (SHHS2: 2651)")
+    ap.add_argument("--bn-mode", default="calibrated", choices=["calibrated", "batch"],
+                    help="--scaling strong only: batch = the reference's exact batch-statistic BatchNorm over the sharded cohort "
+                         "(per-layer statistics all-reduced over the ranks in every sweep)")
     ap.add_argument("--skip-extras", action="store_true", help="headline + roofline + e2e only")
     ap.add_argument("--variant", type=int, default=None)
     ap.add_argument("--skip-e2e", action="store_true")
@@ -263,12 +266,16 @@ def main():
         if world > 1:
             eng.set_stats_exchange(sh.StatsExchange(), global_windows=n_cohort)
         try:
-            eng.calibrate(xs, n_passes=1, seed=seed, window_base=cs)
+            if args.bn_mode == "batch":     # exact Keras semantics: every sweep's statistics are all-reduced over the ranks
+                out = uq.mc_dropout_uq(model, xs, n_pred=T, seed=seed, bn_mode="batch", device_out=True, window_base=cs)
+            else:
+                eng.calibrate(xs, n_passes=1, seed=seed, window_base=cs)
         finally:
             if world > 1:
                 eng.set_stats_exchange(None)
-        out = uq.mc_dropout_uq(model, xs, n_pred=T, seed=seed, bn_mode="calibrated", recalibrate=False, device_out=True,
-                               window_base=cs)
+        if args.bn_mode != "batch":
+            out = uq.mc_dropout_uq(model, xs, n_pred=T, seed=seed, bn_mode="calibrated", recalibrate=False, device_out=True,
+                                   window_base=cs)
         rows = eng.patient_reduce(out["pred_variance"], out["predictive_entropy_bits"], strong["y"], out["predicted_label"],
                                   strong["seg"], device_out=True)
         if world > 1:
@@ -318,7 +325,8 @@ def main():
                     "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
                     "config": {"workload": f"SHHS2-scale synthetic cohort ({args.patients} patients, {n_cohort} windows) MC Dropout T={T} with "
                                            "patient-level aggregation, split over the GPUs at patient boundaries (BASELINE configs[3])",
-                               "bn_mode": "calibrated (one exact pass over the whole cohort, inside the step)",
+                               "bn_mode": "calibrated (one exact pass over the whole cohort, inside the step)" if args.bn_mode != "batch" else
+                                          "batch: exact batch-statistic BatchNorm of the whole cohort (one tensor-core sweep per layer, statistics all-reduced over the ranks)",
                                "input": "float64 (N,60,4) resident per shard, larger than L2", "detail": info},
                     "clocks": clocks, "e2e": None, "gpu_launches": int(launches), "roofline": None, "cpu_baseline": None}
             print(json.dumps(line), flush=True)
