@@ -158,7 +158,8 @@ int uqk_refine_band(uqk_handle* h, int mode_de, const void* x_dev, int x_dtype, 
  *   codes 1..23: barrier watchdog -- a warp of a fused kernel waited ~2 s (4e9 clock ticks) at one mbarrier, which
  *     only a protocol fault can cause; the kernel then TRAPS, the CUDA context of the process is lost (every later
  *     CUDA call fails) and the process must be restarted.  The budget is fixed: under cuda-gdb, a sanitizer or heavy
- *     time-slicing a healthy kernel could exceed it.
+ *     time-slicing a healthy kernel could exceed it -- uqk_set_option(h, "watchdog", 0) switches the budget off (the
+ *     kernels then wait indefinitely, as ordinary CUDA kernels do).
  *   code 50: a batch-statistics accumulator (2^-24 fixed point in 64 bits) overflowed -- sum of squares of one
  *     channel above 5.5e11; no trap, the flag is cleared when reported, the results of that call are invalid.
  * uqk_debug_trip_watchdog (tests): runs a kernel that waits on a barrier nobody signals; returns UQK_E_KERNEL and
@@ -236,7 +237,15 @@ int uqk_write_detail_csv(const char* path, int64_t n, const int64_t* patient_id,
 int uqk_window_summary(const float* entropy_dev, const float* variance_dev, const int32_t* true_label_dev,
                        const int32_t* pred_label_dev, int64_t n_windows, int n_bins, double* out_dev, void* stream);
 
-/* Diagnostics for tests: selects the fused-kernel variant (0 = default). */
+/* Handle options (all integers):
+ *   "variant"          fused-kernel selector for tests and probes: value >> 4 = 0 two-tile CTA pairs (default), 1 one tile per
+ *                      CTA (the only kernel with the activation dump), 2 one-tile CTA pairs, 4 two tiles per CTA;
+ *                      bit 0 = release/acquire cluster signalling; bits 1..3 = perf-decomposition switches (results WRONG)
+ *   "watchdog"         1 (default) / 0: time budget of the kernels' barrier waits, see uqk_poll_error
+ *   "calib_fp32_max"   calibration sets up to this many windows use the fp32 kernels (default 8192)
+ *   "exact_chunk_max"  cap on the passes per chunk of the exact mode (0 = by memory budget)
+ *   "exact_pipelined"  1: resumed sweeps of the exact mode as a three-stage pipeline (bit-identical, measured slower)
+ *   "dbg_dump"         1: the one-tile kernel dumps the activations of its first unit (uqk_debug_read_dump) */
 int uqk_set_option(uqk_handle* h, const char* key, int64_t value);
 
 #ifdef __cplusplus

@@ -196,3 +196,44 @@ def test_standardize_matches_reference_golden(golden_dir):
     assert out32.dtype == np.float32
     np.testing.assert_allclose(out32, g["out"], rtol=2e-3, atol=2e-3)     # float32 input quantisation of 95 +- 3 signals
     assert eng.standardize(g["raw"][:0]).shape == (0, 60, 4)
+
+
+def test_stochastic_calls_draw_fresh_masks_unless_seeded(uq, uqk, monkeypatch):
+    """The reference draws new dropout masks on every call (TensorFlow's stateful generator, uq_techniques.py:22):
+    two calls differ; UQK_SEED (or seed=) pins the Philox key and makes a call reproducible bit for bit; re-seeding
+    through tf.random.set_seed restarts the call counter."""
+    model = importlib.import_module(PKG_NAME + ".model")
+    x = uqk.synthetic.make_windows(40, seed=43)
+    m0 = model.UQModel(members()[0])
+    monkeypatch.delenv("UQK_SEED", raising=False)
+    with contextlib.redirect_stdout(io.StringIO()):
+        a = uq.mc_dropout_predict(m0, x, n_pred=2)
+        b = uq.mc_dropout_predict(m0, x, n_pred=2)
+        assert np.abs(a - b).max() > 1e-4
+        fa = uq.mc_dropout_uq(m0, x, n_pred=3, bn_mode="inference")["mean_pred"]
+        fb = uq.mc_dropout_uq(m0, x, n_pred=3, bn_mode="inference")["mean_pred"]
+        assert np.abs(fa - fb).max() > 1e-5
+        sys.path.insert(0, os.path.join(ROOT, PKG_NAME, "shim"))
+        for k in [k for k in sys.modules if k == "tensorflow" or k.startswith("tensorflow.")]:
+            del sys.modules[k]
+        try:
+            import tensorflow as tf               # the shim
+            tf.random.set_seed(777)
+            c1 = uq.mc_dropout_predict(m0, x, n_pred=2)
+            c1b = uq.mc_dropout_predict(m0, x, n_pred=2)
+            tf.random.set_seed(777)               # re-seeding restarts the sequence of keys
+            c2 = uq.mc_dropout_predict(m0, x, n_pred=2)
+            np.testing.assert_array_equal(c1, c2)
+            assert np.abs(c1 - c1b).max() > 1e-4
+        finally:
+            sys.path.remove(os.path.join(ROOT, PKG_NAME, "shim"))
+            for k in [k for k in sys.modules if k == "tensorflow" or k.startswith("tensorflow.")]:
+                del sys.modules[k]
+            model.UQModel._global_seed = 2025
+        monkeypatch.setenv("UQK_SEED", "5")
+        d1 = uq.mc_dropout_predict(m0, x, n_pred=2)
+        d2 = uq.mc_dropout_predict(m0, x, n_pred=2)
+    np.testing.assert_array_equal(d1, d2)
+    s1 = uq.mc_dropout_uq(m0, x, n_pred=3, bn_mode="inference", seed=9)["mean_pred"]
+    s2 = uq.mc_dropout_uq(m0, x, n_pred=3, bn_mode="inference", seed=9)["mean_pred"]
+    np.testing.assert_array_equal(s1, s2)

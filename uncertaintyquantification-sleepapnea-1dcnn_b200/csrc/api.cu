@@ -56,6 +56,7 @@ struct Handle {
   int dbg_dump = 0;
   int64_t calib_fp32_max = 8192;  // calibration sets up to this size use the fp32 layer-synchronous kernels
   int exact_chunk_max = 0;        // tests: cap on the passes per chunk of the exact mode (0 = memory budget only)
+  int watchdog = 1;               // 0: the kernels wait on their barriers without a time budget (debuggers, sanitizers)
   int exact_pipelined = 0;        // resumed sweeps of the exact mode as a three-stage pipeline (measured slower; variant kept for tests)
   // cross-rank exchange of batch statistics (uqk_set_stats_exchange)
   uqk_stats_exchange_fn xchg = nullptr;
@@ -180,7 +181,7 @@ static int run_fused(Handle* h, int member0, const void* x, int x_dtype, int64_t
   p.seed = seed; p.window_base = window_base; p.mask_bits = mask_bits;
   p.packed = reinterpret_cast<const uint16_t*>(reinterpret_cast<const uint8_t*>(h->d_packed) + (size_t)member0 * pb);
   p.packed_pair = reinterpret_cast<const uint16_t*>(reinterpret_cast<const uint8_t*>(h->d_packed_pair) + (size_t)member0 * pb);
-  p.tables = tables; p.err_flag = h->d_err; p.variant = h->variant;
+  p.tables = tables; p.err_flag = h->watchdog ? h->d_err : nullptr; p.variant = h->variant;
   p.dbg_act = h->dbg_dump ? h->d_dbg : nullptr;
   if (n_groups <= kMaxFusedGroups) {
     p.probs = probs; p.out = out;
@@ -225,7 +226,7 @@ static int run_exact_sweeps(Handle* h, const void* x, int x_dtype, int64_t n, in
   p.seed = seed; p.window_base = window_base; p.pass_base = pass0;
   p.mask_bits = mask_bits ? mask_bits + (size_t)pass0 * n * kBlocks * kL * 8 : nullptr;
   p.packed = h->d_packed; p.packed_pair = h->d_packed_pair;
-  p.tables = h->d_tables_pass; p.tab_per_group = 1; p.err_flag = h->d_err; p.variant = h->variant;
+  p.tables = h->d_tables_pass; p.tab_per_group = 1; p.err_flag = h->watchdog ? h->d_err : nullptr; p.variant = h->variant;
   p.pipelined = h->exact_pipelined;
   if (stat_windows < 1) return UQK_OK;
   for (int k = 0; k < kBlocks; ++k) {
@@ -376,6 +377,7 @@ int uqk_set_option(uqk_handle* hh, const char* key, int64_t value) {
   if (!strcmp(key, "variant")) { h->variant = (int)value; return UQK_OK; }
   if (!strcmp(key, "dbg_dump")) { h->dbg_dump = (int)value; return UQK_OK; }
   if (!strcmp(key, "calib_fp32_max")) { h->calib_fp32_max = value; return UQK_OK; }   // see uqk_calibrate
+  if (!strcmp(key, "watchdog")) { h->watchdog = value ? 1 : 0; return UQK_OK; }
   if (!strcmp(key, "exact_pipelined")) { h->exact_pipelined = (int)value; return UQK_OK; }
   if (!strcmp(key, "exact_chunk_max")) { h->exact_chunk_max = (int)value; return UQK_OK; }   // passes per chunk of the exact mode (0 = by memory budget)
   set_error("unknown option '%s'", key);

@@ -91,7 +91,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, int* er
   if (mbar_try_wait(bar, parity)) return;
   const long long t0 = clock64();
   while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > 4000000000ll) mbar_timeout(err_flag, code);
+    if (err_flag && clock64() - t0 > 4000000000ll) mbar_timeout(err_flag, code);
   }
 }
 __device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
@@ -286,7 +286,7 @@ __device__ __forceinline__ void mbar_wait2(uint32_t bar, uint32_t parity, int* e
     if (ok) return;
     const long long now = clock64();                  // watchdog: ~2 s of waiting is a protocol bug
     if (t0 == 0) t0 = now;
-    else if (now - t0 > 4000000000ll) mbar_timeout(err_flag, code);
+    else if (err_flag && now - t0 > 4000000000ll) mbar_timeout(err_flag, code);   // err_flag == null: watchdog off
   }
 }
 __device__ __forceinline__ bool elect_one() {
@@ -1403,7 +1403,7 @@ __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity,
     if (ok) return;
     const long long now = clock64();
     if (t0 == 0) t0 = now;
-    else if (now - t0 > 4000000000ll) mbar_timeout(err_flag, code);
+    else if (err_flag && now - t0 > 4000000000ll) mbar_timeout(err_flag, code);   // err_flag == null: watchdog off
   }
 }
 

@@ -36,6 +36,7 @@ class UQModel:
     """The 6-block 1D-CNN (models/cnn_baseline_train.py:55-94) as a bag of weights + GPU forward."""
 
     _global_seed = 2025   # set by tf.random.set_seed in the shim (analyze_mcd_patient_level.py:31)
+    _seed_epoch = 0       # bumped by every tf.random.set_seed: the per-call key counter restarts, like TF's generator
 
     def __init__(self, weights: Sequence[np.ndarray], name: str = "Alarcon_1D_CNN_Model"):
         self._blob = synthetic.weights_to_blob(weights)   # validates the 38 shapes

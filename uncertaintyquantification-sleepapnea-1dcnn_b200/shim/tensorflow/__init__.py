@@ -26,6 +26,7 @@ class _Random:
     def set_seed(seed):
         """Seeds the Philox key of the dropout masks (the reference seeds TF's global generator)."""
         _model.UQModel._global_seed = int(seed)
+        _model.UQModel._seed_epoch += 1
 
 
 random = _Random()

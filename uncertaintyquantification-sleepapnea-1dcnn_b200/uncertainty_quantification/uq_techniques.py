@@ -62,9 +62,10 @@ def _call_seed() -> int:
     s = os.environ.get("UQK_SEED")
     if s is not None:
         return int(s)
-    base = int(_model.UQModel._global_seed)
+    base = (int(_model.UQModel._global_seed), int(_model.UQModel._seed_epoch))
     if _calls["base"] != base:
         _calls["base"], _calls["n"] = base, 0
+    base = base[0]
     k = (base * 0x9E3779B97F4A7C15 + 0xD1B54A32D192ED03 * _calls["n"]) & (2 ** 64 - 1)
     _calls["n"] += 1
     return k
