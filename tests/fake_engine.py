@@ -15,6 +15,12 @@ class FakeEngine:
         self.members, self._key = [], None
         self.calibrated, self.last_guard_band, self.calls = False, (0, 0), []
         self._stats = None
+        self._xchg, self._global_n = None, 0
+
+    def set_stats_exchange(self, reduce_fn, global_windows=0):
+        """Host model of Engine.set_stats_exchange: ``reduce_fn`` is a sharding.StatsExchange (its exchange_moments
+        quantises the moments to the library's 2^-24 fixed point and all-reduces them)."""
+        self._xchg, self._global_n = reduce_fn, int(global_windows)
 
     # model ------------------------------------------------------------------------------------------------------------
     def ensure_members(self, blobs_fn, key):
@@ -46,7 +52,8 @@ class FakeEngine:
     def calibrate(self, x, n_windows=None, n_passes=1, seed=2025, sampling="strided", window_base=0):
         self.calls.append(("calibrate", len(x)))
         masks = self._masks(len(x), 0, seed, window_base)
-        _, self._stats = network.forward_f64(self.members[0], self._check_x(x), training=True, masks=masks, return_stats=True)
+        kw = {} if self._xchg is None else {"stats_exchange": self._xchg.exchange_moments, "global_windows": self._global_n}
+        _, self._stats = network.forward_f64(self.members[0], self._check_x(x), training=True, masks=masks, return_stats=True, **kw)
         self.calibrated = True
 
     def _masks(self, n, t, seed, window_base):
@@ -72,7 +79,14 @@ class FakeEngine:
         out = self._metrics(probs, metrics)
         if return_probs:
             out["probs"] = probs
-        return out
+        return self._dev(out, device_out)
+
+    @staticmethod
+    def _dev(out, device_out):
+        if not device_out:
+            return out
+        import torch
+        return {k: torch.from_numpy(np.ascontiguousarray(v)) for k, v in out.items()}
 
     def de(self, x, n_members=None, precision="fp32", return_probs=False,
            metrics=("mean_pred", "pred_variance", "total_pred_entropy", "expected_aleatoric_entropy", "mutual_info", "entropy_bits", "label"),

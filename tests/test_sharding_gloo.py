@@ -94,3 +94,49 @@ def test_exact_batch_stats_exchange_world2_gloo(uqk, tmp_path, n, port):
     assert got.shape == want.shape
     # the exchanged moments are quantised to 2^-24 per rank and the variance comes from E[x^2]-mu^2
     assert np.abs(got - want).max() < 1e-6
+
+
+def _sharded_worker(rank, world, port, n, tmp):
+    """sharding.sharded_mc_dropout_uq as the product calls it, over gloo, with the GPU engine replaced by the oracle-backed
+    fake (tests/fake_engine.py): shards, one key for the whole call, calibration of every rank's shard through the
+    statistics exchange, window_base, final gather."""
+    import sys
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    sys.path.insert(0, os.path.join(ROOT, PKG_NAME, "uncertainty_quantification"))
+    pkg = importlib.import_module(PKG_NAME)
+    sh = importlib.import_module(PKG_NAME + ".sharding")
+    engine_mod = importlib.import_module(PKG_NAME + ".engine")
+    model_mod = importlib.import_module(PKG_NAME + ".model")
+    from fake_engine import FakeEngine
+    fake = FakeEngine(pkg.arch, pkg.synthetic)
+    engine_mod.get_engine = lambda device=None: fake
+    uq = importlib.import_module("uq_techniques")
+    if world > 1:
+        os.environ["MASTER_ADDR"] = "127.0.0.1"
+        os.environ["MASTER_PORT"] = str(port)
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+    x = pkg.synthetic.make_windows(n, seed=21)
+    pid = pkg.synthetic.make_patient_ids(n_patients=6, seed=5, lo=3, hi=6)[:n]
+    model = model_mod.UQModel(pkg.synthetic.make_member_weights(0))
+    full = sh.sharded_mc_dropout_uq(uq, model, x, n_pred=2, patient_ids=pid, seed=31, bn_mode="calibrated")
+    assert ("calibrate", len(x) if world == 1 else sh.patient_aligned_shards(pid, world)[rank][1] - sh.patient_aligned_shards(pid, world)[rank][0]) in fake.calls
+    assert fake._xchg is None                                     # the exchange is removed again after the calibration
+    np.savez(os.path.join(tmp, f"sharded_w{world}_r{rank}.npz"), **{k: v for k, v in full.items()})
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def test_sharded_calibrated_call_world2_gloo(tmp_path):
+    n = 21
+    mp.spawn(_sharded_worker, args=(2, 29551, n, str(tmp_path)), nprocs=2, join=True)
+    mp.spawn(_sharded_worker, args=(1, 0, n, str(tmp_path)), nprocs=1, join=True)     # one rank holding all windows (own process:
+    # the worker replaces engine.get_engine)
+    one = np.load(os.path.join(str(tmp_path), "sharded_w1_r0.npz"))
+    for r in range(2):
+        two = np.load(os.path.join(str(tmp_path), f"sharded_w2_r{r}.npz"))
+        assert set(two.files) == set(one.files) and len(two["mean_pred"]) == n
+        for k in one.files:
+            # same masks (global window index), statistics of ALL windows through the fixed-point exchange
+            np.testing.assert_allclose(two[k], one[k], rtol=0, atol=2e-6, err_msg=k)
