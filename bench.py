@@ -5,7 +5,7 @@
   torchrun --nproc-per-node N ... bench.py --gpus N ...        (one rank per GPU, weak scaling)
 
 A "step" = one pass of the hot path over one batch of synthetic windows: calibration of the BatchNorm
-statistics (32768 windows x 2 passes, statistics sweeps of the tensor-core kernel) + the fused tcgen05 kernel
+statistics (one exact pass over all windows of the call: one tensor-core sweep per layer) + the fused tcgen05 kernel
 (T stochastic passes + per-window reductions) [+ NCCL all-gather of the per-window metrics when N > 1].
 Prints ONE JSON line (rank 0).  Timing: CUDA events on the launching stream, barrier + synchronize on both
 sides, max over ranks; inputs (1.9 GB float64 per GPU) are larger than L2 (126 MB).

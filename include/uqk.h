@@ -43,10 +43,10 @@ extern "C" {
 #define UQK_BN_INFERENCE 0  /* moving statistics (frozen BN; what model.predict uses, uq_techniques.py:29) */
 #define UQK_BN_BATCH 1      /* exact Keras training=True semantics: batch mean / biased variance over (N,L) of the
                                whole call, per pass (uq_techniques.py:22).  UQK_PREC_FP32: layer-synchronous kernels
-                               (activations of the call in HBM).  UQK_PREC_BF16_TC: the fused kernel is swept once
-                               per layer to collect that layer's statistics of every pass; the sixth sweep also
-                               leaves what the linear head needs; later sweeps resume from bf16 checkpoints of
-                               the inputs of layers 3 and 5 (1.89x the flops of one run) */
+                               (activations of the call in HBM).  UQK_PREC_BF16_TC: one tensor-core sweep per
+                               layer: sweep k reads layer k-1's post-ReLU output (bf16) from HBM, normalises it
+                               with the statistics sweep k-1 produced, computes layer k once, collects its per-pass
+                               statistics and stores its output; the sixth sweep leaves what the linear head needs */
 #define UQK_BN_CALIBRATED 2 /* batch statistics estimated once by uqk_calibrate() and frozen for all passes */
 
 /* arithmetic of the forward passes */

@@ -1,5 +1,5 @@
 """Exact Keras ``training=True`` semantics (batch-statistic BatchNorm over the whole call, uq_techniques.py:22) on the
-tensor-core kernel: six statistics sweeps + the final run (csrc/api.cu run_fused_exact).
+tensor-core kernel: one statistics sweep per layer + the head kernel (csrc/api.cu run_fused_exact).
 
 Oracle: float64 restatement with the same dropout masks.  Tolerances are the bf16 ones of tests/test_gpu_fused.py
 (max |dp| <= 3.5e-2 under dropout; mean |dp| <= 5e-3 for n >= 64); the per-layer statistics themselves are checked much

@@ -103,7 +103,7 @@ def test_calibrated_T50_vs_oracle_with_the_same_statistics(uqk, windows, masks, 
     _use(eng, which)
     n = _n(which)
     windows, masks = windows[:n], [[m[:n] for m in mt] for mt in masks]
-    eng.calibrate(windows, n_windows=n, n_passes=2, seed=SEED)       # what bench.py does (there on 32768 windows)
+    eng.calibrate(windows, n_windows=n, n_passes=2, seed=SEED)       # what bench.py does (there: one pass over all windows)
     mean, var = eng.get_bn_stats()
     stats = [(mean[l, :b.cout].astype(np.float64), var[l, :b.cout].astype(np.float64)) for l, b in enumerate(uqk.arch.BLOCKS)]
     out = eng.mcd(windows, n_passes=T, seed=SEED, bn_mode="calibrated", precision="bf16", return_probs=True)

@@ -80,7 +80,7 @@ def flops_per_window_pass(valid_taps: bool = True) -> int:
     return total
 
 
-def dropout_threshold_u15(rate: float) -> int:
-    """15-bit integer threshold: an element is KEPT iff its 15-bit uniform draw >= threshold
-    (TF semantics: keep iff u >= rate, u in [0,1))."""
-    return int(round(rate * 32768.0))
+def dropout_threshold_u16(rate: float) -> int:
+    """16-bit integer threshold: an element is KEPT iff its 16-bit uniform draw >= threshold
+    (TF semantics: keep iff u >= rate, u in [0,1)); csrc/common.cuh ``drop_thr16``."""
+    return int(round(rate * 65536.0))

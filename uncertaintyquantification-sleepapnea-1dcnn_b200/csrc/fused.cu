@@ -21,10 +21,13 @@
 //  * Warp roles: warp 0 = weight producer, then one warp per accumulator = TMEM allocator / MMA issuer (one elected
 //    lane), 8 warps per tile = epilogue (TMEM lane quarter = warp_id % 4, two warps per quarter on alternate 16-column
 //    chunks).
-//  * Kernels in this file, all with this mapping: fused_forward_kernel<TILES,...> (one CTA per unit, no clusters),
-//    fused_pair_kernel (cta_group::2 CTA pairs, one tile per CTA, two CTAs per SM; its STAT instantiation runs the
-//    statistics sweeps of the exact batch-statistic mode) and fused_pair2_kernel (CTA pairs with two tile-pairs per
-//    pair sharing one weight stream -- the default).
+//  * Kernels (fused_kernels.cuh; one translation unit per family so that they compile in parallel), all with this
+//    mapping: fused_forward_kernel<TILES,...> (one CTA per unit, no clusters; fused_single1.cu / fused_single2.cu),
+//    fused_pair_kernel (cta_group::2 CTA pairs, one tile per CTA, two CTAs per SM; fused_pair.cu) and
+//    fused_pair2_kernel (CTA pairs with two tile-pairs per pair sharing one weight stream -- the default,
+//    fused_pair2.cu; its STAT instantiation runs the per-layer sweeps of the exact batch-statistic mode,
+//    fused_pair_stat.cu).  This file holds the host side: weight packing, epilogue tables, the exact mode's small
+//    kernels and the dispatcher.
 #include "fused_kernels.cuh"
 
 namespace uqk {

@@ -347,11 +347,10 @@ __device__ __forceinline__ uint32_t keep_extract(const uint32_t (&kb)[4], int t)
 // One 16-column chunk of the epilogue: ReLU -> BatchNorm affine (dropout scale folded) -> dropout -> bf16 store
 // (layers 1-5) or dot with the dense kernel (layer 6).  The conv bias is already in the accumulator (bias MMA step).
 //
-// Dropout: one Philox4x32-10 call per 8 channels; element e uses 15-bit field (word e>>1, half e&1, low 15 bits) and
-// is kept iff field >= thr15 = round(rate * 32768) (TF: keep iff u >= rate).  For the stored layers the compare is
-// done on both halves of a word at once -- ((w & 0x7FFF7FFF) | 0x80008000) - thr15*0x00010001 leaves the keep flag in
-// bits 15 / 31, PRMT with sign replication turns it into a 0xFFFF / 0 mask per bf16 half, and one LOP3 applies the
-// mask (and the zero-row mask) to the packed pair: 4 ALU instructions per 2 elements, no predicates.
+// Dropout: the thread's keep-flags of the layer arrive as flag words (make_keep_flags: bit-sliced Philox words or
+// injected bits, byte-lane layout); zq[] holds the flags of this chunk's four channel quads in the byte sign bits.
+// PRMT with sign replication turns two flags into the 0xFFFF / 0 masks of one bf16 pair and one LOP3 applies the mask
+// (and the zero-row mask) to the packed pair: no per-element compare, no predicates.
 template <int DROP, bool LAST, bool DBG, bool RELU = true>
 __device__ __forceinline__ void epi_chunk16(const uint32_t (&v)[16], int c0, const float* __restrict__ tab_s,
                                             const float* __restrict__ tab_h, const float* __restrict__ tab_w,
