@@ -147,6 +147,12 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
   return r;
 }
+// bf16 pair of (max(lo, 0), max(hi, 0)): the ReLU rides on the conversion
+__device__ __forceinline__ uint32_t pack_bf16x2_relu(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
@@ -721,7 +727,7 @@ __device__ __forceinline__ void epi_stats(const EpiCtx& c, const FusedArgs& a, i
   uint32_t* out32 = nullptr;
   if (kStore) {
     if (a.ckpt_out && win_ok)
-      out32 = reinterpret_cast<uint32_t*>(a.ckpt_out + (((size_t)g * a.n + win) * (cout / 8)) * kL + t0) + q;
+      out32 = reinterpret_cast<uint32_t*>(a.ckpt_out + (((size_t)g * a.n + win) * (cout / 8) + 2 * c.colhalf) * kL + t0) + q;
   }
   // software pipeline: the TMEM loads of chunk j + 1 are in flight while chunk j is processed
   uint32_t lo[8], hi[8], lo2[8], hi2[8];
@@ -743,28 +749,32 @@ __device__ __forceinline__ void epi_stats(const EpiCtx& c, const FusedArgs& a, i
       x[0][cc] = __uint_as_float(lo[o]); x[1][cc] = __uint_as_float(lo[o + 2]);
       x[2][cc] = __uint_as_float(hi[o]); x[3][cc] = __uint_as_float(hi[o + 2]);
     }
-#pragma unroll
-    for (int k = 0; k < 4; ++k)
-#pragma unroll
-      for (int cc = 0; cc < 4; ++cc) x[k][cc] = ok[k] ? fmaxf(x[k][cc], 0.f) : 0.f;
     if (kStore) {
+      // ReLU + rounding to bf16 in one conversion; padding rows are masked to zero; the statistics below are those of
+      // the rounded values.  Plane base out32 already points at this thread's first chunk (2 * colhalf planes in).
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
-        const uint32_t p0 = pack_bf16x2(x[k][0], x[k][1]), p1 = pack_bf16x2(x[k][2], x[k][3]);
+        const uint32_t okm = ok[k] ? 0xFFFFFFFFu : 0u;
+        const uint32_t p0 = pack_bf16x2_relu(x[k][0], x[k][1]) & okm, p1 = pack_bf16x2_relu(x[k][2], x[k][3]) & okm;
         x[k][0] = __uint_as_float(p0 << 16); x[k][1] = __uint_as_float(p0 & 0xFFFF0000u);
         x[k][2] = __uint_as_float(p1 << 16); x[k][3] = __uint_as_float(p1 & 0xFFFF0000u);
         if (out32 && ok[k]) {
           // a quad of lanes writes the 16 bytes (8 channels) of one row; 8 rows per store instruction = 128 contiguous bytes
-          __stcs(out32 + ((size_t)(col0 >> 3) * kL + 8 * k) * 4, p0);
-          __stcs(out32 + ((size_t)((col0 >> 3) + 1) * kL + 8 * k) * 4, p1);
+          __stcs(out32 + ((4 * j) * kL + 8 * k) * 4, p0);
+          __stcs(out32 + ((4 * j + 1) * kL + 8 * k) * 4, p1);
         }
       }
+    } else {
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc) x[k][cc] = ok[k] ? fmaxf(x[k][cc], 0.f) : 0.f;
     }
     float v[NV];
 #pragma unroll
     for (int cc = 0; cc < 4; ++cc) {
       v[cc] = (x[0][cc] + x[1][cc]) + (x[2][cc] + x[3][cc]);
-      v[4 + cc] = fmaf(x[0][cc], x[0][cc], x[1][cc] * x[1][cc]) + fmaf(x[2][cc], x[2][cc], x[3][cc] * x[3][cc]);
+      v[4 + cc] = fmaf(x[3][cc], x[3][cc], fmaf(x[2][cc], x[2][cc], fmaf(x[1][cc], x[1][cc], x[0][cc] * x[0][cc])));
     }
     if (kHead) {
       // dropout-masked column sums and kept-row counts (flags are zero on padding rows)
