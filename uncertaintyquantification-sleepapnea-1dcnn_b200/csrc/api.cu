@@ -49,6 +49,7 @@ struct Handle {
   float* d_ckpt2 = nullptr; size_t ckpt2_cap = 0;               // ... and B (outputs of layers 3 and 5)
   float* d_tables_all = nullptr; size_t tables_all_cap = 0;     // exact mode: the per-pass epilogue tables of ALL passes of the last call
   int exact_passes = 0; uint64_t exact_seed = 0; int64_t exact_n = -1;   // ... which call they belong to (guard-band re-evaluation)
+  unsigned long long* d_stats_l0 = nullptr;                     // exact mode: layer 1's (exchanged) statistics of the current call
   float* d_band_idx = nullptr; size_t band_idx_cap = 0;         // guard band: int64 positions of the windows to re-evaluate (as floats x2)
   unsigned long long* d_band_count = nullptr;
   float* d_dbg = nullptr;         // 6 x 128 x 256 debug dump of the fused kernel (tests)
@@ -211,8 +212,12 @@ constexpr size_t kExactBytesPerWindowPass = exact_buf_bytes(0) + exact_buf_bytes
 
 static int run_exact_sweeps(Handle* h, const void* x, int x_dtype, int64_t n, int pass0, int n_passes, uint64_t seed,
                             int64_t window_base, const uint32_t* mask_bits, float* frozen, float* head_sum,
-                            unsigned char* head_cnt, void* bufA, void* bufB, cudaStream_t s) {
+                            unsigned char* head_cnt, void* bufA, void* bufB, cudaStream_t s, bool reuse_l0 = false) {
+  // reuse_l0: layer 1 sees neither dropout nor another layer's normalisation, so its statistics are the same for every
+  // pass AND every chunk of passes of a call: later chunks take them from the first chunk (already exchanged over the
+  // ranks) instead of sweeping the windows again
   int rc;
+  if (!h->d_stats_l0) UQK_CUDA(cudaMalloc(&h->d_stats_l0, sizeof(unsigned long long) * 2 * kMaxCh));
   if ((rc = ensure(&h->d_tables_pass, &h->tables_pass_cap, (size_t)n_passes * kTableFloats))) return rc;
   if ((rc = ensure(&h->d_stats_pass, &h->stats_pass_cap, (size_t)n_passes * 2 * kMaxCh * 2))) return rc;
   unsigned long long* stats = reinterpret_cast<unsigned long long*>(h->d_stats_pass);
@@ -242,13 +247,16 @@ static int run_exact_sweeps(Handle* h, const void* x, int x_dtype, int64_t n, in
     p.n_layers = k + 1;
     p.ckpt_in = k >= 2 ? buf_of[k - 1] : nullptr;
     p.ckpt_out = buf_of[k];
-    if ((rc = fused_launch(p, s))) return rc;           // n == 0 (empty shard): no launch, statistics stay zero
+    const bool reuse = k == 0 && reuse_l0;
+    if (reuse) UQK_CUDA(cudaMemcpyAsync(stats, h->d_stats_l0, sizeof(unsigned long long) * 2 * kMaxCh, cudaMemcpyDeviceToDevice, s));
+    else if ((rc = fused_launch(p, s))) return rc;      // n == 0 (empty shard): no launch, statistics stay zero
     if (k == 0 && n_passes > 1 && (rc = exact_replicate_stats(stats, n_passes, s))) return rc;
-    if (exchanging &&
+    if (exchanging && !reuse &&
         h->xchg(h->xchg_user, reinterpret_cast<long long*>(stats), n_passes * 2 * kMaxCh, static_cast<void*>(s)) != 0) {
       set_error("batch-statistics exchange callback failed at layer %d", k);
       return UQK_E_STATE;
     }
+    if (k == 0 && !reuse) UQK_CUDA(cudaMemcpyAsync(h->d_stats_l0, stats, sizeof(unsigned long long) * 2 * kMaxCh, cudaMemcpyDeviceToDevice, s));
     if ((rc = exact_layer_tables(h->d_blobs, stats, (double)stat_windows * kL, k, n_passes, h->d_tables_pass,
                                  (h->variant & 14) ? nullptr : h->d_err /* perf-decomposition switches compute garbage */, s))) return rc;
     if (frozen && (rc = exact_layer_average(stats, (double)stat_windows * kL, k, n_passes, frozen, s))) return rc;
@@ -302,7 +310,8 @@ static int run_fused_exact(Handle* h, const void* x, int x_dtype, int64_t n, int
   if ((rc = ensure(&h->d_tables_all, &h->tables_all_cap, (size_t)n_passes * kTableFloats))) return rc;
   for (int g0 = 0; g0 < n_passes; g0 += chunk) {
     const int gc = std::min(chunk, n_passes - g0);
-    if ((rc = run_exact_sweeps(h, x, x_dtype, n, g0, gc, seed, window_base, mask_bits, nullptr, h->d_head_sum, head_cnt, h->d_ckpt, h->d_ckpt2, s))) return rc;
+    if ((rc = run_exact_sweeps(h, x, x_dtype, n, g0, gc, seed, window_base, mask_bits, nullptr, h->d_head_sum, head_cnt, h->d_ckpt, h->d_ckpt2, s,
+                               /*reuse_l0=*/g0 > 0))) return rc;
     // keep every pass's BatchNorm affine: uqk_refine_band re-evaluates guard-band windows with exactly these statistics
     UQK_CUDA(cudaMemcpyAsync(h->d_tables_all + (size_t)g0 * kTableFloats, h->d_tables_pass, sizeof(float) * (size_t)gc * kTableFloats,
                              cudaMemcpyDeviceToDevice, s));
@@ -363,7 +372,7 @@ int uqk_destroy(uqk_handle* hh) {
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
   void* ptrs[] = {h->d_blobs, h->d_packed, h->d_packed_pair, h->d_tables_inf, h->d_table_mcd, h->d_frozen, h->d_stats, h->d_affine,
-                  h->d_accum, h->d_tables_all, h->d_band_idx, h->d_band_count, h->d_x32, h->d_act[0], h->d_act[1], h->d_probs_tmp, h->d_dbg, h->d_tables_pass, h->d_stats_pass, h->d_head_sum, h->d_head_cnt, h->d_ckpt, h->d_ckpt2};
+                  h->d_accum, h->d_tables_all, h->d_stats_l0, h->d_band_idx, h->d_band_count, h->d_x32, h->d_act[0], h->d_act[1], h->d_probs_tmp, h->d_dbg, h->d_tables_pass, h->d_stats_pass, h->d_head_sum, h->d_head_cnt, h->d_ckpt, h->d_ckpt2};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (h->h_err) cudaFreeHost(h->h_err);
   cudaGetLastError();

@@ -1745,10 +1745,15 @@ struct Pair2Cfg {
   static constexpr int kTabFloats = 2 * 512 + 128;
   static constexpr int oTab = oRing + NSLOTS * kSlot;
   static constexpr int oBar = oTab + 2 * kTabFloats * 4;
-  static constexpr int kNumBars = 3 * NSLOTS + 10; // full, empty, peer_full [NSLOTS]; acc[2], act[2], peer_act[2], in[2], tfree[2] (sweeps)
-  static constexpr int oMisc = oBar + 8 * kNumBars;
-  static constexpr int oAlo = oMisc + 16 + 64;
-  static constexpr int oProbs = (oAlo + 4 * 392 + 15) & ~15;   // probs[4][n_groups]
+  static constexpr int kNumBars = 2 * NSLOTS + 8;  // full, empty [NSLOTS]; acc[2], act[2], in[2], tfree[2] (the last two: sweeps)
+  static constexpr int oMisc = oBar + 8 * kNumBars;            // tmem ptr (16 B)
+  static constexpr int oAlo = oMisc + 16;                      // A-descriptor low words, one per (layer, step)
+  static constexpr int oZ = oAlo + 4 * 392;                    // zpart[2][2][4] head partials (64 B)
+  static constexpr int oProbs = (oZ + 64 + 15) & ~15;          // probs[4][n_groups]
+  // statistics sweeps use neither zpart nor probs: their [2 x 256] u64 accumulators start at oZ, which lets a ninth ring
+  // slot fit the 227 KB of shared memory exactly
+  static constexpr int oStats = oZ;
+  static_assert(oZ % 8 == 0, "statistics accumulators are 64-bit");
 };
 
 // STAT = true: statistics sweep of the exact batch-statistic mode (see FusedArgs::n_layers, stat_epilogue_loop): the
@@ -1767,15 +1772,13 @@ fused_pair2_kernel(const FusedArgs a) {
 
   const uint32_t bar_full = s_base + Cfg::oBar;
   const uint32_t bar_empty = bar_full + 8 * NSLOTS;
-  const uint32_t bar_peer_full = bar_empty + 8 * NSLOTS;        // leader only
-  const uint32_t bar_acc = bar_peer_full + 8 * NSLOTS;          // [2]
+  const uint32_t bar_acc = bar_empty + 8 * NSLOTS;              // [2]
   const uint32_t bar_act = bar_acc + 16;                        // [2] leader only: its own epilogue threads
-  const uint32_t bar_peer_act = bar_act + 16;                   // [2] leader only: one remote arrive per layer
-  const uint32_t bar_in = bar_peer_act + 16;                    // [2] statistics sweeps: the tile's input planes have landed
+  const uint32_t bar_in = bar_act + 16;                         // [2] statistics sweeps: the tile's input planes have landed
   const uint32_t bar_tfree = bar_in + 16;                       // [2] pipelined sweeps: accumulator read out (leader: + peer relay)
   const bool pipe = STAT && a.first_layer >= 2 && a.pipelined;  // pipelined single-stream sweep (stat_pipelined_loop)
   volatile uint32_t* tmem_ptr = reinterpret_cast<volatile uint32_t*>(smem + Cfg::oMisc);
-  float* zpart = reinterpret_cast<float*>(smem + Cfg::oMisc + 16);
+  float* zpart = reinterpret_cast<float*>(smem + Cfg::oZ);
   uint32_t* s_alo = reinterpret_cast<uint32_t*>(smem + Cfg::oAlo);
   float* probs_s = reinterpret_cast<float*>(smem + Cfg::oProbs);
 
@@ -1800,10 +1803,10 @@ fused_pair2_kernel(const FusedArgs a) {
     // BOTH tile-pairs have consumed it (two commits)
     const uint32_t extra = rank == 0 ? 1u : 0u;
     for (int i = 0; i < NSLOTS; ++i) {
-      mbar_init(bar_full + 8 * i, 1 + extra); mbar_init(bar_empty + 8 * i, pipe ? 1 : 2); mbar_init(bar_peer_full + 8 * i, 1);
+      mbar_init(bar_full + 8 * i, 1 + extra); mbar_init(bar_empty + 8 * i, pipe ? 1 : 2);
     }
     for (int i = 0; i < 2; ++i) {
-      mbar_init(bar_acc + 8 * i, 1); mbar_init(bar_act + 8 * i, Cfg::kEpiThreads / 32 + extra); mbar_init(bar_peer_act + 8 * i, 1);
+      mbar_init(bar_acc + 8 * i, 1); mbar_init(bar_act + 8 * i, Cfg::kEpiThreads / 32 + extra);
       mbar_init(bar_in + 8 * i, 1);
       mbar_init(bar_tfree + 8 * i, Cfg::kEpiThreads / 32 + extra);
     }
@@ -1953,13 +1956,13 @@ fused_pair2_kernel(const FusedArgs a) {
       PipeGeo pg;
       pg.act_base = s_base + Cfg::oAct; pg.bar_in = bar_in; pg.bar_acc = bar_acc; pg.bar_act = bar_act; pg.bar_tfree = bar_tfree;
       pg.tmem_base = tmem_base; pg.rank = rank; pg.pair_id = pair_id; pg.n_pairs = n_pairs;
-      stat_pipelined_loop<DROP, Cfg::kEpiThreads>(c, a, pg, reinterpret_cast<unsigned long long*>(smem + Cfg::oProbs));
+      stat_pipelined_loop<DROP, Cfg::kEpiThreads>(c, a, pg, reinterpret_cast<unsigned long long*>(smem + Cfg::oStats));
     } else if constexpr (STAT) {
       StatGeo geo;
       geo.act_base = s_base + Cfg::oAct + c.tl * kActBytes;
       geo.bar_in = bar_in + 8 * c.tl;
       geo.rank = rank; geo.pair_id = pair_id; geo.n_pairs = n_pairs; geo.all_threads = 2 * Cfg::kEpiThreads;
-      stat_epilogue_loop<DROP, Cfg::kEpiThreads, Cfg::kWpu>(c, a, geo, reinterpret_cast<unsigned long long*>(smem + Cfg::oProbs), n_acc);
+      stat_epilogue_loop<DROP, Cfg::kEpiThreads, Cfg::kWpu>(c, a, geo, reinterpret_cast<unsigned long long*>(smem + Cfg::oStats), n_acc);
     } else
     for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
       // unit = 8 windows: tile-pair tl covers windows 4*tl .. 4*tl+3; this CTA (rank) takes 2 of them
@@ -2045,8 +2048,8 @@ static int launch_pair2_variant(const FusedParams& p, cudaStream_t s) {
     }
   }
   // the probability buffer of the fused reductions doubles as the statistics accumulator [2 x 256] u64 of a sweep
-  const size_t smem = (size_t)Cfg::oProbs + (STAT ? (size_t)2 * kMaxCh * sizeof(unsigned long long)
-                                                  : (p.no_smem_probs ? 0 : (size_t)4 * p.n_groups * sizeof(float)));
+  const size_t smem = STAT ? (size_t)Cfg::oStats + (size_t)2 * kMaxCh * sizeof(unsigned long long)
+                           : (size_t)Cfg::oProbs + (p.no_smem_probs ? 0 : (size_t)4 * p.n_groups * sizeof(float));
   if (smem > 227 * 1024) return UQK_E_SHAPE;
   int dev = 0, sms = 148;
   UQK_CUDA(cudaGetDevice(&dev));
