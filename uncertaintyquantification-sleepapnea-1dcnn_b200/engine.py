@@ -20,6 +20,8 @@ _PREC = {"bf16": _lib.PREC_BF16_TC, "bf16_tc": _lib.PREC_BF16_TC, "fp32": _lib.P
 # measured |d mean_pred| of the bf16 path against the float64 oracle is <= 2.4e-3 over both test models
 # (profiles/r02_parity_distribution.json), so 5e-3 leaves a factor 2.
 GUARD_DELTA = 5e-3
+# Largest calibration set swept in one go (scratch: 53,760 B per window, held by the handle); UQK_CALIB_MAX_WINDOWS overrides.
+CALIB_MAX_WINDOWS = int(os.environ.get("UQK_CALIB_MAX_WINDOWS", "2000000"))
 _BN = {"inference": _lib.BN_INFERENCE, "frozen": _lib.BN_INFERENCE, "batch": _lib.BN_BATCH,
        "calibrated": _lib.BN_CALIBRATED}
 
@@ -172,6 +174,10 @@ class Engine:
         with torch.cuda.device(self.device):
             n = len(x)
             xs = x
+            if n_windows is None and n > CALIB_MAX_WINDOWS:
+                # the sweeps hand one pass of activations through HBM (54 KB per window): beyond ~2 M windows that does
+                # not fit next to the data, so the statistics come from a strided subset of that size (error ~1e-4)
+                n_windows = CALIB_MAX_WINDOWS
             if n_windows is not None and 0 < int(n_windows) < n:
                 if sampling == "strided":
                     xs = x[::max(1, n // int(n_windows))][:int(n_windows)]
