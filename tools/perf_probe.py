@@ -7,6 +7,8 @@ sys.path.insert(0, ROOT)
 PKG = "uncertaintyquantification-sleepapnea-1dcnn_b200"
 import numpy as np, torch
 pkg = importlib.import_module(PKG)
+if os.environ.get("UQK_PROBE_LIB"):      # A/B runs of two builds on the same box (bring-up only)
+    importlib.import_module(PKG + "._lib").LIB_PATH = os.path.join(ROOT, PKG, os.environ["UQK_PROBE_LIB"])
 engine = importlib.import_module(PKG + ".engine")
 syn = pkg.synthetic
 

@@ -322,9 +322,15 @@ static int run_fused_exact(Handle* h, const void* x, int x_dtype, int64_t n, int
   return want_metrics ? launch_reduce(probs, n_passes, n, out, s) : UQK_OK;
 }
 
+#ifdef UQK_TIMELINE
+long long* g_uqk_timeline = nullptr;   // timeline build (tools/timeline_probe.py) only
+#endif
 }  // namespace uqk
 
 using namespace uqk;
+#ifdef UQK_TIMELINE
+extern "C" void uqk_debug_set_timeline(long long* dev_buf) { uqk::g_uqk_timeline = dev_buf; }
+#endif
 
 extern "C" {
 

@@ -51,7 +51,9 @@ static inline float bf16_to_f32(uint16_t h) {
 // Host-side packing of one member into the shared-memory image the kernel streams:
 //   layer l, step s, plane p (K elements 8p..8p+7 of the step), output channel n, element kk:
 //   dst[(w_off/2) + ((s*2 + p)*cout + n)*8 + kk]
-//   layers 2..6: tap j = s / (cin/16), slab i = s % (cin/16), channel c = 16 i + 8 p + kk  -> W[j][c][n]
+//   layers 2..6: slab i = s / k, tap j = s % k (slab-major: the steps that read the first input channels come first, so
+//                a layer can start while the previous layer's epilogue is still writing the later channels),
+//                channel c = 16 i + 8 p + kk                                               -> W[j][c][n]
 //   layer 1    : tap j = 2 s + p, channel kk (<4)                                        -> W[j][kk][n], else 0
 //   bias step (s = nconv): plane 0, kk = 0 -> bf16(bias[n]), kk = 1 -> bf16(bias[n] - hi)  (hi + lo split: the MMA
 //   adds the bias with 16 mantissa bits because the A operand of this step is the constant [1, 1, 0, ...] plane)
@@ -75,8 +77,7 @@ void fused_pack_member(const float* blob, uint16_t* dst) {
               const int j = 2 * s + p;
               if (j < b.k && kk < b.cin) o = f32_to_bf16_rne(w[((size_t)j * b.cin + kk) * b.cout + n]);
             } else {
-              const int slabs = b.cin / 16;
-              const int j = s / slabs, i = s % slabs;
+              const int j = s % b.k, i = s / b.k;
               const int c = 16 * i + 8 * p + kk;
               o = f32_to_bf16_rne(w[((size_t)j * b.cin + c) * b.cout + n]);
             }
@@ -254,7 +255,7 @@ int fused_launch(const FusedParams& p, cudaStream_t s) {
   // variant >> 4: 0 / 3 = CTA pairs with two tiles per CTA (default), 2 = CTA pairs with one tile per CTA and two CTAs
   // per SM, 4 = two tiles per CTA, 1 = one tile per CTA.  Every configuration falls through to a smaller one when T
   // (or M) probabilities per window do not fit its shared memory.
-  const int v = p.variant >> 4;
+  const int v = (p.variant >> 4) & 15;
   if (p.stats) return fused_launch_pair_stat(p, s);   // statistics sweeps exist in the CTA-pair kernel only
   int rc = UQK_E_SHAPE;
   if (v == 0 || v == 3) rc = fused_launch_pair2(p, s);

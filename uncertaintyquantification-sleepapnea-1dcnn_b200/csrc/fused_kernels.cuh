@@ -237,7 +237,21 @@ struct FusedArgs {
   const uint4* ckpt_in;           // post-ReLU output of layer first_layer-1 (first_layer >= 2), or null
   int first_layer;                // first layer this sweep computes; 0 = start from the windows
   int pipelined;                  // 1: resumed sweeps run the three-stage pipeline over 4-window units (option exact_pipelined)
+#ifdef UQK_TIMELINE
+  long long* tl_buf;              // tools/timeline_probe.py: clock64 stamps [tile-pair][16 passes][6 layers][8 events] of one unit
+#endif
 };
+#ifdef UQK_TIMELINE
+extern long long* g_uqk_timeline;   // api.cu, set through uqk_debug_set_timeline (timeline build only, not part of the C-ABI)
+#define UQK_TL(buf, tl, g, L, ev) do { if ((buf) && (g) < 16) (buf)[((((tl) * 16 + (g)) * 6 + (L)) << 3) + (ev)] = clock64(); } while (0)
+#else
+#define UQK_TL(buf, tl, g, L, ev) do { } while (0)
+#endif
+#ifdef UQK_TIMELINE
+#define UQK_TLE(c, g, L, ev) UQK_TL((c).tlb, (c).tl, g, L, ev)
+#else
+#define UQK_TLE(c, g, L, ev) do { } while (0)
+#endif
 
 // dropout source of the epilogue
 constexpr int kDropNone = 0, kDropPhilox = 1, kDropBits = 2;
@@ -469,12 +483,16 @@ struct EpiCtx {
   DropTie tie = {0u, 0u};    // dropout tie-break bytes of this thread's (window, pass, row, column half), see common.cuh
   bool strong_sync = false;  // pair kernels: release / acquire cluster signalling (variant bit 0)
   uint32_t remote_act = 0;   // pair kernels, peer CTA: cluster address of the leader's "peer activations ready" barrier
+  uint32_t bar_half = 0, remote_half = 0;   // two-tile pair kernel: "first half of the output channels is in place" (early_half)
   int t, colhalf, tid_t, we, lane, quarter, slot_w, tl;
   bool row_valid;
   float* tab;
   float* tab_w;
   float* zp;
   int* err_flag;
+#ifdef UQK_TIMELINE
+  long long* tlb = nullptr;  // non-null in the one unit whose schedule is recorded (lane 0 of the tile's first and last warp)
+#endif
 };
 
 // "this tile's activations are in place": local arrive (the issuer lives in this CTA), or -- peer CTA of a pair -- one
@@ -489,6 +507,29 @@ __device__ __forceinline__ void epi_signal_act(const EpiCtx& c) {
   } else {
     named_bar_sync(1 + c.tl, EPI_THREADS);
     if (c.tid_t == 0) mbar_arrive_remote(c.remote_act, c.strong_sync);
+  }
+}
+
+// Early start of the next layer (two-tile pair kernel).  The K steps of a layer are slab-major (all taps of input
+// channels 0..15, then 16..31, ...), and every epilogue warp walks its 16-column chunks in ascending order, so after
+// half_chunks(L) chunks per warp the first 2 * half_chunks(L) slabs of the next layer's input are complete: the epilogue
+// signals bar_half there, and the next layer's issuer starts on those slabs while the remaining chunks are still being
+// written (different planes).  The accumulator columns the early MMAs overwrite must already have been read:
+//   layer 1 -> 2: layer 1 accumulates at column 128 ([128,256); read first: [128,192)), layer 2 writes [0,192)
+//   layer 3 -> 4: layer 3 at [0,224), read first [0,128); layer 4 writes [0,96)
+//   layer 5 -> 6: layer 5 at [0,256), read first [0,128); layer 6 writes [0,96)
+// Layers 2 -> 3 and 4 -> 5 do not fit (the unread half plus the next accumulator exceed the 256 columns of a tile-pair).
+__host__ __device__ constexpr bool early_producer(int l) { return l == 0 || l == 2 || l == 4; }
+__host__ __device__ constexpr int half_chunks(int l) { return (((fl_cout(l) / 32 + 1) / 2) + 1) & ~1; }   // per warp: 2, 4, 4
+__host__ __device__ constexpr int acc_col(int l, bool early) { return (early && l == 0) ? 128 : 0; }
+template <int EPI_THREADS>
+__device__ __forceinline__ void epi_signal_half(const EpiCtx& c) {
+  if (c.remote_half == 0) {
+    __syncwarp();
+    if (c.lane == 0) mbar_arrive(c.bar_half);
+  } else {
+    named_bar_sync(1 + c.tl, EPI_THREADS);
+    if (c.tid_t == 0) mbar_arrive_remote(c.remote_half, c.strong_sync);
   }
 }
 
@@ -540,12 +581,15 @@ __device__ __forceinline__ void make_keep_flags(const EpiCtx& c, const FusedArgs
   }
 }
 
-template <int L, int DROP, bool DBG, int EPI_THREADS>
+template <int L, int DROP, bool DBG, int EPI_THREADS, bool EARLY = false>
 __device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, const float* __restrict__ tab_g, int g,
                                           long long win, uint32_t& n_acc, float* probs_s, float* dbg_base) {
   constexpr int cout = fl_cout(L);
   constexpr int my = cout / 32;            // 16-column chunks owned by this warp (chunks colhalf, colhalf+2, ...)
+  constexpr int kHalfJ = (EARLY && early_producer(L)) ? half_chunks(L) : 0;   // signal bar_half after this many chunks
+  const uint32_t taddr = c.taddr + (uint32_t)acc_col(L, EARLY);
   constexpr bool kLastLayer = (L == kBlocks - 1);
+  if (c.we == 0) UQK_TLE(c, g, L, 6);
   // stage this layer's scale / shift (double buffered) while the MMAs run
   float* tab_s = c.tab + (L & 1) * 512;
   float* tab_h = tab_s + 256;
@@ -564,6 +608,7 @@ __device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, c
 
   // one warp polls the accumulator barrier; the others sleep in the named barrier (no issue slots burnt)
   if (c.we == 0) {
+    UQK_TLE(c, g, L, 2);
     mbar_wait2(c.bar_acc, n_acc & 1, c.err_flag, 4);
     tc_fence_after();
     tc_fence_before();
@@ -571,6 +616,7 @@ __device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, c
   ++n_acc;
   named_bar_sync(1 + c.tl, EPI_THREADS);
   tc_fence_after();
+  if (c.we == 0) UQK_TLE(c, g, L, 3);
 
   float* dbg = nullptr;
   if (DBG) {
@@ -579,11 +625,11 @@ __device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, c
   float zacc = 0.f;
   // software pipeline: the TMEM load of the next chunk is in flight while the current one is processed
   uint32_t va[16], vb[16];
-  tmem_ld16(c.taddr + (uint32_t)(16 * c.colhalf), va);
+  tmem_ld16(taddr + (uint32_t)(16 * c.colhalf), va);
 #pragma unroll
   for (int j = 0; j < my; j += 2) {
     tmem_wait16(va);
-    if (j + 1 < my) tmem_ld16(c.taddr + (uint32_t)(16 * (c.colhalf + 2 * (j + 1))), vb);
+    if (j + 1 < my) tmem_ld16(taddr + (uint32_t)(16 * (c.colhalf + 2 * (j + 1))), vb);
     {
       const uint32_t zq[4] = {keep_extract(kb, 4 * j), keep_extract(kb, 4 * j + 1), keep_extract(kb, 4 * j + 2), keep_extract(kb, 4 * j + 3)};
       epi_chunk16<DROP, kLastLayer, DBG>(va, 16 * (c.colhalf + 2 * j), tab_s, tab_h, c.tab_w, c.act_row, c.row_valid, row_mask,
@@ -591,10 +637,16 @@ __device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, c
     }
     if (j + 1 < my) {
       tmem_wait16(vb);
-      if (j + 2 < my) tmem_ld16(c.taddr + (uint32_t)(16 * (c.colhalf + 2 * (j + 2))), va);
+      if (j + 2 < my) tmem_ld16(taddr + (uint32_t)(16 * (c.colhalf + 2 * (j + 2))), va);
       const uint32_t zq[4] = {keep_extract(kb, 4 * j + 4), keep_extract(kb, 4 * j + 5), keep_extract(kb, 4 * j + 6), keep_extract(kb, 4 * j + 7)};
       epi_chunk16<DROP, kLastLayer, DBG>(vb, 16 * (c.colhalf + 2 * (j + 1)), tab_s, tab_h, c.tab_w, c.act_row, c.row_valid,
                                                row_mask, thr2, c.c0w, (uint32_t)g, c2, c.k0, c.k1, zq, zacc, dbg);
+    }
+    if (kHalfJ != 0 && j + 2 == kHalfJ) {
+      // the first 2 * kHalfJ slabs of the next layer's input are in place and their accumulator columns have been read
+      fence_proxy_async();
+      tc_fence_before();
+      epi_signal_half<EPI_THREADS>(c);
     }
   }
 
@@ -618,6 +670,7 @@ __device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, c
       if (a.probs && win < a.n) a.probs[(size_t)g * a.n + win] = p;
     }
   }
+  UQK_TLE(c, g, L, c.we == 0 ? 4 : 5);
 }
 
 // ---- statistics epilogue (exact batch-statistic mode) -------------------------------------------------------------
@@ -1184,7 +1237,7 @@ fused_forward_kernel(const FusedArgs a) {
     if (sidx == fl.nconv) { a_off = (uint32_t)kOnesPlane * kPlaneBytes + 4u * 16u; a_lbo = 16u; }          // bias step
     else if (l == 0) { a_off = (uint32_t)(2 * sidx + 1) * 16u; a_lbo = 16u; }                               // tap pair
     else {
-      const int slabs = fl.cinp / 16, tap = sidx / slabs, slab = sidx % slabs;
+      const int tap = sidx % fl.taps, slab = sidx / fl.taps;   // slab-major K order (see fused_pack_member)
       a_off = (uint32_t)(2 * slab) * kPlaneBytes + (uint32_t)(tap - fl.halo + 4) * 16u;                     // shifted rows
       a_lbo = kPlaneBytes;
     }
@@ -1368,7 +1421,7 @@ struct PairCfg {
   static constexpr int oProbs = oAlo + 4 * 392;    // probs[2][n_groups]
 };
 
-__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity, int* err_flag, int code, bool strong = false) {
+static __device__ __noinline__ void mbar_wait_cluster_slow(uint32_t bar, uint32_t parity, int* err_flag, int code, bool strong) {
   long long t0 = 0;
   for (;;) {
     uint32_t ok;
@@ -1416,45 +1469,98 @@ __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity,
   }
 }
 
-template <int L, int NSLOTS, typename Cfg>
+// Cluster-scope wait of the MMA issuers.  Fast path: ONE try_wait (it suspends inside the instruction for up to
+// kWaitHintNs, so in practice it returns exactly when the phase completes); the polling loop with the watchdog is a
+// separate function, which keeps the issuer's per-stage instruction stream short (it is the latency-critical warp:
+// every stage of 2-3 MMAs passes through it).
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity, int* err_flag, int code, bool strong = false) {
+  uint32_t ok;
+  if (strong)
+    asm volatile("{\n\t.reg .pred p;\n\t"
+                 "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2, %3;\n\t"
+                 "selp.b32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(bar), "r"(parity), "r"(kWaitHintNs) : "memory");
+  else
+    asm volatile("{\n\t.reg .pred p;\n\t"
+                 "mbarrier.try_wait.parity.relaxed.cluster.shared::cta.b64 p, [%1], %2, %3;\n\t"
+                 "selp.b32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(bar), "r"(parity), "r"(kWaitHintNs) : "memory");
+  if (!ok) mbar_wait_cluster_slow(bar, parity, err_flag, code, strong);
+}
+
+// ONE = true: called by a single thread (the two-tile pair kernel's leader: lane 0 of the issuer warp walks the schedule
+// alone -- no election, no warp re-convergence per stage); ONE = false: called by a converged warp, one elected lane issues.
+// EARLY = true (two-tile pair kernel, all six layers in one launch): layers 2, 4 and 6 start on the first half of their
+// input slabs as soon as the previous layer's epilogue has signalled bar_half (see early_producer) and wait for the full
+// hand-off (bar_act) only before the first step that reads a later slab; layer 1 accumulates at column 128.
+template <int L, int NSLOTS, typename Cfg, bool ONE = false, bool EARLY = false>
 __device__ __forceinline__ void issue_layer_pair(uint32_t s_base, uint32_t tmem_base, const uint32_t* s_alo,
                                                  uint32_t bar_full, uint32_t bar_empty, uint32_t bar_peer_full,
                                                  uint32_t bar_acc, uint32_t bar_act, uint32_t bar_peer_act, uint32_t& it,
-                                                 uint32_t& n_act, int* err_flag, int flags, uint32_t a_tile = 0u) {
+                                                 uint32_t& n_act, int* err_flag, int flags, uint32_t a_tile = 0u,
+                                                 long long* tlp = nullptr, uint32_t bar_half = 0u, uint32_t* n_half = nullptr) {
   const bool no_mma = (flags & 8) != 0, strong = (flags & 1) != 0;   // debug switch / release-acquire cluster signalling
   constexpr FusedLayer fl = fused_layer(L);
   constexpr uint32_t kHi = (128u >> 4) | (1u << 14);
   constexpr uint32_t kBLbo = ((uint32_t)((fl.cout / 2) * 16) >> 4) << 16;
   constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(fl.cout >> 3) << 17) | ((256u >> 4) << 24);
   constexpr int kLast = fl.nsteps - (fl.nstages - 1) * fl.sps;
-  mbar_wait_cluster(bar_act, n_act & 1, err_flag, 2, strong);      // 8 local warp arrivals + 1 relayed from the peer
-  ++n_act;
+  // ring position of the layer's first stage; advanced incrementally (no division per stage)
+  uint32_t slot = it % NSLOTS, ph = (it / NSLOTS) & 1;
+  const uint32_t ring_lo = ((s_base + Cfg::oRing) >> 4) | kBLbo;    // shared-memory addresses are < 2^18: no carry into the LBO field
+  const uint32_t* alo = s_alo + fl_step_base(L);
+  // early start: this layer's first kHalfSt stages read only the slabs the previous epilogue signals with bar_half
+  constexpr bool kEarly = EARLY && L >= 1 && early_producer(L - 1);
+  constexpr int kHalfSt = kEarly ? (2 * half_chunks(L >= 1 ? L - 1 : 0) * fl.taps) / fl.sps : 0;
+  static_assert(!kEarly || (kHalfSt > 0 && kHalfSt < fl.nstages), "early start: the split must fall inside the layer");
+  tmem_base += (uint32_t)acc_col(L, EARLY);
+  if (kEarly) {
+    mbar_wait_cluster(bar_half, *n_half & 1, err_flag, 7, strong);
+    ++*n_half;
+  } else {
+    mbar_wait_cluster(bar_act, n_act & 1, err_flag, 2, strong);      // 8 local warp arrivals + 1 relayed from the peer
+    ++n_act;
+  }
   tc_fence_after();
+#ifdef UQK_TIMELINE
+  if (tlp) tlp[0] = clock64();
+#endif
 #pragma unroll 1
-  for (int st = 0; st < fl.nstages; ++st, ++it) {
-    const int slot = it % NSLOTS;
-    const uint32_t ph = (it / NSLOTS) & 1;
+  for (int st = 0; st < fl.nstages; ++st) {
+    // A-descriptor low words of the stage: read before the wait, so that the load latency hides behind it
+    uint32_t av[fl.sps];
+#pragma unroll
+    for (int sl = 0; sl < fl.sps; ++sl) av[sl] = alo[st * fl.sps + sl] + a_tile;   // s_alo has 392 entries: a partial last stage reads past its layer, never past the array
+    if (kEarly && st == kHalfSt) {
+      mbar_wait_cluster(bar_act, n_act & 1, err_flag, 2, strong);    // the rest of the input is in place
+      ++n_act;
+      tc_fence_after();
+    }
     mbar_wait_cluster(bar_full + 8 * slot, ph, err_flag, 3, strong);   // own half landed (tx) + peer's half (relayed arrive)
     tc_fence_after();
     const int nst = (st == fl.nstages - 1) ? kLast : fl.sps;
-    const uint32_t b_lo0 = (((s_base + Cfg::oRing + slot * Cfg::kSlot) >> 4) & 0x3FFFu) | kBLbo;
-    if (elect_one()) {
-      const uint32_t* alo = s_alo + fl_step_base(L) + st * fl.sps;
+    const uint32_t b_lo0 = ring_lo + slot * (uint32_t)(Cfg::kSlot >> 4);
+    if (ONE || elect_one()) {
       if (!no_mma) {
 #pragma unroll
         for (int sl = 0; sl < fl.sps; ++sl) {
           if (sl < nst) {
             const uint64_t bdesc = mk64(b_lo0 + (uint32_t)sl * (uint32_t)(fl.step_bytes >> 5), kHi);
-            umma_bf16_2cta(tmem_base, mk64(alo[sl] + a_tile, kHi), bdesc, kIdesc, (st > 0 || sl > 0) ? 1u : 0u);
+            umma_bf16_2cta(tmem_base, mk64(av[sl], kHi), bdesc, kIdesc, (st > 0 || sl > 0) ? 1u : 0u);
           }
         }
       }
       umma_commit_2cta(bar_empty + 8 * slot);   // both CTAs' ring slots are free once these MMAs have read them
     }
-    __syncwarp();
+    if (!ONE) __syncwarp();
+    if (++slot == NSLOTS) { slot = 0; ph ^= 1u; }
   }
-  if (elect_one()) umma_commit_2cta(bar_acc);   // both CTAs' accumulators complete
-  __syncwarp();
+  it += fl.nstages;
+  if (ONE || elect_one()) umma_commit_2cta(bar_acc);   // both CTAs' accumulators complete
+  if (!ONE) __syncwarp();
+#ifdef UQK_TIMELINE
+  if (tlp) tlp[1] = clock64();
+#endif
 }
 
 template <int L, int NSLOTS>
@@ -1505,7 +1611,7 @@ fused_pair_kernel(const FusedArgs a) {
     if (sidx == fl.nconv) { a_off = (uint32_t)kOnesPlane * kPlaneBytes + 4u * 16u; a_lbo = 16u; }
     else if (l == 0) { a_off = (uint32_t)(2 * sidx + 1) * 16u; a_lbo = 16u; }
     else {
-      const int slabs = fl.cinp / 16, tap = sidx / slabs, slab = sidx % slabs;
+      const int tap = sidx % fl.taps, slab = sidx / fl.taps;   // slab-major K order (see fused_pack_member)
       a_off = (uint32_t)(2 * slab) * kPlaneBytes + (uint32_t)(tap - fl.halo + 4) * 16u;
       a_lbo = kPlaneBytes;
     }
@@ -1792,7 +1898,7 @@ fused_pair2_kernel(const FusedArgs a) {
     if (sidx == fl.nconv) { a_off = (uint32_t)kOnesPlane * kPlaneBytes + 4u * 16u; a_lbo = 16u; }
     else if (l == 0) { a_off = (uint32_t)(2 * sidx + 1) * 16u; a_lbo = 16u; }
     else {
-      const int slabs = fl.cinp / 16, tap = sidx / slabs, slab = sidx % slabs;
+      const int tap = sidx % fl.taps, slab = sidx / fl.taps;   // slab-major K order (see fused_pack_member)
       a_off = (uint32_t)(2 * slab) * kPlaneBytes + (uint32_t)(tap - fl.halo + 4) * 16u;
       a_lbo = kPlaneBytes;
     }
@@ -1807,7 +1913,7 @@ fused_pair2_kernel(const FusedArgs a) {
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar_acc + 8 * i, 1); mbar_init(bar_act + 8 * i, Cfg::kEpiThreads / 32 + extra);
-      mbar_init(bar_in + 8 * i, 1);
+      mbar_init(bar_in + 8 * i, STAT ? 1 : Cfg::kEpiThreads / 32 + extra);   // sweeps: input planes landed; else: bar_half (early start)
       mbar_init(bar_tfree + 8 * i, Cfg::kEpiThreads / 32 + extra);
     }
     fence_barrier_init();
@@ -1897,18 +2003,31 @@ fused_pair2_kernel(const FusedArgs a) {
     } else if (rank == 0) {
       // ---- leader: one MMA-issuer warp per tile-pair.  Both walk the same weight stream; they drift apart at layer
       //      boundaries (one waits for its epilogue while the other keeps the tensor pipe busy), bounded by the ring.
-      uint32_t it = 0, n_act = 0;
+      uint32_t it = 0, n_act = 0, n_half = 0;
+      const uint32_t b_half = bar_in + 8 * tl;
       const uint32_t tm = tmem_base + (uint32_t)tl * 256u;
       const uint32_t a_tile = (uint32_t)tl * (uint32_t)(kActBytes >> 4);
       const uint32_t b_acc = bar_acc + 8 * tl, b_act = bar_act + 8 * tl;
       for (long long unit = pair_id; unit < a.n_units; unit += n_pairs) {
         for (int g = 0; g < a.n_groups; ++g) {
-          if (!STAT || a.first_layer <= 0) issue_layer_pair<0, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, a.variant, a_tile);
-          if (!STAT || (a.n_layers > 1 && a.first_layer <= 1)) issue_layer_pair<1, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, a.variant, a_tile);
-          if (!STAT || (a.n_layers > 2 && a.first_layer <= 2)) issue_layer_pair<2, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, a.variant, a_tile);
-          if (!STAT || (a.n_layers > 3 && a.first_layer <= 3)) issue_layer_pair<3, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, a.variant, a_tile);
-          if (!STAT || (a.n_layers > 4 && a.first_layer <= 4)) issue_layer_pair<4, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, a.variant, a_tile);
-          if (!STAT || (a.n_layers > 5 && a.first_layer <= 5)) issue_layer_pair<5, NSLOTS, Cfg>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, a.variant, a_tile);
+#ifdef UQK_TIMELINE
+          if (!STAT) {
+            long long* tb = (a.tl_buf && blockIdx.x == 0 && unit == pair_id + (long long)((a.variant >> 12) & 15) * n_pairs && g < 16 && lane == 0) ? a.tl_buf + ((tl * 16 + g) * 6 << 3) : nullptr;
+            issue_layer_pair<0, NSLOTS, Cfg, false, true>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, a.variant, a_tile, tb, b_half, &n_half);
+            issue_layer_pair<1, NSLOTS, Cfg, false, true>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, a.variant, a_tile, tb ? tb + 8 : tb, b_half, &n_half);
+            issue_layer_pair<2, NSLOTS, Cfg, false, true>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, a.variant, a_tile, tb ? tb + 16 : tb, b_half, &n_half);
+            issue_layer_pair<3, NSLOTS, Cfg, false, true>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, a.variant, a_tile, tb ? tb + 24 : tb, b_half, &n_half);
+            issue_layer_pair<4, NSLOTS, Cfg, false, true>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, a.variant, a_tile, tb ? tb + 32 : tb, b_half, &n_half);
+            issue_layer_pair<5, NSLOTS, Cfg, false, true>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, a.variant, a_tile, tb ? tb + 40 : tb, b_half, &n_half);
+            continue;
+          }
+#endif
+          if (!STAT || a.first_layer <= 0) issue_layer_pair<0, NSLOTS, Cfg, false, !STAT>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, a.variant, a_tile, nullptr, b_half, &n_half);
+          if (!STAT || (a.n_layers > 1 && a.first_layer <= 1)) issue_layer_pair<1, NSLOTS, Cfg, false, !STAT>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, a.variant, a_tile, nullptr, b_half, &n_half);
+          if (!STAT || (a.n_layers > 2 && a.first_layer <= 2)) issue_layer_pair<2, NSLOTS, Cfg, false, !STAT>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, a.variant, a_tile, nullptr, b_half, &n_half);
+          if (!STAT || (a.n_layers > 3 && a.first_layer <= 3)) issue_layer_pair<3, NSLOTS, Cfg, false, !STAT>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, a.variant, a_tile, nullptr, b_half, &n_half);
+          if (!STAT || (a.n_layers > 4 && a.first_layer <= 4)) issue_layer_pair<4, NSLOTS, Cfg, false, !STAT>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, a.variant, a_tile, nullptr, b_half, &n_half);
+          if (!STAT || (a.n_layers > 5 && a.first_layer <= 5)) issue_layer_pair<5, NSLOTS, Cfg, false, !STAT>(s_base, tm, s_alo, bar_full, bar_empty, 0u, b_acc, b_act, 0u, it, n_act, a.err_flag, a.variant, a_tile, nullptr, b_half, &n_half);
         }
       }
     } else if (warp == 1 && lane == 0) {
@@ -1948,6 +2067,8 @@ fused_pair2_kernel(const FusedArgs a) {
     c.bar_acc = bar_acc + 8 * c.tl;
     c.bar_act = bar_act + 8 * c.tl;
     c.remote_act = rank == 0 ? 0u : mapa_shared(bar_act + 8 * c.tl, 0);
+    c.bar_half = bar_in + 8 * c.tl;
+    c.remote_half = rank == 0 ? 0u : mapa_shared(bar_in + 8 * c.tl, 0);
     c.k0 = a.k0; c.k1 = a.k1;
     c.err_flag = a.err_flag;
     c.strong_sync = (a.variant & 1) != 0;
@@ -1987,6 +2108,9 @@ fused_pair2_kernel(const FusedArgs a) {
         st_shared_v4(c.act_row + (uint32_t)kOnesPlane * kPlaneBytes, c.row_valid ? 0x3F803F80u : 0u, 0u, 0u, 0u);
       }
       c.c0w = (uint32_t)(a.window_base + win);
+#ifdef UQK_TIMELINE
+      c.tlb = (a.tl_buf && blockIdx.x == 0 && unit == pair_id + (long long)((a.variant >> 12) & 15) * n_pairs && lane == 0 && (c.we == 0 || c.we == 7)) ? a.tl_buf : nullptr;
+#endif
       float* dbg_base = nullptr;
       if (DBG) {
         if (a.dbg_act && blockIdx.x == 0 && unit == pair_id && c.tl == 0) dbg_base = a.dbg_act + (size_t)row * 256;
@@ -1996,14 +2120,15 @@ fused_pair2_kernel(const FusedArgs a) {
         if (c.colhalf == 0) st_shared_v4(c.act_row, xin0, xin1, 0u, 0u);
         fence_proxy_async();
         epi_signal_act<Cfg::kEpiThreads>(c);
+        if (c.we == 0) UQK_TLE(c, g, 0, 7);
         const float* tab_g = a.tables + (size_t)((a.mode_de || a.tab_per_group) ? g : 0) * kTableFloats;
         float* dbg_g = (DBG && g == 0) ? dbg_base : nullptr;
-        epi_layer<0, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
-        epi_layer<1, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
-        epi_layer<2, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
-        epi_layer<3, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
-        epi_layer<4, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
-        epi_layer<5, DROP, DBG, Cfg::kEpiThreads>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
+        epi_layer<0, DROP, DBG, Cfg::kEpiThreads, true>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
+        epi_layer<1, DROP, DBG, Cfg::kEpiThreads, true>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
+        epi_layer<2, DROP, DBG, Cfg::kEpiThreads, true>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
+        epi_layer<3, DROP, DBG, Cfg::kEpiThreads, true>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
+        epi_layer<4, DROP, DBG, Cfg::kEpiThreads, true>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
+        epi_layer<5, DROP, DBG, Cfg::kEpiThreads, true>(c, a, tab_g, g, win, n_acc, probs_s, dbg_g);
       }
       if (a.smem_probs && c.colhalf == 0 && c.t == 0 && (c.quarter & 1) == 0 && win < a.n) {
         const float* pw = probs_s + (2 * c.tl + c.slot_w) * a.n_groups;
@@ -2030,6 +2155,9 @@ static int launch_pair2_variant(const FusedParams& p, cudaStream_t s) {
   a.window_base = p.window_base; a.mask_bits = p.mask_bits; a.packed = reinterpret_cast<const uint8_t*>(p.packed_pair);
   a.tables = p.tables; a.probs = p.probs; a.out = p.out; a.dbg_act = p.dbg_act; a.err_flag = p.err_flag;
   a.variant = p.variant;
+#ifdef UQK_TIMELINE
+  a.tl_buf = STAT ? nullptr : g_uqk_timeline;
+#endif
   a.n_layers = STAT ? p.n_layers : kBlocks; a.stats = STAT ? p.stats : nullptr; a.first_layer = STAT ? p.first_layer : 0;
   // option exact_pipelined: resumed sweeps run pipelined over 4-window units (stat_pipelined_loop); default: 8-window units
   a.pipelined = (STAT && p.pipelined && a.first_layer >= 2) ? 1 : 0;
