@@ -20,7 +20,7 @@ PKG = "uncertaintyquantification-sleepapnea-1dcnn_b200"
 import numpy as np, torch
 pkg = importlib.import_module(PKG)
 _lib = importlib.import_module(PKG + "._lib")
-_lib.LIB_PATH = os.path.join(ROOT, PKG, "libuqk_timeline.so")
+_lib.LIB_PATH = os.path.join(ROOT, PKG, os.environ.get("UQK_PROBE_LIB", "libuqk_timeline.so"))
 engine = importlib.import_module(PKG + ".engine")
 syn = pkg.synthetic
 
@@ -36,7 +36,7 @@ def main():
     lib.uqk_debug_set_timeline.argtypes = [ctypes.c_void_p]
     eng.set_members(np.stack([syn.weights_to_blob(syn.make_member_weights(m)) for m in range(16)]))
     x = torch.from_numpy(syn.make_windows(n, seed=6)).cuda()
-    buf = torch.zeros(2 * 16 * 6 * 8, dtype=torch.int64, device="cuda")
+    buf = torch.zeros(2 * 2 * 16 * 6 * 8, dtype=torch.int64, device="cuda")
 
     def run():
         if mode == "mcd":
@@ -47,7 +47,8 @@ def main():
     lib.uqk_debug_set_timeline(ctypes.c_void_p(buf.data_ptr()))
     run(); torch.cuda.synchronize()
     lib.uqk_debug_set_timeline(ctypes.c_void_p(0))
-    t = buf.cpu().numpy().reshape(2, 16, 6, 8)
+    both = buf.cpu().numpy().reshape(2, 2, 16, 6, 8)
+    t, seg = both[0], both[1]
     g_n = min(T, 16)
     t0 = t[:, :g_n][t[:, :g_n] > 0].min()
     rel = np.where(t > 0, t - t0, -1)
@@ -71,6 +72,10 @@ def main():
         poll = e[..., 3] - e[..., 2]
         summ.append({"layer": L + 1, "act_to_acc": mma.mean(), "issue": issue.mean(), "epilogue": epi.mean(), "flags": flags.mean(), "epi_warp_idle": poll.mean()})
     out["per_layer_mean_clk"] = summ
+    # issuer segments (clk per layer, mean over passes 2..): waiting for the stage's weights / issuing MMAs + commit / loop overhead
+    for L in range(6):
+        e = seg[:, sl, L].astype(np.float64).mean(axis=(0, 1))
+        print(json.dumps({"layer": L + 1, "issuer_wait_full": round(e[0]), "issuer_issue_commit": round(e[1]), "issuer_other": round(e[2])}))
     per_pass = (t[:, g_n - 1, 5, 4] - t[:, 2, 5, 4]).astype(np.float64) / max(g_n - 3, 1)
     out["clk_per_pass"] = per_pass.tolist()
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)

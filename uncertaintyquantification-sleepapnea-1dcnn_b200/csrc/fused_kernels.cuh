@@ -37,8 +37,8 @@ __host__ __device__ constexpr int fl_cout(int l) { return l == 0 ? 128 : l == 1 
 __host__ __device__ constexpr int fl_nconv(int l) { return l == 0 ? 4 : l == 1 ? 40 : l == 2 ? 36 : l == 3 ? 98 : l == 4 ? 54 : 144; }
 __host__ __device__ constexpr uint32_t fl_bytes(int l) { return (uint32_t)(fl_nconv(l) + 1) * (uint32_t)fl_cout(l) * 32u; }
 __host__ __device__ constexpr uint32_t fl_off(int l) { return l == 0 ? 0u : fl_off(l - 1) + fl_bytes(l - 1); }
-__host__ __device__ constexpr FusedLayer fused_layer(int l) {
-  const int cout = fl_cout(l), nsteps = fl_nconv(l) + 1, sb = cout * 32, sps = kSlotBytes / sb;
+__host__ __device__ constexpr FusedLayer fused_layer(int l, int slot_bytes = kSlotBytes) {
+  const int cout = fl_cout(l), nsteps = fl_nconv(l) + 1, sb = cout * 32, sps = slot_bytes / sb;
   return FusedLayer{l == 0 ? 8 : l == 1 ? 128 : l == 2 ? 192 : l == 3 ? 224 : l == 4 ? 96 : 256,
                     cout,
                     l == 0 ? 7 : l == 1 ? 5 : l == 2 ? 3 : l == 3 ? 7 : 9,
@@ -49,6 +49,11 @@ constexpr uint32_t kPackedBytes = fl_off(5) + fl_bytes(5);
 // Run-time indexable copies (the constexpr helpers above recurse, which is only free at compile time).
 static __constant__ FusedLayer c_layers[kBlocks] = {fused_layer(0), fused_layer(1), fused_layer(2),
                                              fused_layer(3), fused_layer(4), fused_layer(5)};
+// The two-tile pair kernel streams stages of twice the size (32 KB per CTA pair, 16 KB per CTA): its MMA issuers pay
+// ~300 clk of waits / commit / loop latency per stage, which 2-3 MMAs per tile-pair (192-256 clk) do not cover.
+constexpr int kSlotBytesBig = 2 * kSlotBytes;
+static __constant__ FusedLayer c_layers_big[kBlocks] = {fused_layer(0, kSlotBytesBig), fused_layer(1, kSlotBytesBig), fused_layer(2, kSlotBytesBig),
+                                                 fused_layer(3, kSlotBytesBig), fused_layer(4, kSlotBytesBig), fused_layer(5, kSlotBytesBig)};
 
 constexpr double kFusedStatScale = 16777216.0;   // 2^24 fixed point of batch statistics, as in layersync.cu
 
@@ -1409,7 +1414,8 @@ struct PairCfg {
   static constexpr int kThreads = 32 * kWarps;
   static constexpr int kWpu = 4;                   // windows per pair unit
   static constexpr int kTmemCols = 256;
-  static constexpr int kSlot = kSlotBytes / 2;     // each CTA keeps half of a stage
+  static constexpr int kSlotPair = kSlotBytes;
+  static constexpr int kSlot = kSlotPair / 2;      // each CTA keeps half of a stage
   static constexpr int oAct = 0;
   static constexpr int oRing = oAct + kActBytes;
   static constexpr int kTabFloats = 2 * 512 + 128;
@@ -1500,7 +1506,7 @@ __device__ __forceinline__ void issue_layer_pair(uint32_t s_base, uint32_t tmem_
                                                  uint32_t& n_act, int* err_flag, int flags, uint32_t a_tile = 0u,
                                                  long long* tlp = nullptr, uint32_t bar_half = 0u, uint32_t* n_half = nullptr) {
   const bool no_mma = (flags & 8) != 0, strong = (flags & 1) != 0;   // debug switch / release-acquire cluster signalling
-  constexpr FusedLayer fl = fused_layer(L);
+  constexpr FusedLayer fl = fused_layer(L, Cfg::kSlotPair);
   constexpr uint32_t kHi = (128u >> 4) | (1u << 14);
   constexpr uint32_t kBLbo = ((uint32_t)((fl.cout / 2) * 16) >> 4) << 16;
   constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(fl.cout >> 3) << 17) | ((256u >> 4) << 24);
@@ -1525,6 +1531,12 @@ __device__ __forceinline__ void issue_layer_pair(uint32_t s_base, uint32_t tmem_
 #ifdef UQK_TIMELINE
   if (tlp) tlp[0] = clock64();
 #endif
+#ifdef UQK_TIMELINE
+  long long tseg0 = 0, tseg1 = 0, tseg2 = 0, tq = clock64();
+#define UQK_SEG(acc) do { const long long tn_ = clock64(); acc += tn_ - tq; tq = tn_; } while (0)
+#else
+#define UQK_SEG(acc) do { } while (0)
+#endif
 #pragma unroll 1
   for (int st = 0; st < fl.nstages; ++st) {
     // A-descriptor low words of the stage: read before the wait, so that the load latency hides behind it
@@ -1536,8 +1548,10 @@ __device__ __forceinline__ void issue_layer_pair(uint32_t s_base, uint32_t tmem_
       ++n_act;
       tc_fence_after();
     }
+    UQK_SEG(tseg2);
     mbar_wait_cluster(bar_full + 8 * slot, ph, err_flag, 3, strong);   // own half landed (tx) + peer's half (relayed arrive)
     tc_fence_after();
+    UQK_SEG(tseg0);
     const int nst = (st == fl.nstages - 1) ? kLast : fl.sps;
     const uint32_t b_lo0 = ring_lo + slot * (uint32_t)(Cfg::kSlot >> 4);
     if (ONE || elect_one()) {
@@ -1553,13 +1567,14 @@ __device__ __forceinline__ void issue_layer_pair(uint32_t s_base, uint32_t tmem_
       umma_commit_2cta(bar_empty + 8 * slot);   // both CTAs' ring slots are free once these MMAs have read them
     }
     if (!ONE) __syncwarp();
+    UQK_SEG(tseg1);
     if (++slot == NSLOTS) { slot = 0; ph ^= 1u; }
   }
   it += fl.nstages;
   if (ONE || elect_one()) umma_commit_2cta(bar_acc);   // both CTAs' accumulators complete
   if (!ONE) __syncwarp();
 #ifdef UQK_TIMELINE
-  if (tlp) tlp[1] = clock64();
+  if (tlp) { tlp[1] = clock64(); tlp[1536] = tseg0; tlp[1537] = tseg1; tlp[1538] = tseg2; }   // second half of the buffer: time per segment
 #endif
 }
 
@@ -1845,7 +1860,8 @@ struct Pair2Cfg {
   static constexpr int kThreads = 32 * kWarps;
   static constexpr int kWpu = 8;                   // windows per pair unit
   static constexpr int kTmemCols = 512;
-  static constexpr int kSlot = kSlotBytes / 2;
+  static constexpr int kSlotPair = kSlotBytesBig;  // 32 KB stages: 16 KB per CTA
+  static constexpr int kSlot = kSlotPair / 2;
   static constexpr int oAct = 0;
   static constexpr int oRing = oAct + 2 * kActBytes;
   static constexpr int kTabFloats = 2 * 512 + 128;
@@ -1854,7 +1870,7 @@ struct Pair2Cfg {
   static constexpr int kNumBars = 2 * NSLOTS + 8;  // full, empty [NSLOTS]; acc[2], act[2], in[2], tfree[2] (the last two: sweeps)
   static constexpr int oMisc = oBar + 8 * kNumBars;            // tmem ptr (16 B)
   static constexpr int oAlo = oMisc + 16;                      // A-descriptor low words, one per (layer, step)
-  static constexpr int oZ = oAlo + 4 * 392;                    // zpart[2][2][4] head partials (64 B)
+  static constexpr int oZ = oAlo + 4 * 400;                    // (stages of up to 10 steps read a few entries past the 388 used)                    // zpart[2][2][4] head partials (64 B)
   static constexpr int oProbs = (oZ + 64 + 15) & ~15;          // probs[4][n_groups]
   // statistics sweeps use neither zpart nor probs: their [2 x 256] u64 accumulators start at oZ, which lets a ninth ring
   // slot fit the 227 KB of shared memory exactly
@@ -1943,7 +1959,7 @@ fused_pair2_kernel(const FusedArgs a) {
           const int l_end = STAT ? a.n_layers : kBlocks;
 #pragma unroll 1
           for (int l = STAT ? a.first_layer : 0; l < l_end; ++l) {
-            const FusedLayer fl = c_layers[l];
+            const FusedLayer fl = c_layers_big[l];
             const uint32_t sb = (uint32_t)fl.step_bytes / 2;
             int step = 0;
             for (int st = 0; st < fl.nstages; ++st, ++it) {
@@ -1992,7 +2008,7 @@ fused_pair2_kernel(const FusedArgs a) {
         const uint32_t r_full = mapa_shared(bar_full, 0);
         uint32_t it = 0;
         const long long my_units = pair_id < a.n_units ? (a.n_units - pair_id + n_pairs - 1) / n_pairs : 0;
-        const int ns = c_layers[a.first_layer].nstages;
+        const int ns = c_layers_big[a.first_layer].nstages;
         for (long long q = 0; q < my_units * a.n_groups; ++q)
           for (int st = 0; st < ns; ++st, ++it) {
             const int slot = it % NSLOTS;
@@ -2038,7 +2054,7 @@ fused_pair2_kernel(const FusedArgs a) {
         for (int g = 0; g < a.n_groups; ++g)
 #pragma unroll 1
           for (int l = STAT ? a.first_layer : 0; l < (STAT ? a.n_layers : kBlocks); ++l) {
-            const int ns = c_layers[l].nstages;
+            const int ns = c_layers_big[l].nstages;
             for (int st = 0; st < ns; ++st, ++it) {
               const int slot = it % NSLOTS;
               mbar_wait2(bar_full + 8 * slot, (it / NSLOTS) & 1, a.err_flag, 23);

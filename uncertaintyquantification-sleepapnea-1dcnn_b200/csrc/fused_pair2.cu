@@ -3,6 +3,9 @@
 
 namespace uqk {
 
-int fused_launch_pair2(const FusedParams& p, cudaStream_t s) { return launch_pair2<9>(p, s); }
+#ifndef UQK_PAIR2_SLOTS
+#define UQK_PAIR2_SLOTS 4
+#endif
+int fused_launch_pair2(const FusedParams& p, cudaStream_t s) { return launch_pair2<UQK_PAIR2_SLOTS>(p, s); }
 
 }  // namespace uqk
