@@ -489,6 +489,10 @@ struct EpiCtx {
   bool strong_sync = false;  // pair kernels: release / acquire cluster signalling (variant bit 0)
   uint32_t remote_act = 0;   // pair kernels, peer CTA: cluster address of the leader's "peer activations ready" barrier
   uint32_t bar_half = 0, remote_half = 0;   // two-tile pair kernel: "first half of the output channels is in place" (early_half)
+  uint32_t xin0 = 0, xin1 = 0;              // this thread's row of the window as bf16 (column half 0), re-staged for every pass
+  // EARLY: layer 1's keep-flags and the tie-break bytes of the NEXT pass, generated while the last layer's MMAs run
+  mutable uint32_t kb1[4] = {0u, 0u, 0u, 0u};
+  mutable DropTie tie_next = {0u, 0u};
   int t, colhalf, tid_t, we, lane, quarter, slot_w, tl;
   bool row_valid;
   float* tab;
@@ -606,7 +610,19 @@ __device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, c
 
   // keep-flags of this thread's row for this layer (see keep_insert): produced while the layer's MMAs run
   uint32_t kb[4];
-  make_keep_flags<L, DROP>(c, a, g, win, kb);
+  if (EARLY && L == 0 && DROP != kDropNone && g > 0) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) kb[i] = c.kb1[i];            // made during the previous pass's last layer
+  } else {
+    make_keep_flags<L, DROP>(c, a, g, win, kb);
+  }
+  if (EARLY && kLastLayer && DROP != kDropNone && g + 1 < a.n_groups) {
+    // next pass, layer 1: its MMAs take no time, so its flags would be exposed -- make them here, in this layer's shadow
+    EpiCtx cn = c;
+    if (DROP == kDropPhilox) cn.tie = drop_tie(c.c0w, (uint32_t)(a.pass_base + g + 1), (uint32_t)c.t, (uint32_t)c.colhalf, c.k0, c.k1);
+    make_keep_flags<0, DROP>(cn, a, g + 1, win, c.kb1);
+    c.tie_next = cn.tie;
+  }
   constexpr uint32_t thr2 = 0u;
   const uint32_t c2 = ((uint32_t)L << 16) | (uint32_t)c.t;
   const uint32_t row_mask = c.row_valid ? 0xFFFFFFFFu : 0u;   // zero rows = the next layer's `same` padding
@@ -622,6 +638,13 @@ __device__ __forceinline__ void epi_layer(const EpiCtx& c, const FusedArgs& a, c
   named_bar_sync(1 + c.tl, EPI_THREADS);
   tc_fence_after();
   if (c.we == 0) UQK_TLE(c, g, L, 3);
+  if (EARLY && kLastLayer && g + 1 < a.n_groups) {
+    // the last layer's MMAs have retired: the planes are free, so the next pass's input goes in now and its layer 1
+    // (accumulator at column 128, this layer's at [0,96)) runs while the head below is evaluated
+    if (c.colhalf == 0) st_shared_v4(c.act_row, c.xin0, c.xin1, 0u, 0u);
+    fence_proxy_async();
+    epi_signal_act<EPI_THREADS>(c);
+  }
 
   float* dbg = nullptr;
   if (DBG) {
@@ -1870,7 +1893,7 @@ struct Pair2Cfg {
   static constexpr int kNumBars = 2 * NSLOTS + 8;  // full, empty [NSLOTS]; acc[2], act[2], in[2], tfree[2] (the last two: sweeps)
   static constexpr int oMisc = oBar + 8 * kNumBars;            // tmem ptr (16 B)
   static constexpr int oAlo = oMisc + 16;                      // A-descriptor low words, one per (layer, step)
-  static constexpr int oZ = oAlo + 4 * 400;                    // (stages of up to 10 steps read a few entries past the 388 used)                    // zpart[2][2][4] head partials (64 B)
+  static constexpr int oZ = oAlo + 4 * 400;                    // zpart[2][2][4] head partials (64 B); s_alo: 388 used, stages of up to 10 steps read a few past
   static constexpr int oProbs = (oZ + 64 + 15) & ~15;          // probs[4][n_groups]
   // statistics sweeps use neither zpart nor probs: their [2 x 256] u64 accumulators start at oZ, which lets a ninth ring
   // slot fit the 227 KB of shared memory exactly
@@ -2124,6 +2147,7 @@ fused_pair2_kernel(const FusedArgs a) {
         st_shared_v4(c.act_row + (uint32_t)kOnesPlane * kPlaneBytes, c.row_valid ? 0x3F803F80u : 0u, 0u, 0u, 0u);
       }
       c.c0w = (uint32_t)(a.window_base + win);
+      c.xin0 = xin0; c.xin1 = xin1;
 #ifdef UQK_TIMELINE
       c.tlb = (a.tl_buf && blockIdx.x == 0 && unit == pair_id + (long long)((a.variant >> 12) & 15) * n_pairs && lane == 0 && (c.we == 0 || c.we == 7)) ? a.tl_buf : nullptr;
 #endif
@@ -2132,10 +2156,12 @@ fused_pair2_kernel(const FusedArgs a) {
         if (a.dbg_act && blockIdx.x == 0 && unit == pair_id && c.tl == 0) dbg_base = a.dbg_act + (size_t)row * 256;
       }
       for (int g = 0; g < a.n_groups; ++g) {
-        epi_pass_setup<DROP>(c, a, g);
-        if (c.colhalf == 0) st_shared_v4(c.act_row, xin0, xin1, 0u, 0u);
-        fence_proxy_async();
-        epi_signal_act<Cfg::kEpiThreads>(c);
+        if (g == 0) epi_pass_setup<DROP>(c, a, g); else c.tie = c.tie_next;
+        if (g == 0) {   // later passes: staged by the previous pass's last epilogue (epi_layer, EARLY)
+          if (c.colhalf == 0) st_shared_v4(c.act_row, xin0, xin1, 0u, 0u);
+          fence_proxy_async();
+          epi_signal_act<Cfg::kEpiThreads>(c);
+        }
         if (c.we == 0) UQK_TLE(c, g, 0, 7);
         const float* tab_g = a.tables + (size_t)((a.mode_de || a.tab_per_group) ? g : 0) * kTableFloats;
         float* dbg_g = (DBG && g == 0) ? dbg_base : nullptr;
