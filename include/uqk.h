@@ -244,7 +244,8 @@ int uqk_window_summary(const float* entropy_dev, const float* variance_dev, cons
  *   "watchdog"         1 (default) / 0: time budget of the kernels' barrier waits, see uqk_poll_error
  *   "calib_fp32_max"   calibration sets up to this many windows use the fp32 kernels (default 8192)
  *   "exact_chunk_max"  cap on the passes per chunk of the exact mode (0 = by memory budget)
- *   "exact_pipelined"  1: resumed sweeps of the exact mode as a three-stage pipeline (bit-identical, measured slower)
+ *   "exact_pipelined"  1 (default): resumed sweeps of the exact mode as a three-stage pipeline over 4-window units;
+ *                      0: both tiles of a CTA in lock-step over 8-window units (bit-identical, 5 % slower)
  *   "dbg_dump"         1: the one-tile kernel dumps the activations of its first unit (uqk_debug_read_dump) */
 int uqk_set_option(uqk_handle* h, const char* key, int64_t value);
 

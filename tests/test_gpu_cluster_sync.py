@@ -44,12 +44,15 @@ def test_pair_kernels_relaxed_and_release_acquire_match_the_single_cta_kernel(uq
         x = x_all[:50]
         eng.option("variant", 0)
         a = eng.mcd(x, n_passes=3, seed=9, bn_mode="batch", precision="bf16", return_probs=True)["probs"]
-        eng.option("variant", 1)
-        for _ in range(20):
-            b = eng.mcd(x, n_passes=3, seed=9, bn_mode="batch", precision="bf16", return_probs=True)["probs"]
-            np.testing.assert_array_equal(a, b)
+        for pipelined in (1, 0):                      # pipelined sweeps (default) and the lock-step form
+            eng.option("exact_pipelined", pipelined)
+            eng.option("variant", 1)
+            for _ in range(10):
+                b = eng.mcd(x, n_passes=3, seed=9, bn_mode="batch", precision="bf16", return_probs=True)["probs"]
+                np.testing.assert_array_equal(a, b)
     finally:
         eng.option("variant", 0)
+        eng.option("exact_pipelined", 1)
     assert launches == 10_000
     eng.poll_error()
 

@@ -173,19 +173,20 @@ def test_exact_batch_is_independent_of_the_pass_chunking(uqk):
 
 
 def test_pipelined_sweep_variant_is_bit_identical(uqk):
-    """Option exact_pipelined: the resumed sweeps as a three-stage pipeline over two buffers (loader warps / MMAs /
-    statistics warps).  Same arithmetic and the same integer statistics, so every output must be identical."""
+    """Option exact_pipelined (default 1): the resumed sweeps as a three-stage pipeline over two buffers (loader warps /
+    MMAs / statistics warps) against the lock-step form (0: both tiles of a CTA walk the layer together).  Same arithmetic
+    and the same integer statistics, so every output must be identical."""
     eng = engine_with_members()
     n, T, seed = 203, 3, 23
     x = _x(uqk, n, seed=29)
-    want = eng.mcd(x, n_passes=T, seed=seed, bn_mode="batch", precision="bf16", return_probs=True)
-    eng.option("exact_pipelined", 1)
+    got = eng.mcd(x, n_passes=T, seed=seed, bn_mode="batch", precision="bf16", return_probs=True)
+    tiny = eng.mcd(x[:3], n_passes=2, seed=seed, bn_mode="batch", precision="bf16", return_probs=True)
+    eng.option("exact_pipelined", 0)
     try:
-        got = eng.mcd(x, n_passes=T, seed=seed, bn_mode="batch", precision="bf16", return_probs=True)
-        tiny = eng.mcd(x[:3], n_passes=2, seed=seed, bn_mode="batch", precision="bf16", return_probs=True)
+        want = eng.mcd(x, n_passes=T, seed=seed, bn_mode="batch", precision="bf16", return_probs=True)
+        ref = eng.mcd(x[:3], n_passes=2, seed=seed, bn_mode="batch", precision="bf16", return_probs=True)
     finally:
-        eng.option("exact_pipelined", 0)
+        eng.option("exact_pipelined", 1)
     for k in ("probs", "mean_pred", "pred_variance", "label"):
         np.testing.assert_array_equal(got[k], want[k])
-    ref = eng.mcd(x[:3], n_passes=2, seed=seed, bn_mode="batch", precision="bf16", return_probs=True)
     np.testing.assert_array_equal(tiny["probs"], ref["probs"])

@@ -17,6 +17,9 @@ def main():
     n = int(sys.argv[2]) if len(sys.argv) > 2 else 40000
     T = int(sys.argv[3]) if len(sys.argv) > 3 else 10
     eng = engine.Engine(0)
+    for kv in os.environ.get("UQK_PROBE_OPTS", "").split(","):      # e.g. UQK_PROBE_OPTS=exact_pipelined=1
+        if "=" in kv:
+            eng.option(kv.split("=")[0], int(kv.split("=")[1]))
     eng.set_members(np.stack([syn.weights_to_blob(syn.make_member_weights(m)) for m in range(2)]))
     x = torch.from_numpy(syn.make_windows(4096, seed=6)).cuda()
     x = x.repeat((n + 4095) // 4096, 1, 1)[:n].contiguous()

@@ -58,7 +58,7 @@ struct Handle {
   int64_t calib_fp32_max = 8192;  // calibration sets up to this size use the fp32 layer-synchronous kernels
   int exact_chunk_max = 0;        // tests: cap on the passes per chunk of the exact mode (0 = memory budget only)
   int watchdog = 1;               // 0: the kernels wait on their barriers without a time budget (debuggers, sanitizers)
-  int exact_pipelined = 0;        // resumed sweeps of the exact mode as a three-stage pipeline (measured slower; variant kept for tests)
+  int exact_pipelined = 1;        // resumed sweeps of the exact mode as a three-stage pipeline over 4-window units (0: both tiles in lock-step, 8-window units)
   // cross-rank exchange of batch statistics (uqk_set_stats_exchange)
   uqk_stats_exchange_fn xchg = nullptr;
   void* xchg_user = nullptr;
