@@ -525,12 +525,12 @@ __device__ __forceinline__ void epi_signal_act(const EpiCtx& c) {
 // signals bar_half there, and the next layer's issuer starts on those slabs while the remaining chunks are still being
 // written (different planes).  The accumulator columns the early MMAs overwrite must already have been read:
 //   layer 1 -> 2: layer 1 accumulates at column 128 ([128,256); read first: [128,192)), layer 2 writes [0,192)
-//   layer 3 -> 4: layer 3 at [0,224), read first [0,128); layer 4 writes [0,96)
+//   layer 3 -> 4: layer 3 at [32,256), read first [32,96); layer 4 writes [0,96)
 //   layer 5 -> 6: layer 5 at [0,256), read first [0,128); layer 6 writes [0,96)
 // Layers 2 -> 3 and 4 -> 5 do not fit (the unread half plus the next accumulator exceed the 256 columns of a tile-pair).
 __host__ __device__ constexpr bool early_producer(int l) { return l == 0 || l == 2 || l == 4; }
-__host__ __device__ constexpr int half_chunks(int l) { return (((fl_cout(l) / 32 + 1) / 2) + 1) & ~1; }   // per warp: 2, 4, 4
-__host__ __device__ constexpr int acc_col(int l, bool early) { return (early && l == 0) ? 128 : 0; }
+__host__ __device__ constexpr int half_chunks(int l) { return l == 2 ? 2 : (((fl_cout(l) / 32 + 1) / 2) + 1) & ~1; }   // per warp: 2, 2, 4
+__host__ __device__ constexpr int acc_col(int l, bool early) { return !early ? 0 : l == 0 ? 128 : l == 2 ? 32 : 0; }
 template <int EPI_THREADS>
 __device__ __forceinline__ void epi_signal_half(const EpiCtx& c) {
   if (c.remote_half == 0) {
