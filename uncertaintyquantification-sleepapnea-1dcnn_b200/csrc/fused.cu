@@ -15,7 +15,7 @@
 //         Y[t, o] = sum_j sum_c X[t + j - h, c] * W[j, c, o]   ==   sum over (j, 16-channel slab) of one tcgen05.mma.
 //  * Activations are updated IN PLACE: the accumulator of layer l lives in TMEM until every MMA of layer l has
 //    retired (tcgen05.commit -> mbarrier), then the epilogue warps overwrite the layer's input with
-//    bias+ReLU -> BN affine -> Philox dropout -> bf16.  One 68 KB buffer per tile instead of two.
+//    bias+ReLU -> BN affine -> Philox dropout -> bf16.  One 71.8 KB buffer per tile instead of two.
 //  * Weights (1.7 MB bf16 per member, L2 resident) stream through a shared-memory ring with cp.async.bulk (TMA
 //    bulk copies, mbarrier complete_tx); they are pre-packed on the host into the exact shared-memory image.
 //  * Warp roles: warp 0 = weight producer, then one warp per accumulator = TMEM allocator / MMA issuer (one elected

@@ -1870,10 +1870,11 @@ static int launch_pair(const FusedParams& p, cudaStream_t s) {
 // =====================================================================================================================
 // CTA-pair variant with TWO tiles per CTA ("P2"): 1 CTA per SM, the pair owns a unit of 8 windows = tile-pairs A and B
 // (each an M=256 accumulator spanning both SMs).  Both tile-pairs consume the SAME weight stream (R = 8 window-passes
-// per stream, half the L2->SM traffic of the default pair kernel) through a 9-slot ring of half-stages.  The leader CTA
-// runs ONE MMA-ISSUER WARP PER TILE-PAIR: each walks the schedule on its own, blocks only on its own activations,
-// and the two drift apart at layer boundaries so one tile-pair's MMAs cover the other's epilogue.  A ring slot is
-// free when BOTH tile-pairs have consumed it (mbarrier count 2, tcgen05.commit multicast to both CTAs).
+// per stream, half the L2->SM traffic of the one-tile pair kernel) through a ring of 4 slots of 16 KB per CTA (32 KB
+// stages: the issuer's ~300 clk of wait / commit / loop latency per stage then covers 4-10 MMAs per tile-pair).  The
+// leader CTA runs ONE MMA-ISSUER WARP PER TILE-PAIR.  A ring slot is free when BOTH tile-pairs have consumed it
+// (mbarrier count 2, tcgen05.commit multicast to both CTAs), which keeps the two tile-pairs in lock-step (measured,
+// tools/timeline_probe.py); the epilogues are taken off the critical path by the early hand-off instead (early_producer).
 // =====================================================================================================================
 template <int NSLOTS>
 struct Pair2Cfg {
@@ -1895,8 +1896,7 @@ struct Pair2Cfg {
   static constexpr int oAlo = oMisc + 16;                      // A-descriptor low words, one per (layer, step)
   static constexpr int oZ = oAlo + 4 * 400;                    // zpart[2][2][4] head partials (64 B); s_alo: 388 used, stages of up to 10 steps read a few past
   static constexpr int oProbs = (oZ + 64 + 15) & ~15;          // probs[4][n_groups]
-  // statistics sweeps use neither zpart nor probs: their [2 x 256] u64 accumulators start at oZ, which lets a ninth ring
-  // slot fit the 227 KB of shared memory exactly
+  // statistics sweeps use neither zpart nor probs: their [2 x 256] u64 accumulators start at oZ
   static constexpr int oStats = oZ;
   static_assert(oZ % 8 == 0, "statistics accumulators are 64-bit");
 };

@@ -3,8 +3,8 @@
 
 namespace uqk {
 
-// statistics sweeps of the exact batch-statistic mode: two-tile CTA-pair kernel, 9-slot weight ring (the statistics
-// accumulators overlay the head partials / probability buffer the sweeps do not use: exactly 227 KB of shared memory)
+// statistics sweeps of the exact batch-statistic mode: two-tile CTA-pair kernel, 4 ring slots of 16 KB per CTA (the
+// statistics accumulators overlay the head partials / probability buffer the sweeps do not use)
 int fused_launch_pair_stat(const FusedParams& p, cudaStream_t s) { return launch_pair2_stat<4>(p, s); }
 
 }  // namespace uqk
