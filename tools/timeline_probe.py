@@ -11,7 +11,8 @@ tile-pair and layer:
   ev3  epilogue warp 0: accumulator complete (after the tile's named barrier)
   ev4  epilogue warp 0 / ev5 warp 7: layer's epilogue done ("activations ready" signalled)
 
-  python tools/timeline_probe.py [windows] [passes] [mcd|det]
+  python tools/timeline_probe.py [windows] [passes] [mcd|det] [variant] [--all]
+(variant bits 12-15 select the unit of CTA 0 that is recorded; --all prints every pass instead of passes 4-5)
 """
 import ctypes, importlib, json, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -84,7 +85,7 @@ def main():
         print(json.dumps({k: (round(v, 0) if isinstance(v, float) else v) for k, v in s.items()}))
     print("clk per pass (tile-pair 0, 1):", per_pass)
     # a compact chart of passes 4..5
-    for g in range(4, min(6, g_n)):
+    for g in (range(0, g_n) if "--all" in sys.argv else range(4, min(6, g_n))):
         for L in range(6):
             for tl in range(2):
                 e = rel[tl, g, L]
