@@ -36,3 +36,14 @@ def test_reference_arm_other_ranks_exit_quietly():
     assert _run({"RANK": "1", "WORLD_SIZE": "2", "LOCAL_RANK": "1"}) == []
     d = json.loads(_run({"RANK": "0", "WORLD_SIZE": "2", "LOCAL_RANK": "0", "OMP_NUM_THREADS": "1"})[0])
     assert d["cpu_baseline"]["cores"] == len(os.sched_getaffinity(0))
+
+
+def test_own_arm_refuses_to_run_without_a_gpu():
+    """No CPU fallback: without CUDA the product arm stops with an error instead of timing something else."""
+    import torch
+    if torch.cuda.is_available():
+        import pytest
+        pytest.skip("a GPU is present")
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "1", "--warmup", "1"],
+                         capture_output=True, text=True, timeout=600)
+    assert out.returncode != 0 and out.stdout.strip() == "" and "no CPU fallback" in out.stderr
